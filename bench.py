@@ -1,0 +1,410 @@
+#!/usr/bin/env python
+"""bench.py -- libear-b200 benchmark (contract in the task prompt / DESIGN.md section 6).
+
+Headline metric (BASELINE.json): object gain vectors/s for extent objects on BS.2051 9+10+3
+(config 1: 1M objects per GPU, P = 1,652-point spreading grid), plus the GainInterpolator
+render throughput (config 2: 128 objects x 60 s x 48 kHz into 4+9+0) as a second block.
+
+  python bench.py --gpus N --steps K --warmup W            our arm (one rank per GPU)
+  python bench.py --impl reference ...                     libear's CPU path on the host cores
+
+One "step" = one pass of the hot path over one batch of synthetic input.  `value` is
+measured with inputs resident in HBM (CUDA events on the launching stream, max over
+ranks); `e2e` goes through the reference-facing C-ABI host entry points with pinned HOST
+buffers, host<->device copies inside the timed region.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+LAYOUT = "9+10+3"
+N_OBJECTS = 1_000_000            # per GPU (weak scaling)
+FLOP_PER_PASS = 2 * 1652 * 22    # contraction flops per spreading pass
+RENDER = dict(N=128, M=14, T=2_880_000, ramp=512, layout="4+9+0")
+
+
+def synth_objects(n, seed):
+    """SURVEY.md 8(d) cfg 2: directions uniform on the sphere, distance U(0.2, 1.5), width and
+    height U(0, 360), depth 0 for half the objects and U(0, 1) for the rest, gain/diffuse U(0, 1)."""
+    rng = np.random.default_rng(seed)
+    az = rng.uniform(-180, 180, n)
+    el = np.degrees(np.arcsin(rng.uniform(-1, 1, n)))
+    dist = rng.uniform(0.2, 1.5, n)
+    w, h = rng.uniform(0, 360, n), rng.uniform(0, 360, n)
+    depth = np.where(rng.uniform(size=n) < 0.5, 0.0, rng.uniform(0, 1, n))
+    return [az, el, dist, w, h, depth, rng.uniform(0, 1, n), rng.uniform(0, 1, n)]
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.proc = None
+        self.gpu = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+            out, _ = self.proc.communicate()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1]))
+                smax.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None,
+                "sm_max_mhz": float(max(smax)) if smax else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        p = json.load(open(path))
+        return p.get("hbm_gbs", 6650.0), p.get("bf16_tflops", 1590.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, 1590.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------ CPU baseline (libear itself)
+def cpu_objects_throughput(args_list, threads, target_seconds):
+    """libear's GainCalculatorObjects::calculate<float> on `threads` host threads, one calculator
+    instance per thread (instances are not re-entrant), on a bounded sample of the workload."""
+    from oracle import ref
+    calcs = [ref.Objects(LAYOUT) for _ in range(threads)]
+    probe = [a[:2000] for a in args_list]
+    t0 = time.perf_counter()
+    calcs[0].calculate(*probe, dtype=np.float32)
+    per_obj = (time.perf_counter() - t0) / 2000
+    per_thread = int(max(2000, min(len(args_list[0]) // threads, target_seconds / per_obj)))
+
+    def work(i):
+        sl = slice(i * per_thread, (i + 1) * per_thread)
+        calcs[i].calculate(*[a[sl] for a in args_list], dtype=np.float32)
+
+    ths = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
+    t0 = time.perf_counter()
+    [t.start() for t in ths]
+    [t.join() for t in ths]
+    dt = time.perf_counter() - t0
+    n = per_thread * threads
+    return n / dt, n, dt
+
+
+def host_threads():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation on the host cores."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import ref
+    if not ref.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libear_ref.so not built"}))
+        return
+    threads = host_threads()
+    objs = synth_objects(400_000, 2)
+    # size one step at ~3 s of wall time on all threads
+    rate, n, dt = cpu_objects_throughput(objs, threads, 1.0)
+    step_n = int(max(threads * 500, min(len(objs[0]) // threads * threads, rate * 3.0)))
+    step_n -= step_n % threads
+    calcs = [ref.Objects(LAYOUT) for _ in range(threads)]
+    per = step_n // threads
+
+    def step():
+        def work(i):
+            sl = slice(i * per, (i + 1) * per)
+            calcs[i].calculate(*[a[sl] for a in objs], dtype=np.float32)
+        ths = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
+        [t.start() for t in ths]
+        [t.join() for t in ths]
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    value = step_n * args.steps / dt
+    line = {
+        "impl": "reference", "metric": "object gain vectors/s (9+10+3, extent)", "value": value,
+        "unit": "vectors/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"cfg1 sample: {step_n} extent objects/step on {LAYOUT} "
+                               "(same distribution as the GPU arm's 1M objects/GPU)",
+                   "layout": LAYOUT},
+        "cpu_baseline": {"value": value, "unit": "vectors/s", "cores": threads, "kind": "reference",
+                         "sample": f"{step_n} objects/step x {args.steps} steps, libear "
+                                   f"GainCalculatorObjects::calculate<float>, xsimd ISA {ref.extent_isa()}"},
+        "e2e": {"value": value, "unit": "vectors/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------ our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    import libear_b200 as eb
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: libear-b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    hbm_peak, bf16_peak, peak_src = measured_peaks()
+    stream = torch.cuda.current_stream().cuda_stream
+    sampler = ClockSampler(local_rank)
+
+    # ---------------- objects: BASELINE config 1 (1M extent objects per GPU on 9+10+3)
+    n = args.objects
+    objs = synth_objects(n, 2 + rank)
+    n_passes = n + int(np.count_nonzero(objs[5]))
+    gc = eb.GainCalculatorObjects(LAYOUT, device=local_rank)
+    C_out = gc.num_outputs
+    d_in = torch.from_numpy(np.stack(objs)).to(dev)  # [8][n] float64
+    d_direct = torch.empty((n, C_out), dtype=torch.float32, device=dev)
+    d_diffuse = torch.empty((n, C_out), dtype=torch.float32, device=dev)
+    soa = [d_in[k].data_ptr() for k in range(8)]
+
+    def step_objects():
+        gc.calculate_device(n, soa, d_direct.data_ptr(), d_diffuse.data_ptr(), stream=stream)
+
+    for _ in range(args.warmup):
+        step_objects()
+    barrier()
+    gc.set_profiling(True)
+    launches0 = gc.launch_count
+    sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        step_objects()
+    ev1.record()
+    barrier()
+    clocks = sampler.stop()
+    ms_total = max_over_ranks(ev0.elapsed_time(ev1))
+    core_ms, core_launches, _ = gc.kernel_time()
+    gc.set_profiling(False)
+    gpu_launches = gc.launch_count - launches0
+    value = n * world * args.steps / (ms_total * 1e-3)
+    core_tflops = FLOP_PER_PASS * n_passes * args.steps / (core_ms * 1e-3) / 1e12
+    weight_evals = 1652.0 * n_passes * args.steps / (core_ms * 1e-3)
+
+    # end to end through the C-ABI host entry point, pinned host buffers
+    h_in = [torch.from_numpy(a).pin_memory() for a in objs]
+    h_direct = torch.empty((n, C_out), dtype=torch.float32).pin_memory()
+    h_diffuse = torch.empty((n, C_out), dtype=torch.float32).pin_memory()
+    e2e_steps = max(1, min(args.steps, 5))
+
+    import ctypes as C
+    soa_h = eb._ObjectsSoA(*[t.data_ptr() for t in h_in], None)
+
+    def step_e2e_abi():
+        eb._chk(eb._lib.earb200_objects_calculate_host(gc.h, C.c_int64(n), C.byref(soa_h), 0,
+                                                       C.c_void_p(h_direct.data_ptr()),
+                                                       C.c_void_p(h_diffuse.data_ptr()), None))
+
+    step_e2e_abi()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        step_e2e_abi()
+    torch.cuda.synchronize()
+    e2e_dt = max_over_ranks(time.perf_counter() - t0)
+    e2e_value = n * world * e2e_steps / e2e_dt
+    e2e_checksum = float(h_direct[:1000].double().sum())
+
+    # ---------------- render: BASELINE config 2 (128 objects x 60 s x 48 kHz into 4+9+0)
+    render = None
+    if not args.no_render:
+        R = RENDER
+        N, M, T = R["N"], R["M"], R["T"]
+        g = torch.Generator(device=dev).manual_seed(100 + rank)
+        x = (torch.randn((N, T), generator=g, device=dev, dtype=torch.float32) * 0.25).clamp_(-1, 1)
+        y = torch.empty((M, T), dtype=torch.float32, device=dev)
+        samples = np.arange(0, T + R["ramp"], R["ramp"], dtype=np.int64)
+        rng = np.random.default_rng(3 + rank)
+        gains = (rng.uniform(0, 1, size=(len(samples), N, M)) / np.sqrt(N)).astype(np.float32)
+        gi = eb.GainInterpolator(N, M, device=local_rank)
+        gi.set_points(samples, gains)
+
+        def step_render():
+            gi.process_device(0, T, x.data_ptr(), T, y.data_ptr(), T, stream=stream)
+            if world > 1:
+                # object-sharded mixing: sum the per-GPU partial loudspeaker buses
+                dist.all_reduce(y)
+
+        for _ in range(args.warmup):
+            step_render()
+        barrier()
+        gi.set_profiling(True)
+        rl0 = gi.launch_count
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        r0.record()
+        for _ in range(args.steps):
+            step_render()
+        r1.record()
+        barrier()
+        r_ms = max_over_ranks(r0.elapsed_time(r1))
+        k_ms, k_launches = gi.kernel_time()
+        gi.set_profiling(False)
+        gpu_launches += gi.launch_count - rl0
+        alg_bytes = 4.0 * T * (N + M) + 4.0 * N * M * len(samples)
+        achieved = alg_bytes * args.steps / (k_ms * 1e-3) / 1e9
+        render = {
+            "metric": "render Msamples/s (input object-samples)",
+            "value": N * T * world * args.steps / (r_ms * 1e-3) / 1e6, "unit": "Msamples/s",
+            "ms_per_step": r_ms / args.steps,
+            "config": {"workload": f"cfg2: {N} objects/GPU x 60 s x 48 kHz into {R['layout']} (M={M}), "
+                                   f"{R['ramp']}-sample linear gain ramps; inputs 1.6 GB/step > L2",
+                       "bus_reduce": "nccl all_reduce(sum, f32) of the [M x T] bus" if world > 1 else "none"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "render_kernel<16,4,true>", "kernel_ms": k_ms / max(1, k_launches),
+                         "algorithmic_bytes_per_launch": alg_bytes},
+        }
+        # end to end: pinned host input/output through the C-ABI host entry point
+        if world == 1 and not args.no_render_e2e:
+            hx = torch.empty((N, T), dtype=torch.float32).pin_memory()
+            hx.copy_(x)
+            hy = torch.empty((M, T), dtype=torch.float32).pin_memory()
+
+            def render_e2e():
+                eb._chk(eb._lib.earb200_interp_process_host(gi.h, C.c_int64(0), C.c_int64(T),
+                                                            C.c_void_p(hx.data_ptr()), C.c_int64(T),
+                                                            C.c_void_p(hy.data_ptr()), C.c_int64(T)))
+            render_e2e()
+            t0 = time.perf_counter()
+            for _ in range(2):
+                render_e2e()
+            dt = time.perf_counter() - t0
+            render["e2e"] = {"value": N * T * 2 / dt / 1e6, "unit": "Msamples/s",
+                             "h2d_bytes_per_step": 4 * N * T, "d2h_bytes_per_step": 4 * M * T}
+            del hx, hy
+        del x, y
+
+    if rank == 0:
+        line = {
+            "metric": "object gain vectors/s (9+10+3, extent)", "value": value, "unit": "vectors/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"cfg1: {n} extent objects/GPU on {LAYOUT} via the batched "
+                                   "GainCalculatorObjects C-ABI (1,652-point spreading grid, depth != 0 for half)",
+                       "layout": LAYOUT, "objects_per_gpu": n, "passes_per_step_per_gpu": n_passes,
+                       "l2": "inputs+outputs 256 MB/step/GPU > 126 MB L2", "sharding": "objects, no collective"},
+            "roofline": {"bound": "tensor", "achieved": core_tflops, "peak": bf16_peak, "unit": "TFLOP/s",
+                         "frac": core_tflops / bf16_peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "extent_core_kernel", "kernel_ms": core_ms / max(1, core_launches),
+                         "algorithmic_flop_per_pass": FLOP_PER_PASS,
+                         "note": "contraction flops only; the kernel is FP32-ALU bound by the 1,652 weight "
+                                 "evaluations per pass (DESIGN.md section 4)",
+                         "weight_evals_per_s": weight_evals,
+                         "kernel_share_of_step": core_ms / ms_total},
+            "e2e": {"value": e2e_value, "unit": "vectors/s", "h2d_bytes_per_step": 8 * 8 * n,
+                    "d2h_bytes_per_step": 2 * 4 * C_out * n, "steps": e2e_steps, "checksum": e2e_checksum},
+            "gpu_launches": int(gpu_launches),
+            "clocks": clocks,
+        }
+        if render is not None:
+            line["render"] = render
+        if world == 1 and not args.no_cpu_baseline:
+            from oracle import ref
+            if ref.available():
+                threads = host_threads()
+                rate, cn, cdt = cpu_objects_throughput(objs, threads, 12.0)
+                line["cpu_baseline"] = {
+                    "value": rate, "unit": "vectors/s", "cores": threads, "kind": "reference",
+                    "sample": f"{cn} of the {n} objects, {cdt:.1f} s wall, libear "
+                              f"GainCalculatorObjects::calculate<float> (xsimd ISA {ref.extent_isa()}), "
+                              "one calculator per thread"}
+            else:
+                line["cpu_baseline"] = {"value": None, "unit": "vectors/s", "cores": 0, "kind": "reference",
+                                        "sample": "oracle/_ref/libear_ref.so not built"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--objects", type=int, default=N_OBJECTS)
+    ap.add_argument("--no-render", action="store_true")
+    ap.add_argument("--no-render-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "ours":
+        args.warmup = 3  # timing rule: at least three warm-up steps
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,232 @@
+/* earb200.h -- C ABI of libear-b200: libear's data-parallel rendering hot path on
+ * NVIDIA B200 (sm_100a).
+ *
+ * libear (ebu/libear) has no C ABI; its seams are C++ classes.  Each entry point
+ * below names the libear interface it replaces (file:line under the libear tree).
+ * The C++ facade in libear_b200/include/ear/ re-implements those classes with their
+ * original signatures on top of these functions, and INTEGRATION.md shows the
+ * binding a libear maintainer would add.
+ *
+ * Conventions
+ *  - every function returns an earb200_status; on failure earb200_last_error()
+ *    (thread-local) holds the message.  Codes 1..5 map 1:1 onto libear's exception
+ *    classes (include/ear/exceptions.hpp:8-43), which the C++ facade re-throws.
+ *  - handles are opaque, bound to one CUDA device, and -- like the libear objects
+ *    they replace -- not thread-safe per instance.
+ *  - *_host entry points take host buffers, copy, run and synchronise;
+ *    *_device entry points take device pointers plus a cudaStream_t (passed as
+ *    void*) and are asynchronous.  Buffers are caller-owned.
+ *  - there is no CPU fallback: without a CUDA device every create call fails with
+ *    EARB200_CUDA_ERROR.
+ */
+#ifndef EARB200_H
+#define EARB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum earb200_status {
+  EARB200_OK = 0,
+  EARB200_NOT_IMPLEMENTED = 1,  /* ear::not_implemented */
+  EARB200_INTERNAL_ERROR = 2,   /* ear::internal_error  */
+  EARB200_ADM_ERROR = 3,        /* ear::adm_error       */
+  EARB200_UNKNOWN_LAYOUT = 4,   /* ear::unknown_layout  */
+  EARB200_INVALID_ARGUMENT = 5, /* ear::invalid_argument */
+  EARB200_CUDA_ERROR = 6        /* CUDA runtime failure / no device */
+} earb200_status;
+
+const char *earb200_last_error(void);
+const char *earb200_version(void);
+
+/* ---------------------------------------------------------------- layouts
+ * replaces ear::getLayout / ear::Layout (include/ear/bs2051.hpp:9,
+ * include/ear/layout.hpp:15-96, src/bs2051.cpp:13-22). */
+typedef struct earb200_layout earb200_layout;
+
+int earb200_num_layouts(void);
+const char *earb200_layout_name_at(int i);
+/* a tabulated ITU-R BS.2051 layout by name, e.g. "9+10+3" */
+int earb200_layout_create(const char *name, earb200_layout **out);
+/* a BS.2051 layout with real loudspeaker positions that differ from the nominal
+ * ones: `name` selects the tabulated layout (channel set, nominal positions);
+ * real_pos is [n][3] = azimuth, elevation, distance per channel, table order. */
+int earb200_layout_create_with_positions(const char *name, int n_channels,
+                                         const double *real_pos, earb200_layout **out);
+void earb200_layout_destroy(earb200_layout *layout);
+int earb200_layout_num_channels(const earb200_layout *layout);
+const char *earb200_layout_channel_name(const earb200_layout *layout, int i);
+int earb200_layout_channel_is_lfe(const earb200_layout *layout, int i);
+/* pos[3] = azimuth, elevation, distance (real position); nominal likewise */
+int earb200_layout_channel_position(const earb200_layout *layout, int i, double *pos,
+                                    double *nominal);
+
+/* ------------------------------------------------- point-source panner (K1)
+ * replaces ear::configurePolarPanner(layout.withoutLfe())->handle(position)
+ * (src/common/point_source_panner.cpp:586-600, 234-244, 201-211).  Besides the S
+ * gains it reports which region accepted the position: the index into the region
+ * list configureFullPolarPanner builds (:495-554; virtual n-gons first, then the
+ * hull facets in table order) and, for n-gons, the inner triplet index. */
+typedef struct earb200_panner earb200_panner;
+
+int earb200_panner_create(const earb200_layout *layout, int device, earb200_panner **out);
+void earb200_panner_destroy(earb200_panner *panner);
+int earb200_panner_num_channels(const earb200_panner *panner); /* S (no LFE) */
+int earb200_panner_num_regions(const earb200_panner *panner);
+/* xyz [n][3]; gains [n][S] (double); region_idx / inner_idx [n], nullable */
+int earb200_panner_handle_host(earb200_panner *panner, int64_t n, const double *xyz,
+                               double *gains, int32_t *region_idx, int32_t *inner_idx);
+int earb200_panner_handle_device(earb200_panner *panner, int64_t n, const double *d_xyz,
+                                 double *d_gains, int32_t *d_region_idx,
+                                 int32_t *d_inner_idx, void *stream);
+
+/* ------------------------------------------- Objects gain calculator (K1+K2)
+ * replaces ear::GainCalculatorObjects (include/ear/gain_calculators.hpp:37-64,
+ * src/object_based/gain_calculator_objects.cpp:26-57) for a batch of objects. */
+typedef struct earb200_objects earb200_objects;
+
+/* struct-of-arrays form of ear::ObjectsTypeMetadata (include/ear/metadata.hpp:127-145):
+ * polar position (degrees / normalised distance), extent (degrees), gain, diffuse.
+ * `flags` (nullable) carries the features libear refuses with ear::not_implemented
+ * (gain_calculator_objects.cpp:37-43); a batch containing any of them fails the
+ * same way. */
+typedef struct earb200_objects_soa {
+  const double *azimuth;
+  const double *elevation;
+  const double *distance;
+  const double *width;
+  const double *height;
+  const double *depth;
+  const double *gain;
+  const double *diffuse;
+  const int32_t *flags;
+} earb200_objects_soa;
+
+enum {
+  EARB200_OBJ_CARTESIAN = 1,          /* metadata.cartesian == true           */
+  EARB200_OBJ_CHANNEL_LOCK = 2,       /* channelLock.flag                     */
+  EARB200_OBJ_SCREEN_REF = 4,         /* screenRef                            */
+  EARB200_OBJ_DIVERGENCE = 8,         /* objectDivergence.divergence != 0     */
+  EARB200_OBJ_ZONE_EXCLUSION = 16,    /* zoneExclusion.zones non-empty        */
+  EARB200_OBJ_CARTESIAN_POSITION = 32 /* position holds a CartesianPosition   */
+};
+
+int earb200_objects_create(const earb200_layout *layout, int device, earb200_objects **out);
+void earb200_objects_destroy(earb200_objects *calc);
+int earb200_objects_num_outputs(const earb200_objects *calc); /* C_out incl. LFE */
+/* direct / diffuse: [n][C_out] row-major, float (out_is_double = 0) or double;
+ * region_idx [n] nullable: region of the point-source panner at the object position.
+ * In the _device variant the SoA pointers (including flags) are HOST pointers for
+ * flags and DEVICE pointers for the eight double arrays. */
+int earb200_objects_calculate_host(earb200_objects *calc, int64_t n,
+                                   const earb200_objects_soa *in, int out_is_double,
+                                   void *direct, void *diffuse, int32_t *region_idx);
+int earb200_objects_calculate_device(earb200_objects *calc, int64_t n,
+                                     const earb200_objects_soa *d_in, int out_is_double,
+                                     void *d_direct, void *d_diffuse,
+                                     int32_t *d_region_idx, void *stream);
+/* PolarExtent::handle on Cartesian positions (src/object_based/polar_extent.cpp:281-302):
+ * xyz [n][3], width/height/depth [n]; out [n][S] double.  Host buffers. */
+int earb200_objects_extent_host(earb200_objects *calc, int64_t n, const double *xyz,
+                                const double *width, const double *height,
+                                const double *depth, double *out);
+/* number of kernels this handle has launched so far (bench bookkeeping) */
+int64_t earb200_objects_launch_count(const earb200_objects *calc);
+/* measurement hooks: with profiling on, every launch of the dominant kernel (the extent
+ * core) is bracketed by CUDA events on the launching stream; _kernel_time synchronises,
+ * returns the summed device time [ms] and launch count since the last query and the
+ * number of pass slots (two per object; the second is idle when depth == 0) those
+ * launches covered, then resets. */
+int earb200_objects_set_profiling(earb200_objects *calc, int enable);
+int earb200_objects_kernel_time(earb200_objects *calc, double *ms, int64_t *launches,
+                                int64_t *passes);
+
+/* -------------------------------------------------- gain interpolator (K3)
+ * replaces ear::dsp::GainInterpolator<LinearInterpMatrix|Vector|Single>
+ * (include/ear/dsp/gain_interpolator.hpp:40-130, 183-300): N input channels are
+ * mixed into M outputs with piecewise-linear gains between interpolation points. */
+typedef struct earb200_interp earb200_interp;
+
+int earb200_interp_create(int n_in, int n_out, int device, earb200_interp **out);
+void earb200_interp_destroy(earb200_interp *interp);
+/* interp_points: sample index + [n_in][n_out] gain matrix each (host buffers).
+ * Unsorted sample indices are reported lazily by process, as in libear (:123-124). */
+int earb200_interp_set_points(earb200_interp *interp, int64_t n_points,
+                              const int64_t *sample_idx, const float *gains);
+/* process(block_start, nsamples, in, out): in is n_in planar channels of nsamples
+ * floats, channel c at in + c*in_stride; out likewise (overwritten). */
+int earb200_interp_process_host(earb200_interp *interp, int64_t block_start,
+                                int64_t nsamples, const float *in, int64_t in_stride,
+                                float *out, int64_t out_stride);
+int earb200_interp_process_device(earb200_interp *interp, int64_t block_start,
+                                  int64_t nsamples, const float *d_in, int64_t in_stride,
+                                  float *d_out, int64_t out_stride, void *stream);
+int64_t earb200_interp_launch_count(const earb200_interp *interp);
+int earb200_interp_set_profiling(earb200_interp *interp, int enable);
+int earb200_interp_kernel_time(earb200_interp *interp, double *ms, int64_t *launches);
+
+/* ----------------------------------------------------- block convolver (K4)
+ * replaces ear::dsp::block_convolver::{Context,Filter,BlockConvolver}
+ * (include/ear/dsp/block_convolver.hpp:28-112, src/dsp/block_convolver_impl.cpp) and
+ * the FFT plug-in it is built on (include/ear/fft.hpp:14-67): a bank of n_channels
+ * independent uniformly-partitioned overlap-add convolvers of block size B. */
+typedef struct earb200_convolver earb200_convolver;
+
+/* block_size must be a power of two in [16, 4096]; num_blocks = max partitions */
+int earb200_convolver_create(int64_t block_size, int n_channels, int64_t num_blocks,
+                             int device, earb200_convolver **out);
+void earb200_convolver_destroy(earb200_convolver *conv);
+/* Filter::Filter(ctx, n, taps): returns the filter id and its number of blocks */
+int earb200_convolver_add_filter(earb200_convolver *conv, int64_t n_taps,
+                                 const float *taps, int *filter_id, int *num_blocks);
+/* set_filter / crossfade_filter on one channel (channel < 0: all channels);
+ * filter_id < 0 = no filter (unset_filter / fade_down) */
+int earb200_convolver_set_filter(earb200_convolver *conv, int channel, int filter_id);
+int earb200_convolver_crossfade_filter(earb200_convolver *conv, int channel, int filter_id);
+/* process n_blocks consecutive blocks per channel; channel c at in + c*in_stride.
+ * in may be NULL (silence, as process(nullptr, out)). */
+int earb200_convolver_process_host(earb200_convolver *conv, int64_t n_blocks,
+                                   const float *in, int64_t in_stride, float *out,
+                                   int64_t out_stride);
+int earb200_convolver_process_device(earb200_convolver *conv, int64_t n_blocks,
+                                     const float *d_in, int64_t in_stride, float *d_out,
+                                     int64_t out_stride, void *stream);
+int64_t earb200_convolver_launch_count(const earb200_convolver *conv);
+int earb200_convolver_set_profiling(earb200_convolver *conv, int enable);
+int earb200_convolver_kernel_time(earb200_convolver *conv, double *ms, int64_t *launches);
+
+/* ------------------------------------------------ HOA decoder design (K5)
+ * replaces ear::GainCalculatorHOA (include/ear/gain_calculators.hpp:67-82,
+ * src/hoa/gain_calculator_hoa.cpp:8-72, src/hoa/hoa.hpp:88-143). */
+typedef struct earb200_hoa earb200_hoa;
+
+enum {
+  EARB200_WARN_HOA_SCREENREF = 4,  /* Warning::Code::HOA_SCREENREF_NOT_IMPLEMENTED  */
+  EARB200_WARN_HOA_NFCREFDIST = 5  /* Warning::Code::HOA_NFCREFDIST_NOT_IMPLEMENTED */
+};
+
+int earb200_hoa_create(const earb200_layout *layout, int device, earb200_hoa **out);
+void earb200_hoa_destroy(earb200_hoa *hoa);
+/* decode [n_channels][C_out] row-major double (one vector of per-loudspeaker gains
+ * per HOA input channel).  warnings: bitmask of (1 << code) raised, nullable. */
+int earb200_hoa_calculate(earb200_hoa *hoa, int n_channels, const int *orders,
+                          const int *degrees, const char *normalization,
+                          double nfc_ref_dist, int screen_ref, double *decode,
+                          uint32_t *warnings);
+
+/* ---------------------------------------------------------- decorrelators
+ * replaces ear::designDecorrelators / decorrelatorCompensationDelay
+ * (include/ear/decorrelate.hpp:17-34, src/decorrelate.cpp:31-97).  Setup-time, host. */
+int earb200_decorrelator_size(void);               /* 512 */
+int earb200_decorrelator_compensation_delay(void); /* 255 */
+/* filters [n_channels][512]; float_out / double_out nullable */
+int earb200_design_decorrelators(const earb200_layout *layout, float *float_out,
+                                 double *double_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EARB200_H */

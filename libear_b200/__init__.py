@@ -1,0 +1,381 @@
+"""libear_b200 -- Python harness over the C ABI of libear-b200 (include/earb200.h).
+
+The product is the C-ABI shared library ``libear_b200/libearb200.so`` (hand-written
+sm_100a CUDA kernels + C++ host code) and the C++ facade in
+``libear_b200/include/ear``.  This module only binds the C ABI with ctypes so that the
+parity tests and ``bench.py`` can call it; the class names mirror libear's
+(``GainCalculatorObjects``, ``GainInterpolator``, ``BlockConvolver`` ...).
+
+There is no CPU fallback: if the shared library is missing, importing this module
+raises; if no CUDA device is present, creating any calculator raises ``CudaError``.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libearb200.so")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError(
+        f"{LIB_PATH} not found: build it with `make -C libear_b200` (or "
+        "`python -c 'import __graft_entry__ as g; g.build()'`). libear-b200 has no CPU fallback.")
+
+_lib = C.CDLL(LIB_PATH)
+_lib.earb200_last_error.restype = C.c_char_p
+_lib.earb200_version.restype = C.c_char_p
+_lib.earb200_layout_name_at.restype = C.c_char_p
+_lib.earb200_layout_channel_name.restype = C.c_char_p
+for _f in ("earb200_objects_launch_count", "earb200_interp_launch_count",
+           "earb200_convolver_launch_count"):
+    getattr(_lib, _f).restype = C.c_int64
+
+
+# exception classes mirroring libear's (include/ear/exceptions.hpp:8-43)
+class EarError(RuntimeError):
+    pass
+
+
+class NotImplementedFeature(EarError):      # ear::not_implemented
+    pass
+
+
+class InternalError(EarError):              # ear::internal_error
+    pass
+
+
+class AdmError(EarError, ValueError):       # ear::adm_error
+    pass
+
+
+class UnknownLayout(EarError, ValueError):  # ear::unknown_layout
+    pass
+
+
+class InvalidArgument(EarError, ValueError):  # ear::invalid_argument
+    pass
+
+
+class CudaError(EarError):
+    pass
+
+
+_ERRORS = {1: NotImplementedFeature, 2: InternalError, 3: AdmError, 4: UnknownLayout,
+           5: InvalidArgument, 6: CudaError}
+
+
+def _chk(rc):
+    if rc != 0:
+        raise _ERRORS.get(rc, EarError)(_lib.earb200_last_error().decode())
+
+
+def _ptr(a):
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data_as(C.c_void_p)
+    return C.c_void_p(int(a))  # raw device pointer
+
+
+def _f64(a, n=None):
+    a = np.ascontiguousarray(np.broadcast_to(np.asarray(a, dtype=np.float64), (n,)) if n is not None
+                             else np.asarray(a, dtype=np.float64))
+    return a
+
+
+def version():
+    return _lib.earb200_version().decode()
+
+
+def layout_names():
+    return [_lib.earb200_layout_name_at(i).decode() for i in range(_lib.earb200_num_layouts())]
+
+
+class Layout:
+    """ear::Layout / ear::getLayout (include/ear/layout.hpp:62-96, src/bs2051.cpp:13-22)."""
+
+    def __init__(self, name, real_positions=None):
+        self.h = C.c_void_p()
+        self.name = name
+        if real_positions is None:
+            _chk(_lib.earb200_layout_create(name.encode(), C.byref(self.h)))
+        else:
+            rp = np.ascontiguousarray(real_positions, dtype=np.float64).reshape(-1, 3)
+            _chk(_lib.earb200_layout_create_with_positions(name.encode(), len(rp), _ptr(rp),
+                                                           C.byref(self.h)))
+        n = _lib.earb200_layout_num_channels(self.h)
+        self.channel_names = [_lib.earb200_layout_channel_name(self.h, i).decode() for i in range(n)]
+        self.is_lfe = np.array([bool(_lib.earb200_layout_channel_is_lfe(self.h, i)) for i in range(n)])
+        self.positions = np.zeros((n, 3))
+        self.nominal_positions = np.zeros((n, 3))
+        for i in range(n):
+            _chk(_lib.earb200_layout_channel_position(self.h, i, _ptr(self.positions[i:i + 1]),
+                                                      _ptr(self.nominal_positions[i:i + 1])))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            _lib.earb200_layout_destroy(self.h)
+            self.h = None
+
+
+def get_layout(name):
+    return Layout(name)
+
+
+def _as_layout(layout):
+    return layout if isinstance(layout, Layout) else Layout(layout)
+
+
+class PointSourcePanner:
+    """ear::configurePolarPanner(layout.withoutLfe()) (src/common/point_source_panner.cpp:586-600)."""
+
+    def __init__(self, layout, device=0):
+        self.layout = _as_layout(layout)
+        self.h = C.c_void_p()
+        _chk(_lib.earb200_panner_create(self.layout.h, device, C.byref(self.h)))
+        self.num_channels = _lib.earb200_panner_num_channels(self.h)
+        self.num_regions = _lib.earb200_panner_num_regions(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            _lib.earb200_panner_destroy(self.h)
+            self.h = None
+
+    def handle(self, xyz, regions=False):
+        xyz = np.ascontiguousarray(xyz, dtype=np.float64).reshape(-1, 3)
+        n = len(xyz)
+        gains = np.zeros((n, self.num_channels))
+        reg = np.zeros(n, dtype=np.int32) if regions else None
+        inner = np.zeros(n, dtype=np.int32) if regions else None
+        _chk(_lib.earb200_panner_handle_host(self.h, C.c_int64(n), _ptr(xyz), _ptr(gains),
+                                             _ptr(reg), _ptr(inner)))
+        return (gains, reg, inner) if regions else gains
+
+
+class _ObjectsSoA(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in ("azimuth", "elevation", "distance", "width", "height",
+                                          "depth", "gain", "diffuse", "flags")]
+
+
+# feature bits libear refuses with ear::not_implemented (earb200.h)
+OBJ_CARTESIAN, OBJ_CHANNEL_LOCK, OBJ_SCREEN_REF = 1, 2, 4
+OBJ_DIVERGENCE, OBJ_ZONE_EXCLUSION, OBJ_CARTESIAN_POSITION = 8, 16, 32
+
+
+class GainCalculatorObjects:
+    """ear::GainCalculatorObjects (include/ear/gain_calculators.hpp:37-64), batched."""
+
+    def __init__(self, layout, device=0):
+        self.layout = _as_layout(layout)
+        self.h = C.c_void_p()
+        _chk(_lib.earb200_objects_create(self.layout.h, device, C.byref(self.h)))
+        self.num_outputs = _lib.earb200_objects_num_outputs(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            _lib.earb200_objects_destroy(self.h)
+            self.h = None
+
+    @property
+    def launch_count(self):
+        return _lib.earb200_objects_launch_count(self.h)
+
+    def set_profiling(self, enable=True):
+        _chk(_lib.earb200_objects_set_profiling(self.h, int(enable)))
+
+    def kernel_time(self):
+        """(ms, launches, pass_slots) of the extent core kernel since the last query."""
+        ms, n, p = C.c_double(0), C.c_int64(0), C.c_int64(0)
+        _chk(_lib.earb200_objects_kernel_time(self.h, C.byref(ms), C.byref(n), C.byref(p)))
+        return ms.value, n.value, p.value
+
+    def calculate(self, azimuth, elevation, distance=1.0, width=0.0, height=0.0, depth=0.0,
+                  gain=1.0, diffuse=0.0, flags=None, dtype=np.float32, regions=False):
+        """Host buffers in, host buffers out: (direct, diffuse[, region_idx])."""
+        az = np.atleast_1d(np.asarray(azimuth, dtype=np.float64))
+        n = len(az)
+        arrs = [_f64(a, n) for a in (az, elevation, distance, width, height, depth, gain, diffuse)]
+        fl = None if flags is None else np.ascontiguousarray(np.broadcast_to(flags, (n,)), dtype=np.int32)
+        soa = _ObjectsSoA(*[a.ctypes.data for a in arrs], fl.ctypes.data if fl is not None else None)
+        direct = np.zeros((n, self.num_outputs), dtype=dtype)
+        diffuse_out = np.zeros((n, self.num_outputs), dtype=dtype)
+        reg = np.zeros(n, dtype=np.int32) if regions else None
+        _chk(_lib.earb200_objects_calculate_host(self.h, C.c_int64(n), C.byref(soa),
+                                                 int(np.dtype(dtype) == np.float64), _ptr(direct),
+                                                 _ptr(diffuse_out), _ptr(reg)))
+        return (direct, diffuse_out, reg) if regions else (direct, diffuse_out)
+
+    def calculate_device(self, n, d_soa, d_direct, d_diffuse, d_regions=None, out_is_double=False,
+                         stream=0):
+        """Device pointers (ints) in d_soa = 8 device addresses in field order; asynchronous."""
+        soa = _ObjectsSoA(*[int(p) for p in d_soa], None)
+        _chk(_lib.earb200_objects_calculate_device(self.h, C.c_int64(n), C.byref(soa), int(out_is_double),
+                                                   _ptr(d_direct), _ptr(d_diffuse), _ptr(d_regions),
+                                                   C.c_void_p(int(stream))))
+
+    def extent(self, xyz, width, height, depth):
+        """ear::PolarExtent::handle (src/object_based/polar_extent.cpp:281-302): [n][S] double."""
+        xyz = np.ascontiguousarray(xyz, dtype=np.float64).reshape(-1, 3)
+        n = len(xyz)
+        w, h, d = (_f64(a, n) for a in (width, height, depth))
+        S = int((~self.layout.is_lfe).sum())
+        out = np.zeros((n, S))
+        _chk(_lib.earb200_objects_extent_host(self.h, C.c_int64(n), _ptr(xyz), _ptr(w), _ptr(h), _ptr(d),
+                                              _ptr(out)))
+        return out
+
+
+class GainInterpolator:
+    """ear::dsp::GainInterpolator<LinearInterpMatrix> (include/ear/dsp/gain_interpolator.hpp).
+
+    ``interp_points`` is a list of (sample_index, gains[n_in][n_out]); call
+    ``set_points`` after changing it.  N = 1 gives LinearInterpVector, N = M = 1
+    LinearInterpSingle.
+    """
+
+    def __init__(self, n_in, n_out, device=0):
+        self.n_in, self.n_out = n_in, n_out
+        self.h = C.c_void_p()
+        _chk(_lib.earb200_interp_create(n_in, n_out, device, C.byref(self.h)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            _lib.earb200_interp_destroy(self.h)
+            self.h = None
+
+    @property
+    def launch_count(self):
+        return _lib.earb200_interp_launch_count(self.h)
+
+    def set_profiling(self, enable=True):
+        _chk(_lib.earb200_interp_set_profiling(self.h, int(enable)))
+
+    def kernel_time(self):
+        ms, n = C.c_double(0), C.c_int64(0)
+        _chk(_lib.earb200_interp_kernel_time(self.h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def set_points(self, sample_idx, gains):
+        s = np.ascontiguousarray(sample_idx, dtype=np.int64)
+        g = np.ascontiguousarray(gains, dtype=np.float32).reshape(len(s), self.n_in, self.n_out)
+        _chk(_lib.earb200_interp_set_points(self.h, C.c_int64(len(s)), _ptr(s), _ptr(g)))
+
+    def process(self, block_start, inp):
+        """inp: float32 [n_in][nsamples] host array -> out float32 [n_out][nsamples]."""
+        inp = np.ascontiguousarray(inp, dtype=np.float32).reshape(self.n_in, -1)
+        n = inp.shape[1]
+        out = np.zeros((self.n_out, n), dtype=np.float32)
+        _chk(_lib.earb200_interp_process_host(self.h, C.c_int64(block_start), C.c_int64(n), _ptr(inp),
+                                              C.c_int64(n), _ptr(out), C.c_int64(n)))
+        return out
+
+    def process_device(self, block_start, nsamples, d_in, in_stride, d_out, out_stride, stream=0):
+        _chk(_lib.earb200_interp_process_device(self.h, C.c_int64(block_start), C.c_int64(nsamples),
+                                                _ptr(d_in), C.c_int64(in_stride), _ptr(d_out),
+                                                C.c_int64(out_stride), C.c_void_p(int(stream))))
+
+
+class BlockConvolver:
+    """A bank of ear::dsp::block_convolver::BlockConvolver (include/ear/dsp/block_convolver.hpp)."""
+
+    def __init__(self, block_size, n_channels, num_blocks, device=0):
+        self.block_size, self.n_channels, self.num_blocks = block_size, n_channels, num_blocks
+        self.h = C.c_void_p()
+        _chk(_lib.earb200_convolver_create(C.c_int64(block_size), n_channels, C.c_int64(num_blocks),
+                                           device, C.byref(self.h)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            _lib.earb200_convolver_destroy(self.h)
+            self.h = None
+
+    @property
+    def launch_count(self):
+        return _lib.earb200_convolver_launch_count(self.h)
+
+    def set_profiling(self, enable=True):
+        _chk(_lib.earb200_convolver_set_profiling(self.h, int(enable)))
+
+    def kernel_time(self):
+        ms, n = C.c_double(0), C.c_int64(0)
+        _chk(_lib.earb200_convolver_kernel_time(self.h, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
+    def add_filter(self, taps):
+        taps = np.ascontiguousarray(taps, dtype=np.float32)
+        fid, nb = C.c_int(0), C.c_int(0)
+        _chk(_lib.earb200_convolver_add_filter(self.h, C.c_int64(len(taps)), _ptr(taps), C.byref(fid),
+                                               C.byref(nb)))
+        return fid.value, nb.value
+
+    def set_filter(self, filter_id, channel=-1):
+        _chk(_lib.earb200_convolver_set_filter(self.h, channel, -1 if filter_id is None else filter_id))
+
+    def crossfade_filter(self, filter_id, channel=-1):
+        _chk(_lib.earb200_convolver_crossfade_filter(self.h, channel,
+                                                     -1 if filter_id is None else filter_id))
+
+    def process(self, x, n_blocks=None):
+        """x: float32 [n_channels][n_blocks*B] host array, or None for silence."""
+        if x is None:
+            out = np.zeros((self.n_channels, n_blocks * self.block_size), dtype=np.float32)
+            _chk(_lib.earb200_convolver_process_host(self.h, C.c_int64(n_blocks), None, C.c_int64(0),
+                                                     _ptr(out), C.c_int64(out.shape[1])))
+            return out
+        x = np.ascontiguousarray(x, dtype=np.float32).reshape(self.n_channels, -1)
+        nb = x.shape[1] // self.block_size
+        out = np.zeros((self.n_channels, nb * self.block_size), dtype=np.float32)
+        _chk(_lib.earb200_convolver_process_host(self.h, C.c_int64(nb), _ptr(x), C.c_int64(x.shape[1]),
+                                                 _ptr(out), C.c_int64(out.shape[1])))
+        return out
+
+    def process_device(self, n_blocks, d_in, in_stride, d_out, out_stride, stream=0):
+        _chk(_lib.earb200_convolver_process_device(self.h, C.c_int64(n_blocks), _ptr(d_in),
+                                                   C.c_int64(in_stride), _ptr(d_out),
+                                                   C.c_int64(out_stride), C.c_void_p(int(stream))))
+
+
+WARN_HOA_SCREENREF, WARN_HOA_NFCREFDIST = 4, 5
+
+
+class GainCalculatorHOA:
+    """ear::GainCalculatorHOA (include/ear/gain_calculators.hpp:67-82)."""
+
+    def __init__(self, layout, device=0):
+        self.layout = _as_layout(layout)
+        self.h = C.c_void_p()
+        _chk(_lib.earb200_hoa_create(self.layout.h, device, C.byref(self.h)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            _lib.earb200_hoa_destroy(self.h)
+            self.h = None
+
+    def calculate(self, orders, degrees, normalization="SN3D", nfc_ref_dist=0.0, screen_ref=False):
+        """Returns (decode[n_channels][C_out], [warning codes])."""
+        o = np.ascontiguousarray(orders, dtype=np.int32)
+        d = np.ascontiguousarray(degrees, dtype=np.int32)
+        if len(o) != len(d):
+            raise InvalidArgument("orders and degrees must be the same size")
+        n_out = len(self.layout.channel_names)
+        D = np.zeros((len(o), n_out))
+        w = C.c_uint32(0)
+        _chk(_lib.earb200_hoa_calculate(self.h, len(o), _ptr(o), _ptr(d), normalization.encode(),
+                                        C.c_double(nfc_ref_dist), int(screen_ref), _ptr(D), C.byref(w)))
+        return D, [c for c in range(32) if w.value >> c & 1]
+
+
+def design_decorrelators(layout, dtype=np.float32):
+    """ear::designDecorrelators<T> (src/decorrelate.cpp:83-90); host-side setup."""
+    layout = _as_layout(layout)
+    out = np.zeros((len(layout.channel_names), _lib.earb200_decorrelator_size()), dtype=dtype)
+    if np.dtype(dtype) == np.float32:
+        _chk(_lib.earb200_design_decorrelators(layout.h, _ptr(out), None))
+    else:
+        _chk(_lib.earb200_design_decorrelators(layout.h, None, _ptr(out)))
+    return out
+
+
+def decorrelator_compensation_delay():
+    return _lib.earb200_decorrelator_compensation_delay()

@@ -1,0 +1,434 @@
+// C ABI: layouts, point-source panner (K1) and Objects gain calculator (K1+K2).
+#include <cmath>
+#include <cstring>
+#include <memory>
+#include <vector>
+
+#include "capi_common.hpp"
+#include "kernels.hpp"
+
+namespace earb {
+  std::string &last_error() {
+    static thread_local std::string err;
+    return err;
+  }
+}  // namespace earb
+
+using namespace earb;
+
+// ===================================================================== panner
+struct earb200_panner {
+  int device = 0;
+  PspTables tables;
+  PspTables *d_tables = nullptr;
+  DeviceBuffer<double> d_xyz, d_gains;
+  DeviceBuffer<int32_t> d_region, d_inner;
+  ~earb200_panner() {
+    if (d_tables) cudaFree(d_tables);
+  }
+};
+
+namespace {
+  void panner_init(earb200_panner &p, const HostLayout &layout, int device) {
+    use_device(device);
+    p.device = device;
+    buildPspTables(layout, p.tables);
+    EARB_CUDA(cudaMalloc(&p.d_tables, sizeof(PspTables)));
+    EARB_CUDA(cudaMemcpy(p.d_tables, &p.tables, sizeof(PspTables), cudaMemcpyHostToDevice));
+  }
+
+  void panner_handle_host(earb200_panner &p, int64_t n, const double *xyz, double *gains,
+                          int32_t *region, int32_t *inner) {
+    if (n < 0) throw Error(INVALID_ARGUMENT, "negative batch size");
+    if (n == 0) return;
+    use_device(p.device);
+    const int S = p.tables.n_real;
+    p.d_xyz.reserve(3 * n);
+    p.d_gains.reserve((size_t)S * n);
+    if (region) p.d_region.reserve(n);
+    if (inner) p.d_inner.reserve(n);
+    EARB_CUDA(cudaMemcpy(p.d_xyz.ptr, xyz, sizeof(double) * 3 * n, cudaMemcpyHostToDevice));
+    launch_psp_batch(p.d_tables, n, p.d_xyz.ptr, p.d_gains.ptr, region ? p.d_region.ptr : nullptr,
+                     inner ? p.d_inner.ptr : nullptr, 0);
+    EARB_CUDA(cudaGetLastError());
+    EARB_CUDA(cudaMemcpy(gains, p.d_gains.ptr, sizeof(double) * S * n, cudaMemcpyDeviceToHost));
+    if (region)
+      EARB_CUDA(cudaMemcpy(region, p.d_region.ptr, sizeof(int32_t) * n, cudaMemcpyDeviceToHost));
+    if (inner)
+      EARB_CUDA(cudaMemcpy(inner, p.d_inner.ptr, sizeof(int32_t) * n, cudaMemcpyDeviceToHost));
+  }
+}  // namespace
+
+// ===================================================================== objects
+struct earb200_objects {
+  int device = 0;
+  int n_sms = 0;
+  HostLayout layout;
+  earb200_panner panner;
+  int n_out = 0;  // C_out incl. LFE
+  int S = 0;
+  ExtentGrid grid{};
+  DeviceBuffer<int32_t> d_out_index, d_identity_index;
+  DeviceBuffer<float> d_grid_xyz, d_grid_gains, d_grid_sums;
+  // per-chunk scratch
+  static constexpr int64_t kChunk = 131072;
+  DeviceBuffer<ExtentPass> d_passes;
+  DeviceBuffer<ObjectAux> d_aux;
+  DeviceBuffer<float> d_results;
+  DeviceBuffer<unsigned long long> d_counter;
+  // staging for the *_host entry points
+  DeviceBuffer<double> d_in, d_out_d;
+  DeviceBuffer<float> d_out_f;
+  DeviceBuffer<int32_t> d_region;
+  int64_t launches = 0;
+  KernelTimer timer;
+  int64_t timed_passes = 0;
+};
+
+namespace {
+  void objects_init(earb200_objects &o, const HostLayout &layout, int device) {
+    use_device(device);
+    o.device = device;
+    o.layout = layout;
+    cudaDeviceProp prop;
+    EARB_CUDA(cudaGetDeviceProperties(&prop, device));
+    o.n_sms = prop.multiProcessorCount;
+    panner_init(o.panner, layout, device);
+    o.n_out = (int)layout.channels.size();
+    o.S = o.panner.tables.n_real;
+    if (o.n_out > EARB_MAX_OUT) throw Error(INVALID_ARGUMENT, "too many output channels");
+
+    // LFE scatter map (ref gain_calculator_objects.cpp:51-52)
+    std::vector<int32_t> out_index(EARB_MAX_SPK, 0), identity(EARB_MAX_SPK, 0);
+    int s = 0;
+    for (int c = 0; c < o.n_out; c++)
+      if (!layout.channels[c].lfe) out_index[s++] = c;
+    if (s != o.S) throw Error(INTERNAL_ERROR, "loudspeaker count mismatch");
+    for (int i = 0; i < EARB_MAX_SPK; i++) identity[i] = i;
+    EARB_CUDA(cudaMemcpy(o.d_out_index.reserve(EARB_MAX_SPK), out_index.data(),
+                         sizeof(int32_t) * EARB_MAX_SPK, cudaMemcpyHostToDevice));
+    EARB_CUDA(cudaMemcpy(o.d_identity_index.reserve(EARB_MAX_SPK), identity.data(),
+                         sizeof(int32_t) * EARB_MAX_SPK, cudaMemcpyHostToDevice));
+
+    // extent grid: positions, cached point-source gains (computed by K1 on the device),
+    // per-block sums (ref polar_extent.cpp:98-165)
+    std::vector<Vec3> pts = extentGridPositions(37);
+    const int P = (int)pts.size();
+    const int Pp = (P + EARB_EXT_BLOCK - 1) / EARB_EXT_BLOCK * EARB_EXT_BLOCK;
+    const int NB = Pp / EARB_EXT_BLOCK;
+    o.grid.n_points = P;
+    o.grid.n_points_pad = Pp;
+    o.grid.n_blocks = NB;
+    o.grid.n_spk = o.S;
+    if (extent_core_smem_bytes(o.grid) > 227 * 1024)
+      throw Error(INTERNAL_ERROR, "extent tables do not fit in shared memory");
+
+    std::vector<double> xyz(3 * (size_t)P), gains((size_t)P * o.S);
+    for (int p = 0; p < P; p++) {
+      xyz[3 * p] = pts[p].x;
+      xyz[3 * p + 1] = pts[p].y;
+      xyz[3 * p + 2] = pts[p].z;
+    }
+    panner_handle_host(o.panner, P, xyz.data(), gains.data(), nullptr, nullptr);
+    o.launches++;
+
+    std::vector<float> fxyz(3 * (size_t)Pp), fg((size_t)o.S * Pp, 0.0f), fsum((size_t)NB * 32, 0.0f);
+    for (int p = 0; p < Pp; p++) {
+      const int q = p < P ? p : P - 1;  // padding repeats the last point, with zero gains
+      fxyz[p] = (float)pts[q].x;
+      fxyz[Pp + p] = (float)pts[q].y;
+      fxyz[2 * Pp + p] = (float)pts[q].z;
+    }
+    for (int p = 0; p < P; p++)
+      for (int sp = 0; sp < o.S; sp++) {
+        float g = (float)gains[(size_t)p * o.S + sp];
+        fg[(size_t)sp * Pp + p] = g;
+        fsum[(size_t)(p / EARB_EXT_BLOCK) * 32 + sp] += g;
+      }
+    EARB_CUDA(cudaMemcpy(o.d_grid_xyz.reserve(fxyz.size()), fxyz.data(), sizeof(float) * fxyz.size(),
+                         cudaMemcpyHostToDevice));
+    EARB_CUDA(cudaMemcpy(o.d_grid_gains.reserve(fg.size()), fg.data(), sizeof(float) * fg.size(),
+                         cudaMemcpyHostToDevice));
+    EARB_CUDA(cudaMemcpy(o.d_grid_sums.reserve(fsum.size()), fsum.data(), sizeof(float) * fsum.size(),
+                         cudaMemcpyHostToDevice));
+
+    o.d_passes.reserve(2 * earb200_objects::kChunk);
+    o.d_aux.reserve(earb200_objects::kChunk);
+    o.d_results.reserve(2 * earb200_objects::kChunk * EARB_MAX_SPK);
+    o.d_counter.reserve(1);
+  }
+
+  // features libear rejects (ref gain_calculator_objects.cpp:37-43), same order
+  void check_flags(int64_t n, const int32_t *flags) {
+    if (!flags) return;
+    for (int64_t i = 0; i < n; i++) {
+      const int32_t f = flags[i];
+      if (!f) continue;
+      if (f & EARB200_OBJ_CARTESIAN) throw Error(NOT_IMPLEMENTED, "not implemented: cartesian");
+      if (f & EARB200_OBJ_CARTESIAN_POSITION)
+        throw Error(NOT_IMPLEMENTED, "not implemented: cartesian");
+      if (f & EARB200_OBJ_DIVERGENCE) throw Error(NOT_IMPLEMENTED, "not implemented: divergence");
+      if (f & EARB200_OBJ_CHANNEL_LOCK)
+        throw Error(NOT_IMPLEMENTED, "not implemented: channelLock");
+      if (f & EARB200_OBJ_ZONE_EXCLUSION)
+        throw Error(NOT_IMPLEMENTED, "not implemented: zoneExclusion");
+      if (f & EARB200_OBJ_SCREEN_REF) throw Error(NOT_IMPLEMENTED, "not implemented: screenRef");
+    }
+  }
+
+  template <typename OutT>
+  void objects_run(earb200_objects &o, int64_t n, const ObjectsSoA &in, int n_out,
+                   const int32_t *d_out_index, OutT *d_direct, OutT *d_diffuse,
+                   int32_t *d_region, cudaStream_t stream) {
+    for (int64_t start = 0; start < n; start += earb200_objects::kChunk) {
+      const int64_t m = std::min<int64_t>(earb200_objects::kChunk, n - start);
+      ObjectsSoA c = in;
+      if (c.xyz) {
+        c.xyz += 3 * start;
+      } else {
+        c.azimuth += start;
+        c.elevation += start;
+        c.distance += start;
+      }
+      c.width += start;
+      c.height += start;
+      c.depth += start;
+      c.gain += start;
+      c.diffuse += start;
+      launch_objects_prelude(m, c, o.d_passes.ptr, o.d_aux.ptr, stream);
+      o.timer.start(stream);
+      launch_extent_core(o.grid, o.d_grid_xyz.ptr, o.d_grid_gains.ptr, o.d_grid_sums.ptr, 2 * m,
+                         o.d_passes.ptr, o.d_results.ptr, o.d_counter.ptr, o.n_sms, stream);
+      o.timer.stop(stream);
+      if (o.timer.enabled) o.timed_passes += 2 * m;
+      launch_objects_epilogue<OutT>(o.panner.d_tables, m, c, o.d_passes.ptr, o.d_aux.ptr,
+                                    o.d_results.ptr, n_out, d_out_index, d_direct + start * n_out,
+                                    d_diffuse + start * n_out, d_region ? d_region + start : nullptr,
+                                    stream);
+      o.launches += 3;
+    }
+    EARB_CUDA(cudaGetLastError());
+  }
+}  // namespace
+
+extern "C" {
+
+const char *earb200_last_error(void) { return last_error().c_str(); }
+const char *earb200_version(void) { return "libear-b200 0.1.0 (libear 0.9.0 API)"; }
+
+// ----------------------------------------------------------------- layouts
+int earb200_num_layouts(void) { return (int)layoutNames().size(); }
+const char *earb200_layout_name_at(int i) {
+  const auto &n = layoutNames();
+  return (i >= 0 && i < (int)n.size()) ? n[i].c_str() : nullptr;
+}
+int earb200_layout_create(const char *name, earb200_layout **out) {
+  return guarded([&] {
+    if (!name || !out) throw Error(INVALID_ARGUMENT, "null argument");
+    auto l = std::make_unique<earb200_layout>();
+    l->layout = getLayout(name);
+    *out = l.release();
+  });
+}
+int earb200_layout_create_with_positions(const char *name, int n_channels,
+                                         const double *real_pos, earb200_layout **out) {
+  return guarded([&] {
+    if (!name || !out || !real_pos) throw Error(INVALID_ARGUMENT, "null argument");
+    auto l = std::make_unique<earb200_layout>();
+    l->layout = getLayout(name);
+    if ((int)l->layout.channels.size() != n_channels)
+      throw Error(INVALID_ARGUMENT, "number of positions does not match the layout");
+    for (int i = 0; i < n_channels; i++)
+      l->layout.channels[i].pos = {real_pos[3 * i], real_pos[3 * i + 1], real_pos[3 * i + 2]};
+    *out = l.release();
+  });
+}
+void earb200_layout_destroy(earb200_layout *layout) { delete layout; }
+int earb200_layout_num_channels(const earb200_layout *layout) {
+  return layout ? (int)layout->layout.channels.size() : 0;
+}
+const char *earb200_layout_channel_name(const earb200_layout *layout, int i) {
+  if (!layout || i < 0 || i >= (int)layout->layout.channels.size()) return nullptr;
+  return layout->layout.channels[i].name.c_str();
+}
+int earb200_layout_channel_is_lfe(const earb200_layout *layout, int i) {
+  if (!layout || i < 0 || i >= (int)layout->layout.channels.size()) return 0;
+  return layout->layout.channels[i].lfe ? 1 : 0;
+}
+int earb200_layout_channel_position(const earb200_layout *layout, int i, double *pos,
+                                    double *nominal) {
+  return guarded([&] {
+    if (!layout || i < 0 || i >= (int)layout->layout.channels.size())
+      throw Error(INVALID_ARGUMENT, "channel index out of range");
+    const HostChannel &c = layout->layout.channels[i];
+    if (pos) {
+      pos[0] = c.pos.az;
+      pos[1] = c.pos.el;
+      pos[2] = c.pos.dist;
+    }
+    if (nominal) {
+      nominal[0] = c.nominal.az;
+      nominal[1] = c.nominal.el;
+      nominal[2] = c.nominal.dist;
+    }
+  });
+}
+
+// ------------------------------------------------------------------ panner
+int earb200_panner_create(const earb200_layout *layout, int device, earb200_panner **out) {
+  return guarded([&] {
+    if (!layout || !out) throw Error(INVALID_ARGUMENT, "null argument");
+    auto p = std::make_unique<earb200_panner>();
+    panner_init(*p, layout->layout, device);
+    *out = p.release();
+  });
+}
+void earb200_panner_destroy(earb200_panner *panner) { delete panner; }
+int earb200_panner_num_channels(const earb200_panner *panner) {
+  return panner ? panner->tables.n_real : 0;
+}
+int earb200_panner_num_regions(const earb200_panner *panner) {
+  return panner ? panner->tables.n_regions : 0;
+}
+int earb200_panner_handle_host(earb200_panner *panner, int64_t n, const double *xyz,
+                               double *gains, int32_t *region_idx, int32_t *inner_idx) {
+  return guarded([&] {
+    if (!panner || (n > 0 && (!xyz || !gains))) throw Error(INVALID_ARGUMENT, "null argument");
+    panner_handle_host(*panner, n, xyz, gains, region_idx, inner_idx);
+  });
+}
+int earb200_panner_handle_device(earb200_panner *panner, int64_t n, const double *d_xyz,
+                                 double *d_gains, int32_t *d_region_idx,
+                                 int32_t *d_inner_idx, void *stream) {
+  return guarded([&] {
+    if (!panner || (n > 0 && (!d_xyz || !d_gains))) throw Error(INVALID_ARGUMENT, "null argument");
+    use_device(panner->device);
+    launch_psp_batch(panner->d_tables, n, d_xyz, d_gains, d_region_idx, d_inner_idx,
+                     (cudaStream_t)stream);
+    EARB_CUDA(cudaGetLastError());
+  });
+}
+
+// ----------------------------------------------------------------- objects
+int earb200_objects_create(const earb200_layout *layout, int device, earb200_objects **out) {
+  return guarded([&] {
+    if (!layout || !out) throw Error(INVALID_ARGUMENT, "null argument");
+    auto o = std::make_unique<earb200_objects>();
+    objects_init(*o, layout->layout, device);
+    *out = o.release();
+  });
+}
+void earb200_objects_destroy(earb200_objects *calc) { delete calc; }
+int earb200_objects_num_outputs(const earb200_objects *calc) { return calc ? calc->n_out : 0; }
+int64_t earb200_objects_launch_count(const earb200_objects *calc) {
+  return calc ? calc->launches : 0;
+}
+
+int earb200_objects_set_profiling(earb200_objects *calc, int enable) {
+  return guarded([&] {
+    if (!calc) throw Error(INVALID_ARGUMENT, "null argument");
+    calc->timer.enabled = enable != 0;
+  });
+}
+int earb200_objects_kernel_time(earb200_objects *calc, double *ms, int64_t *launches,
+                                int64_t *passes) {
+  return guarded([&] {
+    if (!calc || !ms) throw Error(INVALID_ARGUMENT, "null argument");
+    use_device(calc->device);
+    *ms = calc->timer.collect(launches);
+    if (passes) *passes = calc->timed_passes;
+    calc->timed_passes = 0;
+  });
+}
+
+int earb200_objects_calculate_device(earb200_objects *calc, int64_t n,
+                                     const earb200_objects_soa *d_in, int out_is_double,
+                                     void *d_direct, void *d_diffuse, int32_t *d_region_idx,
+                                     void *stream) {
+  return guarded([&] {
+    if (!calc || !d_in) throw Error(INVALID_ARGUMENT, "null argument");
+    if (n < 0) throw Error(INVALID_ARGUMENT, "negative batch size");
+    if (n == 0) return;
+    if (!d_direct || !d_diffuse) throw Error(INVALID_ARGUMENT, "null output buffer");
+    check_flags(n, d_in->flags);
+    use_device(calc->device);
+    ObjectsSoA soa{d_in->azimuth, d_in->elevation, d_in->distance, d_in->width, d_in->height,
+                   d_in->depth,   d_in->gain,      d_in->diffuse,  nullptr};
+    if (out_is_double)
+      objects_run<double>(*calc, n, soa, calc->n_out, calc->d_out_index.ptr, (double *)d_direct,
+                          (double *)d_diffuse, d_region_idx, (cudaStream_t)stream);
+    else
+      objects_run<float>(*calc, n, soa, calc->n_out, calc->d_out_index.ptr, (float *)d_direct,
+                         (float *)d_diffuse, d_region_idx, (cudaStream_t)stream);
+  });
+}
+
+int earb200_objects_calculate_host(earb200_objects *calc, int64_t n,
+                                   const earb200_objects_soa *in, int out_is_double,
+                                   void *direct, void *diffuse, int32_t *region_idx) {
+  return guarded([&] {
+    if (!calc || !in) throw Error(INVALID_ARGUMENT, "null argument");
+    if (n < 0) throw Error(INVALID_ARGUMENT, "negative batch size");
+    if (n == 0) return;
+    if (!direct || !diffuse) throw Error(INVALID_ARGUMENT, "null output buffer");
+    check_flags(n, in->flags);
+    earb200_objects &o = *calc;
+    use_device(o.device);
+    const double *src[8] = {in->azimuth, in->elevation, in->distance, in->width,
+                            in->height,  in->depth,     in->gain,     in->diffuse};
+    double *d = o.d_in.reserve(8 * (size_t)n);
+    for (int k = 0; k < 8; k++) {
+      if (!src[k]) throw Error(INVALID_ARGUMENT, "null input array");
+      EARB_CUDA(cudaMemcpyAsync(d + (size_t)k * n, src[k], sizeof(double) * n,
+                                cudaMemcpyHostToDevice, 0));
+    }
+    ObjectsSoA soa{d, d + n, d + 2 * n, d + 3 * n, d + 4 * n, d + 5 * n, d + 6 * n, d + 7 * n, nullptr};
+    int32_t *d_reg = region_idx ? o.d_region.reserve(n) : nullptr;
+    const size_t n_el = (size_t)n * o.n_out;
+    if (out_is_double) {
+      double *dd = o.d_out_d.reserve(2 * n_el);
+      objects_run<double>(o, n, soa, o.n_out, o.d_out_index.ptr, dd, dd + n_el, d_reg, 0);
+      EARB_CUDA(cudaMemcpyAsync(direct, dd, sizeof(double) * n_el, cudaMemcpyDeviceToHost, 0));
+      EARB_CUDA(cudaMemcpyAsync(diffuse, dd + n_el, sizeof(double) * n_el, cudaMemcpyDeviceToHost, 0));
+    } else {
+      float *df = o.d_out_f.reserve(2 * n_el);
+      objects_run<float>(o, n, soa, o.n_out, o.d_out_index.ptr, df, df + n_el, d_reg, 0);
+      EARB_CUDA(cudaMemcpyAsync(direct, df, sizeof(float) * n_el, cudaMemcpyDeviceToHost, 0));
+      EARB_CUDA(cudaMemcpyAsync(diffuse, df + n_el, sizeof(float) * n_el, cudaMemcpyDeviceToHost, 0));
+    }
+    if (region_idx)
+      EARB_CUDA(cudaMemcpyAsync(region_idx, d_reg, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, 0));
+    EARB_CUDA(cudaStreamSynchronize(0));
+  });
+}
+
+int earb200_objects_extent_host(earb200_objects *calc, int64_t n, const double *xyz,
+                                const double *width, const double *height,
+                                const double *depth, double *out) {
+  return guarded([&] {
+    if (!calc) throw Error(INVALID_ARGUMENT, "null argument");
+    if (n < 0) throw Error(INVALID_ARGUMENT, "negative batch size");
+    if (n == 0) return;
+    if (!xyz || !width || !height || !depth || !out) throw Error(INVALID_ARGUMENT, "null argument");
+    earb200_objects &o = *calc;
+    use_device(o.device);
+    // layout of the staging buffer: xyz[3n] width[n] height[n] depth[n] ones[n] zeros[n]
+    double *d = o.d_in.reserve(8 * (size_t)n);
+    EARB_CUDA(cudaMemcpyAsync(d, xyz, sizeof(double) * 3 * n, cudaMemcpyHostToDevice, 0));
+    EARB_CUDA(cudaMemcpyAsync(d + 3 * n, width, sizeof(double) * n, cudaMemcpyHostToDevice, 0));
+    EARB_CUDA(cudaMemcpyAsync(d + 4 * n, height, sizeof(double) * n, cudaMemcpyHostToDevice, 0));
+    EARB_CUDA(cudaMemcpyAsync(d + 5 * n, depth, sizeof(double) * n, cudaMemcpyHostToDevice, 0));
+    std::vector<double> ones((size_t)n, 1.0);
+    EARB_CUDA(cudaMemcpyAsync(d + 6 * n, ones.data(), sizeof(double) * n, cudaMemcpyHostToDevice, 0));
+    EARB_CUDA(cudaMemsetAsync(d + 7 * n, 0, sizeof(double) * n, 0));
+    ObjectsSoA soa{nullptr, nullptr, nullptr, d + 3 * n, d + 4 * n, d + 5 * n, d + 6 * n, d + 7 * n, d};
+    const size_t n_el = (size_t)n * o.S;
+    double *dd = o.d_out_d.reserve(2 * n_el);
+    // gain 1, diffuse 0, identity scatter: "direct" is the raw panning vector
+    objects_run<double>(o, n, soa, o.S, o.d_identity_index.ptr, dd, dd + n_el, nullptr, 0);
+    EARB_CUDA(cudaMemcpyAsync(out, dd, sizeof(double) * n_el, cudaMemcpyDeviceToHost, 0));
+    EARB_CUDA(cudaStreamSynchronize(0));
+  });
+}
+
+}  // extern "C"

@@ -1,0 +1,200 @@
+// C ABI: gain interpolator (K3).  Host side = the segmentation logic of
+// GainInterpolator::process / find_block (ref include/ear/dsp/gain_interpolator.hpp:53-129),
+// turned into a table of segments and work items that one kernel launch consumes.
+#include <algorithm>
+#include <memory>
+#include <vector>
+
+#include "capi_common.hpp"
+#include "kernels.hpp"
+
+using namespace earb;
+
+struct earb200_interp {
+  int device = 0;
+  int N = 0, M = 0;
+  // interp_points (host copy) + equality of neighbouring points (constant_interp, :139-141)
+  std::vector<int64_t> sample_idx;
+  std::vector<char> same_as_prev;
+  bool sorted = true;
+  DeviceBuffer<float> d_gains;
+  int64_t n_points = 0;
+  // plan cache for the last (block_start, nsamples)
+  int64_t plan_start = 0, plan_n = -1;
+  long n_ramp = 0, n_const = 0;
+  DeviceBuffer<RenderItem> d_items;
+  DeviceBuffer<RenderSegment> d_segs;
+  // staging for process_host
+  DeviceBuffer<float> d_in, d_out;
+  int64_t launches = 0;
+  KernelTimer timer;
+};
+
+namespace {
+  void build_plan(earb200_interp &h, int64_t block_start, int64_t nsamples) {
+    if (h.plan_n == nsamples && h.plan_start == block_start) return;
+    const int64_t P = h.n_points;
+    if (P == 0) throw Error(INVALID_ARGUMENT, "no interpolation points");
+    if (!h.sorted) throw Error(INVALID_ARGUMENT, "interpolation points are not sorted");
+    std::vector<RenderSegment> segs;
+    std::vector<RenderItem> ramp_items, const_items;
+    const int tile = render_tile_samples(h.M);
+    const int64_t block_end = block_start + nsamples;
+    int64_t cur = block_start;
+    while (cur < block_end) {
+      // block index = number of points at or before `cur`
+      const int64_t idx = std::upper_bound(h.sample_idx.begin(), h.sample_idx.end(), cur) -
+                          h.sample_idx.begin();
+      const int64_t end = (idx == P) ? block_end : std::min(h.sample_idx[idx], block_end);
+      RenderSegment s{};
+      const bool constant = (idx == 0 || idx == P || h.same_as_prev[idx]);
+      if (constant) {
+        s.ramp = 0;
+        s.pa = s.pb = (int)((idx == P) ? idx - 1 : idx);
+        s.ramp_start = 0;
+        s.scale = 0.0f;
+      } else {
+        s.ramp = 1;
+        s.pa = (int)(idx - 1);
+        s.pb = (int)idx;
+        s.ramp_start = h.sample_idx[idx - 1] - block_start;
+        s.scale = 1.0f / (float)(h.sample_idx[idx] - h.sample_idx[idx - 1]);
+      }
+      const int seg_id = (int)segs.size();
+      segs.push_back(s);
+      for (int64_t t = cur; t < end; t += tile) {
+        RenderItem it;
+        it.t0 = t - block_start;
+        it.len = (int)std::min<int64_t>(tile, end - t);
+        it.seg = seg_id;
+        (constant ? const_items : ramp_items).push_back(it);
+      }
+      cur = end;
+    }
+    h.n_ramp = (long)ramp_items.size();
+    h.n_const = (long)const_items.size();
+    std::vector<RenderItem> all(ramp_items);
+    all.insert(all.end(), const_items.begin(), const_items.end());
+    h.d_items.reserve(std::max<size_t>(all.size(), 1));
+    h.d_segs.reserve(std::max<size_t>(segs.size(), 1));
+    EARB_CUDA(cudaMemcpy(h.d_items.ptr, all.data(), sizeof(RenderItem) * all.size(),
+                         cudaMemcpyHostToDevice));
+    EARB_CUDA(cudaMemcpy(h.d_segs.ptr, segs.data(), sizeof(RenderSegment) * segs.size(),
+                         cudaMemcpyHostToDevice));
+    h.plan_start = block_start;
+    h.plan_n = nsamples;
+  }
+
+  void process_device(earb200_interp &h, int64_t block_start, int64_t nsamples, const float *d_in,
+                      int64_t in_stride, float *d_out, int64_t out_stride, cudaStream_t stream) {
+    if (nsamples < 0) throw Error(INVALID_ARGUMENT, "negative sample count");
+    if (nsamples == 0) return;
+    if (!d_in || !d_out) throw Error(INVALID_ARGUMENT, "null buffer");
+    use_device(h.device);
+    build_plan(h, block_start, nsamples);
+    h.timer.start(stream);
+    launch_render(h.N, h.M, d_in, (long)in_stride, d_out, (long)out_stride, h.d_items.ptr, h.n_ramp,
+                  h.d_items.ptr + h.n_ramp, h.n_const, h.d_segs.ptr, h.d_gains.ptr, stream);
+    h.timer.stop(stream);
+    EARB_CUDA(cudaGetLastError());
+    h.launches += (h.n_ramp > 0) + (h.n_const > 0);
+  }
+}  // namespace
+
+extern "C" {
+
+int earb200_interp_create(int n_in, int n_out, int device, earb200_interp **out) {
+  return guarded([&] {
+    if (!out) throw Error(INVALID_ARGUMENT, "null argument");
+    if (n_in < 1 || n_out < 1 || n_out > EARB_MAX_OUT)
+      throw Error(INVALID_ARGUMENT, "unsupported channel counts");
+    if (render_smem_bytes(n_in, n_out) > 200 * 1024)
+      throw Error(INVALID_ARGUMENT, "too many input channels for one gain interpolator");
+    use_device(device);
+    auto h = std::make_unique<earb200_interp>();
+    h->device = device;
+    h->N = n_in;
+    h->M = n_out;
+    *out = h.release();
+  });
+}
+void earb200_interp_destroy(earb200_interp *interp) { delete interp; }
+int64_t earb200_interp_launch_count(const earb200_interp *interp) {
+  return interp ? interp->launches : 0;
+}
+
+int earb200_interp_set_profiling(earb200_interp *interp, int enable) {
+  return guarded([&] {
+    if (!interp) throw Error(INVALID_ARGUMENT, "null argument");
+    interp->timer.enabled = enable != 0;
+  });
+}
+int earb200_interp_kernel_time(earb200_interp *interp, double *ms, int64_t *launches) {
+  return guarded([&] {
+    if (!interp || !ms) throw Error(INVALID_ARGUMENT, "null argument");
+    use_device(interp->device);
+    *ms = interp->timer.collect(launches);
+  });
+}
+
+int earb200_interp_set_points(earb200_interp *interp, int64_t n_points,
+                              const int64_t *sample_idx, const float *gains) {
+  return guarded([&] {
+    if (!interp || n_points < 0 || (n_points > 0 && (!sample_idx || !gains)))
+      throw Error(INVALID_ARGUMENT, "null argument");
+    earb200_interp &h = *interp;
+    use_device(h.device);
+    const size_t mat = (size_t)h.N * h.M;
+    h.sample_idx.assign(sample_idx, sample_idx + n_points);
+    h.same_as_prev.assign(n_points, 0);
+    h.sorted = std::is_sorted(h.sample_idx.begin(), h.sample_idx.end());
+    for (int64_t i = 1; i < n_points; i++) {
+      const float *a = gains + (size_t)(i - 1) * mat, *b = gains + (size_t)i * mat;
+      bool same = true;
+      for (size_t k = 0; k < mat && same; k++) same = (a[k] == b[k]);
+      h.same_as_prev[i] = same;
+    }
+    h.n_points = n_points;
+    h.plan_n = -1;
+    if (n_points > 0) {
+      h.d_gains.reserve(mat * n_points);
+      EARB_CUDA(cudaMemcpy(h.d_gains.ptr, gains, sizeof(float) * mat * n_points,
+                           cudaMemcpyHostToDevice));
+    }
+  });
+}
+
+int earb200_interp_process_device(earb200_interp *interp, int64_t block_start,
+                                  int64_t nsamples, const float *d_in, int64_t in_stride,
+                                  float *d_out, int64_t out_stride, void *stream) {
+  return guarded([&] {
+    if (!interp) throw Error(INVALID_ARGUMENT, "null argument");
+    process_device(*interp, block_start, nsamples, d_in, in_stride, d_out, out_stride,
+                   (cudaStream_t)stream);
+  });
+}
+
+int earb200_interp_process_host(earb200_interp *interp, int64_t block_start,
+                                int64_t nsamples, const float *in, int64_t in_stride,
+                                float *out, int64_t out_stride) {
+  return guarded([&] {
+    if (!interp) throw Error(INVALID_ARGUMENT, "null argument");
+    if (nsamples < 0) throw Error(INVALID_ARGUMENT, "negative sample count");
+    if (nsamples == 0) return;
+    if (!in || !out) throw Error(INVALID_ARGUMENT, "null buffer");
+    earb200_interp &h = *interp;
+    use_device(h.device);
+    // device copies are packed with a 16-byte aligned channel stride
+    const int64_t stride = (nsamples + 3) / 4 * 4;
+    float *d_in = h.d_in.reserve((size_t)stride * h.N);
+    float *d_out = h.d_out.reserve((size_t)stride * h.M);
+    EARB_CUDA(cudaMemcpy2DAsync(d_in, sizeof(float) * stride, in, sizeof(float) * in_stride,
+                                sizeof(float) * nsamples, h.N, cudaMemcpyHostToDevice, 0));
+    process_device(h, block_start, nsamples, d_in, stride, d_out, stride, 0);
+    EARB_CUDA(cudaMemcpy2DAsync(out, sizeof(float) * out_stride, d_out, sizeof(float) * stride,
+                                sizeof(float) * nsamples, h.M, cudaMemcpyDeviceToHost, 0));
+    EARB_CUDA(cudaStreamSynchronize(0));
+  });
+}
+
+}  // extern "C"

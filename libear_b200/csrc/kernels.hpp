@@ -1,0 +1,95 @@
+// Launchers of the CUDA kernels (implemented in the *_kernels.cu files).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "tables.h"
+
+#define EARB_CORE_THREADS 512
+
+namespace earb {
+
+  // device-resident struct-of-arrays form of ear::ObjectsTypeMetadata
+  // (ref include/ear/metadata.hpp:127-145): the eight fields the polar path reads
+  struct ObjectsSoA {
+    const double *azimuth, *elevation, *distance;
+    const double *width, *height, *depth;
+    const double *gain, *diffuse;
+    // optional [n][3] Cartesian positions used instead of azimuth/elevation/distance
+    // (PolarExtent::handle takes the Cartesian position; ref polar_extent.hpp:62)
+    const double *xyz;
+  };
+
+  // ---- K1 / K2: gain calculation (objects_kernels.cu)
+  void launch_psp_batch(const PspTables *d_tables, long n, const double *d_xyz,
+                        double *d_gains, int32_t *d_region, int32_t *d_inner,
+                        cudaStream_t stream);
+  void launch_objects_prelude(long n, const ObjectsSoA &in, ExtentPass *d_passes,
+                              ObjectAux *d_aux, cudaStream_t stream);
+  size_t extent_core_smem_bytes(const ExtentGrid &grid);
+  void launch_extent_core(const ExtentGrid &grid, const float *d_xyz, const float *d_gains,
+                          const float *d_block_sums, long n_slots,
+                          const ExtentPass *d_passes, float *d_results,
+                          unsigned long long *d_counter, int n_sms, cudaStream_t stream);
+  template <typename OutT>
+  void launch_objects_epilogue(const PspTables *d_tables, long n, const ObjectsSoA &in,
+                               const ExtentPass *d_passes, const ObjectAux *d_aux,
+                               const float *d_results, int n_out, const int32_t *d_out_index,
+                               OutT *d_direct, OutT *d_diffuse, int32_t *d_region,
+                               cudaStream_t stream);
+
+  // ---- K3: interpolated mixing (render_kernels.cu)
+#define RENDER_THREADS 128
+#define RENDER_UNROLL 4
+  // one interpolation segment of the call: gains ramp from point pa to point pb
+  // between ramp_start and ramp_start + 1/scale (sample offsets relative to the start of
+  // the call, may be negative), or stay at point pa (ramp == 0)
+  struct RenderSegment {
+    long long ramp_start;
+    float scale;  // 1.0f / (end - start)   (ref gain_interpolator.hpp:255)
+    int pa, pb;
+    int ramp;
+  };
+  // a run of samples [t0, t0 + len) of the call inside one segment
+  struct RenderItem {
+    long long t0;
+    int len;
+    int seg;
+  };
+  int render_tile_samples(int M);
+  size_t render_smem_bytes(int N, int M);
+  void launch_render(int N, int M, const float *in, long in_stride, float *out, long out_stride,
+                     const RenderItem *d_items_ramp, long n_ramp, const RenderItem *d_items_const,
+                     long n_const, const RenderSegment *d_segs, const float *d_gains,
+                     cudaStream_t stream);
+
+  // ---- K4: partitioned FFT convolver bank (convolver_kernels.cu)
+#define CONV_THREADS 128
+  struct ConvLaunch {
+    int B, nb, C, R, Kg;
+    long K;
+    const float *in;  // may be null (silence)
+    long in_stride;
+    float *out;
+    long out_stride;
+    const float *hist;      // [C][nb][B]
+    float *hist_new;        // [C][nb][B]
+    const float *tail;      // [C][B]
+    float *tail_new;        // [C][B]
+    const float *filt;      // [n_filters][nb][B+1] complex
+    const short *ftab;      // [C][Kg][nb][2]
+    const int *uniform;     // [C]
+    const unsigned char *faded;  // [C][nb + Kg]
+    const float *tw2;       // [2B] complex: exp(-2 pi i k / 2B)
+  };
+  size_t conv_smem_bytes(int B, int nb);
+  void launch_convolver(const ConvLaunch &L, cudaStream_t stream);
+
+  // ---- K5: HOA decoder design (hoa_kernels.cu)
+  int hoa_power_blocks(int P);
+  // Y [C][P], D [S][C], partial [hoa_power_blocks(P)]
+  void launch_hoa_design(int P, int S, int C, const double *d_xyz, const double *d_G,
+                         const int *d_orders, const int *d_degrees, const double *d_norms,
+                         double *d_Y, double *d_D, double *d_partial, cudaStream_t stream);
+
+}  // namespace earb

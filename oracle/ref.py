@@ -82,6 +82,18 @@ def layout_info(name):
     return dict(names=nm, is_lfe=is_lfe.astype(bool), pos=pos, nominal=nom, ranges=rng)
 
 
+def facets(name):
+    buf = np.zeros(4096, dtype=np.int32)
+    n = C.c_int(0)
+    _chk(lib().ref_facets(name.encode(), _p(buf), len(buf), C.byref(n)))
+    out, k = [], 0
+    while k < n.value:
+        c = int(buf[k])
+        out.append([int(v) for v in buf[k + 1:k + 1 + c]])
+        k += 1 + c
+    return out
+
+
 class PointSourcePanner:
     """ear::configurePolarPanner(layout.withoutLfe()) + region-index probe."""
 

@@ -135,6 +135,22 @@ int ref_layout_info(const char *name, int *n_channels, int *is_lfe, double *pos,
   REF_CATCH
 }
 
+// facets of a layout in FACETS order, each facet's vertices in std::set (ascending)
+// order; out: flat int array, each facet = [count, v0, v1, ...]; returns length via *n
+int ref_facets(const char *layout_name, int *out, int cap, int *n) {
+  REF_TRY
+  const auto &f = FACETS.at(layout_name);
+  int k = 0;
+  for (const auto &facet : f) {
+    if (k + 1 + (int)facet.size() > cap) return 8;
+    out[k++] = (int)facet.size();
+    for (int v : facet) out[k++] = v;
+  }
+  *n = k;
+  return 0;
+  REF_CATCH
+}
+
 // ---- point source panner + region index --------------------------------
 int ref_psp_new(const char *layout_name, void **out) {
   REF_TRY

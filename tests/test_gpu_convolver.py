@@ -1,0 +1,112 @@
+"""K4 parity: BlockConvolver bank vs the compiled libear reference (KISS float FFT).
+
+Mirrors the scenarios of tests/block_convolver_tests.cpp :208-356 (multi-partition
+filters, crossfades, fades to/from silence, different num_blocks, zero and NULL input
+blocks) with the reference convolver itself as the oracle, plus an exact float64
+direct convolution.  Tolerance: 1e-6 of peak (the reference's own test uses 1e-6
+absolute on unit-scale signals, block_convolver_tests.cpp:77,192).
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def peak_err(a, b):
+    return np.abs(a - b).max() / max(np.abs(b).max(), 1e-30)
+
+
+def run_script(eb, ref, B, nb, filters, script, n_channels=1, chunk=None):
+    """script: list of ('set'|'xfade', fid|None) or ('run', x[n_blocks*B]) or ('silence', n_blocks)."""
+    r = [ref.Convolver(B, nb) for _ in range(n_channels)]
+    g = eb.BlockConvolver(B, n_channels, nb)
+    for taps in filters:
+        ids = [rc.add_filter(taps)[0] for rc in r]
+        gid, gnb = g.add_filter(taps)
+        assert gid == ids[0] and gnb == -(-len(taps) // B)
+    out_r, out_g = [], []
+    for op, arg in script:
+        if op == "set":
+            [rc.set_filter(arg) for rc in r]
+            g.set_filter(arg)
+        elif op == "xfade":
+            [rc.crossfade_filter(arg) for rc in r]
+            g.crossfade_filter(arg)
+        elif op == "silence":
+            out_r.append(np.stack([rc.process(None, arg) for rc in r]))
+            out_g.append(g.process(None, arg))
+        else:
+            x = arg.reshape(n_channels, -1)
+            out_r.append(np.stack([rc.process(x[c]) for c, rc in enumerate(r)]))
+            step = chunk or x.shape[1]
+            out_g.append(np.concatenate([g.process(x[:, t:t + step]) for t in range(0, x.shape[1], step)], 1))
+    return np.concatenate(out_g, 1), np.concatenate(out_r, 1)
+
+
+@pytest.mark.parametrize("B,nb,taps", [(512, 1, 512), (128, 4, 512), (64, 2, 100), (32, 7, 200), (16, 3, 40),
+                                       (1024, 1, 700), (256, 2, 256)])
+def test_single_filter(eb, ref, B, nb, taps):
+    rng = np.random.default_rng(B + nb)
+    h = rng.normal(size=taps).astype(np.float32)
+    x = rng.normal(0, 0.25, size=B * 40).astype(np.float32)
+    out, exp = run_script(eb, ref, B, nb, [h], [("set", 0), ("run", x)])
+    assert peak_err(out, exp) < 1e-6
+    direct = np.convolve(x.astype(np.float64), h.astype(np.float64))[:len(x)]
+    assert peak_err(out[0], direct) < 1e-6
+
+
+def test_streaming_calls_match_one_call(eb, ref):
+    rng = np.random.default_rng(1)
+    B, nb = 64, 3
+    h = rng.normal(size=150).astype(np.float32)
+    x = rng.normal(size=B * 50).astype(np.float32)
+    for chunk in [B, 2 * B, 7 * B]:
+        out, exp = run_script(eb, ref, B, nb, [h], [("set", 0), ("run", x)], chunk=chunk)
+        assert peak_err(out, exp) < 1e-6, chunk
+
+
+def test_crossfades_and_filter_changes(eb, ref):
+    rng = np.random.default_rng(2)
+    B, nb = 64, 3
+    f = [rng.normal(size=n).astype(np.float32) for n in (150, 64, 192, 10)]
+    blk = lambda k: rng.normal(size=B * k).astype(np.float32)
+    script = [("set", 0), ("run", blk(5)), ("xfade", 1), ("run", blk(6)), ("xfade", 2), ("run", blk(1)),
+              ("xfade", 0), ("run", blk(8)), ("xfade", None), ("run", blk(6)), ("xfade", 3), ("run", blk(6)),
+              ("set", 1), ("run", blk(4)), ("xfade", 2), ("run", blk(1)), ("set", 0), ("run", blk(5)),
+              ("set", None), ("run", blk(3)), ("set", 2), ("silence", 4), ("run", blk(3)), ("silence", 5)]
+    for chunk in [None, B]:
+        rng = np.random.default_rng(2)
+        out, exp = run_script(eb, ref, B, nb, f, script, chunk=chunk)
+        assert peak_err(out, exp) < 1e-6, chunk
+
+
+def test_too_many_blocks_rejected(eb):
+    g = eb.BlockConvolver(64, 1, 2)
+    fid, nb = g.add_filter(np.ones(200, dtype=np.float32))
+    assert nb == 4
+    with pytest.raises(eb.InvalidArgument, match="too many blocks"):
+        g.set_filter(fid)
+    with pytest.raises(eb.InvalidArgument):
+        eb.BlockConvolver(100, 1, 1)  # not a power of two
+
+
+def test_decorrelator_bank_9_10_3(eb, ref):
+    # BASELINE config 3 shape (24 channels, B = 512, 512-tap decorrelators) on 30 blocks
+    rng = np.random.default_rng(3)
+    filt = eb.design_decorrelators("9+10+3")
+    assert np.array_equal(filt, ref.decorrelators("9+10+3"))
+    C, B, K = 24, 512, 30
+    x = np.clip(rng.normal(0, 0.25, size=(C, B * K)), -1, 1).astype(np.float32)
+    g = eb.BlockConvolver(B, C, 1)
+    for c in range(C):
+        fid, _ = g.add_filter(filt[c])
+        g.set_filter(fid, channel=c)
+    out = g.process(x)
+    for c in range(C):
+        r = ref.Convolver(B, 1)
+        fid, _ = r.add_filter(filt[c])
+        r.set_filter(fid)
+        assert peak_err(out[c], r.process(x[c])) < 1e-6, c
+    # all-pass property at full length scale: output energy == input energy (after the tail)
+    e_in, e_out = (x.astype(np.float64) ** 2).sum(1), (out.astype(np.float64) ** 2).sum(1)
+    assert np.abs(e_out / e_in - 1).max() < 0.05

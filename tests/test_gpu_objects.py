@@ -1,0 +1,155 @@
+"""K1+K2 parity: GainCalculatorObjects / PolarExtent vs the compiled libear reference.
+
+Mirrors tests/extent_tests.cpp (same_as_reference :136-166, test_pv :110-134) and
+tests/gain_calculator_objects_tests.cpp (:74-169) of the reference.
+Tolerances: gains within 1e-5 absolute (north star); region indices bit-exact.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def random_dirs(rng, n):
+    v = rng.normal(size=(n, 3))
+    return v / np.linalg.norm(v, axis=1, keepdims=True)
+
+
+def cfg_objects(rng, n, extent=True):
+    az = rng.uniform(-180, 180, n)
+    el = np.degrees(np.arcsin(rng.uniform(-1, 1, n)))
+    if extent:
+        dist = rng.uniform(0.2, 1.5, n)
+        w, h = rng.uniform(0, 360, n), rng.uniform(0, 360, n)
+        depth = np.where(rng.uniform(size=n) < 0.5, 0.0, rng.uniform(0, 1, n))
+    else:
+        dist, w, h, depth = np.ones(n), np.zeros(n), np.zeros(n), np.zeros(n)
+    return az, el, dist, w, h, depth, rng.uniform(0, 1, n), rng.uniform(0, 1, n)
+
+
+def test_cfg1_point_sources_0_5_0(eb, ref):
+    # BASELINE config 0: 1,024 random point-source objects on 0+5+0
+    rng = np.random.default_rng(1)
+    args = cfg_objects(rng, 1024, extent=False)
+    d_ref, f_ref = ref.Objects("0+5+0").calculate(*args, dtype=np.float32)
+    gc = eb.GainCalculatorObjects("0+5+0")
+    d, f, reg = gc.calculate(*args, dtype=np.float32, regions=True)
+    assert np.abs(d - d_ref).max() < 1e-6 and np.abs(f - f_ref).max() < 1e-6
+    az, el = np.radians(args[0]), np.radians(args[1])
+    xyz = np.stack([np.sin(-az) * np.cos(el), np.cos(-az) * np.cos(el), np.sin(el)], -1)
+    _, reg_ref, _ = ref.PointSourcePanner("0+5+0").handle(xyz)
+    assert (reg == reg_ref).all()
+    d64, f64 = gc.calculate(*args, dtype=np.float64)
+    d_ref64, f_ref64 = ref.Objects("0+5+0").calculate(*args, dtype=np.float64)
+    assert np.abs(d64 - d_ref64).max() < 1e-12 and np.abs(f64 - f_ref64).max() < 1e-12
+
+
+def test_extent_same_as_reference(eb, ref):
+    # extent_tests.cpp same_as_reference: random pos, width, height in U(0, 360), depth 0
+    rng = np.random.default_rng(2)
+    n = 1000
+    xyz = random_dirs(rng, n)
+    w, h = rng.uniform(0, 360, n), rng.uniform(0, 360, n)
+    gc = eb.GainCalculatorObjects("9+10+3")
+    out = gc.extent(xyz, w, h, 0.0)
+    simd = ref.Extent("9+10+3", 0).handle(xyz, w, h, 0.0)
+    dbl = ref.Extent("9+10+3", 2).handle(xyz, w, h, 0.0)
+    assert np.abs(out - simd).max() < 1e-5
+    assert np.abs(out - dbl).max() < 1e-5
+    assert np.abs(np.linalg.norm(out, axis=1) - 1).max() < 1e-5
+
+
+def test_extent_small_sizes_depth_and_distance(eb, ref):
+    rng = np.random.default_rng(3)
+    n = 2000
+    xyz = random_dirs(rng, n) * rng.uniform(0.0, 2.0, size=(n, 1))
+    xyz[:5] = 0.0                      # centre of the room: safeNormPosition fallback
+    xyz[5] = [0, 0, 1.0]               # poles
+    xyz[6] = [0, 0, -0.7]
+    w = rng.choice([0.0, 2.0, 5.0, 9.999, 10.0, 20.0, 90.0, 180.0, 359.0, 360.0], n)
+    h = rng.choice([0.0, 3.0, 5.0, 10.0, 45.0, 180.0, 360.0], n)
+    depth = rng.choice([0.0, 0.1, 0.5, 1.0, 5.0], n)
+    gc = eb.GainCalculatorObjects("9+10+3")
+    out = gc.extent(xyz, w, h, depth)
+    exp = ref.Extent("9+10+3", 0).handle(xyz, w, h, depth)
+    ok = np.isfinite(exp).all(axis=1)
+    assert ok.mean() > 0.99
+    assert np.abs(out[ok] - exp[ok]).max() < 1e-5
+    assert (np.isfinite(out).all(axis=1) == ok).all()
+
+
+def test_zero_extent_is_point_panner(eb, ref):
+    # extent_tests.cpp test_pv: extent 0 at distance 1 == psp->handle exactly
+    rng = np.random.default_rng(4)
+    xyz = random_dirs(rng, 500)
+    gc = eb.GainCalculatorObjects("9+10+3")
+    out = gc.extent(xyz, 0.0, 0.0, 0.0)
+    psp = eb.PointSourcePanner("9+10+3").handle(xyz)
+    assert np.abs(out - psp).max() < 1e-15
+    assert np.abs(out - ref.PointSourcePanner("9+10+3").handle(xyz, regions=False)).max() < 1e-12
+
+
+@pytest.mark.parametrize("layout", ["0+5+0", "4+7+0", "4+9+0", "9+10+3", "0+2+0"])
+def test_objects_extent_batch(eb, ref, layout):
+    # BASELINE config 1 shape at a size the CPU oracle finishes in seconds
+    rng = np.random.default_rng(10)
+    args = cfg_objects(rng, 3000)
+    d_ref, f_ref = ref.Objects(layout).calculate(*args, dtype=np.float32)
+    d, f = eb.GainCalculatorObjects(layout).calculate(*args, dtype=np.float32)
+    assert d.shape == d_ref.shape
+    assert np.abs(d - d_ref).max() < 1e-5 and np.abs(f - f_ref).max() < 1e-5
+
+
+def test_objects_large_batch_crosses_chunks(eb, ref):
+    rng = np.random.default_rng(11)
+    n = 300000  # > one 131072-object chunk
+    args = cfg_objects(rng, n)
+    gc = eb.GainCalculatorObjects("9+10+3")
+    d, f = gc.calculate(*args, dtype=np.float32)
+    idx = np.concatenate([np.arange(0, 64), np.arange(131072 - 32, 131072 + 32),
+                          np.arange(262144 - 32, 262144 + 32), np.arange(n - 64, n)])
+    sub = [a[idx] for a in args]
+    d_ref, f_ref = ref.Objects("9+10+3").calculate(*sub, dtype=np.float32)
+    assert np.abs(d[idx] - d_ref).max() < 1e-5 and np.abs(f[idx] - f_ref).max() < 1e-5
+    # size-independent properties over the full batch: power preserved, LFE silent
+    g = np.sqrt(d.astype(np.float64) ** 2 + f.astype(np.float64) ** 2)
+    assert np.abs(np.linalg.norm(g, axis=1) - args[6]).max() < 1e-5
+    lfe = eb.Layout("9+10+3").is_lfe
+    assert (d[:, lfe] == 0).all() and (f[:, lfe] == 0).all()
+
+
+def test_gain_calculator_known_answers(eb):
+    # gain_calculator_objects_tests.cpp :74-132
+    gc = eb.GainCalculatorObjects("4+7+0")
+    names = gc.layout.channel_names
+    for az, el, name in [(0, 0, "M+000"), (30, 0, "M+030"), (45, 30, "U+045")]:
+        d, f = gc.calculate(az, el, 1.0, dtype=np.float64)
+        assert abs(d[0, names.index(name)] - 1.0) < 1e-9 and np.count_nonzero(np.abs(d[0]) > 1e-6) == 1
+        assert (np.abs(f) < 1e-6).all()
+    d, f = gc.calculate(0, 0, 1.0, diffuse=0.5, dtype=np.float64)
+    i = names.index("M+000")
+    assert abs(d[0, i] - np.sqrt(0.5)) < 1e-9 and abs(f[0, i] - np.sqrt(0.5)) < 1e-9
+    d, f = gc.calculate(0, 0, 1.0, diffuse=1.0, dtype=np.float64)
+    assert (np.abs(d) < 1e-6).all() and abs(f[0, i] - 1.0) < 1e-9
+    d, f = gc.calculate(0, 0, 1.0, gain=0.5, dtype=np.float64)
+    assert abs(d[0, i] - 0.5) < 1e-9
+
+
+def test_not_implemented_features_raise(eb, ref):
+    # gain_calculator_objects_tests.cpp :134-169: same exception class and message
+    gc = eb.GainCalculatorObjects("4+7+0")
+    r = ref.Objects("4+7+0")
+    for flag in [eb.OBJ_CARTESIAN, eb.OBJ_CHANNEL_LOCK, eb.OBJ_SCREEN_REF, eb.OBJ_DIVERGENCE,
+                 eb.OBJ_ZONE_EXCLUSION, eb.OBJ_CARTESIAN_POSITION]:
+        with pytest.raises(eb.NotImplementedFeature) as e:
+            gc.calculate([0.0, 10.0], 0.0, flags=[0, flag])
+        with pytest.raises(ref.RefError) as e_ref:
+            r.calculate([0.0, 10.0], 0.0, 1.0, 0.0, 0.0, 0.0, 1.0, 0.0, flags=[0, flag])
+        assert e_ref.value.kind == "not_implemented"
+        assert str(e.value) in str(e_ref.value)
+
+
+def test_empty_batch(eb):
+    gc = eb.GainCalculatorObjects("0+5+0")
+    d, f = gc.calculate(np.zeros(0), np.zeros(0))
+    assert d.shape == (0, 6)
