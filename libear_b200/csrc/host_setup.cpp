@@ -343,11 +343,56 @@ namespace earb {
     return out;
   }
 
+  namespace {
+    // Sum of one column of an n x 3 column-major matrix in the order Eigen's SSE2
+    // (2-double packet) linear-vectorised reduction uses -- the libear reference takes
+    // the centre as vertices.colwise().mean() (ref geom.cpp:39).  Mirror-symmetric
+    // layouts make the "least collinear vertex" choice below an exact tie that only this
+    // rounding breaks, and the choice fixes the scan order of a virtual n-gon's inner
+    // triangles, so the order is reproduced rather than approximated.  `col` decides the
+    // alignment of the column inside the 16-byte aligned matrix: elements before the
+    // first aligned one and after the last full packet are added last, one by one.
+    double eigenColumnSum(const double *v, int n, int col) {
+      const int start = (col * n) & 1;
+      const int aligned2 = ((n - start) / 4) * 4, aligned = ((n - start) / 2) * 2;
+      const int end2 = start + aligned2, end = start + aligned;
+      if (!aligned) {
+        double r = v[0];
+        for (int i = 1; i < n; i++) r += v[i];
+        return r;
+      }
+      double p0[2] = {v[start], v[start + 1]};
+      if (aligned > 2) {
+        double p1[2] = {v[start + 2], v[start + 3]};
+        for (int i = start + 4; i < end2; i += 4) {
+          p0[0] += v[i];
+          p0[1] += v[i + 1];
+          p1[0] += v[i + 2];
+          p1[1] += v[i + 3];
+        }
+        p0[0] += p1[0];
+        p0[1] += p1[1];
+        if (end > end2) {
+          p0[0] += v[end2];
+          p0[1] += v[end2 + 1];
+        }
+      }
+      double r = p0[0] + p0[1];
+      for (int i = 0; i < start; i++) r += v[i];
+      for (int i = end; i < n; i++) r += v[i];
+      return r;
+    }
+  }  // namespace
+
   std::vector<int> ngonVertexOrder(const std::vector<Vec3> &verts) {
     const int n = (int)verts.size();
-    Vec3 centre = {0, 0, 0};
-    for (const auto &v : verts) centre = centre + v;
-    centre = {centre.x / n, centre.y / n, centre.z / n};
+    std::vector<double> col(n);
+    double mean[3];
+    for (int k = 0; k < 3; k++) {
+      for (int i = 0; i < n; i++) col[i] = k == 0 ? verts[i].x : (k == 1 ? verts[i].y : verts[i].z);
+      mean[k] = eigenColumnSum(col.data(), n, k) / (double)n;
+    }
+    const Vec3 centre = {mean[0], mean[1], mean[2]};
     // two in-plane axes: the first vertex, and the vertex least collinear with it
     Vec3 a = verts[0] - centre;
     Vec3 b = {0, 0, 0};

@@ -5,7 +5,7 @@
 
 #include "tables.h"
 
-#define EARB_CORE_THREADS 512
+#define EARB_CORE_THREADS 1024
 
 namespace earb {
 
