@@ -2,7 +2,10 @@
 // GainInterpolator::process / find_block (ref include/ear/dsp/gain_interpolator.hpp:53-129),
 // turned into a table of segments and work items that one kernel launch consumes.
 #include <algorithm>
+#include <cstdint>
+#include <cstdlib>
 #include <memory>
+#include <string>
 #include <vector>
 
 #include "capi_common.hpp"
@@ -19,25 +22,30 @@ struct earb200_interp {
   bool sorted = true;
   DeviceBuffer<float> d_gains;
   int64_t n_points = 0;
-  // plan cache for the last (block_start, nsamples)
+  // plan cache for the last (block_start, nsamples, buffer alignment)
   int64_t plan_start = 0, plan_n = -1;
-  long n_ramp = 0, n_const = 0;
+  int plan_align = -1;
+  long n_items[4] = {0, 0, 0, 0};  // fast ramp, fast const, slow ramp, slow const
   DeviceBuffer<RenderItem> d_items;
   DeviceBuffer<RenderSegment> d_segs;
   // staging for process_host
   DeviceBuffer<float> d_in, d_out;
   int64_t launches = 0;
   KernelTimer timer;
+  int use_tc = 0;  // tensor-core (tcgen05) fast path; EARB200_RENDER_PATH=cuda selects the FFMA kernel
 };
 
 namespace {
-  void build_plan(earb200_interp &h, int64_t block_start, int64_t nsamples) {
-    if (h.plan_n == nsamples && h.plan_start == block_start) return;
+  // align: sample phase p in [0, 4) such that call-relative samples t with (t + p) % 4 == 0
+  // are 16-byte aligned in both buffers, or -1 when no such phase exists
+  void build_plan(earb200_interp &h, int64_t block_start, int64_t nsamples, int align) {
+    if (h.plan_n == nsamples && h.plan_start == block_start && h.plan_align == align) return;
+    const int fast_tile = h.use_tc ? RENDER_TC_TILE : RENDER_PIPE_TILE;
     const int64_t P = h.n_points;
     if (P == 0) throw Error(INVALID_ARGUMENT, "no interpolation points");
     if (!h.sorted) throw Error(INVALID_ARGUMENT, "interpolation points are not sorted");
     std::vector<RenderSegment> segs;
-    std::vector<RenderItem> ramp_items, const_items;
+    std::vector<RenderItem> items[4];
     const int tile = render_tile_samples(h.M);
     const int64_t block_end = block_start + nsamples;
     int64_t cur = block_start;
@@ -62,19 +70,29 @@ namespace {
       }
       const int seg_id = (int)segs.size();
       segs.push_back(s);
-      for (int64_t t = cur; t < end; t += tile) {
+      auto emit = [&](int64_t t, int64_t len, bool fast) {
         RenderItem it;
         it.t0 = t - block_start;
-        it.len = (int)std::min<int64_t>(tile, end - t);
+        it.len = (int)len;
         it.seg = seg_id;
-        (constant ? const_items : ramp_items).push_back(it);
+        items[(fast ? 0 : 2) + (constant ? 1 : 0)].push_back(it);
+      };
+      int64_t t = cur;
+      const int64_t head = (4 - (((t - block_start) + align) & 3)) & 3;
+      if (align >= 0 && end - (t + head) >= fast_tile) {
+        // ragged head up to the first 16-byte aligned sample, then full TMA tiles
+        if (head) emit(t, head, false);
+        t += head;
+        for (; end - t >= fast_tile; t += fast_tile) emit(t, fast_tile, true);
       }
+      for (; t < end; t += tile) emit(t, std::min<int64_t>(tile, end - t), false);
       cur = end;
     }
-    h.n_ramp = (long)ramp_items.size();
-    h.n_const = (long)const_items.size();
-    std::vector<RenderItem> all(ramp_items);
-    all.insert(all.end(), const_items.begin(), const_items.end());
+    std::vector<RenderItem> all;
+    for (int k = 0; k < 4; k++) {
+      h.n_items[k] = (long)items[k].size();
+      all.insert(all.end(), items[k].begin(), items[k].end());
+    }
     h.d_items.reserve(std::max<size_t>(all.size(), 1));
     h.d_segs.reserve(std::max<size_t>(segs.size(), 1));
     EARB_CUDA(cudaMemcpy(h.d_items.ptr, all.data(), sizeof(RenderItem) * all.size(),
@@ -83,6 +101,7 @@ namespace {
                          cudaMemcpyHostToDevice));
     h.plan_start = block_start;
     h.plan_n = nsamples;
+    h.plan_align = align;
   }
 
   void process_device(earb200_interp &h, int64_t block_start, int64_t nsamples, const float *d_in,
@@ -91,13 +110,20 @@ namespace {
     if (nsamples == 0) return;
     if (!d_in || !d_out) throw Error(INVALID_ARGUMENT, "null buffer");
     use_device(h.device);
-    build_plan(h, block_start, nsamples);
+    // the TMA path needs 16-byte aligned rows in both buffers at a common sample phase
+    int align = -1;
+    const uintptr_t ia = reinterpret_cast<uintptr_t>(d_in), oa = reinterpret_cast<uintptr_t>(d_out);
+    if (ia % 4 == 0 && oa % 4 == 0 && in_stride % 4 == 0 && out_stride % 4 == 0 &&
+        ((ia / 4) & 3) == ((oa / 4) & 3))
+      align = (int)((ia / 4) & 3);
+    build_plan(h, block_start, nsamples, align);
+    RenderPlan plan{h.d_items.ptr, h.n_items[0], h.n_items[1], h.n_items[2], h.n_items[3], h.use_tc};
     h.timer.start(stream);
-    launch_render(h.N, h.M, d_in, (long)in_stride, d_out, (long)out_stride, h.d_items.ptr, h.n_ramp,
-                  h.d_items.ptr + h.n_ramp, h.n_const, h.d_segs.ptr, h.d_gains.ptr, stream);
+    launch_render(h.N, h.M, d_in, (long)in_stride, d_out, (long)out_stride, plan, h.d_segs.ptr,
+                  h.d_gains.ptr, stream);
     h.timer.stop(stream);
     EARB_CUDA(cudaGetLastError());
-    h.launches += (h.n_ramp > 0) + (h.n_const > 0);
+    for (int k = 0; k < 4; k++) h.launches += h.n_items[k] > 0;
   }
 }  // namespace
 
@@ -115,6 +141,8 @@ int earb200_interp_create(int n_in, int n_out, int device, earb200_interp **out)
     h->device = device;
     h->N = n_in;
     h->M = n_out;
+    const char *path = std::getenv("EARB200_RENDER_PATH");
+    h->use_tc = render_tc_supported(n_in, n_out) && !(path && std::string(path) == "cuda");
     *out = h.release();
   });
 }

@@ -56,11 +56,26 @@ namespace earb {
     int len;
     int seg;
   };
+#define RENDER_PIPE_TILE 512
+#define RENDER_TC_TILE 256
+  // work items of one call, grouped: full 16-byte aligned RENDER_PIPE_TILE-sample tiles go to
+  // the TMA-staged kernel ("fast"), ragged / unaligned runs to the direct kernel ("slow")
+  struct RenderPlan {
+    const RenderItem *d_items;  // [fast ramp | fast const | slow ramp | slow const]
+    long n_fast_ramp, n_fast_const, n_slow_ramp, n_slow_const;
+    int use_tc;  // fast items are RENDER_TC_TILE-sample tiles for the tcgen05 kernel
+  };
+  // tcgen05 / TMEM variant of the fast path (render_tc_kernels.cu)
+  bool render_tc_supported(int N, int M);
+  size_t render_tc_smem_bytes(int N);
+  void launch_render_tc(int N, int M, const float *in, long in_stride, float *out, long out_stride,
+                        const RenderItem *d_items_ramp, long n_ramp, const RenderItem *d_items_const,
+                        long n_const, const RenderSegment *d_segs, const float *d_gains,
+                        cudaStream_t stream);
   int render_tile_samples(int M);
   size_t render_smem_bytes(int N, int M);
   void launch_render(int N, int M, const float *in, long in_stride, float *out, long out_stride,
-                     const RenderItem *d_items_ramp, long n_ramp, const RenderItem *d_items_const,
-                     long n_const, const RenderSegment *d_segs, const float *d_gains,
+                     const RenderPlan &plan, const RenderSegment *d_segs, const float *d_gains,
                      cudaStream_t stream);
 
   // ---- K4: partitioned FFT convolver bank (convolver_kernels.cu)
