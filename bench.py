@@ -269,15 +269,18 @@ def run_ours(args):
                                                        C.c_void_p(h_direct.data_ptr()),
                                                        C.c_void_p(h_diffuse.data_ptr()), None))
 
-    step_e2e_abi()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
+    if args.no_e2e:   # profiler runs only: the line then carries no end-to-end number
+        e2e_value, e2e_checksum = None, None
+    else:
         step_e2e_abi()
-    torch.cuda.synchronize()
-    e2e_dt = max_over_ranks(time.perf_counter() - t0)
-    e2e_value = n * world * e2e_steps / e2e_dt
-    e2e_checksum = float(h_direct[:1000].double().sum())
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            step_e2e_abi()
+        torch.cuda.synchronize()
+        e2e_dt = max_over_ranks(time.perf_counter() - t0)
+        e2e_value = n * world * e2e_steps / e2e_dt
+        e2e_checksum = float(h_direct[:1000].double().sum())
 
     # ---------------- render: BASELINE config 2 (128 objects x 60 s x 48 kHz into 4+9+0)
     render = None
@@ -401,6 +404,7 @@ def main():
     ap.add_argument("--objects", type=int, default=N_OBJECTS)
     ap.add_argument("--no-render", action="store_true")
     ap.add_argument("--no-render-e2e", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiler runs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":

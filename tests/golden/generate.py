@@ -1,0 +1,261 @@
+#!/usr/bin/env python
+"""Generate tests/golden/*.npz from the compiled, UNMODIFIED libear reference
+(oracle/_ref/libear_ref.so, built by oracle/Makefile from /root/reference).
+
+Run in the build container (where /root/reference exists):
+
+    make -C oracle && python tests/golden/generate.py
+
+The fixtures are small seeded input/output pairs for every row of the hot path; they pin
+the numpy restatement (oracle/ear_oracle.py) on machines where the reference cannot be
+built, and the CUDA path on the GPU box.  Known-answer values that the reference's own
+tests hold are stored next to them (kat.npz) with the test file:line they come from.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+
+from oracle import ref  # noqa: E402
+
+LAYOUTS = ["0+2+0", "0+5+0", "2+5+0", "4+5+0", "4+5+1", "3+7+0", "4+9+0", "9+10+3", "0+7+0", "4+7+0"]
+
+
+def cart(az, el, d=1.0):
+    az, el = np.radians(az), np.radians(el)
+    return np.stack([np.sin(-az) * np.cos(el) * d, np.cos(-az) * np.cos(el) * d, np.sin(el) * d], -1)
+
+
+def sphere(rng, n):
+    v = rng.normal(size=(n, 3))
+    return v / np.linalg.norm(v, axis=1, keepdims=True)
+
+
+def gen_psp():
+    """Point-source panner: the 21 x 11 az/el grid of the reference's test_all_layouts
+    (tests/point_source_panner_tests.cpp:341-419), every loudspeaker position, and random
+    directions, for all ten layouts: gains + region index + inner triplet index."""
+    out = {}
+    rng = np.random.default_rng(11)
+    az, el = np.meshgrid(np.linspace(-180, 180, 21), np.linspace(-90, 90, 11))
+    grid = cart(az.ravel(), el.ravel())
+    for name in LAYOUTS:
+        info = ref.layout_info(name)
+        spk = np.array([cart(p[0], p[1]) for p, l in zip(info["pos"], info["is_lfe"]) if not l])
+        xyz = np.concatenate([grid, spk, sphere(rng, 120) * rng.uniform(0.1, 2.0, (120, 1))])
+        g, reg, inner = ref.PointSourcePanner(name).handle(xyz)
+        out[f"{name}/xyz"] = xyz
+        out[f"{name}/gains"] = g
+        out[f"{name}/region"] = reg
+        out[f"{name}/inner"] = inner
+    np.savez_compressed(os.path.join(HERE, "psp.npz"), **out)
+
+
+def gen_extent():
+    """PolarExtent::handle on 9+10+3 and 0+5+0 with the distribution of the reference's
+    same_as_reference test (tests/extent_tests.cpp:136-166) plus depth/distance: the
+    dispatched SIMD core, the scalar core and the double-precision test restatement
+    (tests/reference/extent.cpp)."""
+    out = {}
+    rng = np.random.default_rng(12)
+    for name, n in (("9+10+3", 96), ("0+5+0", 32), ("4+7+0", 32)):
+        xyz = sphere(rng, n) * rng.uniform(0.2, 1.5, (n, 1))
+        w, h = rng.uniform(0, 360, n), rng.uniform(0, 360, n)
+        depth = np.where(rng.uniform(size=n) < 0.5, 0.0, rng.uniform(0, 1, n))
+        # a few structured cases: zero extent, circular, full sphere, tall, tiny
+        w[:6] = [0, 30, 360, 10, 5, 180]
+        h[:6] = [0, 30, 360, 200, 0, 180]
+        depth[:6] = 0
+        xyz[0] /= np.linalg.norm(xyz[0])
+        out[f"{name}/xyz"], out[f"{name}/width"], out[f"{name}/height"], out[f"{name}/depth"] = xyz, w, h, depth
+        out[f"{name}/simd"] = ref.Extent(name, 0).handle(xyz, w, h, depth)
+        out[f"{name}/scalar"] = ref.Extent(name, 1).handle(xyz, w, h, depth)
+        unit = xyz / np.linalg.norm(xyz, axis=1, keepdims=True)
+        out[f"{name}/double_nodepth_unit"] = ref.Extent(name, 2).handle(unit, w, h, 0.0)
+        out[f"{name}/simd_nodepth_unit"] = ref.Extent(name, 0).handle(unit, w, h, 0.0)
+    out["isa"] = np.array(ref.extent_isa())
+    np.savez_compressed(os.path.join(HERE, "extent.npz"), **out)
+
+
+def gen_objects():
+    """GainCalculatorObjects::calculate: BASELINE cfg 1 distribution (point sources on 0+5+0),
+    cfg 2 distribution (extent objects on 9+10+3) and 4+7+0 (cfg 5), float and double."""
+    out = {}
+    rng = np.random.default_rng(13)
+    for name, n, extent in (("0+5+0", 128, False), ("9+10+3", 96, True), ("4+7+0", 48, True), ("0+2+0", 24, True)):
+        az = rng.uniform(-180, 180, n)
+        el = np.degrees(np.arcsin(rng.uniform(-1, 1, n)))
+        if extent:
+            dist = rng.uniform(0.2, 1.5, n)
+            w, h = rng.uniform(0, 360, n), rng.uniform(0, 360, n)
+            depth = np.where(rng.uniform(size=n) < 0.5, 0.0, rng.uniform(0, 1, n))
+        else:
+            dist, w, h, depth = np.ones(n), np.zeros(n), np.zeros(n), np.zeros(n)
+        gain, diffuse = rng.uniform(0, 1, n), rng.uniform(0, 1, n)
+        calc = ref.Objects(name)
+        d64, f64 = calc.calculate(az, el, dist, w, h, depth, gain, diffuse, dtype=np.float64)
+        d32, f32 = calc.calculate(az, el, dist, w, h, depth, gain, diffuse, dtype=np.float32)
+        out[f"{name}/in"] = np.stack([az, el, dist, w, h, depth, gain, diffuse])
+        out[f"{name}/direct64"], out[f"{name}/diffuse64"] = d64, f64
+        out[f"{name}/direct32"], out[f"{name}/diffuse32"] = d32, f32
+        out[f"{name}/region"] = ref.PointSourcePanner(name).handle(cart(az, el, dist))[1]
+    np.savez_compressed(os.path.join(HERE, "objects.npz"), **out)
+
+
+def gen_interp():
+    """GainInterpolator<LinearInterpMatrix/Vector/Single>::process: ramps, steps (equal
+    sample indices), constant head/tail, equal neighbouring points, call splitting and a
+    non-zero block_start (tests/gain_interpolator_tests.cpp:104-257)."""
+    out = {}
+    rng = np.random.default_rng(14)
+    N, M, T = 6, 5, 1500
+    x = rng.normal(0, 0.25, (N, T)).astype(np.float32)
+    samples = np.array([100, 300, 300, 612, 800, 1124, 1124, 1400], dtype=np.int64)
+    g = rng.uniform(0, 1, (len(samples), N, M)).astype(np.float32)
+    g[5] = g[4]  # constant between 800 and 1124
+    out["matrix/x"], out["matrix/samples"], out["matrix/gains"] = x, samples, g
+    out["matrix/out"] = ref.interp_matrix(x, samples, g)
+    out["matrix/out_calls_of_75"] = ref.interp_matrix(x, samples, g, call_size=75)
+    out["matrix/out_start_250"] = ref.interp_matrix(x[:, :1000], samples, g, block_start0=250)
+    out["vector/out"] = ref.interp_vector(x[0], samples, g[:, 0, :])
+    out["single/out"] = ref.interp_single(x[0], samples, g[:, 0, 0])
+    # BASELINE cfg 3 shape in miniature: 128 -> 14, ramps every 512 samples
+    # (input stored as float16 -- exactly representable -- to keep the fixture small)
+    N, M, T = 128, 14, 2048
+    x16 = np.clip(rng.normal(0, 0.25, (N, T)), -1, 1).astype(np.float16)
+    samples = np.arange(0, T + 512, 512, dtype=np.int64)
+    g = (rng.uniform(0, 1, (len(samples), N, M)) / np.sqrt(N)).astype(np.float32)
+    out["cfg3/x16"], out["cfg3/samples"], out["cfg3/gains"] = x16, samples, g
+    out["cfg3/out"] = ref.interp_matrix(x16.astype(np.float32), samples, g)
+    np.savez_compressed(os.path.join(HERE, "interp.npz"), **out)
+
+
+def gen_convolver():
+    """BlockConvolver::process scenarios of tests/block_convolver_tests.cpp:208-356:
+    multi-partition filters, crossfades, fades to/from silence, zero blocks."""
+    out = {}
+    rng = np.random.default_rng(15)
+    B, nb, blocks = 64, 4, 14
+    x = rng.normal(0, 0.25, B * blocks).astype(np.float32)
+    x[5 * B:6 * B] = 0.0  # an all-zero input block
+    f0 = rng.normal(0, 0.3, 200).astype(np.float32)   # 4 partitions
+    f1 = rng.normal(0, 0.3, 100).astype(np.float32)   # 2 partitions
+    out["B"], out["nb"], out["x"], out["f0"], out["f1"] = np.array(B), np.array(nb), x, f0, f1
+    c = ref.Convolver(B, nb)
+    a, _ = c.add_filter(f0)
+    b, _ = c.add_filter(f1)
+    c.set_filter(a)
+    y = [c.process(x[:3 * B])]
+    c.crossfade_filter(b)
+    y.append(c.process(x[3 * B:7 * B]))
+    c.crossfade_filter(None)                      # fade down to silence
+    y.append(c.process(x[7 * B:9 * B]))
+    y.append(c.process(None, 2))                  # NULL input blocks
+    c.crossfade_filter(a)                         # fade up from silence
+    y.append(c.process(x[11 * B:]))
+    out["y"] = np.concatenate(y)
+    out["script"] = np.array("set f0; 3 blocks; xfade f1; 4 blocks; xfade none; 2 blocks; "
+                             "2 null blocks; xfade f0; 3 blocks")
+    # BASELINE cfg 4 in miniature: decorrelator filters on 9+10+3, B = 512, one partition
+    dec = ref.decorrelators("9+10+3", np.float32)
+    xs = rng.normal(0, 0.25, (3, 512 * 6)).astype(np.float32)
+    ys = []
+    for ch, filt in zip(xs, dec[[0, 7, 23]]):
+        c = ref.Convolver(512, 1)
+        fid, _ = c.add_filter(filt)
+        c.set_filter(fid)
+        ys.append(c.process(ch))
+    out["cfg4/x"], out["cfg4/channels"], out["cfg4/y"] = xs, np.array([0, 7, 23]), np.array(ys)
+    np.savez_compressed(os.path.join(HERE, "convolver.npz"), **out)
+
+
+def gen_decorrelators():
+    out = {}
+    for name in ("0+5+0", "4+7+0", "9+10+3"):
+        out[f"{name}/f32"] = ref.decorrelators(name, np.float32)
+        out[f"{name}/f64"] = ref.decorrelators(name, np.float64)
+    out["delay"] = np.array(ref.decorrelator_delay())
+    np.savez_compressed(os.path.join(HERE, "decorrelators.npz"), **out)
+
+
+def gen_hoa():
+    """GainCalculatorHOA::calculate: ACN 0..15 on 4+7+0 (cfg 5) and 9+10+3, all three
+    normalisations; first/last t-design point (tests/hoa_tests.cpp:7-16)."""
+    out = {}
+    orders = [n for n in range(4) for _ in range(2 * n + 1)]
+    degrees = [m for n in range(4) for m in range(-n, n + 1)]
+    out["orders"], out["degrees"] = np.array(orders), np.array(degrees)
+    for name in ("4+7+0", "9+10+3", "0+5+0"):
+        for norm in ("SN3D", "N3D", "FuMa"):
+            out[f"{name}/{norm}"] = ref.hoa_calc(name, orders, degrees, norm)[0]
+    pts = ref.hoa_points()
+    out["points_first_last"] = pts[[0, -1]]
+    out["n_points"] = np.array(len(pts))
+    np.savez_compressed(os.path.join(HERE, "hoa.npz"), **out)
+
+
+def gen_direct_speakers():
+    """GainCalculatorDirectSpeakers::calculate on 4+7+0 / 9+10+3 / 0+5+0: label and URN
+    matching, LFE, bounds, the point-source fallback and a mapping rule
+    (tests/gain_calculator_direct_speakers_tests.cpp:31-339)."""
+    cases = [
+        ("4+7+0", ["M+000"], 0, 0, 1, None, None, None),
+        ("4+7+0", ["urn:itu:bs:2051:0:speaker:M+030"], 30, 0, 1, None, None, None),
+        ("4+7+0", ["LFE1"], 0, -30, 1, None, None, None),
+        ("4+7+0", ["foo"], 0, -30, 1, None, 120.0, None),          # LFE by lowPass frequency
+        ("4+7+0", ["foo"], 12, 5, 1, None, None, None),             # point-source fallback
+        ("4+7+0", ["foo"], 30, 0, 1, {"azMin": 25, "azMax": 35, "elMin": -5, "elMax": 5}, None, None),
+        ("4+7+0", ["foo"], 70, 28, 1, {"azMin": 40, "azMax": 100, "elMin": 20, "elMax": 40}, None, None),
+        ("9+10+3", ["U+045"], 45, 30, 1, None, None, None),
+        ("9+10+3", ["B-045"], -45, -30, 1, None, None, None),
+        ("0+5+0", ["M+110"], 110, 0, 1, None, None, None),
+        ("0+5+0", ["U+030"], 30, 30, 1, None, None, "urn:itu:bs:2051:0:pack:4+5+0"),  # mapping rule
+        ("0+5+0", ["M+090"], 90, 0, 1, None, None, "urn:itu:bs:2051:0:pack:4+9+0"),
+        ("0+2+0", ["M+000"], 0, 0, 1, None, None, "urn:itu:bs:2051:0:pack:0+5+0"),
+    ]
+    out = {"n": np.array(len(cases))}
+    import json
+    for i, (layout, labels, az, el, d, bounds, low_pass, pack) in enumerate(cases):
+        g, nw = ref.direct_speakers_calc(layout, labels, az, el, d, bounds, low_pass, None, pack)
+        out[f"{i}/case"] = np.array(json.dumps(dict(layout=layout, labels=labels, az=az, el=el, dist=d,
+                                                    bounds=bounds, low_pass=low_pass, pack=pack)))
+        out[f"{i}/gains"] = g
+        out[f"{i}/n_warnings"] = np.array(nw)
+    np.savez_compressed(os.path.join(HERE, "direct_speakers.npz"), **out)
+
+
+def gen_delay():
+    rng = np.random.default_rng(16)
+    x = rng.normal(0, 0.25, (3, 1000)).astype(np.float32)
+    np.savez_compressed(os.path.join(HERE, "delay.npz"), x=x, delay=np.array(255),
+                        y=ref.delay_process(x, 255, call_size=128))
+
+
+def gen_kat():
+    """Known answers held by the reference's own tests (not produced by running anything)."""
+    kat = {
+        # tests/decorrelate_tests.cpp:19-28 -- designDecorrelatorBasic(7, 512) at these taps
+        "decorrelator7_taps": np.array([0, 1, 255, 256, 510, 511]),
+        "decorrelator7_values": np.array([-0.1124280906086625, -0.00944671630601479, 0.057714955000898516,
+                                          -0.018996037984052125, 0.08336121588594464,
+                                          -0.012216595581941523]),
+        # tests/point_source_panner_tests.cpp:421-519 -- 0+5+0, +-15 degrees: (sqrt 1/2, sqrt 1/2)
+        "psp_0+5+0_az15": np.array([np.sqrt(0.5), 0.0, np.sqrt(0.5), 0.0, 0.0]),
+        # tests/hoa_tests.cpp:7-16 -- first / last point of the 5200-point design
+        "hoa_point_first": np.array([-0.007238307489963788, 0.8575241661297168, 0.5143927598714958]),
+        "hoa_point_last": np.array([-0.5784605915309438, 0.5246941913018843, -0.6245633271812653]),
+        "hoa_n_points": np.array(5200),
+    }
+    np.savez_compressed(os.path.join(HERE, "kat.npz"), **kat)
+
+
+if __name__ == "__main__":
+    if not ref.available():
+        raise SystemExit("build oracle/_ref first: make -C oracle")
+    for fn in (gen_psp, gen_extent, gen_objects, gen_interp, gen_convolver, gen_decorrelators, gen_hoa,
+               gen_direct_speakers, gen_delay, gen_kat):
+        fn()
+        print("wrote", fn.__name__[4:])
