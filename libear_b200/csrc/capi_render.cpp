@@ -32,6 +32,7 @@ struct earb200_interp {
   DeviceBuffer<float> d_in, d_out;
   int64_t launches = 0;
   KernelTimer timer;
+  int n_sms = 0;
   int use_tc = 0;  // tensor-core (tcgen05) fast path; EARB200_RENDER_PATH=cuda selects the FFMA kernel
 };
 
@@ -117,13 +118,19 @@ namespace {
         ((ia / 4) & 3) == ((oa / 4) & 3))
       align = (int)((ia / 4) & 3);
     build_plan(h, block_start, nsamples, align);
-    RenderPlan plan{h.d_items.ptr, h.n_items[0], h.n_items[1], h.n_items[2], h.n_items[3], h.use_tc};
+    RenderPlan plan{h.d_items.ptr, h.n_items[0], h.n_items[1], h.n_items[2], h.n_items[3], h.use_tc,
+                    h.n_sms, (long)nsamples};
     h.timer.start(stream);
     launch_render(h.N, h.M, d_in, (long)in_stride, d_out, (long)out_stride, plan, h.d_segs.ptr,
                   h.d_gains.ptr, stream);
     h.timer.stop(stream);
     EARB_CUDA(cudaGetLastError());
-    for (int k = 0; k < 4; k++) h.launches += h.n_items[k] > 0;
+    if (h.use_tc) {
+      h.launches += (h.n_items[0] + h.n_items[1]) > 0;
+      h.launches += (h.n_items[2] > 0) + (h.n_items[3] > 0);
+    } else {
+      for (int k = 0; k < 4; k++) h.launches += h.n_items[k] > 0;
+    }
   }
 }  // namespace
 
@@ -139,6 +146,9 @@ int earb200_interp_create(int n_in, int n_out, int device, earb200_interp **out)
     use_device(device);
     auto h = std::make_unique<earb200_interp>();
     h->device = device;
+    cudaDeviceProp prop;
+    EARB_CUDA(cudaGetDeviceProperties(&prop, device));
+    h->n_sms = prop.multiProcessorCount;
     h->N = n_in;
     h->M = n_out;
     const char *path = std::getenv("EARB200_RENDER_PATH");

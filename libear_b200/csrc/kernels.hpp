@@ -64,13 +64,18 @@ namespace earb {
     const RenderItem *d_items;  // [fast ramp | fast const | slow ramp | slow const]
     long n_fast_ramp, n_fast_const, n_slow_ramp, n_slow_const;
     int use_tc;  // fast items are RENDER_TC_TILE-sample tiles for the tcgen05 kernel
+    int n_sms;   // grid size of the persistent tcgen05 kernel
+    long n_samples;  // samples per channel of this call (extent of the TMA descriptor)
   };
   // tcgen05 / TMEM variant of the fast path (render_tc_kernels.cu)
   bool render_tc_supported(int N, int M);
   size_t render_tc_smem_bytes(int N);
-  void launch_render_tc(int N, int M, const float *in, long in_stride, float *out, long out_stride,
-                        const RenderItem *d_items_ramp, long n_ramp, const RenderItem *d_items_const,
-                        long n_const, const RenderSegment *d_segs, const float *d_gains,
+  // d_items: n_tiles tiles of RENDER_TC_TILE samples, ramp and constant segments alike
+  // (the input is read through a 2-D TMA descriptor over [N][n_samples]); false = descriptor
+  // could not be encoded, nothing launched
+  bool launch_render_tc(int N, int M, const float *in, long in_stride, long n_samples, float *out,
+                        long out_stride, const RenderItem *d_items, long n_tiles,
+                        const RenderSegment *d_segs, const float *d_gains, int n_sms,
                         cudaStream_t stream);
   int render_tile_samples(int M);
   size_t render_smem_bytes(int N, int M);

@@ -19,6 +19,8 @@
 // registers.
 #include <cuda_runtime.h>
 
+#include <stdexcept>
+
 #include <cstdint>
 
 #include "kernels.hpp"
@@ -370,8 +372,10 @@ namespace earb {
     const RenderItem *slow_ramp = fast_const + plan.n_fast_const, *slow_const = slow_ramp + plan.n_slow_ramp;
     long n_fast_ramp = plan.n_fast_ramp, n_fast_const = plan.n_fast_const;
     if (plan.use_tc) {
-      launch_render_tc(N, M, in, in_stride, out, out_stride, fast_ramp, n_fast_ramp, fast_const,
-                       n_fast_const, d_segs, d_gains, stream);
+      // the ramp and constant tiles are adjacent in the item list: one persistent launch
+      if (!launch_render_tc(N, M, in, in_stride, plan.n_samples, out, out_stride, fast_ramp,
+                            n_fast_ramp + n_fast_const, d_segs, d_gains, plan.n_sms, stream))
+        throw std::runtime_error("cuTensorMapEncodeTiled failed for the render input");
       n_fast_ramp = n_fast_const = 0;
     }
 #define EARB_RENDER_CASE(MP, TPT)                                                                      \

@@ -10,19 +10,23 @@
 // (x = x_hi + x_lo, g = g_hi + g_lo; x_hi g_hi accumulates in one TMEM accumulator, the
 // two 2^-11-sized cross terms in a second one, summed in fp32 registers at the end).
 //
-// Data flow per CTA (128 threads, one 256-sample tile = two M=128 UMMA tiles):
-//   * one thread streams the tile's input rows into a shared-memory ring with bulk
-//     asynchronous copies (cp.async.bulk, the 1-D TMA path) completing on mbarriers;
-//   * every thread owns TMEM lane `tid`: it reads its samples of the 8 channels of a
-//     stage from shared memory, splits them and writes them to TMEM as the A operand
-//     (tcgen05.st, K-major: one 32-bit column per input channel);
+// Data flow (one persistent CTA of 448 threads per SM, looping over 256-sample tiles = two
+// M=128 UMMA tiles each):
+//   * a producer warp streams the tiles' input rows into a shared-memory ring with bulk
+//     asynchronous copies (cp.async.bulk, the 1-D TMA path) completing on mbarriers; the ring
+//     runs continuously across tile boundaries;
+//   * eight converter warps (thread = TMEM lane = sample) read their samples of the 16 channels
+//     of a stage from shared memory, split them and write them to TMEM as the A operand
+//     (tcgen05.st, K-major: one 32-bit column per input channel), double buffered;
 //   * one thread issues tcgen05.mma kind::tf32 with A from TMEM and the gain matrix
-//     (K-major, no swizzle, built in shared memory once per tile) as the B descriptor,
-//     and commits to an mbarrier that releases the A buffer;
-//   * the epilogue reads both accumulators back (tcgen05.ld), applies the ramp and
-//     writes the M output rows with coalesced stores.
+//     (K-major, no swizzle, in shared memory) as the B descriptor, into double-buffered TMEM
+//     accumulators, and commits to mbarriers that release the A buffer / publish the tile;
+//   * four epilogue warps read both accumulators back (tcgen05.ld), apply the ramp, write the
+//     M output rows with coalesced streaming stores, and build the gain matrix two tiles ahead.
+#include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdint>
 
 #include "kernels.hpp"
@@ -32,16 +36,7 @@ namespace earb {
     constexpr int kTile = RENDER_TC_TILE;  // samples per CTA (2 UMMA M-tiles)
     constexpr int kMT = kTile / 128;       // M-tiles
     constexpr int kCh = 16;                // channels per stage = two K = 8 UMMA steps
-    constexpr int kStages = 4;
-    constexpr int kThreads = 128;        // converter threads (one per TMEM lane)
-    constexpr int kThreadsTotal = 192;   // + TMA producer warp + MMA issuer warp
     constexpr int kNP = 32;                // UMMA N: 16 columns for S, 16 for D
-    // TMEM columns: [main acc: kMT x 32][corr acc: kMT x 32][A: 2 buffers x kMT x (hi 16 + lo 16)]
-    constexpr int kColMain = 0;
-    constexpr int kColCorr = kMT * kNP;
-    constexpr int kColA = 2 * kMT * kNP;
-    constexpr int kTmemCols = 256;
-    static_assert(kColA + 2 * kMT * 2 * kCh <= kTmemCols, "TMEM budget");
 
     __device__ __forceinline__ uint32_t smem_u32(const void *p) {
       return (uint32_t)__cvta_generic_to_shared(p);
@@ -59,6 +54,19 @@ namespace earb {
               smem_u32(dst)),
           "l"(src), "r"(bytes), "r"(smem_u32(bar))
           : "memory");
+    }
+    // 2-D tiled TMA load: box {kTile samples, kCh channels} at (sample x, channel y)
+    __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, int x, int y, uint64_t *bar) {
+      asm volatile(
+          "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(
+              smem_u32(dst)),
+          "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar))
+          : "memory");
+    }
+    // round-to-nearest (ties away) onto the 10-bit TF32 mantissa with two integer operations;
+    // cvt.rna.tf32.f32 adds NaN/Inf handling the audio path does not need (Inf stays Inf here)
+    __device__ __forceinline__ float round_tf32(float x) {
+      return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
     }
     // spins on the barrier phase; a protocol error traps after ~2 s instead of hanging the GPU
     __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
@@ -140,49 +148,72 @@ namespace earb {
       asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
     }
 
-    // Warp roles: warps 0..3 convert (thread = TMEM lane), warp 4 streams input (TMA),
-    // warp 5 owns TMEM allocation and issues the UMMAs.  All hand-offs are mbarriers:
-    //   full[s]   TMA       -> converters   stage s of the input ring has landed
-    //   empty[s]  converters-> TMA          stage s has been read out of shared memory
-    //   a_full[b] converters-> MMA          A buffer b is complete in TMEM
-    //   a_free[b] MMA commit-> converters   the UMMAs reading A buffer b have finished
-    //   b_ready   converters-> MMA          the gain matrix B is in shared memory
-    template <bool RAMP>
-    __global__ void __launch_bounds__(kThreadsTotal)
-        render_tc_kernel(int N, int M, const float *__restrict__ in, long in_stride,
-                         float *__restrict__ out, long out_stride,
-                         const RenderItem *__restrict__ items,
-                         const RenderSegment *__restrict__ segs, const float *__restrict__ gains) {
+    // ------------------------------------------------------------------------------
+    // Persistent, software-pipelined kernel: one CTA per SM loops over 256-sample tiles
+    // (tile = blockIdx.x, + gridDim.x, ...); every role runs ahead of the others through
+    // mbarriers only, so the input stream never drains between tiles.
+    //
+    //   warps 0..7   converters   warp w owns TMEM lanes 32*(w&3).. of M-tile (w>>2): shared-memory
+    //                             stage -> hi/lo split -> tcgen05.st (A operand)
+    //   warps 8..11  epilogue     accumulators of tile L -> ramp -> global stores, then build the
+    //                             gain matrix B of tile L+2 into the buffer tile L just released
+    //   warp  12     TMA producer cp.async.bulk of [16 channels x 256 samples] stages, ring of
+    //                             n_stages, continuous across tiles
+    //   warp  13     MMA issuer   owns the TMEM allocation, issues tcgen05.mma kind::tf32
+    //
+    //   full[s]     producer   -> converters  stage s has landed               (tx bytes)
+    //   empty[s]    converters -> producer    stage s has been read           (8 warps)
+    //   a_full[b]   converters -> MMA         A buffer b is complete in TMEM  (8 warps)
+    //   a_free[b]   MMA commit -> converters  the UMMAs reading A buffer b are done
+    //   b_full[t]   epilogue   -> MMA         gain matrix buffer t is built   (4 warps)
+    //   acc_full[t] MMA commit -> epilogue    accumulators t are complete (B buffer t is free too)
+    //   acc_free[t] epilogue   -> MMA         accumulators t have been read out (4 warps)
+    constexpr int kConvWarps = 8, kEpiWarps = 4;
+    constexpr int kProducerWarp = kConvWarps + kEpiWarps, kMmaWarp = kProducerWarp + 1;
+    constexpr int kThreadsP = (kMmaWarp + 1) * 32;  // 448
+    constexpr int kMaxStages = 8;
+    constexpr int kTmemColsP = 512;
+    // TMEM columns: accumulators [2 tiles][main: kMT x 32 | corr: kMT x 32], then
+    // A [2 buffers][kMT][hi 16 | lo 16]
+    constexpr int kAccStride = 2 * kMT * kNP;
+    constexpr int kColAP = 2 * kAccStride;
+    static_assert(kColAP + 2 * kMT * 2 * kCh <= kTmemColsP, "TMEM budget");
+
+    __global__ void __launch_bounds__(kThreadsP, 1)
+        render_tc_persistent_kernel(const __grid_constant__ CUtensorMap in_map, int N, int M,
+                                    float *__restrict__ out, long out_stride,
+                                    const RenderItem *__restrict__ items, int n_tiles,
+                                    const RenderSegment *__restrict__ segs,
+                                    const float *__restrict__ gains, int n_stages) {
       extern __shared__ __align__(128) unsigned char smem_raw[];
       const int Kp = (N + kCh - 1) / kCh * kCh;  // K padded to whole stages
-      float *sx = reinterpret_cast<float *>(smem_raw);  // [stages][kCh][kTile]
-      float *sBhi = sx + kStages * kCh * kTile;         // [Kp/4][32][4]
-      float *sBlo = sBhi + (size_t)Kp * kNP;
-      __shared__ __align__(8) uint64_t full[kStages], empty[kStages];
-      __shared__ __align__(8) uint64_t a_full[2], a_free[2], b_ready;
+      const int n_iters = Kp / kCh;
+      float *sB = reinterpret_cast<float *>(smem_raw);       // [2 tiles][hi | lo][Kp/4][32][4]
+      float *sx = sB + (size_t)4 * Kp * kNP;                 // [n_stages][kCh][kTile]
+      __shared__ __align__(8) uint64_t full[kMaxStages], empty[kMaxStages];
+      __shared__ __align__(8) uint64_t a_full[2], a_free[2], b_full[2], acc_full[2], acc_free[2];
       __shared__ uint32_t tmem_base_s;
 
-      const RenderItem item = items[blockIdx.x];
-      const RenderSegment seg = segs[item.seg];
       const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-      const int n_iters = Kp / kCh;
 
       if (tid == 0) {
-        for (int s = 0; s < kStages; s++) {
+        for (int s = 0; s < kMaxStages; s++) {
           mbar_init(&full[s], 1);
-          mbar_init(&empty[s], 4);
+          mbar_init(&empty[s], kConvWarps);
         }
         for (int b = 0; b < 2; b++) {
-          mbar_init(&a_full[b], 4);
+          mbar_init(&a_full[b], kConvWarps);
           mbar_init(&a_free[b], 1);
+          mbar_init(&b_full[b], kEpiWarps);
+          mbar_init(&acc_full[b], 1);
+          mbar_init(&acc_free[b], kEpiWarps);
         }
-        mbar_init(&b_ready, 4);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       }
-      if (warp == 5) {
+      if (warp == kMmaWarp) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
                          smem_u32(&tmem_base_s)),
-                     "r"(kTmemCols)
+                     "r"(kTmemColsP)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
       }
@@ -191,168 +222,257 @@ namespace earb {
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint32_t tmem_base = tmem_base_s;
 
-      if (warp == 4) {
+      if (warp == kProducerWarp) {
         // ------------------------------------------------------------ TMA producer
+        // one tiled TMA load per stage: box = [kCh channels][kTile samples]; channels past N are
+        // zero-filled by the TMA unit (and count towards the transaction bytes)
         if (lane == 0) {
-          const float *base = in + item.t0;
-          for (int it = 0; it < n_iters; it++) {
-            const int slot = it % kStages;
-            if (it >= kStages) mbar_wait(&empty[slot], (uint32_t)(((it / kStages) - 1) & 1));
-            const int nch = min(kCh, N - it * kCh);
-            mbar_expect_tx(&full[slot], (uint32_t)(nch * kTile * sizeof(float)));
-            for (int c = 0; c < nch; c++)
-              bulk_g2s(sx + (size_t)(slot * kCh + c) * kTile, base + (long)(it * kCh + c) * in_stride,
-                       kTile * sizeof(float), &full[slot]);
+          asm volatile("prefetch.tensormap [%0];" ::"l"(&in_map) : "memory");
+          int slot = 0;
+          uint32_t phase = 0;  // parity of the `empty` completion to wait for, once the ring wrapped
+          bool wrapped = false;
+          for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const int t0 = (int)items[tile].t0;
+            for (int it = 0; it < n_iters; it++) {
+              if (wrapped) mbar_wait(&empty[slot], phase);
+              mbar_expect_tx(&full[slot], (uint32_t)(kCh * kTile * sizeof(float)));
+              tma_load_2d(sx + (size_t)slot * kCh * kTile, &in_map, t0, it * kCh, &full[slot]);
+              if (++slot == n_stages) {
+                slot = 0;
+                if (wrapped) phase ^= 1;
+                wrapped = true;
+              }
+            }
           }
         }
-      } else if (warp == 5) {
+      } else if (warp == kMmaWarp) {
         // ------------------------------------------------------------ MMA issuer
         if (lane == 0) {
           // instruction descriptor: D f32, A/B tf32, both K-major, N = 32, M = 128
           const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kNP >> 3) << 17) |
                                  ((uint32_t)(128 >> 4) << 24);
-          const uint32_t bhi_addr = smem_u32(sBhi), blo_addr = smem_u32(sBlo);
-          mbar_wait(&b_ready, 0);
-          for (int it = 0; it < n_iters; it++) {
-            const int abuf = it & 1;
-            mbar_wait(&a_full[abuf], (uint32_t)((it >> 1) & 1));
+          int g = 0, L = 0;
+          for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
+            const int ab = L & 1;
+            const uint32_t bhi_addr = smem_u32(sB + (size_t)ab * 2 * Kp * kNP);
+            const uint32_t blo_addr = bhi_addr + (uint32_t)(Kp * kNP * sizeof(float));
+            const uint32_t acc = tmem_base + ab * kAccStride;
+            mbar_wait(&b_full[ab], (uint32_t)((L >> 1) & 1));
+            if (L >= 2) mbar_wait(&acc_free[ab], (uint32_t)(((L >> 1) - 1) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            for (int it = 0; it < n_iters; it++, g++) {
+              const int abuf = g & 1;
+              mbar_wait(&a_full[abuf], (uint32_t)((g >> 1) & 1));
+              asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
-            for (int ks = 0; ks < kCh / 8; ks++) {
-              // one K = 8 step covers two 4-wide chunks of B (2 x 512 bytes)
-              const int kstep = it * (kCh / 8) + ks;
-              const uint64_t dhi = b_desc(bhi_addr + kstep * 2 * (kNP * 16));
-              const uint64_t dlo = b_desc(blo_addr + kstep * 2 * (kNP * 16));
+              for (int ks = 0; ks < kCh / 8; ks++) {
+                // one K = 8 step covers two 4-wide chunks of B (2 x 512 bytes)
+                const int kstep = it * (kCh / 8) + ks;
+                const uint64_t dhi = b_desc(bhi_addr + kstep * 2 * (kNP * 16));
+                const uint64_t dlo = b_desc(blo_addr + kstep * 2 * (kNP * 16));
 #pragma unroll
-              for (int j = 0; j < kMT; j++) {
-                const uint32_t a_hi = tmem_base + kColA + (abuf * kMT + j) * 2 * kCh + ks * 8;
-                const uint32_t a_lo = a_hi + kCh;
-                umma_tf32_ts(tmem_base + kColMain + j * kNP, a_hi, dhi, idesc, kstep > 0);
-                umma_tf32_ts(tmem_base + kColCorr + j * kNP, a_lo, dhi, idesc, kstep > 0);
-                umma_tf32_ts(tmem_base + kColCorr + j * kNP, a_hi, dlo, idesc, 1);
+                for (int j = 0; j < kMT; j++) {
+                  const uint32_t a_hi = tmem_base + kColAP + (abuf * kMT + j) * 2 * kCh + ks * 8;
+                  const uint32_t a_lo = a_hi + kCh;
+                  umma_tf32_ts(acc + j * kNP, a_hi, dhi, idesc, kstep > 0);
+                  umma_tf32_ts(acc + kMT * kNP + j * kNP, a_lo, dhi, idesc, kstep > 0);
+                  umma_tf32_ts(acc + kMT * kNP + j * kNP, a_hi, dlo, idesc, 1);
+                }
               }
+              umma_commit(&a_free[abuf]);  // arrives when every UMMA issued so far has finished
             }
-            umma_commit(&a_free[abuf]);  // arrives when every UMMA issued so far has finished
+            umma_commit(&acc_full[ab]);
           }
         }
-      } else {
-        // ------------------------------------------------------------ converters (+ epilogue)
-        const uint32_t lane_base = tmem_base + ((uint32_t)(warp * 32) << 16);
-        // gain matrix B: rows 0..15 = start gains s, rows 16..31 = e - s, split hi/lo.  Zero
-        // everything first (padding rows m >= M and channels k >= N must be finite), then
-        // scatter the N x M raw gains, read coalesced with several loads in flight.
-        {
-          float4 *z = reinterpret_cast<float4 *>(sBhi);
-          const float4 zero = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-          for (int i = tid; i < 2 * Kp * kNP / 4; i += kThreads) z[i] = zero;
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        {
-          const float *ga = gains + (size_t)seg.pa * N * M;
-          const float *gb = gains + (size_t)seg.pb * N * M;
-          const int total = N * M;
-#pragma unroll 4
-          for (int r = tid; r < total; r += kThreads) {
-            const float sv = __ldg(ga + r);
-            const float dv = RAMP ? __ldg(gb + r) - sv : 0.0f;
-            const int k = r / M, m = r - k * M;
-            const float shi = to_tf32(sv), dhi = to_tf32(dv);
-            const int o = b_offset_floats(m, k);
-            sBhi[o] = shi;
-            sBlo[o] = to_tf32(sv - shi);
-            sBhi[o + 16 * 4] = dhi;  // row 16 + m
-            sBlo[o + 16 * 4] = to_tf32(dv - dhi);
-          }
-        }
-        // make the generic-proxy writes of B visible to the tensor core (async proxy)
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&b_ready);
-
-        for (int it = 0; it < n_iters; it++) {
-          const int slot = it % kStages;
-          const int abuf = it & 1;
-          mbar_wait(&full[slot], (uint32_t)((it / kStages) & 1));
-          // the UMMAs of iteration it - 2 must have finished reading this A buffer
-          if (it >= 2) {
-            mbar_wait(&a_free[abuf], (uint32_t)(((it >> 1) - 1) & 1));
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          }
-          const int nch = min(kCh, N - it * kCh);
-#pragma unroll
-          for (int j = 0; j < kMT; j++) {
+      } else if (warp < kConvWarps) {
+        // ------------------------------------------------------------ converters
+        const int q = warp & 3, j = warp >> 2;
+        const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+        const int row = j * 128 + q * 32 + lane;
+        int g = 0, slot = 0;
+        uint32_t full_phase = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+          for (int it = 0; it < n_iters; it++, g++) {
+            const int abuf = g & 1;
+            mbar_wait(&full[slot], full_phase);
+            const float *src = sx + (size_t)slot * kCh * kTile + row;
             float hi[kCh], lo[kCh];
 #pragma unroll
             for (int c = 0; c < kCh; c++) {
-              const float x = (c < nch) ? sx[(size_t)(slot * kCh + c) * kTile + j * 128 + tid] : 0.0f;
-              hi[c] = to_tf32(x);
-              lo[c] = to_tf32(x - hi[c]);
+              const float x = src[c * kTile];
+              hi[c] = round_tf32(x);
+              lo[c] = round_tf32(x - hi[c]);
             }
-            const uint32_t a_col = kColA + (abuf * kMT + j) * 2 * kCh;
+            // the UMMAs of iteration g - 2 must have finished reading this A buffer
+            if (g >= 2) {
+              mbar_wait(&a_free[abuf], (uint32_t)(((g >> 1) - 1) & 1));
+              asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            }
+            const uint32_t a_col = kColAP + (abuf * kMT + j) * 2 * kCh;
             tmem_st16(lane_base + a_col, hi);
             tmem_st16(lane_base + a_col + kCh, lo);
-          }
-          asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-          __syncwarp();
-          if (lane == 0) {
-            mbar_arrive(&a_full[abuf]);
-            mbar_arrive(&empty[slot]);
-          }
-        }
-        // the last commit covers every UMMA of the tile
-        {
-          const int last = n_iters - 1;
-          mbar_wait(&a_free[last & 1], (uint32_t)((last >> 1) & 1));
-          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        }
-#pragma unroll
-        for (int j = 0; j < kMT; j++) {
-          float a[32], b[32];
-          tmem_ld32(lane_base + kColMain + j * kNP, a);
-          tmem_ld32(lane_base + kColCorr + j * kNP, b);
-          const long t = item.t0 + j * 128 + tid;
-          const float p = RAMP ? (float)(t - seg.ramp_start) * seg.scale : 0.0f;
-#pragma unroll
-          for (int m = 0; m < 16; m++) {
-            if (m < M) {
-              const float sv = a[m] + b[m];
-              const float dv = a[16 + m] + b[16 + m];
-              __stcs(out + (long)m * out_stride + t, RAMP ? fmaf(p, dv, sv) : sv);
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) {
+              mbar_arrive(&a_full[abuf]);
+              mbar_arrive(&empty[slot]);
+            }
+            if (++slot == n_stages) {
+              slot = 0;
+              full_phase ^= 1;
             }
           }
+        }
+      } else {
+        // ------------------------------------------------------------ epilogue + gain matrices
+        const int q = warp & 3;
+        const int et = (warp - kConvWarps) * 32 + lane;  // 0..127
+        const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+        // Gain matrix B of a tile: rows 0..15 = start gains s, rows 16..31 = e - s, split hi/lo.
+        // Padding rows (m >= M) and channels (k >= N) are zeroed once and never written.
+        {
+          float4 *z = reinterpret_cast<float4 *>(sB);
+          const float4 zero = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+          for (int i = et; i < 4 * Kp * kNP / 4; i += kEpiWarps * 32) z[i] = zero;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        auto build_b = [&](int tile, int ab) {
+          const RenderSegment seg = segs[items[tile].seg];
+          float *bhi = sB + (size_t)ab * 2 * Kp * kNP, *blo = bhi + (size_t)Kp * kNP;
+          const float *ga = gains + (size_t)seg.pa * N * M;
+          const float *gb = gains + (size_t)seg.pb * N * M;
+          const int total = N * M;
+          const bool ramp = seg.ramp != 0;
+#pragma unroll 4
+          for (int r = et; r < total; r += kEpiWarps * 32) {
+            const float sv = __ldg(ga + r);
+            const float dv = ramp ? __ldg(gb + r) - sv : 0.0f;
+            const int k = r / M, m = r - k * M;
+            const float shi = to_tf32(sv), dhi = to_tf32(dv);
+            const int o = b_offset_floats(m, k);
+            bhi[o] = shi;
+            blo[o] = to_tf32(sv - shi);
+            bhi[o + 16 * 4] = dhi;  // row 16 + m
+            blo[o + 16 * 4] = to_tf32(dv - dhi);
+          }
+          // make the generic-proxy writes visible to the tensor core (async proxy)
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&b_full[ab]);
+        };
+        if (blockIdx.x < n_tiles) build_b(blockIdx.x, 0);
+        if (blockIdx.x + gridDim.x < n_tiles) build_b(blockIdx.x + gridDim.x, 1);
+
+        int L = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
+          const int ab = L & 1;
+          const RenderItem item = items[tile];
+          const RenderSegment seg = segs[item.seg];
+          const bool ramp = seg.ramp != 0;
+          mbar_wait(&acc_full[ab], (uint32_t)((L >> 1) & 1));
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t acc = lane_base + ab * kAccStride;
+#pragma unroll
+          for (int j = 0; j < kMT; j++) {
+            float a[32], b[32];
+            tmem_ld32(acc + j * kNP, a);
+            tmem_ld32(acc + kMT * kNP + j * kNP, b);
+            const long t = item.t0 + j * 128 + q * 32 + lane;
+            const float p = ramp ? (float)(t - seg.ramp_start) * seg.scale : 0.0f;
+#pragma unroll
+            for (int m = 0; m < 16; m++) {
+              if (m < M) {
+                const float sv = a[m] + b[m];
+                const float dv = a[16 + m] + b[16 + m];
+                __stcs(out + (long)m * out_stride + t, ramp ? fmaf(p, dv, sv) : sv);
+              }
+            }
+          }
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&acc_free[ab]);
+          // every UMMA of tile L has finished (acc_full), so its B buffer can take tile L + 2
+          const int next = tile + 2 * gridDim.x;
+          if (next < n_tiles) build_b(next, ab);
         }
       }
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncthreads();
-      if (warp == 5) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols)
+      if (warp == kMmaWarp) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemColsP)
                      : "memory");
       }
     }
   }  // namespace
 
+  namespace {
+    constexpr size_t kSmemBudget = 220 * 1024;  // dynamic shared memory we ask for at most
+    size_t b_bytes(int N) {
+      const int Kp = (N + kCh - 1) / kCh * kCh;
+      return sizeof(float) * (size_t)4 * Kp * kNP;  // two tiles x (hi | lo)
+    }
+    int stages_for(int N) {
+      const size_t stage = sizeof(float) * kCh * kTile;
+      const size_t left = kSmemBudget - b_bytes(N);
+      return (int)std::min<size_t>(kMaxStages, left / stage);
+    }
+  }  // namespace
+
   size_t render_tc_smem_bytes(int N) {
-    const int Kp = (N + kCh - 1) / kCh * kCh;
-    return sizeof(float) * ((size_t)kStages * kCh * kTile + (size_t)2 * Kp * kNP);
+    return b_bytes(N) + sizeof(float) * (size_t)stages_for(N) * kCh * kTile;
   }
 
   bool render_tc_supported(int N, int M) { return M <= 16 && N <= 256; }
 
-  void launch_render_tc(int N, int M, const float *in, long in_stride, float *out, long out_stride,
-                        const RenderItem *d_items_ramp, long n_ramp, const RenderItem *d_items_const,
-                        long n_const, const RenderSegment *d_segs, const float *d_gains,
+  namespace {
+    typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                      const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                      CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                      CUtensorMapFloatOOBfill);
+    // the driver entry point, resolved through the runtime (no link-time dependency on libcuda)
+    EncodeTiledFn encode_tiled() {
+      static EncodeTiledFn fn = [] {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+          p = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+      }();
+      return fn;
+    }
+  }  // namespace
+
+  // d_items: the ramp tiles followed by the constant tiles (one persistent launch covers both).
+  // Returns false when the TMA descriptor cannot be built (the caller then uses the FFMA path).
+  bool launch_render_tc(int N, int M, const float *in, long in_stride, long n_samples, float *out,
+                        long out_stride, const RenderItem *d_items, long n_tiles,
+                        const RenderSegment *d_segs, const float *d_gains, int n_sms,
                         cudaStream_t stream) {
+    if (n_tiles <= 0) return true;
+    EncodeTiledFn encode = encode_tiled();
+    if (!encode) return false;
+    // the input as a [N channels][n_samples] float tensor with a row pitch of in_stride floats
+    CUtensorMap map;
+    const cuuint64_t dims[2] = {(cuuint64_t)n_samples, (cuuint64_t)N};
+    const cuuint64_t strides[1] = {(cuuint64_t)in_stride * sizeof(float)};
+    const cuuint32_t box[2] = {(cuuint32_t)kTile, (cuuint32_t)kCh};
+    const cuuint32_t estr[2] = {1, 1};
+    if (encode(&map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(in), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return false;
     const size_t smem = render_tc_smem_bytes(N);
-    if (n_ramp > 0) {
-      cudaFuncSetAttribute(render_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      render_tc_kernel<true><<<(unsigned)n_ramp, kThreadsTotal, smem, stream>>>(
-          N, M, in, in_stride, out, out_stride, d_items_ramp, d_segs, d_gains);
+    static bool configured = false;
+    if (!configured) {
+      cudaFuncSetAttribute(render_tc_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)kSmemBudget);
+      configured = true;
     }
-    if (n_const > 0) {
-      cudaFuncSetAttribute(render_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      render_tc_kernel<false><<<(unsigned)n_const, kThreadsTotal, smem, stream>>>(
-          N, M, in, in_stride, out, out_stride, d_items_const, d_segs, d_gains);
-    }
+    const unsigned grid = (unsigned)std::min<long>(n_tiles, n_sms > 0 ? n_sms : 148);
+    render_tc_persistent_kernel<<<grid, kThreadsP, smem, stream>>>(
+        map, N, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_gains, stages_for(N));
+    return true;
   }
 }  // namespace earb
