@@ -136,10 +136,10 @@ namespace earb {
     // K-major, non-swizzled canonical layout of an [32 rows] x [K] tf32 operand: core matrices
     // of 8 rows x 16 bytes; the 32 rows of one 4-wide K chunk are contiguous (512 bytes)
     __device__ __forceinline__ int b_offset_floats(int row, int k) {
-      return (k >> 2) * (kNP * 4) + row * 4 + (k & 3);
+      return (k >> 2) * (2 * kNP * 4) + row * 4 + (k & 3);
     }
     __device__ __forceinline__ uint64_t b_desc(uint32_t smem_addr) {
-      const uint64_t lbo = (kNP * 16) >> 4;  // next 4-wide K chunk
+      const uint64_t lbo = (2 * kNP * 16) >> 4;  // next 4-wide K chunk (64 rows x 16 bytes)
       const uint64_t sbo = 128 >> 4;         // next 8-row group
       return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (lbo << 16) | (sbo << 32) | (1ull << 46);
     }
@@ -169,15 +169,18 @@ namespace earb {
     //   acc_full[t] MMA commit -> epilogue    accumulators t are complete (B buffer t is free too)
     //   acc_free[t] epilogue   -> MMA         accumulators t have been read out (4 warps)
     constexpr int kConvWarps = 8, kEpiWarps = 4;
+    // two MMA issuer warps, one per M-tile: a single thread cannot issue the UMMAs of both fast
+    // enough (each tcgen05.mma costs the issuing thread ~100 cycles of scalar work)
     constexpr int kProducerWarp = kConvWarps + kEpiWarps, kMmaWarp = kProducerWarp + 1;
-    constexpr int kThreadsP = (kMmaWarp + 1) * 32;  // 448
+    constexpr int kThreadsP = (kMmaWarp + kMT) * 32;  // 480
     constexpr int kMaxStages = 8;
     constexpr int kTmemColsP = 512;
     // TMEM columns: accumulators [2 tiles][main: kMT x 32 | corr: kMT x 32], then
     // A [2 buffers][kMT][hi 16 | lo 16]
     constexpr int kAccStride = 2 * kMT * kNP;
     constexpr int kColAP = 2 * kAccStride;
-    static_assert(kColAP + 2 * kMT * 2 * kCh <= kTmemColsP, "TMEM budget");
+    constexpr int kABufs = 4;  // A-operand ring in TMEM (power of two)
+    static_assert(kColAP + kABufs * kMT * 2 * kCh <= kTmemColsP, "TMEM budget");
 
     __global__ void __launch_bounds__(kThreadsP, 1)
         render_tc_persistent_kernel(const __grid_constant__ CUtensorMap in_map, int N, int M,
@@ -191,7 +194,7 @@ namespace earb {
       float *sB = reinterpret_cast<float *>(smem_raw);       // [2 tiles][hi | lo][Kp/4][32][4]
       float *sx = sB + (size_t)4 * Kp * kNP;                 // [n_stages][kCh][kTile]
       __shared__ __align__(8) uint64_t full[kMaxStages], empty[kMaxStages];
-      __shared__ __align__(8) uint64_t a_full[2], a_free[2], b_full[2], acc_full[2], acc_free[2];
+      __shared__ __align__(8) uint64_t a_full[kABufs], a_free[kABufs], b_full[2], acc_full[2], acc_free[2];
       __shared__ uint32_t tmem_base_s;
 
       const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -201,11 +204,13 @@ namespace earb {
           mbar_init(&full[s], 1);
           mbar_init(&empty[s], kConvWarps);
         }
-        for (int b = 0; b < 2; b++) {
+        for (int b = 0; b < kABufs; b++) {
           mbar_init(&a_full[b], kConvWarps);
-          mbar_init(&a_free[b], 1);
+          mbar_init(&a_free[b], kMT);
+        }
+        for (int b = 0; b < 2; b++) {
           mbar_init(&b_full[b], kEpiWarps);
-          mbar_init(&acc_full[b], 1);
+          mbar_init(&acc_full[b], kMT);
           mbar_init(&acc_free[b], kEpiWarps);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -245,39 +250,36 @@ namespace earb {
             }
           }
         }
-      } else if (warp == kMmaWarp) {
-        // ------------------------------------------------------------ MMA issuer
+      } else if (warp >= kMmaWarp) {
+        // ------------------------------------------------------------ MMA issuers (one per M-tile)
         if (lane == 0) {
-          // instruction descriptor: D f32, A/B tf32, both K-major, N = 32, M = 128
-          const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kNP >> 3) << 17) |
-                                 ((uint32_t)(128 >> 4) << 24);
+          const int j = warp - kMmaWarp;
+          // instruction descriptors: D f32, A/B tf32, both K-major, M = 128, N = 64 / 32
+          const uint32_t idesc_base = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 4) << 24);
+          const uint32_t idesc64 = idesc_base | ((uint32_t)(2 * kNP >> 3) << 17);
+          const uint32_t idesc32 = idesc_base | ((uint32_t)(kNP >> 3) << 17);
           int g = 0, L = 0;
           for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
             const int ab = L & 1;
-            const uint32_t bhi_addr = smem_u32(sB + (size_t)ab * 2 * Kp * kNP);
-            const uint32_t blo_addr = bhi_addr + (uint32_t)(Kp * kNP * sizeof(float));
-            const uint32_t acc = tmem_base + ab * kAccStride;
+            // B of this tile: [Kp/4][64 rows][4]; rows 0..31 = hi, 32..63 = lo
+            const uint64_t bdesc0 = b_desc(smem_u32(sB + (size_t)ab * 2 * Kp * kNP));
+            const uint32_t acc = tmem_base + ab * kAccStride + j * 2 * kNP;  // [main 32 | corr 32]
             mbar_wait(&b_full[ab], (uint32_t)((L >> 1) & 1));
             if (L >= 2) mbar_wait(&acc_free[ab], (uint32_t)(((L >> 1) - 1) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             for (int it = 0; it < n_iters; it++, g++) {
-              const int abuf = g & 1;
-              mbar_wait(&a_full[abuf], (uint32_t)((g >> 1) & 1));
+              const int abuf = g & (kABufs - 1);
+              mbar_wait(&a_full[abuf], (uint32_t)((g / kABufs) & 1));
               asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+              const uint32_t a_hi = tmem_base + kColAP + (abuf * kMT + j) * 2 * kCh;
 #pragma unroll
               for (int ks = 0; ks < kCh / 8; ks++) {
-                // one K = 8 step covers two 4-wide chunks of B (2 x 512 bytes)
+                // one K = 8 step covers two 4-wide chunks of B (2 x 1024 bytes)
                 const int kstep = it * (kCh / 8) + ks;
-                const uint64_t dhi = b_desc(bhi_addr + kstep * 2 * (kNP * 16));
-                const uint64_t dlo = b_desc(blo_addr + kstep * 2 * (kNP * 16));
-#pragma unroll
-                for (int j = 0; j < kMT; j++) {
-                  const uint32_t a_hi = tmem_base + kColAP + (abuf * kMT + j) * 2 * kCh + ks * 8;
-                  const uint32_t a_lo = a_hi + kCh;
-                  umma_tf32_ts(acc + j * kNP, a_hi, dhi, idesc, kstep > 0);
-                  umma_tf32_ts(acc + kMT * kNP + j * kNP, a_lo, dhi, idesc, kstep > 0);
-                  umma_tf32_ts(acc + kMT * kNP + j * kNP, a_hi, dlo, idesc, 1);
-                }
+                const uint64_t bd = bdesc0 + (uint64_t)(kstep * ((2 * 2 * kNP * 16) >> 4));
+                // [main | corr] (+)= x_hi * [g_hi | g_lo];  corr += x_lo * g_hi
+                umma_tf32_ts(acc, a_hi + ks * 8, bd, idesc64, kstep > 0);
+                umma_tf32_ts(acc + kNP, a_hi + kCh + ks * 8, bd, idesc32, 1);
               }
               umma_commit(&a_free[abuf]);  // arrives when every UMMA issued so far has finished
             }
@@ -293,7 +295,7 @@ namespace earb {
         uint32_t full_phase = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
           for (int it = 0; it < n_iters; it++, g++) {
-            const int abuf = g & 1;
+            const int abuf = g & (kABufs - 1);
             mbar_wait(&full[slot], full_phase);
             const float *src = sx + (size_t)slot * kCh * kTile + row;
             float hi[kCh], lo[kCh];
@@ -303,9 +305,9 @@ namespace earb {
               hi[c] = round_tf32(x);
               lo[c] = round_tf32(x - hi[c]);
             }
-            // the UMMAs of iteration g - 2 must have finished reading this A buffer
-            if (g >= 2) {
-              mbar_wait(&a_free[abuf], (uint32_t)(((g >> 1) - 1) & 1));
+            // the UMMAs of iteration g - kABufs must have finished reading this A buffer
+            if (g >= kABufs) {
+              mbar_wait(&a_free[abuf], (uint32_t)(((g / kABufs) - 1) & 1));
               asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             }
             const uint32_t a_col = kColAP + (abuf * kMT + j) * 2 * kCh;
@@ -339,7 +341,7 @@ namespace earb {
         asm volatile("bar.sync 1, 128;" ::: "memory");
         auto build_b = [&](int tile, int ab) {
           const RenderSegment seg = segs[items[tile].seg];
-          float *bhi = sB + (size_t)ab * 2 * Kp * kNP, *blo = bhi + (size_t)Kp * kNP;
+          float *bhi = sB + (size_t)ab * 2 * Kp * kNP, *blo = bhi + kNP * 4;  // lo = rows 32..63
           const float *ga = gains + (size_t)seg.pa * N * M;
           const float *gb = gains + (size_t)seg.pb * N * M;
           const int total = N * M;
@@ -376,8 +378,8 @@ namespace earb {
 #pragma unroll
           for (int j = 0; j < kMT; j++) {
             float a[32], b[32];
-            tmem_ld32(acc + j * kNP, a);
-            tmem_ld32(acc + kMT * kNP + j * kNP, b);
+            tmem_ld32(acc + j * 2 * kNP, a);
+            tmem_ld32(acc + j * 2 * kNP + kNP, b);
             const long t = item.t0 + j * 128 + q * 32 + lane;
             const float p = ramp ? (float)(t - seg.ramp_start) * seg.scale : 0.0f;
 #pragma unroll
