@@ -69,7 +69,7 @@ namespace earb {
   };
   // tcgen05 / TMEM variant of the fast path (render_tc_kernels.cu)
   bool render_tc_supported(int N, int M);
-  size_t render_tc_smem_bytes(int N);
+  size_t render_tc_smem_bytes(int N, int M);
   // d_items: n_tiles tiles of RENDER_TC_TILE samples, ramp and constant segments alike
   // (the input is read through a 2-D TMA descriptor over [N][n_samples]); false = descriptor
   // could not be encoded, nothing launched

@@ -24,6 +24,9 @@
 //   * four epilogue warps read both accumulators back (tcgen05.ld), apply the ramp, write the
 //     M output rows with coalesced streaming stores, and build the gain matrix two tiles ahead.
 #include <cuda.h>
+#ifndef EARB_RENDER_EXPERIMENT
+#define EARB_RENDER_EXPERIMENT 0
+#endif
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -179,6 +182,7 @@ namespace earb {
     // A [2 buffers][kMT][hi 16 | lo 16]
     constexpr int kAccStride = 2 * kMT * kNP;
     constexpr int kColAP = 2 * kAccStride;
+    constexpr int kBBufs = 2;  // gain-matrix buffers in shared memory
     constexpr int kABufs = 4;  // A-operand ring in TMEM (power of two)
     static_assert(kColAP + kABufs * kMT * 2 * kCh <= kTmemColsP, "TMEM budget");
 
@@ -192,9 +196,13 @@ namespace earb {
       const int Kp = (N + kCh - 1) / kCh * kCh;  // K padded to whole stages
       const int n_iters = Kp / kCh;
       float *sB = reinterpret_cast<float *>(smem_raw);       // [2 tiles][hi | lo][Kp/4][32][4]
-      float *sx = sB + (size_t)4 * Kp * kNP;                 // [n_stages][kCh][kTile]
+      // raw gain matrices of the tile being built: [2 tiles][point a | point b][raw_floats]
+      const int raw_floats = (N * M + 31) / 32 * 32;
+      float *sraw = sB + (size_t)kBBufs * 2 * Kp * kNP;
+      const bool raw_tma = ((N * M) & 3) == 0;  // bulk copies need 16-byte multiples
+      float *sx = sraw + (size_t)4 * raw_floats;                 // [n_stages][kCh][kTile]
       __shared__ __align__(8) uint64_t full[kMaxStages], empty[kMaxStages];
-      __shared__ __align__(8) uint64_t a_full[kABufs], a_free[kABufs], b_full[2], acc_full[2], acc_free[2];
+      __shared__ __align__(8) uint64_t a_full[kABufs], a_free[kABufs], b_full[kBBufs], raw_full[2], raw_free[2], acc_full[2], acc_free[2];
       __shared__ uint32_t tmem_base_s;
 
       const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -208,8 +216,10 @@ namespace earb {
           mbar_init(&a_full[b], kConvWarps);
           mbar_init(&a_free[b], kMT);
         }
+        for (int b = 0; b < kBBufs; b++) mbar_init(&b_full[b], kEpiWarps);
         for (int b = 0; b < 2; b++) {
-          mbar_init(&b_full[b], kEpiWarps);
+          mbar_init(&raw_full[b], 1);
+          mbar_init(&raw_free[b], kEpiWarps);
           mbar_init(&acc_full[b], kMT);
           mbar_init(&acc_free[b], kEpiWarps);
         }
@@ -233,10 +243,22 @@ namespace earb {
         // zero-filled by the TMA unit (and count towards the transaction bytes)
         if (lane == 0) {
           asm volatile("prefetch.tensormap [%0];" ::"l"(&in_map) : "memory");
-          int slot = 0;
+          int slot = 0, L = 0;
           uint32_t phase = 0;  // parity of the `empty` completion to wait for, once the ring wrapped
           bool wrapped = false;
-          for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+          // raw gain matrices (points pa, pb of the tile's segment) for the epilogue warps' build
+          auto load_raw = [&](int tile, int rb) {
+            const RenderSegment seg = segs[items[tile].seg];
+            const uint32_t bytes = (uint32_t)(N * M * sizeof(float));
+            mbar_expect_tx(&raw_full[rb], 2 * bytes);
+            bulk_g2s(sraw + (size_t)(rb * 2) * raw_floats, gains + (size_t)seg.pa * N * M, bytes, &raw_full[rb]);
+            bulk_g2s(sraw + (size_t)(rb * 2 + 1) * raw_floats, gains + (size_t)seg.pb * N * M, bytes,
+                     &raw_full[rb]);
+          };
+          if (raw_tma)
+            for (int b = 0; b < 2; b++)
+              if (blockIdx.x + b * gridDim.x < n_tiles) load_raw(blockIdx.x + b * gridDim.x, b);
+          for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
             const int t0 = (int)items[tile].t0;
             for (int it = 0; it < n_iters; it++) {
               if (wrapped) mbar_wait(&empty[slot], phase);
@@ -248,42 +270,57 @@ namespace earb {
                 wrapped = true;
               }
             }
+            // raw gains of tile L + 2 go into the buffer the build of tile L has released (that
+            // build finished before the MMAs of tile L could start, so this does not stall)
+            const int next = tile + 2 * gridDim.x;
+            if (raw_tma && next < n_tiles) {
+              mbar_wait(&raw_free[L & 1], (uint32_t)((L >> 1) & 1));
+              load_raw(next, L & 1);
+            }
           }
         }
       } else if (warp >= kMmaWarp) {
         // ------------------------------------------------------------ MMA issuers (one per M-tile)
-        if (lane == 0) {
-          const int j = warp - kMmaWarp;
-          // instruction descriptors: D f32, A/B tf32, both K-major, M = 128, N = 64 / 32
-          const uint32_t idesc_base = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 4) << 24);
-          const uint32_t idesc64 = idesc_base | ((uint32_t)(2 * kNP >> 3) << 17);
-          const uint32_t idesc32 = idesc_base | ((uint32_t)(kNP >> 3) << 17);
-          int g = 0, L = 0;
-          for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
-            const int ab = L & 1;
-            // B of this tile: [Kp/4][64 rows][4]; rows 0..31 = hi, 32..63 = lo
-            const uint64_t bdesc0 = b_desc(smem_u32(sB + (size_t)ab * 2 * Kp * kNP));
-            const uint32_t acc = tmem_base + ab * kAccStride + j * 2 * kNP;  // [main 32 | corr 32]
-            mbar_wait(&b_full[ab], (uint32_t)((L >> 1) & 1));
-            if (L >= 2) mbar_wait(&acc_free[ab], (uint32_t)(((L >> 1) - 1) & 1));
+        // The whole warp runs the loop so that every operand is warp-uniform (uniform registers);
+        // only the tcgen05 instructions themselves are predicated on one elected lane.
+        const int j = __shfl_sync(0xffffffffu, warp, 0) - kMmaWarp;
+        const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base, 0);
+        uint32_t leader;
+        asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(leader));
+        // instruction descriptors: D f32, A/B tf32, both K-major, M = 128, N = 64 / 32
+        const uint32_t idesc_base = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 4) << 24);
+        const uint32_t idesc64 = idesc_base | ((uint32_t)(2 * kNP >> 3) << 17);
+        const uint32_t idesc32 = idesc_base | ((uint32_t)(kNP >> 3) << 17);
+        const uint64_t bdesc_base = b_desc(smem_u32(sB));
+        const uint32_t b_tile_step = (uint32_t)((2 * Kp * kNP * sizeof(float)) >> 4);  // next B buffer
+        int g = 0, L = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
+          const int ab = L & 1;
+          // B of this tile: [Kp/4][64 rows][4]; rows 0..31 = hi, 32..63 = lo
+          const int bb = L & 1;
+          uint64_t bd = bdesc_base + (uint64_t)(bb * b_tile_step);
+          const uint32_t acc = tm + ab * kAccStride + j * 2 * kNP;  // [main 32 | corr 32]
+          mbar_wait(&b_full[bb], (uint32_t)((L >> 1) & 1));
+          if (L >= 2) mbar_wait(&acc_free[ab], (uint32_t)(((L >> 1) - 1) & 1));
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          for (int it = 0; it < n_iters; it++, g++) {
+            const int abuf = g & (kABufs - 1);
+            mbar_wait(&a_full[abuf], (uint32_t)((g / kABufs) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            for (int it = 0; it < n_iters; it++, g++) {
-              const int abuf = g & (kABufs - 1);
-              mbar_wait(&a_full[abuf], (uint32_t)((g / kABufs) & 1));
-              asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-              const uint32_t a_hi = tmem_base + kColAP + (abuf * kMT + j) * 2 * kCh;
+            const uint32_t a_hi = tm + kColAP + (abuf * kMT + j) * 2 * kCh;
+            if (leader) {
 #pragma unroll
-              for (int ks = 0; ks < kCh / 8; ks++) {
+              for (int ks = 0; ks < (EARB_RENDER_EXPERIMENT >= 2 ? 0 : kCh / 8); ks++) {
                 // one K = 8 step covers two 4-wide chunks of B (2 x 1024 bytes)
-                const int kstep = it * (kCh / 8) + ks;
-                const uint64_t bd = bdesc0 + (uint64_t)(kstep * ((2 * 2 * kNP * 16) >> 4));
                 // [main | corr] (+)= x_hi * [g_hi | g_lo];  corr += x_lo * g_hi
-                umma_tf32_ts(acc, a_hi + ks * 8, bd, idesc64, kstep > 0);
+                umma_tf32_ts(acc, a_hi + ks * 8, bd, idesc64, (it | ks) != 0);
                 umma_tf32_ts(acc + kNP, a_hi + kCh + ks * 8, bd, idesc32, 1);
+                bd += (2 * 2 * kNP * 16) >> 4;
               }
               umma_commit(&a_free[abuf]);  // arrives when every UMMA issued so far has finished
+              if (it == n_iters - 1) umma_commit(&acc_full[ab]);
             }
-            umma_commit(&acc_full[ab]);
+            __syncwarp();
           }
         }
       } else if (warp < kConvWarps) {
@@ -298,12 +335,27 @@ namespace earb {
             const int abuf = g & (kABufs - 1);
             mbar_wait(&full[slot], full_phase);
             const float *src = sx + (size_t)slot * kCh * kTile + row;
+#if EARB_RENDER_EXPERIMENT >= 1  // stream-only ceiling: converters consume stages without work
+            if (g >= kABufs) mbar_wait(&a_free[abuf], (uint32_t)(((g / kABufs) - 1) & 1));
+            __syncwarp();
+            if (lane == 0) {
+              mbar_arrive(&a_full[abuf]);
+              mbar_arrive(&empty[slot]);
+            }
+            if (++slot == n_stages) {
+              slot = 0;
+              full_phase ^= 1;
+            }
+            continue;
+#endif
             float hi[kCh], lo[kCh];
 #pragma unroll
             for (int c = 0; c < kCh; c++) {
+              // hi = x truncated to TF32, lo = x - hi exactly (13 significant bits; the tensor core
+              // reads the top 19 bits of each operand).  Split error <= 2^-21 |x|, see DESIGN.md
               const float x = src[c * kTile];
-              hi[c] = round_tf32(x);
-              lo[c] = round_tf32(x - hi[c]);
+              hi[c] = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+              lo[c] = x - hi[c];
             }
             // the UMMAs of iteration g - kABufs must have finished reading this A buffer
             if (g >= kABufs) {
@@ -336,35 +388,56 @@ namespace earb {
         {
           float4 *z = reinterpret_cast<float4 *>(sB);
           const float4 zero = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-          for (int i = et; i < 4 * Kp * kNP / 4; i += kEpiWarps * 32) z[i] = zero;
+          for (int i = et; i < kBBufs * 2 * Kp * kNP / 4; i += kEpiWarps * 32) z[i] = zero;
         }
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        auto build_b = [&](int tile, int ab) {
+        // Lb = local index of the tile (its B, raw and accumulator buffers are Lb & 1)
+        auto build_b = [&](int tile, int Lb) {
+          const int ab = Lb & 1;
           const RenderSegment seg = segs[items[tile].seg];
           float *bhi = sB + (size_t)ab * 2 * Kp * kNP, *blo = bhi + kNP * 4;  // lo = rows 32..63
-          const float *ga = gains + (size_t)seg.pa * N * M;
-          const float *gb = gains + (size_t)seg.pb * N * M;
+          const float *ga, *gb;
+          if (raw_tma) {
+            ga = sraw + (size_t)(ab * 2) * raw_floats;
+            gb = ga + raw_floats;
+            mbar_wait(&raw_full[ab], (uint32_t)((Lb >> 1) & 1));
+          } else {
+            ga = gains + (size_t)seg.pa * N * M;
+            gb = gains + (size_t)seg.pb * N * M;
+          }
           const int total = N * M;
           const bool ramp = seg.ramp != 0;
+          // element r = k * M + m of the [N][M] matrices; (k, m) advance incrementally by 128
+          constexpr int kStep = kEpiWarps * 32;
+          const int step_k = kStep / M, step_m = kStep % M;
+          int k = et / M, m = et - k * M;
 #pragma unroll 4
-          for (int r = et; r < total; r += kEpiWarps * 32) {
-            const float sv = __ldg(ga + r);
-            const float dv = ramp ? __ldg(gb + r) - sv : 0.0f;
-            const int k = r / M, m = r - k * M;
-            const float shi = to_tf32(sv), dhi = to_tf32(dv);
+          for (int r = et; r < total; r += kStep) {
+            const float sv = ga[r];
+            const float dv = ramp ? gb[r] - sv : 0.0f;
+            const float shi = round_tf32(sv), dhi = round_tf32(dv);
             const int o = b_offset_floats(m, k);
             bhi[o] = shi;
-            blo[o] = to_tf32(sv - shi);
+            blo[o] = round_tf32(sv - shi);
             bhi[o + 16 * 4] = dhi;  // row 16 + m
-            blo[o + 16 * 4] = to_tf32(dv - dhi);
+            blo[o + 16 * 4] = round_tf32(dv - dhi);
+            k += step_k;
+            m += step_m;
+            if (m >= M) {
+              m -= M;
+              k++;
+            }
           }
           // make the generic-proxy writes visible to the tensor core (async proxy)
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
           __syncwarp();
-          if (lane == 0) mbar_arrive(&b_full[ab]);
+          if (lane == 0) {
+            mbar_arrive(&b_full[ab]);
+            if (raw_tma) mbar_arrive(&raw_free[ab]);
+          }
         };
-        if (blockIdx.x < n_tiles) build_b(blockIdx.x, 0);
-        if (blockIdx.x + gridDim.x < n_tiles) build_b(blockIdx.x + gridDim.x, 1);
+        for (int b = 0; b < kBBufs; b++)
+          if (blockIdx.x + b * gridDim.x < n_tiles) build_b((int)(blockIdx.x + b * gridDim.x), b);
 
         int L = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
@@ -387,7 +460,7 @@ namespace earb {
               if (m < M) {
                 const float sv = a[m] + b[m];
                 const float dv = a[16 + m] + b[16 + m];
-                __stcs(out + (long)m * out_stride + t, ramp ? fmaf(p, dv, sv) : sv);
+                if (EARB_RENDER_EXPERIMENT < 3) __stcs(out + (long)m * out_stride + t, ramp ? fmaf(p, dv, sv) : sv);
               }
             }
           }
@@ -395,8 +468,8 @@ namespace earb {
           __syncwarp();
           if (lane == 0) mbar_arrive(&acc_free[ab]);
           // every UMMA of tile L has finished (acc_full), so its B buffer can take tile L + 2
-          const int next = tile + 2 * gridDim.x;
-          if (next < n_tiles) build_b(next, ab);
+          const int next = tile + kBBufs * gridDim.x;
+          if (next < n_tiles) build_b(next, L + kBBufs);
         }
       }
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -409,20 +482,22 @@ namespace earb {
   }  // namespace
 
   namespace {
-    constexpr size_t kSmemBudget = 220 * 1024;  // dynamic shared memory we ask for at most
-    size_t b_bytes(int N) {
+    constexpr size_t kSmemBudget = 224 * 1024;  // dynamic shared memory we ask for at most
+    // gain matrices: kBBufs tiles x (hi | lo), plus the raw staging [2 tiles][2 points][N x M]
+    size_t b_bytes(int N, int M) {
       const int Kp = (N + kCh - 1) / kCh * kCh;
-      return sizeof(float) * (size_t)4 * Kp * kNP;  // two tiles x (hi | lo)
+      const int raw_floats = (N * M + 31) / 32 * 32;
+      return sizeof(float) * ((size_t)kBBufs * 2 * Kp * kNP + (size_t)4 * raw_floats);
     }
-    int stages_for(int N) {
+    int stages_for(int N, int M) {
       const size_t stage = sizeof(float) * kCh * kTile;
-      const size_t left = kSmemBudget - b_bytes(N);
+      const size_t left = kSmemBudget - b_bytes(N, M);
       return (int)std::min<size_t>(kMaxStages, left / stage);
     }
   }  // namespace
 
-  size_t render_tc_smem_bytes(int N) {
-    return b_bytes(N) + sizeof(float) * (size_t)stages_for(N) * kCh * kTile;
+  size_t render_tc_smem_bytes(int N, int M) {
+    return b_bytes(N, M) + sizeof(float) * (size_t)stages_for(N, M) * kCh * kTile;
   }
 
   bool render_tc_supported(int N, int M) { return M <= 16 && N <= 256; }
@@ -465,7 +540,7 @@ namespace earb {
                CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
       return false;
-    const size_t smem = render_tc_smem_bytes(N);
+    const size_t smem = render_tc_smem_bytes(N, M);
     static bool configured = false;
     if (!configured) {
       cudaFuncSetAttribute(render_tc_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -474,7 +549,7 @@ namespace earb {
     }
     const unsigned grid = (unsigned)std::min<long>(n_tiles, n_sms > 0 ? n_sms : 148);
     render_tc_persistent_kernel<<<grid, kThreadsP, smem, stream>>>(
-        map, N, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_gains, stages_for(N));
+        map, N, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_gains, stages_for(N, M));
     return true;
   }
 }  // namespace earb
