@@ -21,6 +21,7 @@ struct earb200_interp {
   std::vector<char> same_as_prev;
   bool sorted = true;
   DeviceBuffer<float> d_gains;
+  DeviceBuffer<float> d_images;  // tcgen05 path: per-point TF32 hi/lo images in UMMA layout
   int64_t n_points = 0;
   // plan cache for the last (block_start, nsamples, buffer alignment)
   int64_t plan_start = 0, plan_n = -1;
@@ -119,7 +120,7 @@ namespace {
       align = (int)((ia / 4) & 3);
     build_plan(h, block_start, nsamples, align);
     RenderPlan plan{h.d_items.ptr, h.n_items[0], h.n_items[1], h.n_items[2], h.n_items[3], h.use_tc,
-                    h.n_sms, (long)nsamples};
+                    h.n_sms, (long)nsamples, h.d_images.ptr};
     h.timer.start(stream);
     launch_render(h.N, h.M, d_in, (long)in_stride, d_out, (long)out_stride, plan, h.d_segs.ptr,
                   h.d_gains.ptr, stream);
@@ -198,6 +199,13 @@ int earb200_interp_set_points(earb200_interp *interp, int64_t n_points,
       h.d_gains.reserve(mat * n_points);
       EARB_CUDA(cudaMemcpy(h.d_gains.ptr, gains, sizeof(float) * mat * n_points,
                            cudaMemcpyHostToDevice));
+      if (h.use_tc) {
+        h.d_images.reserve(render_tc_image_floats(h.N) * n_points);
+        launch_render_prepare_points(h.N, h.M, (long)n_points, h.d_gains.ptr, h.d_images.ptr, 0);
+        EARB_CUDA(cudaGetLastError());
+        EARB_CUDA(cudaStreamSynchronize(0));
+        h.launches++;
+      }
     }
   });
 }

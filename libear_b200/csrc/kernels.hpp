@@ -66,6 +66,7 @@ namespace earb {
     int use_tc;  // fast items are RENDER_TC_TILE-sample tiles for the tcgen05 kernel
     int n_sms;   // grid size of the persistent tcgen05 kernel
     long n_samples;  // samples per channel of this call (extent of the TMA descriptor)
+    const float *d_images;  // per-point gain-matrix images (tcgen05 path)
   };
   // tcgen05 / TMEM variant of the fast path (render_tc_kernels.cu)
   bool render_tc_supported(int N, int M);
@@ -75,8 +76,12 @@ namespace earb {
   // could not be encoded, nothing launched
   bool launch_render_tc(int N, int M, const float *in, long in_stride, long n_samples, float *out,
                         long out_stride, const RenderItem *d_items, long n_tiles,
-                        const RenderSegment *d_segs, const float *d_gains, int n_sms,
+                        const RenderSegment *d_segs, const float *d_images, int n_sms,
                         cudaStream_t stream);
+  // per-point gain-matrix images for the tcgen05 kernel (TF32 hi/lo split in UMMA layout)
+  size_t render_tc_image_floats(int N);
+  void launch_render_prepare_points(int N, int M, long n_points, const float *d_gains, float *d_images,
+                                    cudaStream_t stream);
   int render_tile_samples(int M);
   size_t render_smem_bytes(int N, int M);
   void launch_render(int N, int M, const float *in, long in_stride, float *out, long out_stride,

@@ -136,14 +136,14 @@ namespace earb {
                    : "memory");
     }
 
-    // K-major, non-swizzled canonical layout of an [32 rows] x [K] tf32 operand: core matrices
-    // of 8 rows x 16 bytes; the 32 rows of one 4-wide K chunk are contiguous (512 bytes)
-    __device__ __forceinline__ int b_offset_floats(int row, int k) {
-      return (k >> 2) * (2 * kNP * 4) + row * 4 + (k & 3);
-    }
-    __device__ __forceinline__ uint64_t b_desc(uint32_t smem_addr) {
-      const uint64_t lbo = (2 * kNP * 16) >> 4;  // next 4-wide K chunk (64 rows x 16 bytes)
-      const uint64_t sbo = 128 >> 4;         // next 8-row group
+    // Gain-matrix operand B of a tile, K-major, non-swizzled canonical layout (core matrices of
+    // 8 rows x 16 bytes), stored group-major: [8 row groups][Kp/4 K-chunks][8 rows][4 floats].
+    // Row (= UMMA N index) r: 0..15 point a hi, 16..31 point b hi, 32..47 point a lo, 48..63
+    // point b lo -- so each quarter is one contiguous block that is copied verbatim from the
+    // per-point images render_prepare_points_kernel writes.
+    __device__ __forceinline__ uint64_t b_desc(uint32_t smem_addr, int Kp) {
+      const uint64_t lbo = 128 >> 4;                      // next 4-wide K chunk
+      const uint64_t sbo = (uint64_t)(Kp / 4 * 128) >> 4;  // next 8-row group
       return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (lbo << 16) | (sbo << 32) | (1ull << 46);
     }
 
@@ -175,8 +175,9 @@ namespace earb {
     // two MMA issuer warps, one per M-tile: a single thread cannot issue the UMMAs of both fast
     // enough (each tcgen05.mma costs the issuing thread ~100 cycles of scalar work)
     constexpr int kProducerWarp = kConvWarps + kEpiWarps, kMmaWarp = kProducerWarp + 1;
-    constexpr int kThreadsP = (kMmaWarp + kMT) * 32;  // 480
-    constexpr int kMaxStages = 8;
+    constexpr int kBLoadWarp = kMmaWarp + kMT;        // streams the gain-matrix images
+    constexpr int kThreadsP = (kBLoadWarp + 1) * 32;  // 512
+    constexpr int kMaxStages = 10;
     constexpr int kTmemColsP = 512;
     // TMEM columns: accumulators [2 tiles][main: kMT x 32 | corr: kMT x 32], then
     // A [2 buffers][kMT][hi 16 | lo 16]
@@ -191,18 +192,14 @@ namespace earb {
                                     float *__restrict__ out, long out_stride,
                                     const RenderItem *__restrict__ items, int n_tiles,
                                     const RenderSegment *__restrict__ segs,
-                                    const float *__restrict__ gains, int n_stages) {
+                                    const float *__restrict__ images, int n_stages) {
       extern __shared__ __align__(128) unsigned char smem_raw[];
       const int Kp = (N + kCh - 1) / kCh * kCh;  // K padded to whole stages
       const int n_iters = Kp / kCh;
-      float *sB = reinterpret_cast<float *>(smem_raw);       // [2 tiles][hi | lo][Kp/4][32][4]
-      // raw gain matrices of the tile being built: [2 tiles][point a | point b][raw_floats]
-      const int raw_floats = (N * M + 31) / 32 * 32;
-      float *sraw = sB + (size_t)kBBufs * 2 * Kp * kNP;
-      const bool raw_tma = ((N * M) & 3) == 0;  // bulk copies need 16-byte multiples
-      float *sx = sraw + (size_t)4 * raw_floats;                 // [n_stages][kCh][kTile]
+      float *sB = reinterpret_cast<float *>(smem_raw);       // [2 tiles][8 groups][Kp/4][8][4]
+      float *sx = sB + (size_t)kBBufs * 2 * Kp * kNP;        // [n_stages][kCh][kTile]
       __shared__ __align__(8) uint64_t full[kMaxStages], empty[kMaxStages];
-      __shared__ __align__(8) uint64_t a_full[kABufs], a_free[kABufs], b_full[kBBufs], raw_full[2], raw_free[2], acc_full[2], acc_free[2];
+      __shared__ __align__(8) uint64_t a_full[kABufs], a_free[kABufs], b_full[kBBufs], acc_full[2], acc_free[2];
       __shared__ uint32_t tmem_base_s;
 
       const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -216,10 +213,8 @@ namespace earb {
           mbar_init(&a_full[b], kConvWarps);
           mbar_init(&a_free[b], kMT);
         }
-        for (int b = 0; b < kBBufs; b++) mbar_init(&b_full[b], kEpiWarps);
+        for (int b = 0; b < kBBufs; b++) mbar_init(&b_full[b], 1);
         for (int b = 0; b < 2; b++) {
-          mbar_init(&raw_full[b], 1);
-          mbar_init(&raw_free[b], kEpiWarps);
           mbar_init(&acc_full[b], kMT);
           mbar_init(&acc_free[b], kEpiWarps);
         }
@@ -246,18 +241,6 @@ namespace earb {
           int slot = 0, L = 0;
           uint32_t phase = 0;  // parity of the `empty` completion to wait for, once the ring wrapped
           bool wrapped = false;
-          // raw gain matrices (points pa, pb of the tile's segment) for the epilogue warps' build
-          auto load_raw = [&](int tile, int rb) {
-            const RenderSegment seg = segs[items[tile].seg];
-            const uint32_t bytes = (uint32_t)(N * M * sizeof(float));
-            mbar_expect_tx(&raw_full[rb], 2 * bytes);
-            bulk_g2s(sraw + (size_t)(rb * 2) * raw_floats, gains + (size_t)seg.pa * N * M, bytes, &raw_full[rb]);
-            bulk_g2s(sraw + (size_t)(rb * 2 + 1) * raw_floats, gains + (size_t)seg.pb * N * M, bytes,
-                     &raw_full[rb]);
-          };
-          if (raw_tma)
-            for (int b = 0; b < 2; b++)
-              if (blockIdx.x + b * gridDim.x < n_tiles) load_raw(blockIdx.x + b * gridDim.x, b);
           for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
             const int t0 = (int)items[tile].t0;
             for (int it = 0; it < n_iters; it++) {
@@ -270,13 +253,28 @@ namespace earb {
                 wrapped = true;
               }
             }
-            // raw gains of tile L + 2 go into the buffer the build of tile L has released (that
-            // build finished before the MMAs of tile L could start, so this does not stall)
-            const int next = tile + 2 * gridDim.x;
-            if (raw_tma && next < n_tiles) {
-              mbar_wait(&raw_free[L & 1], (uint32_t)((L >> 1) & 1));
-              load_raw(next, L & 1);
-            }
+          }
+        }
+      } else if (warp == kBLoadWarp) {
+        // ------------------------------------------------------------ gain-matrix loader
+        // B of tile L = four contiguous quarters: point a hi, point b hi, point a lo, point b lo,
+        // copied verbatim from the per-point images.  Buffer L & 1 is free once every UMMA of tile
+        // L - 2 has finished (acc_full).
+        if (lane == 0) {
+          const uint32_t quarter = (uint32_t)(Kp * 16 * sizeof(float));  // 2 row groups x Kp/4 x 128 B
+          const size_t img = (size_t)Kp * 32;                            // floats per point image
+          int L = 0;
+          for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
+            const int ab = L & 1;
+            if (L >= 2) mbar_wait(&acc_full[ab], (uint32_t)(((L >> 1) - 1) & 1));
+            const RenderSegment seg = segs[items[tile].seg];
+            const float *pa = images + (size_t)seg.pa * img, *pb = images + (size_t)seg.pb * img;
+            float *dst = sB + (size_t)ab * 2 * Kp * kNP;
+            mbar_expect_tx(&b_full[ab], 4 * quarter);
+            bulk_g2s(dst, pa, quarter, &b_full[ab]);
+            bulk_g2s(dst + Kp * 16, pb, quarter, &b_full[ab]);
+            bulk_g2s(dst + 2 * Kp * 16, pa + Kp * 16, quarter, &b_full[ab]);
+            bulk_g2s(dst + 3 * Kp * 16, pb + Kp * 16, quarter, &b_full[ab]);
           }
         }
       } else if (warp >= kMmaWarp) {
@@ -291,12 +289,12 @@ namespace earb {
         const uint32_t idesc_base = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 4) << 24);
         const uint32_t idesc64 = idesc_base | ((uint32_t)(2 * kNP >> 3) << 17);
         const uint32_t idesc32 = idesc_base | ((uint32_t)(kNP >> 3) << 17);
-        const uint64_t bdesc_base = b_desc(smem_u32(sB));
+        const uint64_t bdesc_base = b_desc(smem_u32(sB), Kp);
         const uint32_t b_tile_step = (uint32_t)((2 * Kp * kNP * sizeof(float)) >> 4);  // next B buffer
         int g = 0, L = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
           const int ab = L & 1;
-          // B of this tile: [Kp/4][64 rows][4]; rows 0..31 = hi, 32..63 = lo
+          // B of this tile: rows 0..31 = [a | b] hi, 32..63 = [a | b] lo
           const int bb = L & 1;
           uint64_t bd = bdesc_base + (uint64_t)(bb * b_tile_step);
           const uint32_t acc = tm + ab * kAccStride + j * 2 * kNP;  // [main 32 | corr 32]
@@ -311,11 +309,11 @@ namespace earb {
             if (leader) {
 #pragma unroll
               for (int ks = 0; ks < (EARB_RENDER_EXPERIMENT >= 2 ? 0 : kCh / 8); ks++) {
-                // one K = 8 step covers two 4-wide chunks of B (2 x 1024 bytes)
+                // one K = 8 step covers two 4-wide chunks of B (2 x 128 bytes within a row group)
                 // [main | corr] (+)= x_hi * [g_hi | g_lo];  corr += x_lo * g_hi
                 umma_tf32_ts(acc, a_hi + ks * 8, bd, idesc64, (it | ks) != 0);
                 umma_tf32_ts(acc + kNP, a_hi + kCh + ks * 8, bd, idesc32, 1);
-                bd += (2 * 2 * kNP * 16) >> 4;
+                bd += (2 * 128) >> 4;
               }
               umma_commit(&a_free[abuf]);  // arrives when every UMMA issued so far has finished
               if (it == n_iters - 1) umma_commit(&acc_full[ab]);
@@ -381,64 +379,7 @@ namespace earb {
       } else {
         // ------------------------------------------------------------ epilogue + gain matrices
         const int q = warp & 3;
-        const int et = (warp - kConvWarps) * 32 + lane;  // 0..127
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
-        // Gain matrix B of a tile: rows 0..15 = start gains s, rows 16..31 = e - s, split hi/lo.
-        // Padding rows (m >= M) and channels (k >= N) are zeroed once and never written.
-        {
-          float4 *z = reinterpret_cast<float4 *>(sB);
-          const float4 zero = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-          for (int i = et; i < kBBufs * 2 * Kp * kNP / 4; i += kEpiWarps * 32) z[i] = zero;
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        // Lb = local index of the tile (its B, raw and accumulator buffers are Lb & 1)
-        auto build_b = [&](int tile, int Lb) {
-          const int ab = Lb & 1;
-          const RenderSegment seg = segs[items[tile].seg];
-          float *bhi = sB + (size_t)ab * 2 * Kp * kNP, *blo = bhi + kNP * 4;  // lo = rows 32..63
-          const float *ga, *gb;
-          if (raw_tma) {
-            ga = sraw + (size_t)(ab * 2) * raw_floats;
-            gb = ga + raw_floats;
-            mbar_wait(&raw_full[ab], (uint32_t)((Lb >> 1) & 1));
-          } else {
-            ga = gains + (size_t)seg.pa * N * M;
-            gb = gains + (size_t)seg.pb * N * M;
-          }
-          const int total = N * M;
-          const bool ramp = seg.ramp != 0;
-          // element r = k * M + m of the [N][M] matrices; (k, m) advance incrementally by 128
-          constexpr int kStep = kEpiWarps * 32;
-          const int step_k = kStep / M, step_m = kStep % M;
-          int k = et / M, m = et - k * M;
-#pragma unroll 4
-          for (int r = et; r < total; r += kStep) {
-            const float sv = ga[r];
-            const float dv = ramp ? gb[r] - sv : 0.0f;
-            const float shi = round_tf32(sv), dhi = round_tf32(dv);
-            const int o = b_offset_floats(m, k);
-            bhi[o] = shi;
-            blo[o] = round_tf32(sv - shi);
-            bhi[o + 16 * 4] = dhi;  // row 16 + m
-            blo[o + 16 * 4] = round_tf32(dv - dhi);
-            k += step_k;
-            m += step_m;
-            if (m >= M) {
-              m -= M;
-              k++;
-            }
-          }
-          // make the generic-proxy writes visible to the tensor core (async proxy)
-          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-          __syncwarp();
-          if (lane == 0) {
-            mbar_arrive(&b_full[ab]);
-            if (raw_tma) mbar_arrive(&raw_free[ab]);
-          }
-        };
-        for (int b = 0; b < kBBufs; b++)
-          if (blockIdx.x + b * gridDim.x < n_tiles) build_b((int)(blockIdx.x + b * gridDim.x), b);
-
         int L = 0;
         for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
           const int ab = L & 1;
@@ -458,18 +399,16 @@ namespace earb {
 #pragma unroll
             for (int m = 0; m < 16; m++) {
               if (m < M) {
-                const float sv = a[m] + b[m];
-                const float dv = a[16 + m] + b[16 + m];
-                if (EARB_RENDER_EXPERIMENT < 3) __stcs(out + (long)m * out_stride + t, ramp ? fmaf(p, dv, sv) : sv);
+                // columns 0..15: sum_n x * g_a (start point), 16..31: sum_n x * g_b (end point)
+                const float sa = a[m] + b[m];
+                const float sb = a[16 + m] + b[16 + m];
+                if (EARB_RENDER_EXPERIMENT < 3) __stcs(out + (long)m * out_stride + t, ramp ? fmaf(p, sb - sa, sa) : sa);
               }
             }
           }
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
           __syncwarp();
           if (lane == 0) mbar_arrive(&acc_free[ab]);
-          // every UMMA of tile L has finished (acc_full), so its B buffer can take tile L + 2
-          const int next = tile + kBBufs * gridDim.x;
-          if (next < n_tiles) build_b(next, L + kBBufs);
         }
       }
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -482,12 +421,54 @@ namespace earb {
   }  // namespace
 
   namespace {
+    // Per-point image of a gain matrix g[N][M] in the layout the UMMA reads (see b_desc):
+    // [hi | lo][2 row groups][Kp/4][8 rows][4], hi = g rounded to TF32, lo = TF32(g - hi); rows
+    // m >= M and channels k >= N are zero.  Written once per set_points.
+    __global__ void render_prepare_points_kernel(int N, int M, int Kp, long n_points,
+                                                 const float *__restrict__ gains,
+                                                 float *__restrict__ images) {
+      const long total = n_points * Kp * 16;
+      for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+        // i enumerates (point, group, chunk, row-in-group, k-in-chunk) of the hi half
+        const int e = (int)(i % ((long)Kp * 16));
+        const long p = i / ((long)Kp * 16);
+        const int grp = e / (Kp * 8), rem = e % (Kp * 8);
+        const int chunk = rem / 32, r8 = (rem % 32) / 4, k4 = rem % 4;
+        const int m = grp * 8 + r8, k = chunk * 4 + k4;
+        float hi = 0.0f, lo = 0.0f;
+        if (m < M && k < N) {
+          const float g = gains[(p * N + k) * M + m];
+          hi = round_tf32(g);
+          lo = round_tf32(g - hi);
+        }
+        float *img = images + p * ((long)Kp * 32);
+        img[e] = hi;
+        img[Kp * 16 + e] = lo;
+      }
+    }
+  }  // namespace
+
+  size_t render_tc_image_floats(int N) {
+    const int Kp = (N + kCh - 1) / kCh * kCh;
+    return (size_t)Kp * 32;
+  }
+
+  void launch_render_prepare_points(int N, int M, long n_points, const float *d_gains, float *d_images,
+                                    cudaStream_t stream) {
+    if (n_points <= 0) return;
+    const int Kp = (N + kCh - 1) / kCh * kCh;
+    const long total = n_points * Kp * 16;
+    const unsigned blocks = (unsigned)std::min<long>((total + 255) / 256, 148 * 16);
+    render_prepare_points_kernel<<<blocks, 256, 0, stream>>>(N, M, Kp, n_points, d_gains, d_images);
+  }
+
+  namespace {
     constexpr size_t kSmemBudget = 224 * 1024;  // dynamic shared memory we ask for at most
-    // gain matrices: kBBufs tiles x (hi | lo), plus the raw staging [2 tiles][2 points][N x M]
+    // gain matrices: kBBufs tiles x 64 rows x Kp
     size_t b_bytes(int N, int M) {
+      (void)M;
       const int Kp = (N + kCh - 1) / kCh * kCh;
-      const int raw_floats = (N * M + 31) / 32 * 32;
-      return sizeof(float) * ((size_t)kBBufs * 2 * Kp * kNP + (size_t)4 * raw_floats);
+      return sizeof(float) * (size_t)kBBufs * 2 * Kp * kNP;
     }
     int stages_for(int N, int M) {
       const size_t stage = sizeof(float) * kCh * kTile;
@@ -525,7 +506,7 @@ namespace earb {
   // Returns false when the TMA descriptor cannot be built (the caller then uses the FFMA path).
   bool launch_render_tc(int N, int M, const float *in, long in_stride, long n_samples, float *out,
                         long out_stride, const RenderItem *d_items, long n_tiles,
-                        const RenderSegment *d_segs, const float *d_gains, int n_sms,
+                        const RenderSegment *d_segs, const float *d_images, int n_sms,
                         cudaStream_t stream) {
     if (n_tiles <= 0) return true;
     EncodeTiledFn encode = encode_tiled();
@@ -549,7 +530,7 @@ namespace earb {
     }
     const unsigned grid = (unsigned)std::min<long>(n_tiles, n_sms > 0 ? n_sms : 148);
     render_tc_persistent_kernel<<<grid, kThreadsP, smem, stream>>>(
-        map, N, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_gains, stages_for(N, M));
+        map, N, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(N, M));
     return true;
   }
 }  // namespace earb
