@@ -70,6 +70,11 @@ struct earb200_objects {
   ExtentGrid grid{};
   DeviceBuffer<int32_t> d_out_index, d_identity_index;
   DeviceBuffer<float> d_grid_xyz, d_grid_gains, d_grid_sums;
+  // tcgen05 extent core: points as float4, gain table as the UMMA B image (TF32 hi | lo)
+  DeviceBuffer<float4> d_grid_points;
+  DeviceBuffer<float> d_grid_bimage;
+  DeviceBuffer<unsigned int> d_n_active;
+  int use_tc = 1;  // EARB200_EXTENT_PATH=cuda selects the FFMA warp-per-pass core
   // per-chunk scratch
   static constexpr int64_t kChunk = 131072;
   DeviceBuffer<ExtentPass> d_passes;
@@ -114,7 +119,9 @@ namespace {
     // per-block sums (ref polar_extent.cpp:98-165)
     std::vector<Vec3> pts = extentGridPositions(37);
     const int P = (int)pts.size();
-    const int Pp = (P + EARB_EXT_BLOCK - 1) / EARB_EXT_BLOCK * EARB_EXT_BLOCK;
+    // padded to whole B stages of the tcgen05 core (a multiple of the FFMA core's 32-point blocks)
+    static_assert(EXTENT_TC_STAGE_POINTS % EARB_EXT_BLOCK == 0, "padding");
+    const int Pp = (P + EXTENT_TC_STAGE_POINTS - 1) / EXTENT_TC_STAGE_POINTS * EXTENT_TC_STAGE_POINTS;
     const int NB = Pp / EARB_EXT_BLOCK;
     o.grid.n_points = P;
     o.grid.n_points_pad = Pp;
@@ -152,6 +159,19 @@ namespace {
     EARB_CUDA(cudaMemcpy(o.d_grid_sums.reserve(fsum.size()), fsum.data(), sizeof(float) * fsum.size(),
                          cudaMemcpyHostToDevice));
 
+    {
+      std::vector<float4> pts4(Pp);
+      for (int p = 0; p < Pp; p++) pts4[p] = make_float4(fxyz[p], fxyz[Pp + p], fxyz[2 * Pp + p], 0.0f);
+      EARB_CUDA(cudaMemcpy(o.d_grid_points.reserve(pts4.size()), pts4.data(), sizeof(float4) * pts4.size(),
+                           cudaMemcpyHostToDevice));
+      std::vector<float> image(extent_tc_bimage_floats(o.grid));
+      extent_tc_build_bimage(o.grid, fg.data(), image.data());
+      EARB_CUDA(cudaMemcpy(o.d_grid_bimage.reserve(image.size()), image.data(), sizeof(float) * image.size(),
+                           cudaMemcpyHostToDevice));
+      o.d_n_active.reserve(1);
+      const char *path = std::getenv("EARB200_EXTENT_PATH");
+      o.use_tc = !(path && std::string(path) == "cuda");
+    }
     o.d_passes.reserve(2 * earb200_objects::kChunk);
     o.d_aux.reserve(earb200_objects::kChunk);
     o.d_results.reserve(2 * earb200_objects::kChunk * EARB_MAX_SPK);
@@ -195,10 +215,16 @@ namespace {
       c.depth += start;
       c.gain += start;
       c.diffuse += start;
-      launch_objects_prelude(m, c, o.d_passes.ptr, o.d_aux.ptr, stream);
+      EARB_CUDA(cudaMemsetAsync(o.d_n_active.ptr, 0, sizeof(unsigned int), stream));
+      launch_objects_prelude(m, c, o.d_passes.ptr, o.d_aux.ptr, o.d_n_active.ptr, stream);
       o.timer.start(stream);
-      launch_extent_core(o.grid, o.d_grid_xyz.ptr, o.d_grid_gains.ptr, o.d_grid_sums.ptr, 2 * m,
-                         o.d_passes.ptr, o.d_results.ptr, o.d_counter.ptr, o.n_sms, stream);
+      if (o.use_tc)
+        launch_extent_core_tc(o.grid, o.d_grid_points.ptr, o.d_grid_bimage.ptr, o.d_n_active.ptr,
+                              o.d_passes.ptr, o.d_results.ptr, o.n_sms, stream);
+      else
+        launch_extent_core(o.grid, o.d_grid_xyz.ptr, o.d_grid_gains.ptr, o.d_grid_sums.ptr,
+                           o.d_n_active.ptr, o.d_passes.ptr, o.d_results.ptr, o.d_counter.ptr, o.n_sms,
+                           stream);
       o.timer.stop(stream);
       if (o.timer.enabled) o.timed_passes += 2 * m;
       launch_objects_epilogue<OutT>(o.panner.d_tables, m, c, o.d_passes.ptr, o.d_aux.ptr,

@@ -1,0 +1,434 @@
+// K2 core on the 5th-generation tensor cores (tcgen05 + TMEM), sm_100a only.
+//
+// Replaces the hot loop of the extent panner, PolarExtentCoreSimd::run
+// (ref src/object_based/polar_extent_simd.hpp:97-135): for every spreading pass
+//     results[s] = sum_p w_p * G[s][p],   p over the 1,652 virtual sources,
+// i.e. R[passes x S] = W[passes x P] * G^T[P x S] with W generated on the fly.
+//
+// One persistent CTA per SM works on tiles of 512 passes (four M = 128 UMMA tiles):
+//   warps 0..15  generators   thread = pass = TMEM lane.  Each thread keeps its pass context
+//                             (the 21 floats of PolarExtentCoreContext) in registers and
+//                             evaluates the weight of 16 virtual sources at a time -- the point
+//                             coordinates are warp-uniform shared-memory broadcasts -- splits
+//                             each weight into TF32 hi + lo and writes them to TMEM as the A
+//                             operand (tcgen05.st).  After the last chunk the same threads read
+//                             their row of the accumulator back, normalise it and store it.
+//   warp  16     MMA issuer   tcgen05.mma kind::tf32, M = 128:
+//                               [main | corr] (+)= w_hi * [G_hi | G_lo]   (N = 48)
+//                               corr          +=  w_lo * G_hi             (N = 32)
+//   warp  17     B producer   streams the gain table (G_hi rows 0..23, G_lo rows 24..47, K-major
+//                             canonical layout, prepared once per layout) through a
+//                             shared-memory ring with cp.async.bulk, 64 points per stage.
+//
+// The threshold decisions (weight exactly 1 / exactly 0) are the reference's float comparisons
+// with the reference's operation order (polar_extent_simd.hpp:39-95); weights on the 10-degree
+// fade use one branch-free polynomial acos.  3xTF32 keeps the contraction at fp32 accuracy
+// (weights off the fade are 0 or 1, exact in TF32).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdint>
+#include <cstring>
+
+#include "kernels.hpp"
+
+namespace earb {
+  namespace {
+    constexpr int kKC = EXTENT_TC_STAGE_POINTS;  // points per B stage
+    constexpr int kChunk = 16;                   // points per A hand-off
+    constexpr int kMTiles = 4;
+    constexpr int kGenWarps = 4 * kMTiles;
+    constexpr int kMmaWarp = kGenWarps, kProdWarp = kGenWarps + 1;
+    constexpr int kThreads = (kProdWarp + 1) * 32;  // 576
+    constexpr int kBStages = 4;
+    constexpr int kRows = 48;  // B rows: 24 hi + 24 lo
+    constexpr int kStageFloats = kRows * kKC;
+    constexpr int kTmemCols = 512;
+    constexpr int kAccCols = 64;            // per M-tile: [main 24 | corr 24 | spill-over 8 | -]
+    constexpr int kColA = kMTiles * kAccCols;  // A: [M-tile][2 buffers][hi 16 | lo 16]
+    static_assert(kColA + kMTiles * 2 * 2 * kChunk <= kTmemCols, "TMEM budget");
+    static_assert(EARB_MAX_SPK <= 24, "B row packing assumes at most 24 loudspeakers");
+
+    __device__ __forceinline__ uint32_t smem_u32(const void *p) {
+      return (uint32_t)__cvta_generic_to_shared(p);
+    }
+    __device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+    }
+    __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                   : "memory");
+    }
+    __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+      asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+    }
+    __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+      asm volatile(
+          "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+              smem_u32(dst)),
+          "l"(src), "r"(bytes), "r"(smem_u32(bar))
+          : "memory");
+    }
+    // spins on the barrier phase; a protocol error traps after ~2 s instead of hanging the GPU
+    __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+      uint32_t done;
+      const long long t0 = clock64();
+      do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(smem_u32(bar)), "r"(parity)
+            : "memory");
+        if (!done && clock64() - t0 > 4000000000LL) __trap();
+      } while (!done);
+    }
+    __device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16]) {
+      asm volatile(
+          "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+          "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+          "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])),
+          "r"(__float_as_uint(v[3])), "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])),
+          "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7])), "r"(__float_as_uint(v[8])),
+          "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])), "r"(__float_as_uint(v[11])),
+          "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])),
+          "r"(__float_as_uint(v[15]))
+          : "memory");
+    }
+    __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+      uint32_t r[16];
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+            "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
+            "=r"(r[15])
+          : "r"(taddr)
+          : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+      for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
+    }
+    // D[tmem] (+)= A[tmem] * B[smem desc], kind::tf32, issued by one thread
+    __device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc,
+                                                 uint32_t idesc, uint32_t accumulate) {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "setp.ne.b32 p, %4, 0;\n\t"
+          "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+          ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+          : "memory");
+    }
+    __device__ __forceinline__ void umma_commit(uint64_t *bar) {
+      asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                       smem_u32(bar))
+                   : "memory");
+    }
+    // B stage in shared memory: [6 row groups][kKC/4 K-chunks][8 rows][4 floats] -- K-major,
+    // no swizzle; core matrices adjacent in K are 128 bytes apart, row groups kKC/4*128 bytes
+    __device__ __forceinline__ uint64_t b_desc(uint32_t smem_addr) {
+      const uint64_t lbo = 128 >> 4;
+      const uint64_t sbo = (uint64_t)(kKC / 4 * 128) >> 4;
+      return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (lbo << 16) | (sbo << 32) | (1ull << 46);
+    }
+
+    // acos(x) = sqrt(1 - |x|) * P7(|x|), reflected for x < 0 (Abramowitz & Stegun 4.4.46,
+    // |error| <= 2e-8 before rounding).  Out-of-domain arguments give NaN like acosf().
+    __device__ __forceinline__ float fast_acos(float x) {
+      const float ax = fabsf(x);
+      float p = -0.0012624911f;
+      p = fmaf(p, ax, 0.0066700901f);
+      p = fmaf(p, ax, -0.0170881256f);
+      p = fmaf(p, ax, 0.0308918810f);
+      p = fmaf(p, ax, -0.0501743046f);
+      p = fmaf(p, ax, 0.0889789874f);
+      p = fmaf(p, ax, -0.2145988016f);
+      p = fmaf(p, ax, 1.5707963050f);
+      const float r = __fmul_rn(sqrtf(__fsub_rn(1.0f, ax)), p);
+      return x < 0.0f ? __fsub_rn(3.14159265358979f, r) : r;
+    }
+
+    // pass context in registers (PolarExtentCoreContext, ref polar_extent_core.hpp:12-42)
+    struct PassRegs {
+      float b[9];
+      float ct0, ct1, cc0, cc1;
+      float cos_start, cos_end, sin_start, sin_end, m, c;
+      bool circular;
+    };
+
+    // weight of one virtual source (ref polar_extent_simd.hpp:39-95); same comparisons and
+    // operation order as the reference, explicit roundings so the build flags cannot contract
+    __device__ __forceinline__ float point_weight(const PassRegs &c, float x, float y, float z) {
+      const float yt = fmaf(x, c.b[3], fmaf(y, c.b[4], __fmul_rn(z, c.b[5])));
+      float arg = yt;
+      bool is_sin = false;
+      if (!c.circular) {
+        const float xt = fmaf(x, c.b[0], fmaf(y, c.b[1], __fmul_rn(z, c.b[2])));
+        const float zt = fmaf(x, c.b[6], fmaf(y, c.b[7], __fmul_rn(z, c.b[8])));
+        const float ax = fabsf(xt);
+        const float circle_test_dot = fmaf(ax, c.ct0, __fmul_rn(yt, c.ct1));
+        const float circle_dot = fmaf(ax, c.cc0, __fmul_rn(yt, c.cc1));
+        is_sin = circle_test_dot >= 0.0f;
+        arg = is_sin ? fabsf(zt) : circle_dot;
+      }
+      const bool one = is_sin ? (arg <= c.sin_start) : (arg >= c.cos_start);
+      const bool zero = is_sin ? (arg >= c.sin_end) : (arg <= c.cos_end);
+      const float a = fast_acos(arg);
+      const float angle = is_sin ? __fsub_rn(1.57079632679490f, a) : a;
+      const float ramp = __fadd_rn(__fmul_rn(c.m, angle), c.c);
+      return one ? 1.0f : (zero ? 0.0f : ramp);
+    }
+
+    // Barriers
+    //   a_full[mt][b]  generators -> MMA         A buffer b of M-tile mt is complete (4 warps)
+    //   a_free[mt][b]  MMA commit -> generators  the UMMAs reading it have finished
+    //   b_full[s]      producer   -> MMA         B stage s has landed (tx bytes)
+    //   b_empty[s]     MMA commit -> producer    the UMMAs reading B stage s have finished
+    //   acc_full       MMA commit -> generators  every UMMA of the tile has finished
+    __global__ void __launch_bounds__(kThreads, 1)
+        extent_core_tc_kernel(ExtentGrid grid, const float4 *__restrict__ g_points,
+                              const float *__restrict__ g_bimage,
+                              const unsigned int *__restrict__ n_active_ptr,
+                              const ExtentPass *__restrict__ passes, float *__restrict__ results) {
+      extern __shared__ __align__(128) unsigned char smem_raw[];
+      const int Pp = grid.n_points_pad;  // multiple of kKC
+      const int S = grid.n_spk;
+      float *sB = reinterpret_cast<float *>(smem_raw);                 // [kBStages][kStageFloats]
+      float4 *spts = reinterpret_cast<float4 *>(sB + kBStages * kStageFloats);  // [Pp]
+      __shared__ __align__(8) uint64_t a_full[kMTiles][2], a_free[kMTiles][2];
+      __shared__ __align__(8) uint64_t b_full[kBStages], b_empty[kBStages], acc_full;
+      __shared__ uint32_t tmem_base_s;
+
+      const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+      const int n_active = (int)*n_active_ptr;
+      const int n_tiles = (n_active + kMTiles * 128 - 1) / (kMTiles * 128);
+      const int n_chunks = Pp / kChunk, n_stages = Pp / kKC;
+
+      for (int i = tid; i < Pp; i += kThreads) spts[i] = g_points[i];
+      if (tid == 0) {
+        for (int m = 0; m < kMTiles; m++)
+          for (int b = 0; b < 2; b++) {
+            mbar_init(&a_full[m][b], 4);
+            mbar_init(&a_free[m][b], 1);
+          }
+        for (int s = 0; s < kBStages; s++) {
+          mbar_init(&b_full[s], 1);
+          mbar_init(&b_empty[s], 1);
+        }
+        mbar_init(&acc_full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      }
+      if (warp == kMmaWarp) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                         smem_u32(&tmem_base_s)),
+                     "r"(kTmemCols)
+                     : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+      }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncthreads();
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      const uint32_t tmem_base = tmem_base_s;
+
+      if (warp == kProdWarp) {
+        // ------------------------------------------------------------ B producer
+        if (lane == 0) {
+          int g = 0;
+          for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
+            for (int s = 0; s < n_stages; s++, g++) {
+              const int bs = g % kBStages;
+              if (g >= kBStages) mbar_wait(&b_empty[bs], (uint32_t)(((g / kBStages) - 1) & 1));
+              mbar_expect_tx(&b_full[bs], (uint32_t)(kStageFloats * sizeof(float)));
+              bulk_g2s(sB + bs * kStageFloats, g_bimage + (size_t)s * kStageFloats,
+                       (uint32_t)(kStageFloats * sizeof(float)), &b_full[bs]);
+            }
+        }
+      } else if (warp == kMmaWarp) {
+        // ------------------------------------------------------------ MMA issuer
+        // the whole warp runs the loop (warp-uniform operands); one elected lane issues
+        const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base, 0);
+        uint32_t leader;
+        asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(leader));
+        // instruction descriptors: D f32, A/B tf32, both K-major, M = 128, N = 48 / 32
+        const uint32_t idesc_base = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 4) << 24);
+        const uint32_t idesc48 = idesc_base | ((uint32_t)(48 >> 3) << 17);
+        const uint32_t idesc32 = idesc_base | ((uint32_t)(32 >> 3) << 17);
+        const uint64_t bdesc0 = b_desc(smem_u32(sB));
+        int gs = 0, gc = 0;  // B stage / chunk counters, continuous across tiles
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+          for (int c = 0; c < n_chunks; c++, gc++) {
+            const int sub = c % (kKC / kChunk);
+            const int bs = gs % kBStages;
+            if (sub == 0) mbar_wait(&b_full[bs], (uint32_t)((gs / kBStages) & 1));
+            const int buf = gc & 1;
+            // chunk `sub` of the stage: kChunk points = 4 K-chunks of 128 bytes
+            const uint64_t bd = bdesc0 + (uint64_t)((bs * kStageFloats * 4 + sub * (kChunk / 4) * 128) >> 4);
+#pragma unroll
+            for (int mt = 0; mt < kMTiles; mt++) {
+              mbar_wait(&a_full[mt][buf], (uint32_t)((gc >> 1) & 1));
+              asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+              if (leader) {
+                const uint32_t acc = tm + mt * kAccCols;
+                const uint32_t a_hi = tm + kColA + (mt * 2 + buf) * 2 * kChunk;
+#pragma unroll
+                for (int ks = 0; ks < kChunk / 8; ks++) {
+                  umma_tf32_ts(acc, a_hi + ks * 8, bd + (uint64_t)(ks * ((2 * 128) >> 4)), idesc48,
+                               (c | ks) != 0);
+                  umma_tf32_ts(acc + 24, a_hi + kChunk + ks * 8, bd + (uint64_t)(ks * ((2 * 128) >> 4)),
+                               idesc32, 1);
+                }
+                umma_commit(&a_free[mt][buf]);
+              }
+              __syncwarp();
+            }
+            if (sub == kKC / kChunk - 1) {
+              if (leader) umma_commit(&b_empty[bs]);
+              __syncwarp();
+              gs++;
+            }
+          }
+          if (leader) umma_commit(&acc_full);
+          __syncwarp();
+        }
+      } else {
+        // ------------------------------------------------------------ generators + epilogue
+        const int mt = warp >> 2, q = warp & 3;
+        const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+        int gc = 0, L = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
+          const int idx = tile * (kMTiles * 128) + mt * 128 + q * 32 + lane;
+          const bool valid = idx < n_active;
+          const ExtentPass *pp = passes + (valid ? idx : n_active - 1);
+          PassRegs c;
+          int slot;
+          {
+            ExtentPass e;
+            const float4 *src = reinterpret_cast<const float4 *>(pp);
+            float4 *dst = reinterpret_cast<float4 *>(&e);
+#pragma unroll
+            for (int k = 0; k < (int)(sizeof(ExtentPass) / 16); k++) dst[k] = __ldg(src + k);
+#pragma unroll
+            for (int k = 0; k < 9; k++) c.b[k] = e.basis[k];
+            c.ct0 = e.circle_test[0];
+            c.ct1 = e.circle_test[1];
+            c.cc0 = e.circle_centre[0];
+            c.cc1 = e.circle_centre[1];
+            c.cos_start = e.cos_start;
+            c.cos_end = e.cos_end;
+            c.sin_start = e.sin_start;
+            c.sin_end = e.sin_end;
+            c.m = e.m;
+            c.c = e.c;
+            c.circular = e.is_circular != 0;
+            slot = e.slot;
+          }
+          for (int ch = 0; ch < n_chunks; ch++, gc++) {
+            const int buf = gc & 1;
+            float hi[kChunk], lo[kChunk];
+#pragma unroll
+            for (int i = 0; i < kChunk; i++) {
+              const float4 p = spts[ch * kChunk + i];  // warp-uniform broadcast
+              const float w = point_weight(c, p.x, p.y, p.z);
+              hi[i] = __uint_as_float(__float_as_uint(w) & 0xffffe000u);
+              lo[i] = __fsub_rn(w, hi[i]);
+            }
+            if (gc >= 2) {
+              mbar_wait(&a_free[mt][buf], (uint32_t)(((gc >> 1) - 1) & 1));
+              asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            }
+            const uint32_t a_col = kColA + (mt * 2 + buf) * 2 * kChunk;
+            tmem_st16(lane_base + a_col, hi);
+            tmem_st16(lane_base + a_col + kChunk, lo);
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&a_full[mt][buf]);
+          }
+          // epilogue: this thread's row of [main | corr]; results /= ||results|| in float
+          // (ref polar_extent.cpp:271-273)
+          mbar_wait(&acc_full, (uint32_t)(L & 1));
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          float r[48];
+          {
+            float t[16];
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+              tmem_ld16(lane_base + mt * kAccCols + k * 16, t);
+#pragma unroll
+              for (int i = 0; i < 16; i++) r[k * 16 + i] = t[i];
+            }
+          }
+          asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          float v[EARB_MAX_SPK];
+          float sq = 0.0f;
+#pragma unroll
+          for (int s = 0; s < EARB_MAX_SPK; s++) {
+            v[s] = (s < S) ? __fadd_rn(r[s], r[24 + s]) : 0.0f;
+            sq = __fadd_rn(sq, __fmul_rn(v[s], v[s]));
+          }
+          const float scale = (float)(1.0 / (double)sqrtf(sq));
+          if (valid) {
+            float4 *dst = reinterpret_cast<float4 *>(results + (size_t)slot * EARB_MAX_SPK);
+#pragma unroll
+            for (int k = 0; k < EARB_MAX_SPK / 4; k++)
+              dst[k] = make_float4(__fmul_rn(v[4 * k], scale), __fmul_rn(v[4 * k + 1], scale),
+                                   __fmul_rn(v[4 * k + 2], scale), __fmul_rn(v[4 * k + 3], scale));
+          }
+        }
+      }
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncthreads();
+      if (warp == kMmaWarp) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols)
+                     : "memory");
+      }
+    }
+  }  // namespace
+
+  size_t extent_tc_smem_bytes(const ExtentGrid &grid) {
+    return sizeof(float) * (size_t)kBStages * kStageFloats + sizeof(float4) * (size_t)grid.n_points_pad;
+  }
+
+  size_t extent_tc_bimage_floats(const ExtentGrid &grid) { return (size_t)kRows * grid.n_points_pad; }
+
+  // host: K-major canonical image of [G_hi (24 rows) | G_lo (24 rows)] per stage of kKC points:
+  // image[stage][row group 0..5][K-chunk][8 rows][4]; gains is speaker-major [S][Pp] float
+  void extent_tc_build_bimage(const ExtentGrid &grid, const float *gains, float *image) {
+    const int Pp = grid.n_points_pad, S = grid.n_spk;
+    auto tf32 = [](float x) {
+      uint32_t u;
+      memcpy(&u, &x, 4);
+      u = (u + 0x1000u) & 0xffffe000u;
+      float r;
+      memcpy(&r, &u, 4);
+      return r;
+    };
+    std::fill(image, image + (size_t)kRows * Pp, 0.0f);
+    for (int s = 0; s < S; s++)
+      for (int p = 0; p < Pp; p++) {
+        const float g = gains[(size_t)s * Pp + p];
+        const float hi = tf32(g), lo = tf32(g - hi);
+        const int stage = p / kKC, k = p % kKC;
+        auto at = [&](int row) {
+          return (size_t)stage * kStageFloats + (size_t)(row / 8) * (kKC / 4 * 32) + (size_t)(k / 4) * 32 +
+                 (row % 8) * 4 + (k % 4);
+        };
+        image[at(s)] = hi;
+        image[at(24 + s)] = lo;
+      }
+  }
+
+  void launch_extent_core_tc(const ExtentGrid &grid, const float4 *d_points, const float *d_bimage,
+                             const unsigned int *d_n_active, const ExtentPass *d_passes, float *d_results,
+                             int n_sms, cudaStream_t stream) {
+    const size_t smem = extent_tc_smem_bytes(grid);
+    static bool configured = false;
+    if (!configured) {
+      cudaFuncSetAttribute(extent_core_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      configured = true;
+    }
+    extent_core_tc_kernel<<<(unsigned)n_sms, kThreads, smem, stream>>>(grid, d_points, d_bimage, d_n_active,
+                                                                         d_passes, d_results);
+  }
+}  // namespace earb

@@ -24,11 +24,21 @@ namespace earb {
   void launch_psp_batch(const PspTables *d_tables, long n, const double *d_xyz,
                         double *d_gains, int32_t *d_region, int32_t *d_inner,
                         cudaStream_t stream);
+  // writes the active passes compacted to d_passes[0 .. *d_n_active) (d_n_active must be zero)
   void launch_objects_prelude(long n, const ObjectsSoA &in, ExtentPass *d_passes,
-                              ObjectAux *d_aux, cudaStream_t stream);
+                              ObjectAux *d_aux, unsigned int *d_n_active, cudaStream_t stream);
   size_t extent_core_smem_bytes(const ExtentGrid &grid);
+#define EXTENT_TC_STAGE_POINTS 64
+  // tcgen05 extent core (extent_tc_kernels.cu): thread-per-pass weights feeding 3xTF32 UMMAs
+  size_t extent_tc_smem_bytes(const ExtentGrid &grid);
+  size_t extent_tc_bimage_floats(const ExtentGrid &grid);
+  void extent_tc_build_bimage(const ExtentGrid &grid, const float *gains, float *image);
+  void launch_extent_core_tc(const ExtentGrid &grid, const float4 *d_points, const float *d_bimage,
+                             const unsigned int *d_n_active, const ExtentPass *d_passes,
+                             float *d_results, int n_sms, cudaStream_t stream);
+  // FFMA extent core (objects_kernels.cu), warp per pass
   void launch_extent_core(const ExtentGrid &grid, const float *d_xyz, const float *d_gains,
-                          const float *d_block_sums, long n_slots,
+                          const float *d_block_sums, const unsigned int *d_n_active,
                           const ExtentPass *d_passes, float *d_results,
                           unsigned long long *d_counter, int n_sms, cudaStream_t stream);
   template <typename OutT>

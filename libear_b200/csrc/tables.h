@@ -79,12 +79,14 @@ struct __attribute__((aligned(16))) ExtentPass {
   float m, c;
   int32_t is_circular;
   int32_t active;  // 0: spread branch skipped (amount_spread <= 1e-10)
-  int32_t pad[3];
+  int32_t slot;    // 2 * object + pass: where the core kernel writes this pass's results
+  int32_t pad[2];
 };  // 24 words = 96 bytes (loaded as six 16-byte vectors)
 
 // per-object scalars carried from the prelude to the epilogue
 struct ObjectAux {
   double amount_spread[2];  // per pass
   int32_t n_passes;         // 1 or 2 (2 when depth != 0)
-  int32_t has_point;        // bit p set: pass p needs the point-source gains
+  int32_t has_point;        // bit p set: pass p needs the point-source gains;
+                            // bit 2 + p set: pass p has a spread part (an ExtentPass exists)
 };
