@@ -133,51 +133,53 @@ namespace earb {
       return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (lbo << 16) | (sbo << 32) | (1ull << 46);
     }
 
-    // acos(x) = sqrt(1 - |x|) * P7(|x|), reflected for x < 0 (Abramowitz & Stegun 4.4.46,
-    // |error| <= 2e-8 before rounding).  Out-of-domain arguments give NaN like acosf().
-    __device__ __forceinline__ float fast_acos(float x) {
-      const float ax = fabsf(x);
-      float p = -0.0012624911f;
-      p = fmaf(p, ax, 0.0066700901f);
-      p = fmaf(p, ax, -0.0170881256f);
-      p = fmaf(p, ax, 0.0308918810f);
-      p = fmaf(p, ax, -0.0501743046f);
-      p = fmaf(p, ax, 0.0889789874f);
-      p = fmaf(p, ax, -0.2145988016f);
-      p = fmaf(p, ax, 1.5707963050f);
-      const float r = __fmul_rn(sqrtf(__fsub_rn(1.0f, ax)), p);
-      return x < 0.0f ? __fsub_rn(3.14159265358979f, r) : r;
-    }
-
-    // pass context in registers (PolarExtentCoreContext, ref polar_extent_core.hpp:12-42)
+    // pass context in registers (PolarExtentCoreContext, ref polar_extent_core.hpp:12-42).
+    // Circular extents (ref weight_circle, polar_extent_simd.hpp:61-66) run through the stadium
+    // code with constants that reduce it to the circle test exactly: sin_thr = +inf disables the
+    // straight-line part and (cc0, cc1) = (0, 1) makes circle_dot = fma(|x'|, 0, y' * 1) = y'.
     struct PassRegs {
       float b[9];
       float ct0, ct1, cc0, cc1;
-      float cos_start, cos_end, sin_start, sin_end, m, c;
-      bool circular;
+      float sin_thr;  // straight-line part when circle_test_dot >= sin_thr (0, or +inf if circular)
+      float cos_start, cos_end, nsin_start, nsin_end;  // sin thresholds negated
+      float m, c;
     };
 
-    // weight of one virtual source (ref polar_extent_simd.hpp:39-95); same comparisons and
-    // operation order as the reference, explicit roundings so the build flags cannot contract
+    // Weight of one virtual source (ref polar_extent_simd.hpp:39-95): same comparisons and
+    // operation order as the reference, written branch-free.  With v = -|z'| on the straight-line
+    // part and v = circle_dot on the circle part, "weight 1" is v >= T1 and "weight 0" is
+    // v <= T0 in both parts (sin thresholds negated -- negation is exact).  The fade evaluates
+    // acos(|v|) = sqrt(1 - |v|) * P7(|v|) (Abramowitz & Stegun 4.4.46, |error| <= 2e-8) and maps
+    // it to acos(v) = pi - r for v < 0 on the circle part, asin(|z'|) = pi/2 - r on the straight
+    // part.
     __device__ __forceinline__ float point_weight(const PassRegs &c, float x, float y, float z) {
+      const float xt = fmaf(x, c.b[0], fmaf(y, c.b[1], __fmul_rn(z, c.b[2])));
       const float yt = fmaf(x, c.b[3], fmaf(y, c.b[4], __fmul_rn(z, c.b[5])));
-      float arg = yt;
-      bool is_sin = false;
-      if (!c.circular) {
-        const float xt = fmaf(x, c.b[0], fmaf(y, c.b[1], __fmul_rn(z, c.b[2])));
-        const float zt = fmaf(x, c.b[6], fmaf(y, c.b[7], __fmul_rn(z, c.b[8])));
-        const float ax = fabsf(xt);
-        const float circle_test_dot = fmaf(ax, c.ct0, __fmul_rn(yt, c.ct1));
-        const float circle_dot = fmaf(ax, c.cc0, __fmul_rn(yt, c.cc1));
-        is_sin = circle_test_dot >= 0.0f;
-        arg = is_sin ? fabsf(zt) : circle_dot;
-      }
-      const bool one = is_sin ? (arg <= c.sin_start) : (arg >= c.cos_start);
-      const bool zero = is_sin ? (arg >= c.sin_end) : (arg <= c.cos_end);
-      const float a = fast_acos(arg);
-      const float angle = is_sin ? __fsub_rn(1.57079632679490f, a) : a;
+      const float zt = fmaf(x, c.b[6], fmaf(y, c.b[7], __fmul_rn(z, c.b[8])));
+      const float ax = fabsf(xt);
+      const float circle_test_dot = fmaf(ax, c.ct0, __fmul_rn(yt, c.ct1));
+      const float circle_dot = fmaf(ax, c.cc0, __fmul_rn(yt, c.cc1));
+      const bool is_sin = circle_test_dot >= c.sin_thr;
+      const float v = is_sin ? -fabsf(zt) : circle_dot;
+      const float t1 = is_sin ? c.nsin_start : c.cos_start;
+      const float t0 = is_sin ? c.nsin_end : c.cos_end;
+      const float av = fabsf(v);
+      float p = -0.0012624911f;
+      p = fmaf(p, av, 0.0066700901f);
+      p = fmaf(p, av, -0.0170881256f);
+      p = fmaf(p, av, 0.0308918810f);
+      p = fmaf(p, av, -0.0501743046f);
+      p = fmaf(p, av, 0.0889789874f);
+      p = fmaf(p, av, -0.2145988016f);
+      p = fmaf(p, av, 1.5707963050f);
+      float sq;
+      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(__fsub_rn(1.0f, av)));
+      const float r = __fmul_rn(sq, p);
+      const bool flip = is_sin || (v < 0.0f);
+      const float k = flip ? (is_sin ? 1.57079632679490f : 3.14159265358979f) : 0.0f;
+      const float angle = fmaf(flip ? -1.0f : 1.0f, r, k);
       const float ramp = __fadd_rn(__fmul_rn(c.m, angle), c.c);
-      return one ? 1.0f : (zero ? 0.0f : ramp);
+      return (v >= t1) ? 1.0f : ((v <= t0) ? 0.0f : ramp);
     }
 
     // Barriers
@@ -316,11 +318,16 @@ namespace earb {
             c.cc1 = e.circle_centre[1];
             c.cos_start = e.cos_start;
             c.cos_end = e.cos_end;
-            c.sin_start = e.sin_start;
-            c.sin_end = e.sin_end;
+            c.nsin_start = -e.sin_start;
+            c.nsin_end = -e.sin_end;
             c.m = e.m;
             c.c = e.c;
-            c.circular = e.is_circular != 0;
+            c.sin_thr = 0.0f;
+            if (e.is_circular) {
+              c.sin_thr = __int_as_float(0x7f800000);
+              c.cc0 = 0.0f;
+              c.cc1 = 1.0f;
+            }
             slot = e.slot;
           }
           for (int ch = 0; ch < n_chunks; ch++, gc++) {
