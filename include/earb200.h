@@ -217,6 +217,46 @@ int earb200_hoa_calculate(earb200_hoa *hoa, int n_channels, const int *orders,
                           double nfc_ref_dist, int screen_ref, double *decode,
                           uint32_t *warnings);
 
+/* ------------------------------------- DirectSpeakers gain calculator (a12)
+ * replaces ear::GainCalculatorDirectSpeakers (include/ear/gain_calculators.hpp:18-34,
+ * src/direct_speakers/gain_calculator_direct_speakers.cpp:57-320).  The routing decision
+ * is host work (labels, ITU-R BS.2127 mapping rules, bounds); channels that fall through
+ * to the point-source panner are panned by K1 in one launch per call. */
+typedef struct earb200_direct_speakers earb200_direct_speakers;
+
+/* flat form of ear::DirectSpeakersTypeMetadata (include/ear/metadata.hpp:22-72) */
+typedef struct earb200_direct_speakers_metadata {
+  const char *const *speaker_labels; /* speakerLabels, in AXML order */
+  int32_t n_speaker_labels;
+  int32_t cartesian_position; /* position holds a CartesianSpeakerPosition (libear: not_implemented) */
+  double position[3];         /* azimuth, elevation, distance */
+  double bounds[6];           /* azimuthMin, azimuthMax, elevationMin, elevationMax, distanceMin, distanceMax */
+  uint32_t has_bounds;        /* bit i set: bounds[i] is present */
+  uint32_t screen_edge_lock;  /* bit 0: horizontal, bit 1: vertical (libear: not_implemented) */
+  double low_pass, high_pass; /* channelFrequency */
+  uint32_t has_frequency;     /* bit 0: lowPass present, bit 1: highPass present */
+  uint32_t reserved;
+  const char *audio_pack_format_id; /* nullable, e.g. "AP_00010003" */
+} earb200_direct_speakers_metadata;
+
+enum {
+  EARB200_WARN_FREQ_SPEAKERLABEL_LFE_MISMATCH = 1, /* Warning::Code (include/ear/warnings.hpp:13-17) */
+  EARB200_WARN_FREQ_NOT_LFE = 2
+};
+
+/* additionalSubstitutions: n pairs from[i] -> to[i] (nullable when n == 0) */
+int earb200_direct_speakers_create(const earb200_layout *layout, int device, int n_substitutions,
+                                   const char *const *from, const char *const *to,
+                                   earb200_direct_speakers **out);
+void earb200_direct_speakers_destroy(earb200_direct_speakers *calc);
+int earb200_direct_speakers_num_outputs(const earb200_direct_speakers *calc);
+/* n channels; gains [n][C_out] row-major double; warnings [n] bitmask of (1 << code), nullable.
+ * Host buffers. */
+int earb200_direct_speakers_calculate(earb200_direct_speakers *calc, int64_t n,
+                                      const earb200_direct_speakers_metadata *md, double *gains,
+                                      uint32_t *warnings);
+int64_t earb200_direct_speakers_launch_count(const earb200_direct_speakers *calc);
+
 /* ---------------------------------------------------------- decorrelators
  * replaces ear::designDecorrelators / decorrelatorCompensationDelay
  * (include/ear/decorrelate.hpp:17-34, src/decorrelate.cpp:31-97).  Setup-time, host. */

@@ -28,7 +28,7 @@ _lib.earb200_version.restype = C.c_char_p
 _lib.earb200_layout_name_at.restype = C.c_char_p
 _lib.earb200_layout_channel_name.restype = C.c_char_p
 for _f in ("earb200_objects_launch_count", "earb200_interp_launch_count",
-           "earb200_convolver_launch_count"):
+           "earb200_convolver_launch_count", "earb200_direct_speakers_launch_count"):
     getattr(_lib, _f).restype = C.c_int64
 
 
@@ -364,6 +364,81 @@ class GainCalculatorHOA:
         _chk(_lib.earb200_hoa_calculate(self.h, len(o), _ptr(o), _ptr(d), normalization.encode(),
                                         C.c_double(nfc_ref_dist), int(screen_ref), _ptr(D), C.byref(w)))
         return D, [c for c in range(32) if w.value >> c & 1]
+
+
+WARN_FREQ_SPEAKERLABEL_LFE_MISMATCH, WARN_FREQ_NOT_LFE = 1, 2
+
+
+class _DirectSpeakersMetadata(C.Structure):
+    _fields_ = [("speaker_labels", C.POINTER(C.c_char_p)), ("n_speaker_labels", C.c_int32),
+                ("cartesian_position", C.c_int32), ("position", C.c_double * 3),
+                ("bounds", C.c_double * 6), ("has_bounds", C.c_uint32), ("screen_edge_lock", C.c_uint32),
+                ("low_pass", C.c_double), ("high_pass", C.c_double), ("has_frequency", C.c_uint32),
+                ("reserved", C.c_uint32), ("audio_pack_format_id", C.c_char_p)]
+
+
+_BOUND_KEYS = ["azMin", "azMax", "elMin", "elMax", "distMin", "distMax"]
+
+
+class GainCalculatorDirectSpeakers:
+    """ear::GainCalculatorDirectSpeakers (include/ear/gain_calculators.hpp:18-34).  Routing is
+    host-side; only channels that fall through to the point-source panner touch the device."""
+
+    def __init__(self, layout, additional_substitutions=None, device=0):
+        self.layout = _as_layout(layout)
+        subs = dict(additional_substitutions or {})
+        frm = (C.c_char_p * max(1, len(subs)))(*[k.encode() for k in subs])
+        to = (C.c_char_p * max(1, len(subs)))(*[v.encode() for v in subs.values()])
+        self.h = C.c_void_p()
+        _chk(_lib.earb200_direct_speakers_create(self.layout.h, device, len(subs), frm, to, C.byref(self.h)))
+        self.num_outputs = _lib.earb200_direct_speakers_num_outputs(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            _lib.earb200_direct_speakers_destroy(self.h)
+            self.h = None
+
+    @property
+    def launch_count(self):
+        return _lib.earb200_direct_speakers_launch_count(self.h)
+
+    @staticmethod
+    def _flatten(md, keep):
+        m = _DirectSpeakersMetadata()
+        labels = [x.encode() for x in md.get("labels", [])]
+        arr = (C.c_char_p * max(1, len(labels)))(*labels)
+        keep.append(arr)
+        m.speaker_labels = C.cast(arr, C.POINTER(C.c_char_p))
+        m.n_speaker_labels = len(labels)
+        m.cartesian_position = int(bool(md.get("cartesian", False)))
+        m.position[:] = [md.get("az", 0.0), md.get("el", 0.0), md.get("dist", 1.0)]
+        for i, k in enumerate(_BOUND_KEYS):
+            if md.get("bounds") and k in md["bounds"]:
+                m.bounds[i] = md["bounds"][k]
+                m.has_bounds |= 1 << i
+        m.screen_edge_lock = int(md.get("screen_edge_lock", 0))
+        if md.get("low_pass") is not None:
+            m.low_pass, m.has_frequency = md["low_pass"], m.has_frequency | 1
+        if md.get("high_pass") is not None:
+            m.high_pass, m.has_frequency = md["high_pass"], m.has_frequency | 2
+        m.audio_pack_format_id = md["pack"].encode() if md.get("pack") else None
+        return m
+
+    def calculate_batch(self, channels):
+        """channels: list of dicts (labels, az, el, dist, bounds, low_pass, high_pass, pack,
+        cartesian, screen_edge_lock).  Returns (gains[n][C_out], [[warning codes] per channel])."""
+        keep = []
+        mds = (_DirectSpeakersMetadata * max(1, len(channels)))(*[self._flatten(c, keep) for c in channels])
+        gains = np.zeros((len(channels), self.num_outputs))
+        w = np.zeros(max(1, len(channels)), dtype=np.uint32)
+        _chk(_lib.earb200_direct_speakers_calculate(self.h, C.c_int64(len(channels)), mds, _ptr(gains), _ptr(w)))
+        return gains, [[c for c in range(32) if int(x) >> c & 1] for x in w[:len(channels)]]
+
+    def calculate(self, labels, az=0.0, el=0.0, dist=1.0, bounds=None, low_pass=None, high_pass=None,
+                  pack=None, **kw):
+        g, w = self.calculate_batch([dict(labels=labels, az=az, el=el, dist=dist, bounds=bounds,
+                                          low_pass=low_pass, high_pass=high_pass, pack=pack, **kw)])
+        return g[0], w[0]
 
 
 def design_decorrelators(layout, dtype=np.float32):

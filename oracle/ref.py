@@ -187,8 +187,10 @@ def hoa_points():
 
 
 def direct_speakers_calc(layout, labels, az=0.0, el=0.0, dist=1.0, bounds=None,
-                         low_pass=None, high_pass=None, pack_id=None):
-    """bounds: dict with any of azMin, azMax, elMin, elMax, distMin, distMax."""
+                         low_pass=None, high_pass=None, pack_id=None, substitutions=None,
+                         cartesian=False, screen_edge_lock=0, codes=False):
+    """bounds: dict with any of azMin, azMax, elMin, elMax, distMin, distMax.
+    Returns (gains, number of warnings) or, with codes=True, (gains, sorted warning codes)."""
     n_out = len(layout_info(layout)["names"])
     keys = ["azMin", "azMax", "elMin", "elMax", "distMin", "distMax"]
     b = np.zeros(6)
@@ -203,8 +205,12 @@ def direct_speakers_calc(layout, labels, az=0.0, el=0.0, dist=1.0, bounds=None,
     _chk(lib().ref_direct_speakers_calc(
         layout.encode(), "\n".join(labels).encode(), C.c_double(az), C.c_double(el), C.c_double(dist),
         _p(b), mask, C.c_double(low_pass or 0.0), C.c_double(high_pass or 0.0), fmask,
-        (pack_id or "").encode(), n_out, _p(g), C.byref(nw)))
-    return g, nw.value
+        (pack_id or "").encode(), n_out, _p(g), C.byref(nw),
+        "\n".join(f"{k}={v}" for k, v in (substitutions or {}).items()).encode(),
+        int(cartesian), int(screen_edge_lock)))
+    if codes:
+        return g, [c for c in range(1, 8) if nw.value >> (8 + c) & 1]
+    return g, nw.value & 255
 
 
 def decorrelators(layout, dtype=np.float32):

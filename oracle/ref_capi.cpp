@@ -13,6 +13,7 @@
 // region whose handleRemap() returns a value is reported.
 #include <cstdint>
 #include <cstring>
+#include <map>
 #include <memory>
 #include <string>
 #include <vector>
@@ -32,6 +33,7 @@
 #include "common/geom.hpp"
 #include "common/helpers/eigen_helpers.hpp"
 #include "direct_speakers/gain_calculator_direct_speakers.hpp"
+#include "direct_speakers/mapping_rules.hpp"
 #include "ear/bs2051.hpp"
 #include "ear/decorrelate.hpp"
 #include "ear/dsp/block_convolver.hpp"
@@ -393,9 +395,21 @@ int ref_direct_speakers_calc(const char *layout_name, const char *labels,
                              const double *bounds, int has_bounds,
                              double low_pass, double high_pass, int has_freq,
                              const char *pack_id, int n_out, double *gains,
-                             int *n_warnings) {
+                             int *n_warnings, const char *substitutions,
+                             int cartesian, int edge_lock) {
   REF_TRY
-  GainCalculatorDirectSpeakers gc(getLayout(layout_name));
+  // additionalSubstitutions: '\n'-separated "from=to" pairs
+  std::map<std::string, std::string> subs;
+  std::string ss(substitutions ? substitutions : "");
+  for (size_t b = 0; b < ss.size();) {
+    size_t e = ss.find('\n', b);
+    if (e == std::string::npos) e = ss.size();
+    std::string kv = ss.substr(b, e - b);
+    size_t eq = kv.find('=');
+    if (eq != std::string::npos) subs[kv.substr(0, eq)] = kv.substr(eq + 1);
+    b = e + 1;
+  }
+  GainCalculatorDirectSpeakers gc(getLayout(layout_name), subs);
   DirectSpeakersTypeMetadata md;
   std::string ls(labels ? labels : "");
   size_t start = 0;
@@ -412,15 +426,44 @@ int ref_direct_speakers_calc(const char *layout_name, const char *labels,
   if (has_bounds & 8) p.elevationMax = boost::optional<double>(bounds[3]);
   if (has_bounds & 16) p.distanceMin = boost::optional<double>(bounds[4]);
   if (has_bounds & 32) p.distanceMax = boost::optional<double>(bounds[5]);
+  if (edge_lock & 1) p.screenEdgeLock.horizontal = std::string("left");
+  if (edge_lock & 2) p.screenEdgeLock.vertical = std::string("top");
   md.position = p;
+  if (cartesian) md.position = CartesianSpeakerPosition(az, el, dist);
   if (has_freq & 1) md.channelFrequency.lowPass = boost::optional<double>(low_pass);
   if (has_freq & 2) md.channelFrequency.highPass = boost::optional<double>(high_pass);
   if (pack_id && pack_id[0]) md.audioPackFormatID = boost::optional<std::string>(std::string(pack_id));
   std::vector<double> g(n_out);
   int nw = 0;
-  gc.calculate(md, g, [&](const Warning &) { nw++; });
+  // n_warnings: count in the low byte, bitmask of (1 << code) above it
+  gc.calculate(md, g, [&](const Warning &w) { nw = (nw + 1) | (256 << (int)w.code); });
   for (int o = 0; o < n_out; o++) gains[o] = g[o];
   if (n_warnings) *n_warnings = nw;
+  return 0;
+  REF_CATCH
+}
+
+// mapping rules / ITU pack table as text (data export for tools/gen_mapping_rules.py):
+// one rule per line "R|label|ch=gain,ch=gain|in,in|out,out", one pack per line "P|id|layout"
+int ref_mapping_rules_dump(char *buf, long cap, long *needed) {
+  REF_TRY
+  std::string s;
+  char num[64];
+  for (const MappingRule &r : rules) {
+    s += "R|" + r.speakerLabel + "|";
+    for (size_t i = 0; i < r.gains.size(); i++) {
+      snprintf(num, sizeof num, "%.17g", r.gains[i].second);
+      s += (i ? "," : "") + r.gains[i].first + "=" + num;
+    }
+    s += "|";
+    for (size_t i = 0; i < r.input_layouts.size(); i++) s += (i ? "," : "") + r.input_layouts[i];
+    s += "|";
+    for (size_t i = 0; i < r.output_layouts.size(); i++) s += (i ? "," : "") + r.output_layouts[i];
+    s += "\n";
+  }
+  for (const auto &kv : itu_packs) s += "P|" + kv.first + "|" + kv.second + "\n";
+  if (needed) *needed = (long)s.size() + 1;
+  if (buf && cap > (long)s.size()) memcpy(buf, s.c_str(), s.size() + 1);
   return 0;
   REF_CATCH
 }

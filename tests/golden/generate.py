@@ -197,33 +197,101 @@ def gen_hoa():
     np.savez_compressed(os.path.join(HERE, "hoa.npz"), **out)
 
 
-def gen_direct_speakers():
-    """GainCalculatorDirectSpeakers::calculate on 4+7+0 / 9+10+3 / 0+5+0: label and URN
-    matching, LFE, bounds, the point-source fallback and a mapping rule
-    (tests/gain_calculator_direct_speakers_tests.cpp:31-339)."""
+def direct_speakers_cases():
+    """The reference's own test cases (tests/gain_calculator_direct_speakers_tests.cpp:31-339:
+    label / URN matching, LFE by name or frequency, bounds, point-source fallback, mapping rules
+    with common-definitions pack ids, the not_implemented / adm_error throws) plus a seeded random
+    sweep over all layouts."""
     cases = [
-        ("4+7+0", ["M+000"], 0, 0, 1, None, None, None),
-        ("4+7+0", ["urn:itu:bs:2051:0:speaker:M+030"], 30, 0, 1, None, None, None),
-        ("4+7+0", ["LFE1"], 0, -30, 1, None, None, None),
-        ("4+7+0", ["foo"], 0, -30, 1, None, 120.0, None),          # LFE by lowPass frequency
-        ("4+7+0", ["foo"], 12, 5, 1, None, None, None),             # point-source fallback
-        ("4+7+0", ["foo"], 30, 0, 1, {"azMin": 25, "azMax": 35, "elMin": -5, "elMax": 5}, None, None),
-        ("4+7+0", ["foo"], 70, 28, 1, {"azMin": 40, "azMax": 100, "elMin": 20, "elMax": 40}, None, None),
-        ("9+10+3", ["U+045"], 45, 30, 1, None, None, None),
-        ("9+10+3", ["B-045"], -45, -30, 1, None, None, None),
-        ("0+5+0", ["M+110"], 110, 0, 1, None, None, None),
-        ("0+5+0", ["U+030"], 30, 30, 1, None, None, "urn:itu:bs:2051:0:pack:4+5+0"),  # mapping rule
-        ("0+5+0", ["M+090"], 90, 0, 1, None, None, "urn:itu:bs:2051:0:pack:4+9+0"),
-        ("0+2+0", ["M+000"], 0, 0, 1, None, None, "urn:itu:bs:2051:0:pack:0+5+0"),
+        dict(layout="4+7+0", labels=["M+000"]),
+        dict(layout="4+7+0", labels=["urn:itu:bs:2051:0:speaker:M+030"], az=30),
+        dict(layout="4+7+0", labels=["LFE1"], el=-30),
+        dict(layout="4+7+0", labels=["foo"], el=-30, low_pass=120.0),          # LFE by frequency
+        dict(layout="4+7+0", labels=["foo"], el=-30, low_pass=250.0),          # not an LFE frequency
+        dict(layout="4+7+0", labels=["LFE1"], el=-30, low_pass=120.0, high_pass=20.0),
+        dict(layout="4+7+0", labels=["foo"], az=12, el=5),                      # point-source fallback
+        dict(layout="4+7+0", labels=["foo"], az=30, bounds={"azMin": 25, "azMax": 35, "elMin": -5, "elMax": 5}),
+        dict(layout="4+7+0", labels=["foo"], az=70, el=28,
+             bounds={"azMin": 40, "azMax": 100, "elMin": 20, "elMax": 40}),
+        dict(layout="4+7+0", labels=["foo"], az=0, bounds={"azMin": -180, "azMax": 180}),   # ambiguous -> panned
+        dict(layout="4+7+0", labels=[], az=-110),
+        dict(layout="4+7+0", labels=[], az=180, el=90, bounds={"elMin": 80, "elMax": 90}),
+        dict(layout="9+10+3", labels=["U+045"], az=45, el=30),
+        dict(layout="9+10+3", labels=["B-045"], az=-45, el=-30),
+        dict(layout="9+10+3", labels=["LFER"], az=-45, el=-30),
+        dict(layout="9+10+3", labels=["LFE"], az=45, el=-30),
+        dict(layout="9+10+3", labels=["foo"], el=-30, low_pass=100.0, az=-50),
+        dict(layout="0+5+0", labels=["M+110"], az=110),
+        dict(layout="0+5+0", labels=["LFE2"], az=-45, el=-30),                   # no LFE2: LFE rule -> LFE1
+        dict(layout="0+2+0", labels=["LFE1"], az=45, el=-30),                    # no LFE at all: silence
+        dict(layout="0+5+0", labels=["U+030"], az=30, el=30, pack="AP_00010005"),  # 4+5+0 -> 0+5+0 rule
+        dict(layout="0+5+0", labels=["M+090"], az=90, pack="AP_00010008"),
+        dict(layout="0+5+0", labels=["urn:itu:bs:2051:1:speaker:M+135"], az=135, pack="AP_00010017"),
+        dict(layout="0+2+0", labels=["M+000"], pack="AP_00010003"),
+        dict(layout="0+2+0", labels=["M+110"], az=110, pack="AP_00010003"),
+        dict(layout="4+5+0", labels=["UH+180"], az=180, el=45, pack="AP_00010009"),
+        dict(layout="4+5+0", labels=["LFE2"], az=-45, el=-30, pack="AP_00010009"),
+        dict(layout="4+7+0", labels=["T+000"], el=90, pack="AP_00010009"),
+        dict(layout="0+5+0", labels=["U+030"], az=30, el=30, pack="AP_ffffffff"),   # unknown pack
+        dict(layout="0+5+0", labels=["U+030"], az=30, el=30, pack="urn:itu:bs:2051:0:pack:4+5+0"),
+        dict(layout="4+7+0", labels=["left"], az=30, substitutions={"left": "M+030", "LFE": "LFE2"}),
+        dict(layout="4+7+0", labels=["LFE"], el=-30, substitutions={"left": "M+030", "LFE": "LFE2"}),
+        dict(layout="4+7+0", labels=[], pack="AP_00010003"),                      # adm_error
+        dict(layout="4+7+0", labels=["foo"], cartesian=True),                     # not_implemented
+        dict(layout="4+7+0", labels=["foo"], az=5, screen_edge_lock=1),           # not_implemented
+        dict(layout="4+7+0", labels=["M+000"], screen_edge_lock=2),               # label match wins first
     ]
-    out = {"n": np.array(len(cases))}
+    rng = np.random.default_rng(17)
+    names = ref.layout_names()
+    pool = sorted({n for L in names for n in ref.layout_info(L)["names"]}) + [
+        "LFE", "LFEL", "LFER", "foo", "urn:itu:bs:2051:0:speaker:M+030", "urn:itu:bs:2051:12:speaker:U-110",
+        "urn:itu:bs:2051::speaker:M+030", "urn:itu:bs:2051:0:speaker:"]
+    packs = [None, None, "AP_00010001", "AP_00010002", "AP_00010003", "AP_00010004", "AP_00010005",
+             "AP_00010007", "AP_00010008", "AP_00010009", "AP_0001000c", "AP_0001000f", "AP_00010010",
+             "AP_00010017"]
+    for _ in range(400):
+        c = dict(layout=names[rng.integers(len(names))],
+                 labels=[pool[rng.integers(len(pool))] for _ in range(rng.integers(0, 3))],
+                 az=float(rng.choice([0, 30, -30, 110, -110, 45, 90, 180, -180, rng.uniform(-180, 180)])),
+                 el=float(rng.choice([0, 0, 30, -30, 90, rng.uniform(-90, 90)])),
+                 dist=float(rng.choice([1.0, 1.0, 0.5])))
+        if rng.uniform() < 0.4:
+            b = {}
+            if rng.uniform() < 0.7:
+                b["azMin"], b["azMax"] = c["az"] - float(rng.uniform(0, 40)), c["az"] + float(rng.uniform(0, 40))
+            if rng.uniform() < 0.7:
+                b["elMin"], b["elMax"] = c["el"] - float(rng.uniform(0, 20)), c["el"] + float(rng.uniform(0, 20))
+            if rng.uniform() < 0.3:
+                b["distMin"], b["distMax"] = 0.0, 2.0
+            c["bounds"] = b
+        if rng.uniform() < 0.2:
+            c["low_pass"] = float(rng.choice([80.0, 120.0, 200.0, 500.0]))
+        if rng.uniform() < 0.05:
+            c["high_pass"] = 40.0
+        pk = packs[rng.integers(len(packs))]
+        if pk and c["labels"]:
+            c["pack"] = pk
+        cases.append(c)
+    return cases
+
+
+def gen_direct_speakers():
     import json
-    for i, (layout, labels, az, el, d, bounds, low_pass, pack) in enumerate(cases):
-        g, nw = ref.direct_speakers_calc(layout, labels, az, el, d, bounds, low_pass, None, pack)
-        out[f"{i}/case"] = np.array(json.dumps(dict(layout=layout, labels=labels, az=az, el=el, dist=d,
-                                                    bounds=bounds, low_pass=low_pass, pack=pack)))
+    cases = direct_speakers_cases()
+    out = {"n": np.array(len(cases))}
+    for i, c in enumerate(cases):
+        try:
+            g, codes = ref.direct_speakers_calc(c["layout"], c.get("labels", []), c.get("az", 0.0), c.get("el", 0.0),
+                                                c.get("dist", 1.0), c.get("bounds"), c.get("low_pass"),
+                                                c.get("high_pass"), c.get("pack"), c.get("substitutions"),
+                                                c.get("cartesian", False), c.get("screen_edge_lock", 0), codes=True)
+            err = 0
+        except ref.RefError as e:
+            g, codes, err = np.zeros(0), [], e.code
+        out[f"{i}/case"] = np.array(json.dumps(c))
         out[f"{i}/gains"] = g
-        out[f"{i}/n_warnings"] = np.array(nw)
+        out[f"{i}/warnings"] = np.array(codes, dtype=np.int32)
+        out[f"{i}/error"] = np.array(err)
     np.savez_compressed(os.path.join(HERE, "direct_speakers.npz"), **out)
 
 

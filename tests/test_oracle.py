@@ -226,6 +226,14 @@ def test_golden_fixtures_are_current(ref):
     g = golden("direct_speakers")
     for i in range(int(g["n"])):
         c = json.loads(str(g[f"{i}/case"]))
-        gains, _ = ref.direct_speakers_calc(c["layout"], c["labels"], c["az"], c["el"], c["dist"],
-                                            c["bounds"], c["low_pass"], None, c["pack"])
-        assert np.abs(gains - g[f"{i}/gains"]).max() < 1e-15
+        if int(g[f"{i}/error"]):
+            with pytest.raises(ref.RefError):
+                ref.direct_speakers_calc(c["layout"], c.get("labels", []), pack_id=c.get("pack"),
+                                         cartesian=c.get("cartesian", False),
+                                         screen_edge_lock=c.get("screen_edge_lock", 0))
+            continue
+        gains, codes = ref.direct_speakers_calc(
+            c["layout"], c.get("labels", []), c.get("az", 0.0), c.get("el", 0.0), c.get("dist", 1.0),
+            c.get("bounds"), c.get("low_pass"), c.get("high_pass"), c.get("pack"), c.get("substitutions"),
+            screen_edge_lock=c.get("screen_edge_lock", 0), codes=True)
+        assert np.abs(gains - g[f"{i}/gains"]).max() < 1e-15 and codes == list(g[f"{i}/warnings"])
