@@ -198,6 +198,23 @@ int64_t earb200_convolver_launch_count(const earb200_convolver *conv);
 int earb200_convolver_set_profiling(earb200_convolver *conv, int enable);
 int earb200_convolver_kernel_time(earb200_convolver *conv, double *ms, int64_t *launches);
 
+/* -------------------------------------------------------------- delay line
+ * replaces ear::dsp::DelayBuffer (include/ear/dsp/delay_buffer.hpp:12-29,
+ * src/dsp/delay_buffer_impl.cpp:12-47): n_channels planar channels delayed by `delay`
+ * samples; the delay memory persists on the device between calls. */
+typedef struct earb200_delay earb200_delay;
+
+int earb200_delay_create(int n_channels, int64_t delay, int device, earb200_delay **out);
+void earb200_delay_destroy(earb200_delay *d);
+int64_t earb200_delay_get_delay(const earb200_delay *d);
+/* channel c at in + c*in_stride / out + c*out_stride; in may be NULL (silence) */
+int earb200_delay_process_host(earb200_delay *d, int64_t nsamples, const float *in,
+                               int64_t in_stride, float *out, int64_t out_stride);
+int earb200_delay_process_device(earb200_delay *d, int64_t nsamples, const float *d_in,
+                                 int64_t in_stride, float *d_out, int64_t out_stride,
+                                 void *stream);
+int64_t earb200_delay_launch_count(const earb200_delay *d);
+
 /* ------------------------------------------------ HOA decoder design (K5)
  * replaces ear::GainCalculatorHOA (include/ear/gain_calculators.hpp:67-82,
  * src/hoa/gain_calculator_hoa.cpp:8-72, src/hoa/hoa.hpp:88-143). */

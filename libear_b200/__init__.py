@@ -28,7 +28,8 @@ _lib.earb200_version.restype = C.c_char_p
 _lib.earb200_layout_name_at.restype = C.c_char_p
 _lib.earb200_layout_channel_name.restype = C.c_char_p
 for _f in ("earb200_objects_launch_count", "earb200_interp_launch_count",
-           "earb200_convolver_launch_count", "earb200_direct_speakers_launch_count"):
+           "earb200_convolver_launch_count", "earb200_direct_speakers_launch_count",
+           "earb200_delay_launch_count", "earb200_delay_get_delay"):
     getattr(_lib, _f).restype = C.c_int64
 
 
@@ -334,6 +335,39 @@ class BlockConvolver:
         _chk(_lib.earb200_convolver_process_device(self.h, C.c_int64(n_blocks), _ptr(d_in),
                                                    C.c_int64(in_stride), _ptr(d_out),
                                                    C.c_int64(out_stride), C.c_void_p(int(stream))))
+
+
+class DelayBuffer:
+    """ear::dsp::DelayBuffer (include/ear/dsp/delay_buffer.hpp:12-29); delay memory on the device."""
+
+    def __init__(self, n_channels, delay, device=0):
+        self.n_channels, self.delay = n_channels, delay
+        self.h = C.c_void_p()
+        _chk(_lib.earb200_delay_create(n_channels, C.c_int64(delay), device, C.byref(self.h)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            _lib.earb200_delay_destroy(self.h)
+            self.h = None
+
+    @property
+    def launch_count(self):
+        return _lib.earb200_delay_launch_count(self.h)
+
+    def get_delay(self):
+        return _lib.earb200_delay_get_delay(self.h)
+
+    def process(self, x):
+        """x: float32 [n_channels][nsamples] host array -> delayed copy."""
+        x = np.ascontiguousarray(x, dtype=np.float32).reshape(self.n_channels, -1)
+        out = np.zeros_like(x)
+        _chk(_lib.earb200_delay_process_host(self.h, C.c_int64(x.shape[1]), _ptr(x), C.c_int64(x.shape[1]),
+                                             _ptr(out), C.c_int64(x.shape[1])))
+        return out
+
+    def process_device(self, nsamples, d_in, in_stride, d_out, out_stride, stream=0):
+        _chk(_lib.earb200_delay_process_device(self.h, C.c_int64(nsamples), _ptr(d_in), C.c_int64(in_stride),
+                                               _ptr(d_out), C.c_int64(out_stride), C.c_void_p(int(stream))))
 
 
 WARN_HOA_SCREENREF, WARN_HOA_NFCREFDIST = 4, 5

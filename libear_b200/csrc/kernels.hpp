@@ -120,6 +120,14 @@ namespace earb {
   size_t conv_smem_bytes(int B, int nb);
   void launch_convolver(const ConvLaunch &L, cudaStream_t stream);
 
+  // ---- delay line / bus mix of the Objects signal flow (dsp_kernels.cu)
+  // [mem; in] -> [out; mem_new] per channel (mem, mem_new: [C][delay], distinct buffers);
+  // in may be null (silence)
+  void launch_delay(int C, long n, long delay, const float *in, long in_stride, float *out,
+                    long out_stride, const float *mem, float *mem_new, int n_sms, cudaStream_t stream);
+  void launch_add(int C, long n, const float *a, long a_stride, const float *b, long b_stride, float *out,
+                  long out_stride, int n_sms, cudaStream_t stream);
+
   // ---- K5: HOA decoder design (hoa_kernels.cu)
   int hoa_power_blocks(int P);
   // Y [C][P], D [S][C], partial [hoa_power_blocks(P)]
