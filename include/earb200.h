@@ -63,6 +63,9 @@ int earb200_layout_channel_is_lfe(const earb200_layout *layout, int i);
 /* pos[3] = azimuth, elevation, distance (real position); nominal likewise */
 int earb200_layout_channel_position(const earb200_layout *layout, int i, double *pos,
                                     double *nominal);
+/* allowed azimuth range (anticlockwise from [0] to [1]) and elevation range, degrees */
+int earb200_layout_channel_ranges(const earb200_layout *layout, int i, double *az_range,
+                                  double *el_range);
 
 /* ------------------------------------------------- point-source panner (K1)
  * replaces ear::configurePolarPanner(layout.withoutLfe())->handle(position)
@@ -197,6 +200,26 @@ int earb200_convolver_process_device(earb200_convolver *conv, int64_t n_blocks,
 int64_t earb200_convolver_launch_count(const earb200_convolver *conv);
 int earb200_convolver_set_profiling(earb200_convolver *conv, int enable);
 int earb200_convolver_kernel_time(earb200_convolver *conv, double *ms, int64_t *launches);
+
+/* ------------------------------------------------------------ FFT plug-in (a9)
+ * replaces ear::FFTImpl<float>::plan(n_fft) / FFTPlan::transform_forward / transform_reverse
+ * (include/ear/fft.hpp:27-62; KISS implementation src/fft_kiss.cpp:52-99) as a BATCHED
+ * transform: `batch` independent n_fft-point real transforms per call.  forward: [batch][n_fft]
+ * reals -> [batch][n_fft/2+1] complex (interleaved re, im; no packing); reverse: the inverse,
+ * unnormalised (forward then reverse scales by n_fft), imaginary parts of bins 0 and n_fft/2
+ * ignored.  The block convolver runs the same butterflies inside its own kernel. */
+typedef struct earb200_fft earb200_fft;
+
+int earb200_fft_create(int64_t n_fft, int device, earb200_fft **out); /* power of two, 32..8192 */
+void earb200_fft_destroy(earb200_fft *fft);
+int64_t earb200_fft_size(const earb200_fft *fft);
+int earb200_fft_forward_host(earb200_fft *fft, int64_t batch, const float *in, float *out);
+int earb200_fft_reverse_host(earb200_fft *fft, int64_t batch, const float *in, float *out);
+int earb200_fft_forward_device(earb200_fft *fft, int64_t batch, const float *d_in, float *d_out,
+                               void *stream);
+int earb200_fft_reverse_device(earb200_fft *fft, int64_t batch, const float *d_in, float *d_out,
+                               void *stream);
+int64_t earb200_fft_launch_count(const earb200_fft *fft);
 
 /* -------------------------------------------------------------- delay line
  * replaces ear::dsp::DelayBuffer (include/ear/dsp/delay_buffer.hpp:12-29,

@@ -29,7 +29,8 @@ _lib.earb200_layout_name_at.restype = C.c_char_p
 _lib.earb200_layout_channel_name.restype = C.c_char_p
 for _f in ("earb200_objects_launch_count", "earb200_interp_launch_count",
            "earb200_convolver_launch_count", "earb200_direct_speakers_launch_count",
-           "earb200_delay_launch_count", "earb200_delay_get_delay"):
+           "earb200_delay_launch_count", "earb200_delay_get_delay", "earb200_fft_launch_count",
+           "earb200_fft_size"):
     getattr(_lib, _f).restype = C.c_int64
 
 
@@ -335,6 +336,38 @@ class BlockConvolver:
         _chk(_lib.earb200_convolver_process_device(self.h, C.c_int64(n_blocks), _ptr(d_in),
                                                    C.c_int64(in_stride), _ptr(d_out),
                                                    C.c_int64(out_stride), C.c_void_p(int(stream))))
+
+
+class FFT:
+    """Batched r2c / c2r transforms behind ear::FFTImpl / FFTPlan (include/ear/fft.hpp:27-62)."""
+
+    def __init__(self, n_fft, device=0):
+        self.n_fft = n_fft
+        self.h = C.c_void_p()
+        _chk(_lib.earb200_fft_create(C.c_int64(n_fft), device, C.byref(self.h)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            _lib.earb200_fft_destroy(self.h)
+            self.h = None
+
+    @property
+    def launch_count(self):
+        return _lib.earb200_fft_launch_count(self.h)
+
+    def forward(self, x):
+        """x float32 [batch][n_fft] -> complex64 [batch][n_fft/2+1]."""
+        x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, self.n_fft)
+        out = np.zeros((len(x), self.n_fft // 2 + 1), dtype=np.complex64)
+        _chk(_lib.earb200_fft_forward_host(self.h, C.c_int64(len(x)), _ptr(x), _ptr(out)))
+        return out
+
+    def reverse(self, X):
+        """X complex64 [batch][n_fft/2+1] -> float32 [batch][n_fft], unnormalised."""
+        X = np.ascontiguousarray(X, dtype=np.complex64).reshape(-1, self.n_fft // 2 + 1)
+        out = np.zeros((len(X), self.n_fft), dtype=np.float32)
+        _chk(_lib.earb200_fft_reverse_host(self.h, C.c_int64(len(X)), _ptr(X), _ptr(out)))
+        return out
 
 
 class DelayBuffer:

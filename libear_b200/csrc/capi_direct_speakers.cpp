@@ -148,9 +148,9 @@ namespace {
       throw Error(INVALID_ARGUMENT, "speaker_labels is null");
     if (md.audio_pack_format_id && md.n_speaker_labels == 0)
       throw Error(ADM_ERROR,
-                  "common definitions audioPackFormatID specified without any speakerLabels as specified in the "
+                  "ADM error: common definitions audioPackFormatID specified without any speakerLabels as specified in the "
                   "common definitions file");
-    if (md.cartesian_position) throw Error(NOT_IMPLEMENTED, "Cartesian position");
+    if (md.cartesian_position) throw Error(NOT_IMPLEMENTED, "not implemented: Cartesian position");
     const double tol = 1e-5;
     const bool isLfe = isLfeChannel(h, md, warnings);
     for (int c = 0; c < h.n_out; c++) gains[c] = 0.0;
@@ -180,7 +180,7 @@ namespace {
       }
     }
     // ScreenEdgeLockHandler (ref src/common/screen_edge_lock.hpp:14-20)
-    if (md.screen_edge_lock) throw Error(NOT_IMPLEMENTED, "screenEdgeLock");
+    if (md.screen_edge_lock) throw Error(NOT_IMPLEMENTED, "not implemented: screenEdgeLock");
     const int idx = channelWithinBounds(h, md, isLfe, tol);  // ref :295-302
     if (idx >= 0) {
       gains[idx] = 1.0;

@@ -1,6 +1,8 @@
 // C ABI: multi-channel delay line (ear::dsp::DelayBuffer, ref include/ear/dsp/delay_buffer.hpp:12-29,
 // src/dsp/delay_buffer_impl.cpp:12-47).  The delay memory stays on the device between calls.
+#include <cmath>
 #include <memory>
+#include <vector>
 
 #include "capi_common.hpp"
 #include "kernels.hpp"
@@ -14,6 +16,15 @@ struct earb200_delay {
   DeviceBuffer<float> d_mem[2];  // ping-pong: the kernel reads one and writes the other
   int cur = 0;
   DeviceBuffer<float> d_in, d_out;
+  int64_t launches = 0;
+};
+
+// FFT plug-in: batched 2B-point r2c / c2r transforms (ear::FFTImpl / FFTPlan,
+// ref include/ear/fft.hpp:27-62; unpacked n/2+1 bins, unnormalised inverse like src/fft_kiss.cpp:61-88)
+struct earb200_fft {
+  int device = 0, n_sms = 0;
+  int B = 0;  // n_fft / 2
+  DeviceBuffer<float> d_tw2, d_in, d_out;
   int64_t launches = 0;
 };
 
@@ -93,6 +104,95 @@ int earb200_delay_process_host(earb200_delay *d, int64_t nsamples, const float *
     delay_process_device(*d, nsamples, di, nsamples, dout, nsamples, 0);
     EARB_CUDA(cudaMemcpy2D(out, sizeof(float) * out_stride, dout, sizeof(float) * n, sizeof(float) * n, C,
                            cudaMemcpyDeviceToHost));
+  });
+}
+
+int earb200_fft_create(int64_t n_fft, int device, earb200_fft **out) {
+  return guarded([&] {
+    if (!out) throw Error(INVALID_ARGUMENT, "null argument");
+    const int64_t B = n_fft / 2;
+    if (n_fft < 32 || n_fft > 8192 || (n_fft & (n_fft - 1)) != 0)
+      throw Error(INVALID_ARGUMENT, "n_fft must be a power of two in [32, 8192]");
+    use_device(device);
+    auto h = std::make_unique<earb200_fft>();
+    h->device = device;
+    h->B = (int)B;
+    cudaDeviceProp prop;
+    EARB_CUDA(cudaGetDeviceProperties(&prop, device));
+    h->n_sms = prop.multiProcessorCount;
+    std::vector<float> tw(4 * (size_t)B);
+    const double pi = 3.141592653589793238462643383279502884;
+    for (int64_t k = 0; k < 2 * B; k++) {
+      const double ang = -2.0 * pi * (double)k / (double)(2 * B);
+      tw[2 * k] = (float)std::cos(ang);
+      tw[2 * k + 1] = (float)std::sin(ang);
+    }
+    EARB_CUDA(cudaMemcpy(h->d_tw2.reserve(tw.size()), tw.data(), sizeof(float) * tw.size(), cudaMemcpyHostToDevice));
+    *out = h.release();
+  });
+}
+
+void earb200_fft_destroy(earb200_fft *fft) { delete fft; }
+
+int64_t earb200_fft_size(const earb200_fft *fft) { return fft ? 2 * (int64_t)fft->B : 0; }
+
+int64_t earb200_fft_launch_count(const earb200_fft *fft) { return fft ? fft->launches : 0; }
+
+int earb200_fft_forward_device(earb200_fft *fft, int64_t batch, const float *d_in, float *d_out, void *stream) {
+  return guarded([&] {
+    if (!fft || (batch > 0 && (!d_in || !d_out))) throw Error(INVALID_ARGUMENT, "null argument");
+    if (batch < 0) throw Error(INVALID_ARGUMENT, "negative batch size");
+    if (batch == 0) return;
+    use_device(fft->device);
+    launch_fft_r2c(fft->B, batch, d_in, d_out, fft->d_tw2.ptr, fft->n_sms, (cudaStream_t)stream);
+    EARB_CUDA(cudaGetLastError());
+    fft->launches++;
+  });
+}
+
+int earb200_fft_reverse_device(earb200_fft *fft, int64_t batch, const float *d_in, float *d_out, void *stream) {
+  return guarded([&] {
+    if (!fft || (batch > 0 && (!d_in || !d_out))) throw Error(INVALID_ARGUMENT, "null argument");
+    if (batch < 0) throw Error(INVALID_ARGUMENT, "negative batch size");
+    if (batch == 0) return;
+    use_device(fft->device);
+    launch_fft_c2r(fft->B, batch, d_in, d_out, fft->d_tw2.ptr, fft->n_sms, (cudaStream_t)stream);
+    EARB_CUDA(cudaGetLastError());
+    fft->launches++;
+  });
+}
+
+int earb200_fft_forward_host(earb200_fft *fft, int64_t batch, const float *in, float *out) {
+  return guarded([&] {
+    if (!fft || (batch > 0 && (!in || !out))) throw Error(INVALID_ARGUMENT, "null argument");
+    if (batch <= 0) {
+      if (batch < 0) throw Error(INVALID_ARGUMENT, "negative batch size");
+      return;
+    }
+    use_device(fft->device);
+    const size_t n_in = (size_t)batch * 2 * fft->B, n_out = (size_t)batch * (fft->B + 1) * 2;
+    EARB_CUDA(cudaMemcpy(fft->d_in.reserve(n_in), in, sizeof(float) * n_in, cudaMemcpyHostToDevice));
+    launch_fft_r2c(fft->B, batch, fft->d_in.ptr, fft->d_out.reserve(n_out), fft->d_tw2.ptr, fft->n_sms, 0);
+    EARB_CUDA(cudaGetLastError());
+    fft->launches++;
+    EARB_CUDA(cudaMemcpy(out, fft->d_out.ptr, sizeof(float) * n_out, cudaMemcpyDeviceToHost));
+  });
+}
+
+int earb200_fft_reverse_host(earb200_fft *fft, int64_t batch, const float *in, float *out) {
+  return guarded([&] {
+    if (!fft || (batch > 0 && (!in || !out))) throw Error(INVALID_ARGUMENT, "null argument");
+    if (batch <= 0) {
+      if (batch < 0) throw Error(INVALID_ARGUMENT, "negative batch size");
+      return;
+    }
+    use_device(fft->device);
+    const size_t n_in = (size_t)batch * (fft->B + 1) * 2, n_out = (size_t)batch * 2 * fft->B;
+    EARB_CUDA(cudaMemcpy(fft->d_in.reserve(n_in), in, sizeof(float) * n_in, cudaMemcpyHostToDevice));
+    launch_fft_c2r(fft->B, batch, fft->d_in.ptr, fft->d_out.reserve(n_out), fft->d_tw2.ptr, fft->n_sms, 0);
+    EARB_CUDA(cudaGetLastError());
+    fft->launches++;
+    EARB_CUDA(cudaMemcpy(out, fft->d_out.ptr, sizeof(float) * n_out, cudaMemcpyDeviceToHost));
   });
 }
 

@@ -299,6 +299,22 @@ int earb200_layout_channel_position(const earb200_layout *layout, int i, double 
     }
   });
 }
+int earb200_layout_channel_ranges(const earb200_layout *layout, int i, double *az_range,
+                                  double *el_range) {
+  return guarded([&] {
+    if (!layout || i < 0 || i >= (int)layout->layout.channels.size())
+      throw Error(INVALID_ARGUMENT, "channel index out of range");
+    const HostChannel &c = layout->layout.channels[i];
+    if (az_range) {
+      az_range[0] = c.az_lo;
+      az_range[1] = c.az_hi;
+    }
+    if (el_range) {
+      el_range[0] = c.el_lo;
+      el_range[1] = c.el_hi;
+    }
+  });
+}
 
 // ------------------------------------------------------------------ panner
 int earb200_panner_create(const earb200_layout *layout, int device, earb200_panner **out) {

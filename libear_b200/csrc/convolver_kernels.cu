@@ -97,12 +97,14 @@ namespace earb {
     // spectrum X[0..B] (B+1 bins) of the zero-padded 2B-point real signal whose first B
     // samples are `x` (scaled per sample by fade(n)); za/zb: B-complex scratch.
     // FADE: 0 none, 1 down (1 - n/B), 2 up (n/B)   (ref block_convolver_impl.cpp:127-141)
+    // n_real: how many of the 2B real samples are present (B for the convolver's zero-padded
+    // blocks, 2B for the plug-in transform)
     __device__ void r2c_block(const float *__restrict__ x, int fade, float2 *za, float2 *zb, int B,
-                              const float2 *__restrict__ tw2, float2 *X) {
+                              const float2 *__restrict__ tw2, float2 *X, int n_real) {
       const float i_scale = 1.0f / (float)B;
       for (int n = threadIdx.x; n < B; n += kConvThreads) {
         float2 v = make_float2(0.0f, 0.0f);
-        if (n < B / 2) {
+        if (2 * n < n_real) {
           float e = x ? x[2 * n] : 0.0f, o = x ? x[2 * n + 1] : 0.0f;
           if (fade) {
             float ae = (float)(2 * n) * i_scale, ao = (float)(2 * n + 1) * i_scale;
@@ -183,10 +185,10 @@ namespace earb {
         float2 *Xold = ring + (size_t)(slot * 2) * (B + 2);
         float2 *Xnew = Xold + (B + 2);
         if (is_faded) {
-          r2c_block(x, 1, za, zb, B, a.tw2, Xold);
-          r2c_block(x, 2, za, zb, B, a.tw2, Xnew);
+          r2c_block(x, 1, za, zb, B, a.tw2, Xold, B);
+          r2c_block(x, 2, za, zb, B, a.tw2, Xnew, B);
         } else {
-          r2c_block(x, 0, za, zb, B, a.tw2, Xnew);
+          r2c_block(x, 0, za, zb, B, a.tw2, Xnew, B);
         }
         if (threadIdx.x == 0) ring_faded[slot] = is_faded;
         __syncthreads();
@@ -261,6 +263,51 @@ namespace earb {
       }
     }
 
+    // ---- the FFT plug-in (ref include/ear/fft.hpp:27-62, src/fft_kiss.cpp:61-88) as a batched
+    // transform: one CTA per 2B-point real transform, same butterflies as the convolver
+    __global__ void __launch_bounds__(kConvThreads)
+        fft_r2c_kernel(int B, long batch, const float *__restrict__ in, float2 *__restrict__ out,
+                       const float2 *__restrict__ tw2) {
+      extern __shared__ float2 smem2[];
+      float2 *za = smem2, *zb = za + B, *X = zb + B;
+      for (long t = blockIdx.x; t < batch; t += gridDim.x) {
+        r2c_block(in + (size_t)t * 2 * B, 0, za, zb, B, tw2, X, 2 * B);
+        for (int k = threadIdx.x; k <= B; k += kConvThreads) out[(size_t)t * (B + 1) + k] = X[k];
+        __syncthreads();
+      }
+    }
+
+    // unnormalised inverse: B+1 bins -> 2B reals (the imaginary parts of bins 0 and B are ignored,
+    // as a c2r transform does)
+    __global__ void __launch_bounds__(kConvThreads)
+        fft_c2r_kernel(int B, long batch, const float2 *__restrict__ in, float *__restrict__ out,
+                       const float2 *__restrict__ tw2) {
+      extern __shared__ float2 smem2[];
+      float2 *za = smem2, *zb = za + B, *Y = zb + B;
+      for (long t = blockIdx.x; t < batch; t += gridDim.x) {
+        for (int k = threadIdx.x; k <= B; k += kConvThreads) {
+          float2 v = in[(size_t)t * (B + 1) + k];
+          if (k == 0 || k == B) v.y = 0.0f;
+          Y[k] = v;
+        }
+        __syncthreads();
+        for (int k = threadIdx.x; k < B; k += kConvThreads) {
+          const float2 yk = Y[k];
+          const float2 yc = conjf2(Y[B - k]);
+          const float2 E = cadd(yk, yc);
+          float2 w = __ldg(tw2 + k);
+          w.y = -w.y;
+          const float2 O = cmul(csub(yk, yc), w);
+          za[k] = make_float2(E.x - O.y, E.y + O.x);
+        }
+        __syncthreads();
+        const float2 *z = fft_stockham<true>(za, zb, B, tw2);
+        float2 *o = reinterpret_cast<float2 *>(out + (size_t)t * 2 * B);
+        for (int n = threadIdx.x; n < B; n += kConvThreads) o[n] = z[n];
+        __syncthreads();
+      }
+    }
+
     // new history = the last nb input blocks seen (old history shifted when K < nb)
     __global__ void conv_history_kernel(int B, int nb, long K, const float *in, long in_stride,
                                         const float *hist_old, float *hist_new) {
@@ -282,6 +329,28 @@ namespace earb {
 
   size_t conv_smem_bytes(int B, int nb) {
     return sizeof(float2) * ((size_t)2 * B + (B + 2) + (size_t)nb * 2 * (B + 2)) + sizeof(float) * B;
+  }
+
+  void launch_fft_r2c(int B, long batch, const float *in, float *out, const float *tw2, int n_sms,
+                      cudaStream_t stream) {
+    if (batch <= 0) return;
+    const size_t smem = sizeof(float2) * ((size_t)3 * B + 2);
+    if (smem > 48 * 1024)
+      cudaFuncSetAttribute(fft_r2c_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const unsigned grid = (unsigned)std::min<long>(batch, (long)n_sms * 8);
+    fft_r2c_kernel<<<grid, kConvThreads, smem, stream>>>(B, batch, in, reinterpret_cast<float2 *>(out),
+                                                        reinterpret_cast<const float2 *>(tw2));
+  }
+
+  void launch_fft_c2r(int B, long batch, const float *in, float *out, const float *tw2, int n_sms,
+                      cudaStream_t stream) {
+    if (batch <= 0) return;
+    const size_t smem = sizeof(float2) * ((size_t)3 * B + 2);
+    if (smem > 48 * 1024)
+      cudaFuncSetAttribute(fft_c2r_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const unsigned grid = (unsigned)std::min<long>(batch, (long)n_sms * 8);
+    fft_c2r_kernel<<<grid, kConvThreads, smem, stream>>>(B, batch, reinterpret_cast<const float2 *>(in), out,
+                                                        reinterpret_cast<const float2 *>(tw2));
   }
 
   void launch_convolver(const ConvLaunch &L, cudaStream_t stream) {

@@ -120,6 +120,13 @@ namespace earb {
   size_t conv_smem_bytes(int B, int nb);
   void launch_convolver(const ConvLaunch &L, cudaStream_t stream);
 
+  // batched 2B-point real FFTs (the FFT plug-in seam): in [batch][2B] -> out [batch][B+1] complex
+  // and back (unnormalised); tw2 = exp(-2 pi i k / 2B), k in [0, 2B)
+  void launch_fft_r2c(int B, long batch, const float *in, float *out, const float *tw2, int n_sms,
+                      cudaStream_t stream);
+  void launch_fft_c2r(int B, long batch, const float *in, float *out, const float *tw2, int n_sms,
+                      cudaStream_t stream);
+
   // ---- delay line / bus mix of the Objects signal flow (dsp_kernels.cu)
   // [mem; in] -> [out; mem_new] per channel (mem, mem_new: [C][delay], distinct buffers);
   // in may be null (silence)
