@@ -5,6 +5,8 @@
 #include <algorithm>
 #include <cmath>
 #include <complex>
+#include <cstdlib>
+#include <string>
 #include <memory>
 #include <vector>
 
@@ -57,7 +59,8 @@ struct earb200_convolver {
   std::vector<int> filter_blocks;    // partitions per filter
   std::vector<float> filt_host;      // [n_filters][nb][B+1][2]
   bool filt_dirty = false;
-  DeviceBuffer<float> d_filt, d_tw2;
+  DeviceBuffer<float> d_filt, d_tw2, d_tw_fast;
+  bool use_fast = false;  // B = 512, one partition (EARB200_CONV_PATH=generic turns it off)
   DeviceBuffer<float> d_hist[2], d_tail[2];
   int cur = 0;  // which of the ping-pong state buffers is current
   DeviceBuffer<short> d_ftab;
@@ -163,7 +166,12 @@ namespace {
     L.faded = h.d_faded.ptr;
     L.tw2 = h.d_tw2.ptr;
     h.timer.start(stream);
-    launch_convolver(L, stream);
+    if (h.use_fast && Kg == 0 && d_in) {
+      launch_convolver_fast(L, h.d_uniform.ptr, h.d_tw_fast.ptr, h.n_sms, stream);
+      launch_conv_history(L, stream);
+    } else {
+      launch_convolver(L, stream);
+    }
     h.timer.stop(stream);
     EARB_CUDA(cudaGetLastError());
     h.cur = 1 - h.cur;
@@ -211,6 +219,14 @@ int earb200_convolver_create(int64_t block_size, int n_channels, int64_t num_blo
       EARB_CUDA(cudaMemset(h->d_hist[i].reserve((size_t)n_channels * h->nb * B), 0,
                            sizeof(float) * n_channels * h->nb * B));
       EARB_CUDA(cudaMemset(h->d_tail[i].reserve((size_t)n_channels * B), 0, sizeof(float) * n_channels * B));
+    }
+    const char *path = std::getenv("EARB200_CONV_PATH");
+    h->use_fast = conv_fast_supported(h->B, h->nb) && !(path && std::string(path) == "generic");
+    if (h->use_fast) {
+      std::vector<float> twf(conv_fast_tw_floats());
+      conv_fast_build_tw(twf.data());
+      EARB_CUDA(cudaMemcpy(h->d_tw_fast.reserve(twf.size()), twf.data(), sizeof(float) * twf.size(),
+                           cudaMemcpyHostToDevice));
     }
     h->d_filt.reserve(2);
     *out = h.release();

@@ -1,0 +1,291 @@
+// K4 fast path: single-partition (num_blocks == 1) convolver bank with B = 512, no filter change
+// in flight -- the decorrelator case of the Objects signal flow (BASELINE config 4).
+//
+// Same arithmetic as BlockConvolver::process (ref src/dsp/block_convolver_impl.cpp:143-237):
+// zero-pad to 2B, transform, multiply by the filter spectrum, transform back, overlap-add the
+// previous tail, scale by 1/(2B).  The differences are in how the transforms are carried out:
+//
+//  * two consecutive blocks of a channel ride one 1024-point COMPLEX transform as real and
+//    imaginary part.  The filter is real, so conv(h, x0 + i x1) = conv(h, x0) + i conv(h, x1):
+//    no even/odd split and no Hermitian unpacking is needed, the filter spectrum is simply
+//    applied to all 1024 bins.
+//  * one warp owns one pair: lane L holds elements L + 32 r (r = 0..31) in registers.  A 1024-point
+//    transform is two register-resident 32-point transforms per lane around ONE transposition
+//    through shared memory (1024 = 32 x 32); forward uses decimation in frequency (natural in,
+//    bit-reversed out), the inverse decimation in time (bit-reversed in, natural out), so no
+//    reordering pass exists.  After the inverse, y[n] and y[n + 512] sit in the same lane, so the
+//    overlap-add and the tail carried to the next pair never leave the registers.
+//  * a warp walks a run of consecutive pairs of its channel; the tail a run needs from before
+//    its first pair is recomputed from one halo block.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+
+#include "kernels.hpp"
+
+namespace earb {
+  namespace {
+    constexpr int kFastB = 512;
+    constexpr int kWarps = 8;
+    constexpr int kRow = 33;  // padded row of the 32 x 32 transposition tile (float2 units)
+
+    __host__ __device__ constexpr int br5(int x) {
+      return ((x & 1) << 4) | ((x & 2) << 2) | (x & 4) | ((x & 8) >> 2) | ((x & 16) >> 4);
+    }
+
+    // cos / sin of 2 pi k / 32; k is a compile-time constant after unrolling, so the switch folds
+    __device__ __forceinline__ float cos32(int k) {
+      switch (k & 31) {
+        case 0: return 1.0f;
+        case 1: case 31: return 0.98078528040323043f;
+        case 2: case 30: return 0.92387953251128674f;
+        case 3: case 29: return 0.83146961230254524f;
+        case 4: case 28: return 0.70710678118654752f;
+        case 5: case 27: return 0.55557023301960222f;
+        case 6: case 26: return 0.38268343236508977f;
+        case 7: case 25: return 0.19509032201612827f;
+        case 8: case 24: return 0.0f;
+        case 9: case 23: return -0.19509032201612827f;
+        case 10: case 22: return -0.38268343236508977f;
+        case 11: case 21: return -0.55557023301960222f;
+        case 12: case 20: return -0.70710678118654752f;
+        case 13: case 19: return -0.83146961230254524f;
+        case 14: case 18: return -0.92387953251128674f;
+        case 15: case 17: return -0.98078528040323043f;
+        default: return -1.0f;
+      }
+    }
+    __device__ __forceinline__ float sin32(int k) { return cos32(k - 8); }
+
+    // a * exp(-+ 2 pi i k / 32): forward uses the negative exponent
+    template <bool INV>
+    __device__ __forceinline__ float2 mul_w32(float2 a, int k) {
+      k &= 31;
+      if (k == 0) return a;
+      if (k == 8) return INV ? make_float2(-a.y, a.x) : make_float2(a.y, -a.x);
+      if (k == 16) return make_float2(-a.x, -a.y);
+      if (k == 24) return INV ? make_float2(a.y, -a.x) : make_float2(-a.y, a.x);
+      const float c = cos32(k), s = INV ? sin32(k) : -sin32(k);  // w = c + i s
+      if (k == 4 || k == 12 || k == 20 || k == 28) {
+        // |c| == |s|: two multiplies
+        const float m = 0.70710678118654752f;
+        const float sc = c > 0.0f ? 1.0f : -1.0f, ss = s > 0.0f ? 1.0f : -1.0f;
+        return make_float2((sc * a.x - ss * a.y) * m, (ss * a.x + sc * a.y) * m);
+      }
+      return make_float2(fmaf(a.x, c, -a.y * s), fmaf(a.x, s, a.y * c));
+    }
+
+    // 32-point transform in registers, decimation in frequency: natural order in, v[br5(k)] = X[k] out.
+    // UPPER_ZERO: v[16..31] are known to be zero on entry (zero-padded block), first stage pruned.
+    template <bool INV, bool UPPER_ZERO>
+    __device__ __forceinline__ void dif32(float2 (&v)[32]) {
+#pragma unroll
+      for (int i = 0; i < 16; i++) {
+        if (UPPER_ZERO) {
+          v[i + 16] = mul_w32<INV>(v[i], i);
+        } else {
+          const float2 a = v[i], b = v[i + 16];
+          v[i] = make_float2(a.x + b.x, a.y + b.y);
+          v[i + 16] = mul_w32<INV>(make_float2(a.x - b.x, a.y - b.y), i);
+        }
+      }
+#pragma unroll
+      for (int s = 8; s >= 1; s >>= 1) {
+#pragma unroll
+        for (int g = 0; g < 32; g += 2 * s) {
+#pragma unroll
+          for (int i = 0; i < s; i++) {
+            const float2 a = v[g + i], b = v[g + i + s];
+            v[g + i] = make_float2(a.x + b.x, a.y + b.y);
+            v[g + i + s] = mul_w32<INV>(make_float2(a.x - b.x, a.y - b.y), i * (16 / s));
+          }
+        }
+      }
+    }
+
+    // decimation in time: v[br5(a)] = x[a] in, natural order out
+    template <bool INV>
+    __device__ __forceinline__ void dit32(float2 (&v)[32]) {
+#pragma unroll
+      for (int s = 1; s <= 16; s <<= 1) {
+#pragma unroll
+        for (int g = 0; g < 32; g += 2 * s) {
+#pragma unroll
+          for (int i = 0; i < s; i++) {
+            const float2 a = v[g + i];
+            const float2 b = mul_w32<INV>(v[g + i + s], i * (16 / s));
+            v[g + i] = make_float2(a.x + b.x, a.y + b.y);
+            v[g + i + s] = make_float2(a.x - b.x, a.y - b.y);
+          }
+        }
+      }
+    }
+
+    __device__ __forceinline__ float2 cmulf(float2 a, float2 b) {
+      return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
+    }
+    __device__ __forceinline__ float2 cmulcf(float2 a, float2 b) {  // a * conj(b)
+      return make_float2(fmaf(a.x, b.x, a.y * b.y), fmaf(a.y, b.x, -a.x * b.y));
+    }
+
+    struct FastArgs {
+      long K;         // blocks per channel in this call
+      long n_pairs;   // ceil(K / 2)
+      int run_pairs;  // pairs per warp
+      const float *in;
+      long in_stride;
+      float *out;
+      long out_stride;
+      const float *hist;      // [C][B] the input block before the call
+      const float *tail;      // [C][B] unnormalised tail before the call
+      float *tail_new;        // [C][B]
+      const float2 *filt;     // [n_filters][B + 1] (num_blocks == 1)
+      const int *filter_of;   // [C] filter id per channel (-1: none)
+      const float2 *tw;       // [32][32]: tw[k1][b] = exp(-2 pi i b k1 / 1024)
+    };
+
+    // forward transform of the pair held in v (slots 0..15 valid, upper half zero), filter multiply,
+    // inverse transform.  On return v[br5(n2)] = y[lane + 32 n2] (real: first block, imag: second).
+    __device__ __forceinline__ void convolve_pair(float2 (&v)[32], float2 *tile, const float2 *tw_s,
+                                                  const float2 *H_s, int lane) {
+      dif32<false, true>(v);
+#pragma unroll
+      for (int q = 0; q < 32; q++) tile[br5(q) * kRow + lane] = cmulf(v[q], tw_s[br5(q) * 32 + lane]);
+      __syncwarp();
+#pragma unroll
+      for (int b = 0; b < 32; b++) v[b] = tile[lane * kRow + b];
+      __syncwarp();
+      dif32<false, false>(v);
+#pragma unroll
+      for (int q = 0; q < 32; q++) v[q] = cmulf(v[q], H_s[q * 32 + lane]);
+      dit32<true>(v);
+#pragma unroll
+      for (int n1 = 0; n1 < 32; n1++) tile[n1 * kRow + lane] = cmulcf(v[n1], tw_s[n1 * 32 + lane]);
+      __syncwarp();
+#pragma unroll
+      for (int b = 0; b < 32; b++) v[b] = tile[lane * kRow + b];
+      __syncwarp();
+      dif32<true, false>(v);
+    }
+
+    __global__ void __launch_bounds__(kWarps * 32, 2) convolver_fast_kernel(FastArgs a) {
+      extern __shared__ float2 fsm[];
+      float2 *tw_s = fsm;                       // 1024
+      float2 *H_s = tw_s + 1024;                // 1024: H_s[q][lane] = H[lane + 32 br5(q)]
+      float2 *tiles = H_s + 1024;               // kWarps x 32 x kRow
+      const int c = blockIdx.y;
+      const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+      const int f = a.filter_of[c];
+      for (int i = threadIdx.x; i < 1024; i += kWarps * 32) {
+        tw_s[i] = a.tw[i];
+        const int q = i >> 5, L = i & 31;
+        const int k = L + 32 * br5(q);
+        float2 h = make_float2(0.0f, 0.0f);
+        if (f >= 0) {
+          // full spectrum of the real filter from its B + 1 stored bins
+          h = k <= kFastB ? a.filt[(size_t)f * (kFastB + 1) + k] : a.filt[(size_t)f * (kFastB + 1) + (2 * kFastB - k)];
+          if (k > kFastB) h.y = -h.y;
+        }
+        H_s[i] = h;
+      }
+      __syncthreads();
+
+      const long p0 = ((long)blockIdx.x * kWarps + warp) * a.run_pairs;
+      if (p0 >= a.n_pairs) return;
+      const long p1 = min(a.n_pairs, p0 + a.run_pairs);
+      float2 *tile = tiles + (size_t)warp * 32 * kRow;
+      const float *x = a.in + (size_t)c * a.in_stride;
+      float *y = a.out + (size_t)c * a.out_stride;
+      const float norm = 1.0f / (float)(2 * kFastB);
+
+      float2 v[32];
+      float tail[16];
+      if (p0 == 0) {
+#pragma unroll
+        for (int r = 0; r < 16; r++) tail[r] = a.tail[(size_t)c * kFastB + lane + 32 * r];
+      } else {
+        // halo: the block before the run as the imaginary part of a pair
+        const float *xb = x + (size_t)(2 * p0 - 1) * kFastB;
+#pragma unroll
+        for (int r = 0; r < 16; r++) v[r] = make_float2(0.0f, __ldg(xb + lane + 32 * r));
+        convolve_pair(v, tile, tw_s, H_s, lane);
+#pragma unroll
+        for (int r = 0; r < 16; r++) tail[r] = v[br5(r + 16)].y;
+      }
+      for (long p = p0; p < p1; p++) {
+        const bool has_second = 2 * p + 1 < a.K;
+        const float *x0 = x + (size_t)(2 * p) * kFastB;
+#pragma unroll
+        for (int r = 0; r < 16; r++) v[r].x = __ldcs(x0 + lane + 32 * r);
+        if (has_second) {
+#pragma unroll
+          for (int r = 0; r < 16; r++) v[r].y = __ldcs(x0 + kFastB + lane + 32 * r);
+        } else {
+#pragma unroll
+          for (int r = 0; r < 16; r++) v[r].y = 0.0f;
+        }
+        convolve_pair(v, tile, tw_s, H_s, lane);
+        float *y0 = y + (size_t)(2 * p) * kFastB;
+#pragma unroll
+        for (int r = 0; r < 16; r++) __stcs(y0 + lane + 32 * r, (v[br5(r)].x + tail[r]) * norm);
+        if (has_second) {
+#pragma unroll
+          for (int r = 0; r < 16; r++) {
+            __stcs(y0 + kFastB + lane + 32 * r, (v[br5(r)].y + v[br5(r + 16)].x) * norm);
+            tail[r] = v[br5(r + 16)].y;
+          }
+        } else {
+#pragma unroll
+          for (int r = 0; r < 16; r++) tail[r] = v[br5(r + 16)].x;
+        }
+      }
+      if (p1 == a.n_pairs) {
+#pragma unroll
+        for (int r = 0; r < 16; r++) a.tail_new[(size_t)c * kFastB + lane + 32 * r] = tail[r];
+      }
+    }
+  }  // namespace
+
+  size_t conv_fast_tw_floats() { return 2 * 1024; }
+
+  void conv_fast_build_tw(float *tw) {
+    const double pi = 3.141592653589793238462643383279502884;
+    for (int k1 = 0; k1 < 32; k1++)
+      for (int b = 0; b < 32; b++) {
+        const double ang = -2.0 * pi * (double)(b * k1) / 1024.0;
+        tw[2 * (k1 * 32 + b)] = (float)cos(ang);
+        tw[2 * (k1 * 32 + b) + 1] = (float)sin(ang);
+      }
+  }
+
+  bool conv_fast_supported(int B, int nb) { return B == kFastB && nb == 1; }
+
+  void launch_convolver_fast(const ConvLaunch &L, const int *d_filter_of, const float *d_tw_fast, int n_sms,
+                             cudaStream_t stream) {
+    if (L.K <= 0) return;
+    FastArgs a;
+    a.K = L.K;
+    a.n_pairs = (L.K + 1) / 2;
+    // run length: amortise the one-block halo, keep a few waves of warps in flight
+    int run = 32;
+    while (run > 4 && (a.n_pairs + run - 1) / run * L.C < 16L * kWarps * n_sms) run /= 2;
+    a.run_pairs = run;
+    a.in = L.in;
+    a.in_stride = L.in_stride;
+    a.out = L.out;
+    a.out_stride = L.out_stride;
+    a.hist = L.hist;
+    a.tail = L.tail;
+    a.tail_new = L.tail_new;
+    a.filt = reinterpret_cast<const float2 *>(L.filt);
+    a.filter_of = d_filter_of;
+    a.tw = reinterpret_cast<const float2 *>(d_tw_fast);
+    const size_t smem = sizeof(float2) * (2048 + (size_t)kWarps * 32 * kRow);
+    cudaFuncSetAttribute(convolver_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const long warps = (a.n_pairs + run - 1) / run;
+    dim3 grid((unsigned)((warps + kWarps - 1) / kWarps), (unsigned)L.C);
+    convolver_fast_kernel<<<grid, kWarps * 32, smem, stream>>>(a);
+  }
+}  // namespace earb

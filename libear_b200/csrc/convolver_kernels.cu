@@ -380,6 +380,10 @@ namespace earb {
       cudaFuncSetAttribute(convolver_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     dim3 grid((unsigned)((L.K + L.R - 1) / L.R), (unsigned)L.C);
     convolver_kernel<<<grid, kConvThreads, smem, stream>>>(a);
+    launch_conv_history(L, stream);
+  }
+
+  void launch_conv_history(const ConvLaunch &L, cudaStream_t stream) {
     dim3 hgrid((unsigned)std::min<long>(((long)L.nb * L.B + 255) / 256, 64), (unsigned)L.C);
     conv_history_kernel<<<hgrid, 256, 0, stream>>>(L.B, L.nb, L.K, L.in, L.in_stride, L.hist, L.hist_new);
   }

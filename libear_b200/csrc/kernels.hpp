@@ -119,6 +119,14 @@ namespace earb {
   };
   size_t conv_smem_bytes(int B, int nb);
   void launch_convolver(const ConvLaunch &L, cudaStream_t stream);
+  void launch_conv_history(const ConvLaunch &L, cudaStream_t stream);  // hist -> hist_new only
+  // fast path (convolver_fast_kernels.cu): B = 512, one partition, no filter change in flight,
+  // non-null input; warp-per-block-pair register FFTs.  d_filter_of: [C] filter id per channel.
+  bool conv_fast_supported(int B, int nb);
+  size_t conv_fast_tw_floats();
+  void conv_fast_build_tw(float *tw);
+  void launch_convolver_fast(const ConvLaunch &L, const int *d_filter_of, const float *d_tw_fast, int n_sms,
+                             cudaStream_t stream);
 
   // batched 2B-point real FFTs (the FFT plug-in seam): in [batch][2B] -> out [batch][B+1] complex
   // and back (unnormalised); tw2 = exp(-2 pi i k / 2B), k in [0, 2B)

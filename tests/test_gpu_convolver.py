@@ -110,3 +110,37 @@ def test_decorrelator_bank_9_10_3(eb, ref):
     # all-pass property at full length scale: output energy == input energy (after the tail)
     e_in, e_out = (x.astype(np.float64) ** 2).sum(1), (out.astype(np.float64) ** 2).sum(1)
     assert np.abs(e_out / e_in - 1).max() < 0.05
+
+
+def test_fast_path_streaming_odd_counts_and_crossfades(eb, ref):
+    """B = 512, one partition: the warp-per-pair kernel (convolver_fast_kernels.cu) handles calls
+    without a filter change in flight, the generic kernel the rest; state (last tail, last block)
+    must carry across both, for odd and even block counts."""
+    rng = np.random.default_rng(4)
+    B = 512
+    f = [rng.normal(size=n).astype(np.float32) for n in (512, 300, 17)]
+    blk = lambda k: rng.normal(0, 0.25, size=B * k).astype(np.float32)
+    script = [("set", 0), ("run", blk(1)), ("run", blk(2)), ("run", blk(7)), ("run", blk(70)), ("xfade", 1),
+              ("run", blk(5)), ("run", blk(33)), ("silence", 2), ("run", blk(3)), ("set", 2), ("run", blk(64)),
+              ("xfade", None), ("run", blk(4)), ("run", blk(9)), ("set", 0), ("run", blk(301))]
+    out, exp = run_script(eb, ref, B, 1, f, script)
+    assert peak_err(out, exp) < 1e-6
+
+
+def test_fast_path_matches_generic_kernel(eb, monkeypatch):
+    rng = np.random.default_rng(5)
+    C, B, K = 5, 512, 257
+    x = rng.normal(0, 0.25, size=(C, B * K)).astype(np.float32)
+    filt = rng.normal(size=(C, 512)).astype(np.float32)
+    outs = []
+    for path in ("fast", "generic"):
+        monkeypatch.setenv("EARB200_CONV_PATH", path)
+        g = eb.BlockConvolver(B, C, 1)
+        for c in range(C - 1):          # the last channel has no filter: silence out
+            fid, _ = g.add_filter(filt[c])
+            g.set_filter(fid, channel=c)
+        outs.append(np.concatenate([g.process(x[:, :B * 100]), g.process(x[:, B * 100:])], axis=1))
+    assert peak_err(outs[0], outs[1]) < 1e-6
+    assert np.abs(outs[0][C - 1]).max() == 0.0
+    direct = np.stack([np.convolve(x[c].astype(np.float64), filt[c].astype(np.float64))[:B * K] for c in range(C - 1)])
+    assert peak_err(outs[0][:C - 1], direct) < 1e-6
