@@ -29,7 +29,8 @@ namespace earb {
   namespace {
     constexpr int kFastB = 512;
     constexpr int kWarps = 8;
-    constexpr int kRow = 33;  // padded row of the 32 x 32 transposition tile (float2 units)
+    constexpr int kRow = 34;  // padded row of the 32 x 32 transposition tile (float2 units): 16-byte
+                              // aligned rows, float4 row reads and float2 column writes conflict-free
 
     __host__ __device__ constexpr int br5(int x) {
       return ((x & 1) << 4) | ((x & 2) << 2) | (x & 4) | ((x & 8) >> 2) | ((x & 16) >> 4);
@@ -105,20 +106,55 @@ namespace earb {
       }
     }
 
-    // decimation in time: v[br5(a)] = x[a] in, natural order out
+    // (a, b) <- (a + w b, a - w b), w = exp(-+ 2 pi i k / 32), in six FMAs: the complex product is
+    // written as c (b - t i b) with t = s / c (or with the roles of c and s swapped when |s| > |c|),
+    // so that the scaling by c folds into the two additions (Linzer-Feig).
     template <bool INV>
+    __device__ __forceinline__ void bfly_dit(float2 &a, float2 &b, int k) {
+      k &= 15;
+      float2 a0 = a, b0 = b;
+      if (k == 0) {
+        a = make_float2(a0.x + b0.x, a0.y + b0.y);
+        b = make_float2(a0.x - b0.x, a0.y - b0.y);
+        return;
+      }
+      if (k == 8) {  // w = -i (forward), +i (inverse)
+        const float2 wb = INV ? make_float2(-b0.y, b0.x) : make_float2(b0.y, -b0.x);
+        a = make_float2(a0.x + wb.x, a0.y + wb.y);
+        b = make_float2(a0.x - wb.x, a0.y - wb.y);
+        return;
+      }
+      const float c = cos32(k), sn = INV ? sin32(k) : -sin32(k);  // w = c + i sn
+      float u, v, scale;
+      if (fabsf(c) >= fabsf(sn)) {
+        const float t = sn / c;       // compile-time constant
+        u = fmaf(-t, b0.y, b0.x);     // Re(w b) / c
+        v = fmaf(t, b0.x, b0.y);      // Im(w b) / c
+        scale = c;
+      } else {
+        const float t = c / sn;
+        u = fmaf(t, b0.x, -b0.y);     // Re(w b) / sn
+        v = fmaf(t, b0.y, b0.x);      // Im(w b) / sn
+        scale = sn;
+      }
+      a = make_float2(fmaf(scale, u, a0.x), fmaf(scale, v, a0.y));
+      b = make_float2(fmaf(-scale, u, a0.x), fmaf(-scale, v, a0.y));
+    }
+
+    // decimation in time: v[br5(a)] = x[a] in, natural order out.
+    // ODD_ZERO: the odd slots (inputs a >= 16) are known to be zero: first stage pruned.
+    template <bool INV, bool ODD_ZERO>
     __device__ __forceinline__ void dit32(float2 (&v)[32]) {
+      if (ODD_ZERO) {
 #pragma unroll
-      for (int s = 1; s <= 16; s <<= 1) {
+        for (int g = 0; g < 32; g += 2) v[g + 1] = v[g];
+      }
+#pragma unroll
+      for (int s = ODD_ZERO ? 2 : 1; s <= 16; s <<= 1) {
 #pragma unroll
         for (int g = 0; g < 32; g += 2 * s) {
 #pragma unroll
-          for (int i = 0; i < s; i++) {
-            const float2 a = v[g + i];
-            const float2 b = mul_w32<INV>(v[g + i + s], i * (16 / s));
-            v[g + i] = make_float2(a.x + b.x, a.y + b.y);
-            v[g + i + s] = make_float2(a.x - b.x, a.y - b.y);
-          }
+          for (int i = 0; i < s; i++) bfly_dit<INV>(v[g + i], v[g + i + s], i * (16 / s));
         }
       }
     }
@@ -146,49 +182,78 @@ namespace earb {
       const float2 *tw;       // [32][32]: tw[k1][b] = exp(-2 pi i b k1 / 1024)
     };
 
-    // forward transform of the pair held in v (slots 0..15 valid, upper half zero), filter multiply,
-    // inverse transform.  On return v[br5(n2)] = y[lane + 32 n2] (real: first block, imag: second).
-    __device__ __forceinline__ void convolve_pair(float2 (&v)[32], float2 *tile, const float2 *tw_s,
-                                                  const float2 *H_s, int lane) {
-      dif32<false, true>(v);
+    // forward transform of the pair held in v (v[br5(a)] = z[lane + 32 a] for a < 16, odd slots
+    // zero), filter multiply, inverse transform.  On return v[n2] = y[lane + 32 n2] (real part:
+    // first block of the pair, imaginary part: second block).
+    // tw_s / H_s hold two consecutive slots per float4: [slot / 2][lane] = (slot, slot + 1).
+    __device__ __forceinline__ void convolve_pair(float2 (&v)[32], float2 *tile, const float4 *tw_s,
+                                                  const float4 *H_s, int lane) {
+      dit32<false, true>(v);  // over a: v[k1] = A_lane[k1]
 #pragma unroll
-      for (int q = 0; q < 32; q++) tile[br5(q) * kRow + lane] = cmulf(v[q], tw_s[br5(q) * 32 + lane]);
+      for (int k1 = 0; k1 < 32; k1 += 2) {
+        const float4 t = tw_s[(k1 >> 1) * 32 + lane];
+        tile[k1 * kRow + lane] = cmulf(v[k1], make_float2(t.x, t.y));
+        tile[(k1 + 1) * kRow + lane] = cmulf(v[k1 + 1], make_float2(t.z, t.w));
+      }
+      __syncwarp();
+      const float4 *row = reinterpret_cast<const float4 *>(tile + lane * kRow);
+#pragma unroll
+      for (int b = 0; b < 32; b += 2) {
+        const float4 t = row[b >> 1];
+        v[br5(b)] = make_float2(t.x, t.y);
+        v[br5(b + 1)] = make_float2(t.z, t.w);
+      }
+      __syncwarp();
+      dit32<false, false>(v);  // over b: v[k2] = Z[lane + 32 k2]
+#pragma unroll
+      for (int k2 = 0; k2 < 32; k2 += 2) {
+        const float4 h = H_s[(k2 >> 1) * 32 + lane];
+        v[k2] = cmulf(v[k2], make_float2(h.x, h.y));
+        v[k2 + 1] = cmulf(v[k2 + 1], make_float2(h.z, h.w));
+      }
+      dif32<true, false>(v);  // inverse over k2: v[br5(n1)]
+#pragma unroll
+      for (int q = 0; q < 32; q += 2) {
+        // slots q, q + 1 hold n1 = br5(q), br5(q) + 16
+        const int n1 = br5(q);
+        const float4 ta = tw_s[(n1 >> 1) * 32 + lane], tb = tw_s[((n1 + 16) >> 1) * 32 + lane];
+        const float2 wa = (n1 & 1) ? make_float2(ta.z, ta.w) : make_float2(ta.x, ta.y);
+        const float2 wb = (n1 & 1) ? make_float2(tb.z, tb.w) : make_float2(tb.x, tb.y);
+        tile[n1 * kRow + lane] = cmulcf(v[q], wa);
+        tile[(n1 + 16) * kRow + lane] = cmulcf(v[q + 1], wb);
+      }
       __syncwarp();
 #pragma unroll
-      for (int b = 0; b < 32; b++) v[b] = tile[lane * kRow + b];
+      for (int b = 0; b < 32; b += 2) {
+        const float4 t = row[b >> 1];
+        v[br5(b)] = make_float2(t.x, t.y);
+        v[br5(b + 1)] = make_float2(t.z, t.w);
+      }
       __syncwarp();
-      dif32<false, false>(v);
-#pragma unroll
-      for (int q = 0; q < 32; q++) v[q] = cmulf(v[q], H_s[q * 32 + lane]);
-      dit32<true>(v);
-#pragma unroll
-      for (int n1 = 0; n1 < 32; n1++) tile[n1 * kRow + lane] = cmulcf(v[n1], tw_s[n1 * 32 + lane]);
-      __syncwarp();
-#pragma unroll
-      for (int b = 0; b < 32; b++) v[b] = tile[lane * kRow + b];
-      __syncwarp();
-      dif32<true, false>(v);
+      dit32<true, false>(v);  // inverse over b: v[n2] = y[lane + 32 n2]
     }
 
     __global__ void __launch_bounds__(kWarps * 32, 2) convolver_fast_kernel(FastArgs a) {
-      extern __shared__ float2 fsm[];
-      float2 *tw_s = fsm;                       // 1024
-      float2 *H_s = tw_s + 1024;                // 1024: H_s[q][lane] = H[lane + 32 br5(q)]
-      float2 *tiles = H_s + 1024;               // kWarps x 32 x kRow
+      extern __shared__ float4 fsm[];
+      float4 *tw_s = fsm;        // [16][32]: (tw[2j][lane], tw[2j + 1][lane])
+      float4 *H_s = tw_s + 512;  // [16][32]: (H[lane + 32 (2j)], H[lane + 32 (2j + 1)])
+      float2 *tiles = reinterpret_cast<float2 *>(H_s + 512);  // kWarps x 32 x kRow
       const int c = blockIdx.y;
       const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
       const int f = a.filter_of[c];
       for (int i = threadIdx.x; i < 1024; i += kWarps * 32) {
-        tw_s[i] = a.tw[i];
-        const int q = i >> 5, L = i & 31;
-        const int k = L + 32 * br5(q);
+        const int slot = i >> 5, L = i & 31;
+        float2 *tw_dst = reinterpret_cast<float2 *>(tw_s) + ((slot >> 1) * 32 + L) * 2 + (slot & 1);
+        float2 *H_dst = reinterpret_cast<float2 *>(H_s) + ((slot >> 1) * 32 + L) * 2 + (slot & 1);
+        *tw_dst = a.tw[i];
+        const int k = L + 32 * slot;
         float2 h = make_float2(0.0f, 0.0f);
         if (f >= 0) {
           // full spectrum of the real filter from its B + 1 stored bins
           h = k <= kFastB ? a.filt[(size_t)f * (kFastB + 1) + k] : a.filt[(size_t)f * (kFastB + 1) + (2 * kFastB - k)];
           if (k > kFastB) h.y = -h.y;
         }
-        H_s[i] = h;
+        *H_dst = h;
       }
       __syncthreads();
 
@@ -209,36 +274,36 @@ namespace earb {
         // halo: the block before the run as the imaginary part of a pair
         const float *xb = x + (size_t)(2 * p0 - 1) * kFastB;
 #pragma unroll
-        for (int r = 0; r < 16; r++) v[r] = make_float2(0.0f, __ldg(xb + lane + 32 * r));
+        for (int r = 0; r < 16; r++) v[br5(r)] = make_float2(0.0f, __ldg(xb + lane + 32 * r));
         convolve_pair(v, tile, tw_s, H_s, lane);
 #pragma unroll
-        for (int r = 0; r < 16; r++) tail[r] = v[br5(r + 16)].y;
+        for (int r = 0; r < 16; r++) tail[r] = v[r + 16].y;
       }
       for (long p = p0; p < p1; p++) {
         const bool has_second = 2 * p + 1 < a.K;
         const float *x0 = x + (size_t)(2 * p) * kFastB;
 #pragma unroll
-        for (int r = 0; r < 16; r++) v[r].x = __ldcs(x0 + lane + 32 * r);
+        for (int r = 0; r < 16; r++) v[br5(r)].x = __ldcs(x0 + lane + 32 * r);
         if (has_second) {
 #pragma unroll
-          for (int r = 0; r < 16; r++) v[r].y = __ldcs(x0 + kFastB + lane + 32 * r);
+          for (int r = 0; r < 16; r++) v[br5(r)].y = __ldcs(x0 + kFastB + lane + 32 * r);
         } else {
 #pragma unroll
-          for (int r = 0; r < 16; r++) v[r].y = 0.0f;
+          for (int r = 0; r < 16; r++) v[br5(r)].y = 0.0f;
         }
         convolve_pair(v, tile, tw_s, H_s, lane);
         float *y0 = y + (size_t)(2 * p) * kFastB;
 #pragma unroll
-        for (int r = 0; r < 16; r++) __stcs(y0 + lane + 32 * r, (v[br5(r)].x + tail[r]) * norm);
+        for (int r = 0; r < 16; r++) __stcs(y0 + lane + 32 * r, (v[r].x + tail[r]) * norm);
         if (has_second) {
 #pragma unroll
           for (int r = 0; r < 16; r++) {
-            __stcs(y0 + kFastB + lane + 32 * r, (v[br5(r)].y + v[br5(r + 16)].x) * norm);
-            tail[r] = v[br5(r + 16)].y;
+            __stcs(y0 + kFastB + lane + 32 * r, (v[r].y + v[r + 16].x) * norm);
+            tail[r] = v[r + 16].y;
           }
         } else {
 #pragma unroll
-          for (int r = 0; r < 16; r++) tail[r] = v[br5(r + 16)].x;
+          for (int r = 0; r < 16; r++) tail[r] = v[r + 16].x;
         }
       }
       if (p1 == a.n_pairs) {
