@@ -351,6 +351,180 @@ def run_ours(args):
             del hx, hy
         del x, y
 
+
+    # ---------------- convolver: BASELINE config 4 (24 channels x 10 min, 512-tap decorrelators, B = 512)
+    conv_block = None
+    if not args.no_convolver:
+        Cc, Bc = 24, 512
+        Kc = args.conv_blocks
+        Tc = Kc * Bc
+        xs = (torch.randn((Cc, Tc), generator=torch.Generator(device=dev).manual_seed(200 + rank), device=dev,
+                          dtype=torch.float32) * 0.25).clamp_(-1, 1)
+        ys = torch.empty_like(xs)
+        conv = eb.BlockConvolver(Bc, Cc, 1, device=local_rank)
+        filt = eb.design_decorrelators(LAYOUT, np.float32)
+        for c in range(Cc):
+            fid, _ = conv.add_filter(filt[c])
+            conv.set_filter(fid, c)
+
+        def step_conv():
+            conv.process_device(Kc, xs.data_ptr(), Tc, ys.data_ptr(), Tc, stream=stream)
+
+        for _ in range(args.warmup):
+            step_conv()
+        barrier()
+        conv.set_profiling(True)
+        cl0 = conv.launch_count
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        c0.record()
+        for _ in range(args.steps):
+            step_conv()
+        c1.record()
+        barrier()
+        c_ms = max_over_ranks(c0.elapsed_time(c1))
+        ck_ms, ck_n = conv.kernel_time()
+        conv.set_profiling(False)
+        gpu_launches += conv.launch_count - cl0
+        c_bytes = 8.0 * Cc * Tc
+        c_achieved = c_bytes * ck_n / (ck_ms * 1e-3) / 1e9
+        conv_block = {
+            "metric": "decorrelation convolver Msamples/s", "value": Cc * Tc * world * args.steps / (c_ms * 1e-3) / 1e6,
+            "unit": "Msamples/s", "ms_per_step": c_ms / args.steps,
+            "config": {"workload": f"cfg4: {Cc} channels/GPU x {Tc} samples ({Tc / 48000 / 60:.1f} min at 48 kHz), "
+                                   f"designDecorrelators({LAYOUT}) 512-tap filters, block size {Bc}; "
+                                   "5.5 GB/step > L2", "sharding": "replicated channels per GPU, no collective"},
+            "roofline": {"bound": "hbm", "achieved": c_achieved, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": c_achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "convolver_fast_kernel", "kernel_ms": ck_ms / max(1, ck_n),
+                         "algorithmic_bytes_per_launch": c_bytes,
+                         "note": "8 B/sample; the FP32 butterflies (about 2,300 warp instructions per pair of "
+                                 "blocks) bound the kernel before HBM does (DESIGN.md section 3, K4)"},
+        }
+        if world == 1 and not args.no_render_e2e:
+            hx = torch.empty((Cc, Tc), dtype=torch.float32).pin_memory()
+            hx.copy_(xs)
+            hy = torch.empty((Cc, Tc), dtype=torch.float32).pin_memory()
+
+            def conv_e2e():
+                eb._chk(eb._lib.earb200_convolver_process_host(conv.h, C.c_int64(Kc), C.c_void_p(hx.data_ptr()),
+                                                               C.c_int64(Tc), C.c_void_p(hy.data_ptr()), C.c_int64(Tc)))
+            conv_e2e()
+            t0 = time.perf_counter()
+            conv_e2e()
+            dt = time.perf_counter() - t0
+            conv_block["e2e"] = {"value": Cc * Tc / dt / 1e6, "unit": "Msamples/s", "h2d_bytes_per_step": 4 * Cc * Tc,
+                                 "d2h_bytes_per_step": 4 * Cc * Tc}
+            del hx, hy
+        del xs, ys, conv
+
+    # ---------------- HOA decode + object-sharded mixing with an NCCL bus reduce: BASELINE config 5
+    mix_block = None
+    if not args.no_mix:
+        lay5 = "4+7+0"
+        T5 = args.mix_samples
+        n_total = args.mix_objects
+        n_local = n_total // world
+        # HOA order 3 (ACN 0..15, SN3D): design on the device, apply as a static 16 -> 12 matrix
+        hoa = eb.GainCalculatorHOA(lay5, device=local_rank)
+        orders = [n for n in range(4) for _ in range(2 * n + 1)]
+        degrees = [m for n in range(4) for m in range(-n, n + 1)]
+        hoa.calculate(orders, degrees, "SN3D")
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        D, _ = hoa.calculate(orders, degrees, "SN3D")
+        hoa_design_ms = (time.perf_counter() - t0) * 1e3
+        M5 = D.shape[1]
+        gi_hoa = eb.GainInterpolator(16, M5, device=local_rank)
+        gi_hoa.set_points(np.array([0], dtype=np.int64), D.astype(np.float32)[None])
+        xh = torch.randn((16, T5), device=dev, dtype=torch.float32) * 0.25
+        yh = torch.empty((M5, T5), device=dev, dtype=torch.float32)
+        for _ in range(args.warmup):
+            gi_hoa.process_device(0, T5, xh.data_ptr(), T5, yh.data_ptr(), T5, stream=stream)
+        barrier()
+        h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        hl0 = gi_hoa.launch_count
+        h0.record()
+        for _ in range(args.steps):
+            gi_hoa.process_device(0, T5, xh.data_ptr(), T5, yh.data_ptr(), T5, stream=stream)
+        h1.record()
+        barrier()
+        hoa_ms = max_over_ranks(h0.elapsed_time(h1)) / args.steps
+        gpu_launches += gi_hoa.launch_count - hl0
+        del xh, yh
+
+        # objects: gains for slowly moving extent objects from the Objects calculator on the device,
+        # one interpolation point per second, groups of <= 256 objects mixed into one bus
+        gc5 = eb.GainCalculatorObjects(lay5, device=local_rank)
+        n_pts = T5 // 48000 + 1
+        samples5 = np.arange(n_pts, dtype=np.int64) * 48000
+        base = synth_objects(n_local, 500 + rank)
+        rng5 = np.random.default_rng(600 + rank)
+        drift = rng5.uniform(-3, 3, n_local)
+        gains5 = np.empty((n_pts, n_local, M5), dtype=np.float32)
+        for k in range(n_pts):
+            az = (base[0] + drift * k + 180.0) % 360.0 - 180.0
+            d_k, _ = gc5.calculate(az, base[1], base[2], base[3], base[4], base[5], base[6], 0.0)
+            gains5[k] = d_k
+        groups = []
+        for g0 in range(0, n_local, 256):
+            g1 = min(n_local, g0 + 256)
+            gi = eb.GainInterpolator(g1 - g0, M5, device=local_rank)
+            gi.set_points(samples5, gains5[:, g0:g1])
+            gi.set_accumulate(g0 > 0)
+            groups.append((g0, g1, gi))
+        xo = torch.empty((n_local, T5), device=dev, dtype=torch.float32)
+        xo.normal_(0, 0.25, generator=torch.Generator(device=dev).manual_seed(700 + rank))
+        bus = torch.empty((M5, T5), device=dev, dtype=torch.float32)
+        red0, red1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+        def step_mix(timed_reduce=False):
+            for g0, g1, gi in groups:
+                gi.process_device(0, T5, xo[g0].data_ptr(), T5, bus.data_ptr(), T5, stream=stream)
+            if world > 1:
+                if timed_reduce:
+                    red0.record()
+                dist.all_reduce(bus)   # the one collective: sum of the per-GPU partial buses
+                if timed_reduce:
+                    red1.record()
+
+        for _ in range(args.warmup):
+            step_mix()
+        barrier()
+        ml0 = sum(gi.launch_count for _, _, gi in groups)
+        m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        m0.record()
+        for _ in range(args.steps):
+            step_mix()
+        m1.record()
+        barrier()
+        mix_ms = max_over_ranks(m0.elapsed_time(m1)) / args.steps
+        gpu_launches += (sum(gi.launch_count for _, _, gi in groups) - ml0)
+        reduce_ms = None
+        if world > 1:
+            step_mix(timed_reduce=True)
+            torch.cuda.synchronize()
+            reduce_ms = max_over_ranks(red0.elapsed_time(red1))
+        mix_bytes = 4.0 * T5 * (n_local + M5 * (2 * len(groups) - 1)) + 4.0 * n_local * M5 * n_pts
+        mix_block = {
+            "metric": "object mixing Msamples/s (input object-samples, whole job)",
+            "value": n_local * world * T5 / (mix_ms * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": mix_ms,
+            "scaling": "strong",
+            "config": {"workload": f"cfg5: {n_total} extent objects x {T5 / 48000:.0f} s x 48 kHz into {lay5} (M={M5}), "
+                                   f"{n_local} objects/GPU in groups of 256, gains from GainCalculatorObjects at "
+                                   f"{n_pts} points; HOA order 3 (16 ch) decode alongside",
+                       "bus_reduce": "nccl all_reduce(sum, f32) of the [M x T] bus" if world > 1 else "none (1 GPU)"},
+            "roofline": {"bound": "hbm", "achieved": mix_bytes / (mix_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": mix_bytes / (mix_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None,
+                         "peak_source": peak_src, "kernel": "render_tc_persistent_kernel (+ all_reduce when sharded)",
+                         "algorithmic_bytes_per_step_per_gpu": mix_bytes},
+            "bus_reduce_ms": reduce_ms,
+            "bus_reduce_gbs": (4.0 * M5 * T5 / (reduce_ms * 1e-3) / 1e9) if reduce_ms else None,
+            "hoa": {"design_ms": hoa_design_ms, "apply_ms": hoa_ms,
+                    "apply_msamples_per_s": 16 * T5 / (hoa_ms * 1e-3) / 1e6,
+                    "apply_gbs": 4.0 * T5 * (16 + M5) / (hoa_ms * 1e-3) / 1e9},
+        }
+        del xo, bus, groups
+
     if rank == 0:
         line = {
             "metric": "object gain vectors/s (9+10+3, extent)", "value": value, "unit": "vectors/s",
@@ -376,6 +550,10 @@ def run_ours(args):
         }
         if render is not None:
             line["render"] = render
+        if conv_block is not None:
+            line["convolver"] = conv_block
+        if mix_block is not None:
+            line["mix"] = mix_block
         if world == 1 and not args.no_cpu_baseline:
             from oracle import ref
             if ref.available():
@@ -403,6 +581,11 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--objects", type=int, default=N_OBJECTS)
     ap.add_argument("--no-render", action="store_true")
+    ap.add_argument("--no-convolver", action="store_true")
+    ap.add_argument("--no-mix", action="store_true")
+    ap.add_argument("--conv-blocks", type=int, default=56250, help="blocks per channel (cfg4: 10 min)")
+    ap.add_argument("--mix-objects", type=int, default=4096, help="objects of the whole job (cfg5)")
+    ap.add_argument("--mix-samples", type=int, default=2_880_000)
     ap.add_argument("--no-render-e2e", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiler runs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")

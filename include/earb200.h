@@ -167,6 +167,10 @@ int earb200_interp_process_host(earb200_interp *interp, int64_t block_start,
 int earb200_interp_process_device(earb200_interp *interp, int64_t block_start,
                                   int64_t nsamples, const float *d_in, int64_t in_stride,
                                   float *d_out, int64_t out_stride, void *stream);
+/* extension (not in libear): with accumulate on, process ADDS its result to `out` instead of
+ * overwriting it, so several interpolators (e.g. groups of up to 256 objects each) mix into one
+ * loudspeaker bus without an extra pass. */
+int earb200_interp_set_accumulate(earb200_interp *interp, int enable);
 int64_t earb200_interp_launch_count(const earb200_interp *interp);
 int earb200_interp_set_profiling(earb200_interp *interp, int enable);
 int earb200_interp_kernel_time(earb200_interp *interp, double *ms, int64_t *launches);

@@ -258,16 +258,24 @@ class GainInterpolator:
         _chk(_lib.earb200_interp_kernel_time(self.h, C.byref(ms), C.byref(n)))
         return ms.value, n.value
 
+    def set_accumulate(self, enable=True):
+        """Extension: process() adds into the output bus instead of overwriting it."""
+        _chk(_lib.earb200_interp_set_accumulate(self.h, int(enable)))
+
     def set_points(self, sample_idx, gains):
         s = np.ascontiguousarray(sample_idx, dtype=np.int64)
         g = np.ascontiguousarray(gains, dtype=np.float32).reshape(len(s), self.n_in, self.n_out)
         _chk(_lib.earb200_interp_set_points(self.h, C.c_int64(len(s)), _ptr(s), _ptr(g)))
 
-    def process(self, block_start, inp):
-        """inp: float32 [n_in][nsamples] host array -> out float32 [n_out][nsamples]."""
+    def process(self, block_start, inp, out=None):
+        """inp: float32 [n_in][nsamples] host array -> out float32 [n_out][nsamples]; with
+        set_accumulate(True), `out` is the bus the result is added to."""
         inp = np.ascontiguousarray(inp, dtype=np.float32).reshape(self.n_in, -1)
         n = inp.shape[1]
-        out = np.zeros((self.n_out, n), dtype=np.float32)
+        if out is None:
+            out = np.zeros((self.n_out, n), dtype=np.float32)
+        else:
+            out = np.array(out, dtype=np.float32).reshape(self.n_out, n)
         _chk(_lib.earb200_interp_process_host(self.h, C.c_int64(block_start), C.c_int64(n), _ptr(inp),
                                               C.c_int64(n), _ptr(out), C.c_int64(n)))
         return out

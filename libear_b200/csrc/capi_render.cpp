@@ -34,6 +34,7 @@ struct earb200_interp {
   int64_t launches = 0;
   KernelTimer timer;
   int n_sms = 0;
+  int accumulate = 0;  // process() adds into `out` instead of overwriting it
   int use_tc = 0;  // tensor-core (tcgen05) fast path; EARB200_RENDER_PATH=cuda selects the FFMA kernel
 };
 
@@ -120,7 +121,7 @@ namespace {
       align = (int)((ia / 4) & 3);
     build_plan(h, block_start, nsamples, align);
     RenderPlan plan{h.d_items.ptr, h.n_items[0], h.n_items[1], h.n_items[2], h.n_items[3], h.use_tc,
-                    h.n_sms, (long)nsamples, h.d_images.ptr};
+                    h.n_sms, (long)nsamples, h.d_images.ptr, h.accumulate};
     h.timer.start(stream);
     launch_render(h.N, h.M, d_in, (long)in_stride, d_out, (long)out_stride, plan, h.d_segs.ptr,
                   h.d_gains.ptr, stream);
@@ -136,6 +137,13 @@ namespace {
 }  // namespace
 
 extern "C" {
+
+int earb200_interp_set_accumulate(earb200_interp *interp, int enable) {
+  return guarded([&] {
+    if (!interp) throw Error(INVALID_ARGUMENT, "null argument");
+    interp->accumulate = enable ? 1 : 0;
+  });
+}
 
 int earb200_interp_create(int n_in, int n_out, int device, earb200_interp **out) {
   return guarded([&] {
@@ -236,6 +244,9 @@ int earb200_interp_process_host(earb200_interp *interp, int64_t block_start,
     float *d_out = h.d_out.reserve((size_t)stride * h.M);
     EARB_CUDA(cudaMemcpy2DAsync(d_in, sizeof(float) * stride, in, sizeof(float) * in_stride,
                                 sizeof(float) * nsamples, h.N, cudaMemcpyHostToDevice, 0));
+    if (h.accumulate)  // the bus being mixed into travels too
+      EARB_CUDA(cudaMemcpy2DAsync(d_out, sizeof(float) * stride, out, sizeof(float) * out_stride,
+                                  sizeof(float) * nsamples, h.M, cudaMemcpyHostToDevice, 0));
     process_device(h, block_start, nsamples, d_in, stride, d_out, stride, 0);
     EARB_CUDA(cudaMemcpy2DAsync(out, sizeof(float) * out_stride, d_out, sizeof(float) * stride,
                                 sizeof(float) * nsamples, h.M, cudaMemcpyDeviceToHost, 0));

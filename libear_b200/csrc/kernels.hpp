@@ -77,6 +77,7 @@ namespace earb {
     int n_sms;   // grid size of the persistent tcgen05 kernel
     long n_samples;  // samples per channel of this call (extent of the TMA descriptor)
     const float *d_images;  // per-point gain-matrix images (tcgen05 path)
+    int accumulate;         // out += result instead of out = result (mixing channel groups)
   };
   // tcgen05 / TMEM variant of the fast path (render_tc_kernels.cu)
   bool render_tc_supported(int N, int M);
@@ -86,7 +87,7 @@ namespace earb {
   // could not be encoded, nothing launched
   bool launch_render_tc(int N, int M, const float *in, long in_stride, long n_samples, float *out,
                         long out_stride, const RenderItem *d_items, long n_tiles,
-                        const RenderSegment *d_segs, const float *d_images, int n_sms,
+                        const RenderSegment *d_segs, const float *d_images, int n_sms, int accumulate,
                         cudaStream_t stream);
   // per-point gain-matrix images for the tcgen05 kernel (TF32 hi/lo split in UMMA layout)
   size_t render_tc_image_floats(int N);

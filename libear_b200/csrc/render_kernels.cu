@@ -51,7 +51,7 @@ namespace earb {
                       float *__restrict__ out, long out_stride,
                       const RenderItem *__restrict__ items,
                       const RenderSegment *__restrict__ segs,
-                      const float *__restrict__ gains) {
+                      const float *__restrict__ gains, int accumulate) {
       extern __shared__ float4 smem4[];
       float *sS = reinterpret_cast<float *>(smem4);  // [N][MP] start gains
       float *sD = sS + (size_t)N * MP;               // [N][MP] end - start
@@ -153,6 +153,11 @@ namespace earb {
 #pragma unroll
           for (int j = 0; j < TPT; j++) r[j] = RAMP ? fmaf(p[j], accD[j][m], accS[j][m]) : accS[j][m];
           float *o = op + (long)m * out_stride;
+          if (accumulate) {  // mix into the bus instead of overwriting it
+#pragma unroll
+            for (int j = 0; j < TPT; j++)
+              if (j < valid) r[j] += o[j];
+          }
           if (vec_out) {
             using V = typename Vec<TPT>::type;
             V v;
@@ -217,7 +222,7 @@ namespace earb {
                            float *__restrict__ out, long out_stride,
                            const RenderItem *__restrict__ items,
                            const RenderSegment *__restrict__ segs,
-                           const float *__restrict__ gains) {
+                           const float *__restrict__ gains, int accumulate) {
       constexpr int NT = 64 * (MP / 4);
       extern __shared__ __align__(128) unsigned char smem_raw[];
       float *sx = reinterpret_cast<float *>(smem_raw);     // [stages][kPipeCh][tile]
@@ -326,6 +331,13 @@ namespace earb {
             v.y = RAMP ? fmaf(p[1], aD[h][1][k], aS[h][1][k]) : aS[h][1][k];
             v.z = RAMP ? fmaf(p[2], aD[h][2][k], aS[h][2][k]) : aS[h][2][k];
             v.w = RAMP ? fmaf(p[3], aD[h][3][k], aS[h][3][k]) : aS[h][3][k];
+            if (accumulate) {
+              const float4 o = __ldcs(reinterpret_cast<const float4 *>(out + (long)m * out_stride + t));
+              v.x += o.x;
+              v.y += o.y;
+              v.z += o.z;
+              v.w += o.w;
+            }
             __stcs(reinterpret_cast<float4 *>(out + (long)m * out_stride + t), v);
           }
         }
@@ -335,25 +347,25 @@ namespace earb {
     template <int MP, bool RAMP>
     void launch_pipe(int N, int M, const float *in, long in_stride, float *out, long out_stride,
                      const RenderItem *items, long n_items, const RenderSegment *segs,
-                     const float *gains, cudaStream_t stream) {
+                     const float *gains, int accumulate, cudaStream_t stream) {
       if (n_items <= 0) return;
       const size_t smem = sizeof(float) * ((size_t)kPipeStages * kPipeCh * kPipeTile + (size_t)N * MP * 2);
       auto kern = render_pipe_kernel<MP, RAMP>;
       cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       kern<<<(unsigned)n_items, 64 * (MP / 4), smem, stream>>>(N, M, in, in_stride, out, out_stride, items,
-                                                              segs, gains);
+                                                              segs, gains, accumulate);
     }
 
     template <int MP, int TPT, bool RAMP>
     void launch_one(int N, int M, const float *in, long in_stride, float *out, long out_stride,
                     const RenderItem *items, long n_items, const RenderSegment *segs,
-                    const float *gains, cudaStream_t stream) {
+                    const float *gains, int accumulate, cudaStream_t stream) {
       if (n_items <= 0) return;
       const size_t smem = sizeof(float) * (size_t)N * MP * (RAMP ? 2 : 1);
       auto kern = render_kernel<MP, TPT, RAMP>;
       if (smem > 48 * 1024) cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       kern<<<(unsigned)n_items, kThreads, smem, stream>>>(N, M, in, in_stride, out, out_stride, items,
-                                                          segs, gains);
+                                                          segs, gains, accumulate);
     }
   }  // namespace
 
@@ -374,19 +386,20 @@ namespace earb {
     if (plan.use_tc) {
       // the ramp and constant tiles are adjacent in the item list: one persistent launch
       if (!launch_render_tc(N, M, in, in_stride, plan.n_samples, out, out_stride, fast_ramp,
-                            n_fast_ramp + n_fast_const, d_segs, plan.d_images, plan.n_sms, stream))
+                            n_fast_ramp + n_fast_const, d_segs, plan.d_images, plan.n_sms,
+                            plan.accumulate, stream))
         throw std::runtime_error("cuTensorMapEncodeTiled failed for the render input");
       n_fast_ramp = n_fast_const = 0;
     }
 #define EARB_RENDER_CASE(MP, TPT)                                                                      \
   launch_pipe<MP, true>(N, M, in, in_stride, out, out_stride, fast_ramp, n_fast_ramp, d_segs,          \
-                        d_gains, stream);                                                              \
+                        d_gains, plan.accumulate, stream);                                                              \
   launch_pipe<MP, false>(N, M, in, in_stride, out, out_stride, fast_const, n_fast_const, d_segs,       \
-                         d_gains, stream);                                                             \
+                         d_gains, plan.accumulate, stream);                                                             \
   launch_one<MP, TPT, true>(N, M, in, in_stride, out, out_stride, slow_ramp, plan.n_slow_ramp, d_segs, \
-                            d_gains, stream);                                                          \
+                            d_gains, plan.accumulate, stream);                                                          \
   launch_one<MP, TPT, false>(N, M, in, in_stride, out, out_stride, slow_const, plan.n_slow_const,      \
-                             d_segs, d_gains, stream);
+                             d_segs, d_gains, plan.accumulate, stream);
     if (M <= 8) {
       EARB_RENDER_CASE(8, 4)
     } else if (M <= 16) {

@@ -192,7 +192,7 @@ namespace earb {
                                     float *__restrict__ out, long out_stride,
                                     const RenderItem *__restrict__ items, int n_tiles,
                                     const RenderSegment *__restrict__ segs,
-                                    const float *__restrict__ images, int n_stages) {
+                                    const float *__restrict__ images, int n_stages, int accumulate) {
       extern __shared__ __align__(128) unsigned char smem_raw[];
       const int Kp = (N + kCh - 1) / kCh * kCh;  // K padded to whole stages
       const int n_iters = Kp / kCh;
@@ -402,7 +402,9 @@ namespace earb {
                 // columns 0..15: sum_n x * g_a (start point), 16..31: sum_n x * g_b (end point)
                 const float sa = a[m] + b[m];
                 const float sb = a[16 + m] + b[16 + m];
-                if (EARB_RENDER_EXPERIMENT < 3) __stcs(out + (long)m * out_stride + t, ramp ? fmaf(p, sb - sa, sa) : sa);
+                float r = ramp ? fmaf(p, sb - sa, sa) : sa;
+                if (accumulate) r += __ldcs(out + (long)m * out_stride + t);  // mix into the bus
+                if (EARB_RENDER_EXPERIMENT < 3) __stcs(out + (long)m * out_stride + t, r);
               }
             }
           }
@@ -506,7 +508,7 @@ namespace earb {
   // Returns false when the TMA descriptor cannot be built (the caller then uses the FFMA path).
   bool launch_render_tc(int N, int M, const float *in, long in_stride, long n_samples, float *out,
                         long out_stride, const RenderItem *d_items, long n_tiles,
-                        const RenderSegment *d_segs, const float *d_images, int n_sms,
+                        const RenderSegment *d_segs, const float *d_images, int n_sms, int accumulate,
                         cudaStream_t stream) {
     if (n_tiles <= 0) return true;
     EncodeTiledFn encode = encode_tiled();
@@ -530,7 +532,7 @@ namespace earb {
     }
     const unsigned grid = (unsigned)std::min<long>(n_tiles, n_sms > 0 ? n_sms : 148);
     render_tc_persistent_kernel<<<grid, kThreadsP, smem, stream>>>(
-        map, N, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(N, M));
+        map, N, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(N, M), accumulate);
     return true;
   }
 }  // namespace earb

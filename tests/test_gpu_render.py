@@ -113,3 +113,26 @@ def test_linearity_full_size_channels(eb):
     gi.set_points(samples, gains)
     rx, ry, rxy = gi.process(0, x), gi.process(0, y), gi.process(0, 0.5 * x + y)
     assert np.abs(rxy - (0.5 * rx + ry)).max() / np.abs(rxy).max() < 1e-5
+
+
+@pytest.mark.parametrize("T,call", [(4096 + 37, None), (3000, 700)])
+def test_accumulate_mixes_channel_groups(eb, ref, T, call):
+    """Extension earb200_interp_set_accumulate: two groups of objects rendered one after the other
+    into the same bus equal one interpolator over all of them (the reference on the full matrix)."""
+    rng = np.random.default_rng(21)
+    N, M = 48, 12
+    x = rng.normal(0, 0.25, (N, T)).astype(np.float32)
+    samples = np.arange(-100, T + 512, 512)
+    g = (rng.uniform(0, 1, (len(samples), N, M)) / 4).astype(np.float32)
+    exp = ref.interp_matrix(x, samples, g)
+    a, b = eb.GainInterpolator(32, M), eb.GainInterpolator(16, M)
+    a.set_points(samples, g[:, :32])
+    b.set_points(samples, g[:, 32:])
+    b.set_accumulate(True)
+    outs = []
+    step = call or T
+    for t in range(0, T, step):
+        bus = a.process(t, x[:32, t:t + step])
+        outs.append(b.process(t, x[32:, t:t + step], out=bus))
+    out = np.concatenate(outs, axis=1)
+    assert np.abs(out - exp).max() / np.abs(exp).max() < 1e-6

@@ -12,7 +12,7 @@ timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench_$tag.json 2
 cat gpurun_out/bench_$tag.json
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref_$tag.json 2> gpurun_out/bench_ref_$tag.err; echo "ref rc=$?"
 cat gpurun_out/bench_ref_$tag.json
-PCMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-render-e2e --no-e2e"
+PCMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-render-e2e --no-e2e --no-mix"
 timeout 600 $PCMD > gpurun_out/plain_$tag.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_$tag.csv $PCMD > gpurun_out/ncu_launches_$tag.log 2>&1
 echo "ncu launches rc=$?"
