@@ -53,41 +53,48 @@ class ClockSampler:
     def __init__(self, gpu_index):
         self.proc = None
         self.gpu = gpu_index
+        self.sm, self.smax, self.reasons, self.available = [], [], set(), True
 
     def start(self):
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
+            self.available = False
 
     def stop(self):
+        """Ends one sampling window; samples accumulate over windows (one per timed region)."""
         if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return
         self.proc.terminate()
         try:
             out, _ = self.proc.communicate(timeout=5)
         except subprocess.TimeoutExpired:
             self.proc.kill()
             out, _ = self.proc.communicate()
-        sm, smax, reasons = [], [], set()
+        self.proc = None
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         for line in out.strip().splitlines():
             f = [x.strip() for x in line.split(",")]
             if len(f) < 8:
                 continue
             try:
-                sm.append(float(f[1]))
-                smax.append(float(f[2]))
+                self.sm.append(float(f[1]))
+                self.smax.append(float(f[2]))
             except ValueError:
                 continue
             for name, v in zip(names, f[4:8]):
                 if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None,
-                "sm_max_mhz": float(max(smax)) if smax else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                    self.reasons.add(name)
+
+    def summary(self):
+        if not self.sm and not self.available:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None,
+                "sm_max_mhz": float(max(self.smax)) if self.smax else None,
+                "samples": len(self.sm), "reasons": sorted(self.reasons)}
 
 
 def measured_peaks():
@@ -201,7 +208,19 @@ def run_ours(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        # NCCL prints its version banner on stdout at the first collective; stdout carries exactly
+        # one JSON line, so the banner is sent to stderr
+        sys.stdout.flush()
+        saved = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            warm = torch.zeros(1, device=dev)
+            dist.all_reduce(warm)
+            torch.cuda.synchronize()
+        finally:
+            os.dup2(saved, 1)
+            os.close(saved)
 
     def barrier():
         torch.cuda.synchronize()
@@ -246,7 +265,7 @@ def run_ours(args):
         step_objects()
     ev1.record()
     barrier()
-    clocks = sampler.stop()
+    sampler.stop()
     ms_total = max_over_ranks(ev0.elapsed_time(ev1))
     core_ms, core_launches, _ = gc.kernel_time()
     gc.set_profiling(False)
@@ -308,11 +327,13 @@ def run_ours(args):
         gi.set_profiling(True)
         rl0 = gi.launch_count
         r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler.start()
         r0.record()
         for _ in range(args.steps):
             step_render()
         r1.record()
         barrier()
+        sampler.stop()
         r_ms = max_over_ranks(r0.elapsed_time(r1))
         k_ms, k_launches = gi.kernel_time()
         gi.set_profiling(False)
@@ -376,11 +397,13 @@ def run_ours(args):
         conv.set_profiling(True)
         cl0 = conv.launch_count
         c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler.start()
         c0.record()
         for _ in range(args.steps):
             step_conv()
         c1.record()
         barrier()
+        sampler.stop()
         c_ms = max_over_ranks(c0.elapsed_time(c1))
         ck_ms, ck_n = conv.kernel_time()
         conv.set_profiling(False)
@@ -492,11 +515,13 @@ def run_ours(args):
         barrier()
         ml0 = sum(gi.launch_count for _, _, gi in groups)
         m0, m1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler.start()
         m0.record()
         for _ in range(args.steps):
             step_mix()
         m1.record()
         barrier()
+        sampler.stop()
         mix_ms = max_over_ranks(m0.elapsed_time(m1)) / args.steps
         gpu_launches += (sum(gi.launch_count for _, _, gi in groups) - ml0)
         reduce_ms = None
@@ -546,7 +571,7 @@ def run_ours(args):
             "e2e": {"value": e2e_value, "unit": "vectors/s", "h2d_bytes_per_step": 8 * 8 * n,
                     "d2h_bytes_per_step": 2 * 4 * C_out * n, "steps": e2e_steps, "checksum": e2e_checksum},
             "gpu_launches": int(gpu_launches),
-            "clocks": clocks,
+            "clocks": sampler.summary(),
         }
         if render is not None:
             line["render"] = render

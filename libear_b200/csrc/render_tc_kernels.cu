@@ -386,6 +386,17 @@ namespace earb {
           const RenderItem item = items[tile];
           const RenderSegment seg = segs[item.seg];
           const bool ramp = seg.ramp != 0;
+          // accumulate mode: the bus values this thread will add to are fetched before waiting for
+          // the accumulators, so their latency hides behind the MMAs of this tile
+          float prev[kMT][16];
+          if (accumulate) {
+#pragma unroll
+            for (int j = 0; j < kMT; j++) {
+              const long tp = item.t0 + j * 128 + q * 32 + lane;
+#pragma unroll
+              for (int m = 0; m < 16; m++) prev[j][m] = (m < M) ? __ldcs(out + (long)m * out_stride + tp) : 0.0f;
+            }
+          }
           mbar_wait(&acc_full[ab], (uint32_t)((L >> 1) & 1));
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t acc = lane_base + ab * kAccStride;
@@ -403,7 +414,7 @@ namespace earb {
                 const float sa = a[m] + b[m];
                 const float sb = a[16 + m] + b[16 + m];
                 float r = ramp ? fmaf(p, sb - sa, sa) : sa;
-                if (accumulate) r += __ldcs(out + (long)m * out_stride + t);  // mix into the bus
+                if (accumulate) r += prev[j][m];  // mix into the bus
                 if (EARB_RENDER_EXPERIMENT < 3) __stcs(out + (long)m * out_stride + t, r);
               }
             }
