@@ -88,6 +88,16 @@ struct earb200_objects {
   int64_t launches = 0;
   KernelTimer timer;
   int64_t timed_passes = 0;
+  // streams / events of the pipelined *_host entry point
+  cudaStream_t s_in = nullptr, s_compute = nullptr, s_out = nullptr;
+  std::vector<cudaEvent_t> ev_in, ev_done;
+  ~earb200_objects() {
+    for (cudaEvent_t e : ev_in) cudaEventDestroy(e);
+    for (cudaEvent_t e : ev_done) cudaEventDestroy(e);
+    if (s_in) cudaStreamDestroy(s_in);
+    if (s_compute) cudaStreamDestroy(s_compute);
+    if (s_out) cudaStreamDestroy(s_out);
+  }
 };
 
 namespace {
@@ -196,44 +206,99 @@ namespace {
     }
   }
 
+  // one chunk (<= kChunk objects starting at `start`) through prelude -> extent core -> epilogue
+  template <typename OutT>
+  void objects_run_chunk(earb200_objects &o, int64_t start, int64_t m, const ObjectsSoA &in, int n_out,
+                         const int32_t *d_out_index, OutT *d_direct, OutT *d_diffuse, int32_t *d_region,
+                         cudaStream_t stream) {
+    ObjectsSoA c = in;
+    if (c.xyz) {
+      c.xyz += 3 * start;
+    } else {
+      c.azimuth += start;
+      c.elevation += start;
+      c.distance += start;
+    }
+    c.width += start;
+    c.height += start;
+    c.depth += start;
+    c.gain += start;
+    c.diffuse += start;
+    EARB_CUDA(cudaMemsetAsync(o.d_n_active.ptr, 0, sizeof(unsigned int), stream));
+    launch_objects_prelude(m, c, o.d_passes.ptr, o.d_aux.ptr, o.d_n_active.ptr, stream);
+    o.timer.start(stream);
+    if (o.use_tc)
+      launch_extent_core_tc(o.grid, o.d_grid_points.ptr, o.d_grid_bimage.ptr, o.d_n_active.ptr, o.d_passes.ptr,
+                            o.d_results.ptr, o.n_sms, stream);
+    else
+      launch_extent_core(o.grid, o.d_grid_xyz.ptr, o.d_grid_gains.ptr, o.d_grid_sums.ptr, o.d_n_active.ptr,
+                         o.d_passes.ptr, o.d_results.ptr, o.d_counter.ptr, o.n_sms, stream);
+    o.timer.stop(stream);
+    if (o.timer.enabled) o.timed_passes += 2 * m;
+    launch_objects_epilogue<OutT>(o.panner.d_tables, m, c, o.d_passes.ptr, o.d_aux.ptr, o.d_results.ptr, n_out,
+                                  d_out_index, d_direct + start * n_out, d_diffuse + start * n_out,
+                                  d_region ? d_region + start : nullptr, stream);
+    o.launches += 3;
+  }
+
   template <typename OutT>
   void objects_run(earb200_objects &o, int64_t n, const ObjectsSoA &in, int n_out,
                    const int32_t *d_out_index, OutT *d_direct, OutT *d_diffuse,
                    int32_t *d_region, cudaStream_t stream) {
-    for (int64_t start = 0; start < n; start += earb200_objects::kChunk) {
+    for (int64_t start = 0; start < n; start += earb200_objects::kChunk)
+      objects_run_chunk<OutT>(o, start, std::min<int64_t>(earb200_objects::kChunk, n - start), in, n_out,
+                              d_out_index, d_direct, d_diffuse, d_region, stream);
+    EARB_CUDA(cudaGetLastError());
+  }
+
+  // Host buffers in, host buffers out, software-pipelined per chunk over three streams: while chunk
+  // k is computed, chunk k + 1 is on its way in and chunk k - 1 on its way out (the copies overlap
+  // the kernels when the caller's buffers are pinned; with pageable memory they still work, staged).
+  template <typename OutT>
+  void objects_host_pipeline(earb200_objects &o, int64_t n, const double *const src[8], OutT *direct,
+                             OutT *diffuse, int32_t *region_idx) {
+    if (!o.s_in) {
+      EARB_CUDA(cudaStreamCreateWithFlags(&o.s_in, cudaStreamNonBlocking));
+      EARB_CUDA(cudaStreamCreateWithFlags(&o.s_compute, cudaStreamNonBlocking));
+      EARB_CUDA(cudaStreamCreateWithFlags(&o.s_out, cudaStreamNonBlocking));
+    }
+    const int64_t n_chunks = (n + earb200_objects::kChunk - 1) / earb200_objects::kChunk;
+    while ((int64_t)o.ev_in.size() < n_chunks) {
+      cudaEvent_t a, b;
+      EARB_CUDA(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+      EARB_CUDA(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+      o.ev_in.push_back(a);
+      o.ev_done.push_back(b);
+    }
+    double *d = o.d_in.reserve(8 * (size_t)n);
+    ObjectsSoA soa{d, d + n, d + 2 * n, d + 3 * n, d + 4 * n, d + 5 * n, d + 6 * n, d + 7 * n, nullptr};
+    int32_t *d_reg = region_idx ? o.d_region.reserve(n) : nullptr;
+    const size_t n_el = (size_t)n * o.n_out;
+    OutT *d_out = reinterpret_cast<OutT *>(sizeof(OutT) == 8 ? (void *)o.d_out_d.reserve(2 * n_el)
+                                                              : (void *)o.d_out_f.reserve(2 * n_el));
+    OutT *d_direct = d_out, *d_diffuse = d_out + n_el;
+    for (int64_t k = 0; k < n_chunks; k++) {
+      const int64_t start = k * earb200_objects::kChunk;
       const int64_t m = std::min<int64_t>(earb200_objects::kChunk, n - start);
-      ObjectsSoA c = in;
-      if (c.xyz) {
-        c.xyz += 3 * start;
-      } else {
-        c.azimuth += start;
-        c.elevation += start;
-        c.distance += start;
-      }
-      c.width += start;
-      c.height += start;
-      c.depth += start;
-      c.gain += start;
-      c.diffuse += start;
-      EARB_CUDA(cudaMemsetAsync(o.d_n_active.ptr, 0, sizeof(unsigned int), stream));
-      launch_objects_prelude(m, c, o.d_passes.ptr, o.d_aux.ptr, o.d_n_active.ptr, stream);
-      o.timer.start(stream);
-      if (o.use_tc)
-        launch_extent_core_tc(o.grid, o.d_grid_points.ptr, o.d_grid_bimage.ptr, o.d_n_active.ptr,
-                              o.d_passes.ptr, o.d_results.ptr, o.n_sms, stream);
-      else
-        launch_extent_core(o.grid, o.d_grid_xyz.ptr, o.d_grid_gains.ptr, o.d_grid_sums.ptr,
-                           o.d_n_active.ptr, o.d_passes.ptr, o.d_results.ptr, o.d_counter.ptr, o.n_sms,
-                           stream);
-      o.timer.stop(stream);
-      if (o.timer.enabled) o.timed_passes += 2 * m;
-      launch_objects_epilogue<OutT>(o.panner.d_tables, m, c, o.d_passes.ptr, o.d_aux.ptr,
-                                    o.d_results.ptr, n_out, d_out_index, d_direct + start * n_out,
-                                    d_diffuse + start * n_out, d_region ? d_region + start : nullptr,
-                                    stream);
-      o.launches += 3;
+      for (int f = 0; f < 8; f++)
+        EARB_CUDA(cudaMemcpyAsync(d + (size_t)f * n + start, src[f] + start, sizeof(double) * m,
+                                  cudaMemcpyHostToDevice, o.s_in));
+      EARB_CUDA(cudaEventRecord(o.ev_in[k], o.s_in));
+      EARB_CUDA(cudaStreamWaitEvent(o.s_compute, o.ev_in[k], 0));
+      objects_run_chunk<OutT>(o, start, m, soa, o.n_out, o.d_out_index.ptr, d_direct, d_diffuse, d_reg,
+                              o.s_compute);
+      EARB_CUDA(cudaEventRecord(o.ev_done[k], o.s_compute));
+      EARB_CUDA(cudaStreamWaitEvent(o.s_out, o.ev_done[k], 0));
+      const size_t off = (size_t)start * o.n_out, cnt = (size_t)m * o.n_out;
+      EARB_CUDA(cudaMemcpyAsync(direct + off, d_direct + off, sizeof(OutT) * cnt, cudaMemcpyDeviceToHost, o.s_out));
+      EARB_CUDA(cudaMemcpyAsync(diffuse + off, d_diffuse + off, sizeof(OutT) * cnt, cudaMemcpyDeviceToHost, o.s_out));
+      if (region_idx)
+        EARB_CUDA(cudaMemcpyAsync(region_idx + start, d_reg + start, sizeof(int32_t) * m, cudaMemcpyDeviceToHost,
+                                  o.s_out));
     }
     EARB_CUDA(cudaGetLastError());
+    EARB_CUDA(cudaStreamSynchronize(o.s_out));
+    EARB_CUDA(cudaStreamSynchronize(o.s_compute));
   }
 }  // namespace
 
@@ -418,29 +483,12 @@ int earb200_objects_calculate_host(earb200_objects *calc, int64_t n,
     use_device(o.device);
     const double *src[8] = {in->azimuth, in->elevation, in->distance, in->width,
                             in->height,  in->depth,     in->gain,     in->diffuse};
-    double *d = o.d_in.reserve(8 * (size_t)n);
-    for (int k = 0; k < 8; k++) {
+    for (int k = 0; k < 8; k++)
       if (!src[k]) throw Error(INVALID_ARGUMENT, "null input array");
-      EARB_CUDA(cudaMemcpyAsync(d + (size_t)k * n, src[k], sizeof(double) * n,
-                                cudaMemcpyHostToDevice, 0));
-    }
-    ObjectsSoA soa{d, d + n, d + 2 * n, d + 3 * n, d + 4 * n, d + 5 * n, d + 6 * n, d + 7 * n, nullptr};
-    int32_t *d_reg = region_idx ? o.d_region.reserve(n) : nullptr;
-    const size_t n_el = (size_t)n * o.n_out;
-    if (out_is_double) {
-      double *dd = o.d_out_d.reserve(2 * n_el);
-      objects_run<double>(o, n, soa, o.n_out, o.d_out_index.ptr, dd, dd + n_el, d_reg, 0);
-      EARB_CUDA(cudaMemcpyAsync(direct, dd, sizeof(double) * n_el, cudaMemcpyDeviceToHost, 0));
-      EARB_CUDA(cudaMemcpyAsync(diffuse, dd + n_el, sizeof(double) * n_el, cudaMemcpyDeviceToHost, 0));
-    } else {
-      float *df = o.d_out_f.reserve(2 * n_el);
-      objects_run<float>(o, n, soa, o.n_out, o.d_out_index.ptr, df, df + n_el, d_reg, 0);
-      EARB_CUDA(cudaMemcpyAsync(direct, df, sizeof(float) * n_el, cudaMemcpyDeviceToHost, 0));
-      EARB_CUDA(cudaMemcpyAsync(diffuse, df + n_el, sizeof(float) * n_el, cudaMemcpyDeviceToHost, 0));
-    }
-    if (region_idx)
-      EARB_CUDA(cudaMemcpyAsync(region_idx, d_reg, sizeof(int32_t) * n, cudaMemcpyDeviceToHost, 0));
-    EARB_CUDA(cudaStreamSynchronize(0));
+    if (out_is_double)
+      objects_host_pipeline<double>(o, n, src, (double *)direct, (double *)diffuse, region_idx);
+    else
+      objects_host_pipeline<float>(o, n, src, (float *)direct, (float *)diffuse, region_idx);
   });
 }
 
