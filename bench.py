@@ -446,7 +446,9 @@ def run_ours(args):
         lay5 = "4+7+0"
         T5 = args.mix_samples
         n_total = args.mix_objects
-        n_local = n_total // world
+        from libear_b200.sharding import object_groups, reduce_bus, shard_range
+        obj_a, obj_b = shard_range(n_total, rank, world)
+        n_local = obj_b - obj_a
         # HOA order 3 (ACN 0..15, SN3D): design on the device, apply as a static 16 -> 12 matrix
         hoa = eb.GainCalculatorHOA(lay5, device=local_rank)
         orders = [n for n in range(4) for _ in range(2 * n + 1)]
@@ -489,8 +491,7 @@ def run_ours(args):
             d_k, _ = gc5.calculate(az, base[1], base[2], base[3], base[4], base[5], base[6], 0.0)
             gains5[k] = d_k
         groups = []
-        for g0 in range(0, n_local, 256):
-            g1 = min(n_local, g0 + 256)
+        for g0, g1 in object_groups(n_local, 256):
             gi = eb.GainInterpolator(g1 - g0, M5, device=local_rank)
             gi.set_points(samples5, gains5[:, g0:g1])
             gi.set_accumulate(g0 > 0)
@@ -506,7 +507,7 @@ def run_ours(args):
             if world > 1:
                 if timed_reduce:
                     red0.record()
-                dist.all_reduce(bus)   # the one collective: sum of the per-GPU partial buses
+                reduce_bus(bus)   # the one collective: sum of the per-GPU partial buses
                 if timed_reduce:
                     red1.record()
 
@@ -532,7 +533,7 @@ def run_ours(args):
         mix_bytes = 4.0 * T5 * (n_local + M5 * (2 * len(groups) - 1)) + 4.0 * n_local * M5 * n_pts
         mix_block = {
             "metric": "object mixing Msamples/s (input object-samples, whole job)",
-            "value": n_local * world * T5 / (mix_ms * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": mix_ms,
+            "value": n_total * T5 / (mix_ms * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": mix_ms,
             "scaling": "strong",
             "config": {"workload": f"cfg5: {n_total} extent objects x {T5 / 48000:.0f} s x 48 kHz into {lay5} (M={M5}), "
                                    f"{n_local} objects/GPU in groups of 256, gains from GainCalculatorObjects at "

@@ -1,0 +1,79 @@
+"""Multi-GPU plan on CPU: world-size-2 gloo processes.  Objects shard contiguously with
+no collective; object-sharded mixing sums per-rank partial buses with one all-reduce.  The per-rank
+rendering is done by the numpy oracle here (test infrastructure) -- what is under test is the
+sharding arithmetic and the reduce, the same code bench.py drives over NCCL."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from libear_b200.sharding import object_groups, reduce_bus, shard_range
+
+
+def test_shard_range_is_a_partition():
+    for n in (0, 1, 7, 512, 4096, 1_000_003):
+        for world in (1, 2, 3, 8):
+            parts = [shard_range(n, r, world) for r in range(world)]
+            assert parts[0][0] == 0 and parts[-1][1] == n
+            assert all(parts[i][1] == parts[i + 1][0] for i in range(world - 1))
+            sizes = [b - a for a, b in parts]
+            assert max(sizes) - min(sizes) <= 1
+    with pytest.raises(ValueError):
+        shard_range(10, 2, 2)
+
+
+def test_object_groups():
+    assert object_groups(512) == [(0, 256), (256, 512)]
+    assert object_groups(300) == [(0, 256), (256, 300)]
+    assert object_groups(0) == []
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import ear_oracle as eo
+        rng = np.random.default_rng(7)          # same seed on every rank: the global problem
+        N, M, T = 10, 6, 1500
+        x = rng.normal(0, 0.25, (N, T)).astype(np.float32)
+        samples = np.array([0, 400, 400, 1100, 2000])
+        gains = rng.uniform(0, 1, (len(samples), N, M)).astype(np.float32)
+        a, b = shard_range(N, rank, world)
+        partial = np.zeros((M, T), dtype=np.float32)
+        for g0, g1 in object_groups(b - a, max_group=3):          # groups accumulate into the bus
+            partial += eo.interp_matrix(x[a + g0:a + g1], samples, gains[:, a + g0:a + g1])
+        bus = torch.from_numpy(partial.copy())
+        reduce_bus(bus)
+        full = eo.interp_matrix(x, samples, gains)
+        err = float(np.abs(bus.numpy() - full).max() / np.abs(full).max())
+        # gains shard with no collective: each rank's rows are just a slice of the global answer
+        pan = eo.PointSourcePanner("0+5+0")
+        dirs = rng.normal(size=(64, 3))
+        sl = slice(*shard_range(64, rank, world))
+        mine, mine_region, _ = pan.handle(dirs[sl])
+        full_gains, full_region, _ = pan.handle(dirs)
+        ok_slice = bool(np.array_equal(mine, full_gains[sl]) and np.array_equal(mine_region, full_region[sl]))
+        np.save(os.path.join(out_dir, f"r{rank}.npy"), np.array([err, float(ok_slice), a, b]))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_object_sharded_mixing_world2(tmp_path):
+    world = 2
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    res = [np.load(tmp_path / f"r{r}.npy") for r in range(world)]
+    assert [tuple(r[2:]) for r in res] == [(0.0, 5.0), (5.0, 10.0)]
+    for r in res:
+        assert r[0] < 1e-6      # summed partial buses == the full render (within the audio tolerance)
+        assert r[1] == 1.0
