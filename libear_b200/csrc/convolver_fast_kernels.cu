@@ -11,10 +11,11 @@
 //    applied to all 1024 bins.
 //  * one warp owns one pair: lane L holds elements L + 32 r (r = 0..31) in registers.  A 1024-point
 //    transform is two register-resident 32-point transforms per lane around ONE transposition
-//    through shared memory (1024 = 32 x 32); forward uses decimation in frequency (natural in,
-//    bit-reversed out), the inverse decimation in time (bit-reversed in, natural out), so no
-//    reordering pass exists.  After the inverse, y[n] and y[n + 512] sit in the same lane, so the
-//    overlap-add and the tail carried to the next pair never leave the registers.
+//    through shared memory (1024 = 32 x 32).  Three of the four 32-point stages are decimation in
+//    time (bit-reversed in, natural out; six-FMA butterflies), one is decimation in frequency
+//    (natural in, bit-reversed out), chained so that no reordering pass exists -- every register
+//    index is a compile-time constant.  After the inverse, y[n] and y[n + 512] sit in the same
+//    lane, so the overlap-add and the tail carried to the next pair never leave the registers.
 //  * a warp walks a run of consecutive pairs of its channel; the tail a run needs from before
 //    its first pair is recomputed from one halo block.
 #include <cuda_runtime.h>
