@@ -77,9 +77,17 @@ struct earb200_objects {
   int use_tc = 1;  // EARB200_EXTENT_PATH=cuda selects the FFMA warp-per-pass core
   // per-chunk scratch
   static constexpr int64_t kChunk = 131072;
-  DeviceBuffer<ExtentPass> d_passes;
-  DeviceBuffer<ObjectAux> d_aux;
-  DeviceBuffer<float> d_results;
+  // two scratch sets: the FP64 epilogue of chunk k runs on a side stream while the extent core of
+  // chunk k + 1 (a different pipe mix: FP32 issue + tensor) already occupies the SMs
+  struct Scratch {
+    DeviceBuffer<ExtentPass> d_passes;
+    DeviceBuffer<ObjectAux> d_aux;
+    DeviceBuffer<float> d_results;
+    DeviceBuffer<unsigned int> d_n_active;
+    cudaEvent_t ev_core = nullptr, ev_epi = nullptr;
+  } scratch[2];
+  cudaStream_t s_epi = nullptr;
+  int64_t chunk_counter = 0;
   DeviceBuffer<unsigned long long> d_counter;
   // staging for the *_host entry points
   DeviceBuffer<double> d_in, d_out_d;
@@ -94,6 +102,11 @@ struct earb200_objects {
   ~earb200_objects() {
     for (cudaEvent_t e : ev_in) cudaEventDestroy(e);
     for (cudaEvent_t e : ev_done) cudaEventDestroy(e);
+    for (Scratch &sc : scratch) {
+      if (sc.ev_core) cudaEventDestroy(sc.ev_core);
+      if (sc.ev_epi) cudaEventDestroy(sc.ev_epi);
+    }
+    if (s_epi) cudaStreamDestroy(s_epi);
     if (s_in) cudaStreamDestroy(s_in);
     if (s_compute) cudaStreamDestroy(s_compute);
     if (s_out) cudaStreamDestroy(s_out);
@@ -178,13 +191,18 @@ namespace {
       extent_tc_build_bimage(o.grid, fg.data(), image.data());
       EARB_CUDA(cudaMemcpy(o.d_grid_bimage.reserve(image.size()), image.data(), sizeof(float) * image.size(),
                            cudaMemcpyHostToDevice));
-      o.d_n_active.reserve(1);
       const char *path = std::getenv("EARB200_EXTENT_PATH");
       o.use_tc = !(path && std::string(path) == "cuda");
     }
-    o.d_passes.reserve(2 * earb200_objects::kChunk);
-    o.d_aux.reserve(earb200_objects::kChunk);
-    o.d_results.reserve(2 * earb200_objects::kChunk * EARB_MAX_SPK);
+    for (earb200_objects::Scratch &sc : o.scratch) {
+      sc.d_passes.reserve(2 * earb200_objects::kChunk);
+      sc.d_aux.reserve(earb200_objects::kChunk);
+      sc.d_results.reserve(2 * earb200_objects::kChunk * EARB_MAX_SPK);
+      sc.d_n_active.reserve(1);
+      EARB_CUDA(cudaEventCreateWithFlags(&sc.ev_core, cudaEventDisableTiming));
+      EARB_CUDA(cudaEventCreateWithFlags(&sc.ev_epi, cudaEventDisableTiming));
+    }
+    EARB_CUDA(cudaStreamCreateWithFlags(&o.s_epi, cudaStreamNonBlocking));
     o.d_counter.reserve(1);
   }
 
@@ -206,11 +224,12 @@ namespace {
     }
   }
 
-  // one chunk (<= kChunk objects starting at `start`) through prelude -> extent core -> epilogue
+  // one chunk (<= kChunk objects starting at `start`): prelude -> extent core on `stream`, the
+  // epilogue on the side stream.  Returns the event that marks the chunk's outputs complete.
   template <typename OutT>
-  void objects_run_chunk(earb200_objects &o, int64_t start, int64_t m, const ObjectsSoA &in, int n_out,
-                         const int32_t *d_out_index, OutT *d_direct, OutT *d_diffuse, int32_t *d_region,
-                         cudaStream_t stream) {
+  cudaEvent_t objects_run_chunk(earb200_objects &o, int64_t start, int64_t m, const ObjectsSoA &in, int n_out,
+                                const int32_t *d_out_index, OutT *d_direct, OutT *d_diffuse, int32_t *d_region,
+                                cudaStream_t stream) {
     ObjectsSoA c = in;
     if (c.xyz) {
       c.xyz += 3 * start;
@@ -224,21 +243,33 @@ namespace {
     c.depth += start;
     c.gain += start;
     c.diffuse += start;
-    EARB_CUDA(cudaMemsetAsync(o.d_n_active.ptr, 0, sizeof(unsigned int), stream));
-    launch_objects_prelude(m, c, o.d_passes.ptr, o.d_aux.ptr, o.d_n_active.ptr, stream);
+    earb200_objects::Scratch &sc = o.scratch[o.chunk_counter++ & 1];
+    // the epilogue of the chunk that used this scratch set two chunks ago must have read it
+    EARB_CUDA(cudaStreamWaitEvent(stream, sc.ev_epi, 0));
+    EARB_CUDA(cudaMemsetAsync(sc.d_n_active.ptr, 0, sizeof(unsigned int), stream));
+    launch_objects_prelude(m, c, sc.d_passes.ptr, sc.d_aux.ptr, sc.d_n_active.ptr, stream);
     o.timer.start(stream);
     if (o.use_tc)
-      launch_extent_core_tc(o.grid, o.d_grid_points.ptr, o.d_grid_bimage.ptr, o.d_n_active.ptr, o.d_passes.ptr,
-                            o.d_results.ptr, o.n_sms, stream);
+      launch_extent_core_tc(o.grid, o.d_grid_points.ptr, o.d_grid_bimage.ptr, sc.d_n_active.ptr, sc.d_passes.ptr,
+                            sc.d_results.ptr, o.n_sms, stream);
     else
-      launch_extent_core(o.grid, o.d_grid_xyz.ptr, o.d_grid_gains.ptr, o.d_grid_sums.ptr, o.d_n_active.ptr,
-                         o.d_passes.ptr, o.d_results.ptr, o.d_counter.ptr, o.n_sms, stream);
+      launch_extent_core(o.grid, o.d_grid_xyz.ptr, o.d_grid_gains.ptr, o.d_grid_sums.ptr, sc.d_n_active.ptr,
+                         sc.d_passes.ptr, sc.d_results.ptr, o.d_counter.ptr, o.n_sms, stream);
     o.timer.stop(stream);
     if (o.timer.enabled) o.timed_passes += 2 * m;
-    launch_objects_epilogue<OutT>(o.panner.d_tables, m, c, o.d_passes.ptr, o.d_aux.ptr, o.d_results.ptr, n_out,
+    EARB_CUDA(cudaEventRecord(sc.ev_core, stream));
+    EARB_CUDA(cudaStreamWaitEvent(o.s_epi, sc.ev_core, 0));
+    launch_objects_epilogue<OutT>(o.panner.d_tables, m, c, sc.d_passes.ptr, sc.d_aux.ptr, sc.d_results.ptr, n_out,
                                   d_out_index, d_direct + start * n_out, d_diffuse + start * n_out,
-                                  d_region ? d_region + start : nullptr, stream);
+                                  d_region ? d_region + start : nullptr, o.s_epi);
+    EARB_CUDA(cudaEventRecord(sc.ev_epi, o.s_epi));
     o.launches += 3;
+    return sc.ev_epi;
+  }
+
+  // joins the side stream: everything launched so far is ordered before later work on `stream`
+  void objects_join(earb200_objects &o, cudaStream_t stream) {
+    for (earb200_objects::Scratch &sc : o.scratch) EARB_CUDA(cudaStreamWaitEvent(stream, sc.ev_epi, 0));
   }
 
   template <typename OutT>
@@ -248,6 +279,7 @@ namespace {
     for (int64_t start = 0; start < n; start += earb200_objects::kChunk)
       objects_run_chunk<OutT>(o, start, std::min<int64_t>(earb200_objects::kChunk, n - start), in, n_out,
                               d_out_index, d_direct, d_diffuse, d_region, stream);
+    objects_join(o, stream);
     EARB_CUDA(cudaGetLastError());
   }
 
@@ -285,10 +317,9 @@ namespace {
                                   cudaMemcpyHostToDevice, o.s_in));
       EARB_CUDA(cudaEventRecord(o.ev_in[k], o.s_in));
       EARB_CUDA(cudaStreamWaitEvent(o.s_compute, o.ev_in[k], 0));
-      objects_run_chunk<OutT>(o, start, m, soa, o.n_out, o.d_out_index.ptr, d_direct, d_diffuse, d_reg,
-                              o.s_compute);
-      EARB_CUDA(cudaEventRecord(o.ev_done[k], o.s_compute));
-      EARB_CUDA(cudaStreamWaitEvent(o.s_out, o.ev_done[k], 0));
+      cudaEvent_t done = objects_run_chunk<OutT>(o, start, m, soa, o.n_out, o.d_out_index.ptr, d_direct,
+                                                 d_diffuse, d_reg, o.s_compute);
+      EARB_CUDA(cudaStreamWaitEvent(o.s_out, done, 0));
       const size_t off = (size_t)start * o.n_out, cnt = (size_t)m * o.n_out;
       EARB_CUDA(cudaMemcpyAsync(direct + off, d_direct + off, sizeof(OutT) * cnt, cudaMemcpyDeviceToHost, o.s_out));
       EARB_CUDA(cudaMemcpyAsync(diffuse + off, d_diffuse + off, sizeof(OutT) * cnt, cudaMemcpyDeviceToHost, o.s_out));
@@ -299,6 +330,7 @@ namespace {
     EARB_CUDA(cudaGetLastError());
     EARB_CUDA(cudaStreamSynchronize(o.s_out));
     EARB_CUDA(cudaStreamSynchronize(o.s_compute));
+    EARB_CUDA(cudaStreamSynchronize(o.s_epi));
   }
 }  // namespace
 

@@ -141,17 +141,23 @@ namespace earb {
       float b[9];
       float ct0, ct1, cc0, cc1;
       float sin_thr;  // straight-line part when circle_test_dot >= sin_thr (0, or +inf if circular)
-      float cos_start, cos_end, nsin_start, nsin_end;  // sin thresholds negated
-      float m, c;
+      float m, c;     // fade: weight = m * angle + c between the start and end angles
+      float a_sin;    // m * pi/2 + c
+      float a_neg;    // m * pi + c
     };
 
-    // Weight of one virtual source (ref polar_extent_simd.hpp:39-95): same comparisons and
-    // operation order as the reference, written branch-free.  With v = -|z'| on the straight-line
-    // part and v = circle_dot on the circle part, "weight 1" is v >= T1 and "weight 0" is
-    // v <= T0 in both parts (sin thresholds negated -- negation is exact).  The fade evaluates
-    // acos(|v|) = sqrt(1 - |v|) * P7(|v|) (Abramowitz & Stegun 4.4.46, |error| <= 2e-8) and maps
-    // it to acos(v) = pi - r for v < 0 on the circle part, asin(|z'|) = pi/2 - r on the straight
-    // part.
+    // Weight of one virtual source (ref polar_extent_simd.hpp:39-95), branch-free.
+    // The reference returns 1 for angle <= start, 0 for angle >= end and the fade
+    // m * angle + c in between; the fade is 1 at `start`, 0 at `end` and monotone, and the
+    // sentinels libear uses when an angle passes pi (pi/2 for the sine test) only ever disable a
+    // comparison whose fade value is already inside [0, 1] (polar_extent.cpp:176-199), so the whole
+    // function is clamp(m * angle + c, 0, 1) -- one saturating FMA instead of two comparisons and
+    // two selects (weights differ from the reference's by rounding at the fade ends only).
+    // angle = acos(v) on the circle part, asin(|z'|) on the straight part, both from
+    // r = acos(|v|) = sqrt(1 - |v|) * P7(|v|) (Abramowitz & Stegun 4.4.46, |error| <= 2e-8):
+    //   circle, v >= 0:  angle = r            weight = sat( m r + c)
+    //   circle, v <  0:  angle = pi - r       weight = sat(-m r + (m pi + c))
+    //   straight:        angle = pi/2 - r     weight = sat(-m r + (m pi/2 + c))
     __device__ __forceinline__ float point_weight(const PassRegs &c, float x, float y, float z) {
       const float xt = fmaf(x, c.b[0], fmaf(y, c.b[1], __fmul_rn(z, c.b[2])));
       const float yt = fmaf(x, c.b[3], fmaf(y, c.b[4], __fmul_rn(z, c.b[5])));
@@ -160,10 +166,8 @@ namespace earb {
       const float circle_test_dot = fmaf(ax, c.ct0, __fmul_rn(yt, c.ct1));
       const float circle_dot = fmaf(ax, c.cc0, __fmul_rn(yt, c.cc1));
       const bool is_sin = circle_test_dot >= c.sin_thr;
-      const float v = is_sin ? -fabsf(zt) : circle_dot;
-      const float t1 = is_sin ? c.nsin_start : c.cos_start;
-      const float t0 = is_sin ? c.nsin_end : c.cos_end;
-      const float av = fabsf(v);
+      const float v = is_sin ? zt : circle_dot;
+      const float av = fminf(fabsf(v), 1.0f);  // rounding can leave |v| a few ulp above 1
       float p = -0.0012624911f;
       p = fmaf(p, av, 0.0066700901f);
       p = fmaf(p, av, -0.0170881256f);
@@ -175,11 +179,10 @@ namespace earb {
       float sq;
       asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(__fsub_rn(1.0f, av)));
       const float r = __fmul_rn(sq, p);
-      const bool flip = is_sin || (v < 0.0f);
-      const float k = flip ? (is_sin ? 1.57079632679490f : 3.14159265358979f) : 0.0f;
-      const float angle = fmaf(flip ? -1.0f : 1.0f, r, k);
-      const float ramp = __fadd_rn(__fmul_rn(c.m, angle), c.c);
-      return (v >= t1) ? 1.0f : ((v <= t0) ? 0.0f : ramp);
+      const bool neg = circle_dot < 0.0f;
+      const float slope = (is_sin || neg) ? -c.m : c.m;
+      const float offs = is_sin ? c.a_sin : (neg ? c.a_neg : c.c);
+      return __saturatef(fmaf(slope, r, offs));
     }
 
     // Barriers
@@ -316,12 +319,10 @@ namespace earb {
             c.ct1 = e.circle_test[1];
             c.cc0 = e.circle_centre[0];
             c.cc1 = e.circle_centre[1];
-            c.cos_start = e.cos_start;
-            c.cos_end = e.cos_end;
-            c.nsin_start = -e.sin_start;
-            c.nsin_end = -e.sin_end;
             c.m = e.m;
             c.c = e.c;
+            c.a_sin = fmaf(e.m, 1.57079632679490f, e.c);
+            c.a_neg = fmaf(e.m, 3.14159265358979f, e.c);
             c.sin_thr = 0.0f;
             if (e.is_circular) {
               c.sin_thr = __int_as_float(0x7f800000);
