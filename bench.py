@@ -45,56 +45,90 @@ def synth_objects(n, seed):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    """SM clocks and throttle reasons sampled DURING the timed regions: an NVML polling thread
+    (5 ms period) that only records between start() and stop(); samples accumulate over all
+    timed regions of the run.  Falls back to one `nvidia-smi` query per window without NVML."""
+    REASONS = {"hw_slowdown": 0x8, "hw_thermal_slowdown": 0x40, "sw_thermal_slowdown": 0x20,
+               "sw_power_cap": 0x4}
 
     def __init__(self, gpu_index):
-        self.proc = None
         self.gpu = gpu_index
-        self.sm, self.smax, self.reasons, self.available = [], [], set(), True
-
-    def start(self):
+        self.sm, self.smax, self.reasons = [], [], set()
+        self.active = False
+        self.thread = None
+        self.handle = None
+        self.nvml = None
         try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "20"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-        except OSError:
-            self.proc = None
-            self.available = False
+            import pynvml
+            pynvml.nvmlInit()
+            # NVML enumerates physical devices: honour CUDA_VISIBLE_DEVICES when it is a list of indices
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = gpu_index
+            if vis:
+                ids = [v.strip() for v in vis.split(",") if v.strip()]
+                if gpu_index < len(ids) and ids[gpu_index].isdigit():
+                    phys = int(ids[gpu_index])
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nvml = pynvml
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.stop_flag = False
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.nvml = None
 
-    def stop(self):
-        """Ends one sampling window; samples accumulate over windows (one per timed region)."""
-        if self.proc is None:
-            return
-        self.proc.terminate()
+    def _sample_nvml(self):
+        n = self.nvml
+        self.sm.append(float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)))
+        self.smax.append(self.max_mhz)
         try:
-            out, _ = self.proc.communicate(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
-            out, _ = self.proc.communicate()
-        self.proc = None
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for line in out.strip().splitlines():
-            f = [x.strip() for x in line.split(",")]
-            if len(f) < 8:
-                continue
-            try:
-                self.sm.append(float(f[1]))
-                self.smax.append(float(f[2]))
-            except ValueError:
-                continue
-            for name, v in zip(names, f[4:8]):
+            mask = n.nvmlDeviceGetCurrentClocksEventReasons(self.handle)
+        except Exception:
+            mask = n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+        for name, bit in self.REASONS.items():
+            if mask & bit:
+                self.reasons.add(name)
+
+    def _poll(self):
+        while not self.stop_flag:
+            if self.active:
+                try:
+                    self._sample_nvml()
+                except Exception:
+                    pass
+            time.sleep(0.005)
+
+    def _sample_smi(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            out = subprocess.run(["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={q}",
+                                  "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=10).stdout
+            f = [x.strip() for x in out.strip().splitlines()[0].split(",")]
+            self.sm.append(float(f[0]))
+            self.smax.append(float(f[1]))
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], f[2:6]):
                 if v.lower().startswith("active"):
                     self.reasons.add(name)
+        except Exception:
+            pass
+
+    def start(self):
+        self.active = True
+        if self.nvml is None:
+            self._sample_smi()
+
+    def stop(self):
+        """Ends one sampling window; the polling thread sampled while the host sat in the closing
+        synchronize, i.e. while the GPU was running the timed steps."""
+        self.active = False
 
     def summary(self):
-        if not self.sm and not self.available:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None,
-                "sm_max_mhz": float(max(self.smax)) if self.smax else None,
-                "samples": len(self.sm), "reasons": sorted(self.reasons)}
+        if not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "samples": 0, "reasons": ["no clock samples"]}
+        return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": float(max(self.smax)),
+                "samples": len(self.sm), "reasons": sorted(self.reasons),
+                "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 def measured_peaks():
