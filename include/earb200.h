@@ -240,7 +240,39 @@ int earb200_delay_process_host(earb200_delay *d, int64_t nsamples, const float *
 int earb200_delay_process_device(earb200_delay *d, int64_t nsamples, const float *d_in,
                                  int64_t in_stride, float *d_out, int64_t out_stride,
                                  void *stream);
+/* extension: out = delay(in) + add in one pass (direct bus + decorrelated diffuse bus);
+ * d_add must not alias d_out unless it is the same pointer with the same stride */
+int earb200_delay_process_add_device(earb200_delay *d, int64_t nsamples, const float *d_in,
+                                     int64_t in_stride, const float *d_add, int64_t add_stride,
+                                     float *d_out, int64_t out_stride, void *stream);
 int64_t earb200_delay_launch_count(const earb200_delay *d);
+
+/* ------------------------------------------------ Objects signal flow (8f.1)
+ * The rendering chain libear's documentation prescribes for typeDefinition == "Objects"
+ * (docs/dsp.rst:40-71, include/ear/gain_calculators.hpp:43-56) as one device pipeline:
+ * direct and diffuse buses by two gain interpolators, the diffuse bus through the per-channel
+ * decorrelators (designDecorrelators, block size 512), the direct bus through the compensation
+ * delay (255 samples), summed.  Calls process whole blocks of 512 samples. */
+typedef struct earb200_objects_renderer earb200_objects_renderer;
+
+int earb200_objects_renderer_create(const earb200_layout *layout, int n_objects, int device,
+                                    earb200_objects_renderer **out);
+void earb200_objects_renderer_destroy(earb200_objects_renderer *r);
+int earb200_objects_renderer_num_outputs(const earb200_objects_renderer *r);
+int64_t earb200_objects_renderer_block_size(const earb200_objects_renderer *r); /* 512 */
+int earb200_objects_renderer_delay(const earb200_objects_renderer *r);          /* 255 */
+/* interpolation points: direct / diffuse gains [n_points][n_objects][C_out] (e.g. the output of
+ * earb200_objects_calculate_* per metadata block), host buffers */
+int earb200_objects_renderer_set_gains(earb200_objects_renderer *r, int64_t n_points,
+                                       const int64_t *sample_idx, const float *direct,
+                                       const float *diffuse);
+/* n_blocks * 512 samples per channel: in = n_objects planar channels, out = C_out feeds */
+int earb200_objects_renderer_process_host(earb200_objects_renderer *r, int64_t block_start,
+                                          int64_t n_blocks, const float *in, int64_t in_stride,
+                                          float *out, int64_t out_stride);
+int earb200_objects_renderer_process_device(earb200_objects_renderer *r, int64_t block_start,
+                                            int64_t n_blocks, const float *d_in, int64_t in_stride,
+                                            float *d_out, int64_t out_stride, void *stream);
 
 /* ------------------------------------------------ HOA decoder design (K5)
  * replaces ear::GainCalculatorHOA (include/ear/gain_calculators.hpp:67-82,

@@ -30,7 +30,7 @@ _lib.earb200_layout_channel_name.restype = C.c_char_p
 for _f in ("earb200_objects_launch_count", "earb200_interp_launch_count",
            "earb200_convolver_launch_count", "earb200_direct_speakers_launch_count",
            "earb200_delay_launch_count", "earb200_delay_get_delay", "earb200_fft_launch_count",
-           "earb200_fft_size"):
+           "earb200_fft_size", "earb200_objects_renderer_block_size"):
     getattr(_lib, _f).restype = C.c_int64
 
 
@@ -344,6 +344,49 @@ class BlockConvolver:
         _chk(_lib.earb200_convolver_process_device(self.h, C.c_int64(n_blocks), _ptr(d_in),
                                                    C.c_int64(in_stride), _ptr(d_out),
                                                    C.c_int64(out_stride), C.c_void_p(int(stream))))
+
+
+class ObjectsRenderer:
+    """The Objects signal flow of libear's docs (docs/dsp.rst:40-71) as one device pipeline:
+    interpolated direct / diffuse buses, decorrelators on the diffuse bus, compensation delay on
+    the direct bus, sum."""
+
+    def __init__(self, layout, n_objects, device=0):
+        self.layout = _as_layout(layout)
+        self.n_objects = n_objects
+        self.h = C.c_void_p()
+        _chk(_lib.earb200_objects_renderer_create(self.layout.h, n_objects, device, C.byref(self.h)))
+        self.num_outputs = _lib.earb200_objects_renderer_num_outputs(self.h)
+        self.block_size = _lib.earb200_objects_renderer_block_size(self.h)
+        self.delay = _lib.earb200_objects_renderer_delay(self.h)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            _lib.earb200_objects_renderer_destroy(self.h)
+            self.h = None
+
+    def set_gains(self, sample_idx, direct, diffuse):
+        s = np.ascontiguousarray(sample_idx, dtype=np.int64)
+        shape = (len(s), self.n_objects, self.num_outputs)
+        d = np.ascontiguousarray(direct, dtype=np.float32).reshape(shape)
+        f = np.ascontiguousarray(diffuse, dtype=np.float32).reshape(shape)
+        _chk(_lib.earb200_objects_renderer_set_gains(self.h, C.c_int64(len(s)), _ptr(s), _ptr(d), _ptr(f)))
+
+    def process(self, block_start, x):
+        """x: float32 [n_objects][n_blocks * 512] host array -> [C_out][n_blocks * 512]."""
+        x = np.ascontiguousarray(x, dtype=np.float32).reshape(self.n_objects, -1)
+        T = x.shape[1]
+        if T % self.block_size:
+            raise InvalidArgument("the renderer processes whole blocks of %d samples" % self.block_size)
+        out = np.zeros((self.num_outputs, T), dtype=np.float32)
+        _chk(_lib.earb200_objects_renderer_process_host(self.h, C.c_int64(block_start), C.c_int64(T // self.block_size),
+                                                        _ptr(x), C.c_int64(T), _ptr(out), C.c_int64(T)))
+        return out
+
+    def process_device(self, block_start, n_blocks, d_in, in_stride, d_out, out_stride, stream=0):
+        _chk(_lib.earb200_objects_renderer_process_device(self.h, C.c_int64(block_start), C.c_int64(n_blocks),
+                                                          _ptr(d_in), C.c_int64(in_stride), _ptr(d_out),
+                                                          C.c_int64(out_stride), C.c_void_p(int(stream))))
 
 
 class FFT:

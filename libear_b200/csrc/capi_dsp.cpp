@@ -30,12 +30,13 @@ struct earb200_fft {
 
 namespace {
   void delay_process_device(earb200_delay &h, int64_t n, const float *d_in, int64_t in_stride, float *d_out,
-                            int64_t out_stride, cudaStream_t stream) {
+                            int64_t out_stride, cudaStream_t stream, const float *d_add = nullptr,
+                            int64_t add_stride = 0) {
     if (n < 0) throw Error(INVALID_ARGUMENT, "negative sample count");
     if (n == 0 || h.C == 0) return;
     if (!d_out) throw Error(INVALID_ARGUMENT, "null output buffer");
     use_device(h.device);
-    if (h.delay == 0) {  // [in] -> [out]
+    if (h.delay == 0 && !d_add) {  // [in] -> [out]
       if (d_in)
         EARB_CUDA(cudaMemcpy2DAsync(d_out, sizeof(float) * out_stride, d_in, sizeof(float) * in_stride,
                                     sizeof(float) * n, h.C, cudaMemcpyDeviceToDevice, stream));
@@ -44,7 +45,7 @@ namespace {
       return;
     }
     launch_delay(h.C, n, h.delay, d_in, in_stride, d_out, out_stride, h.d_mem[h.cur].ptr, h.d_mem[h.cur ^ 1].ptr,
-                 h.n_sms, stream);
+                 d_add, add_stride, h.n_sms, stream);
     EARB_CUDA(cudaGetLastError());
     h.cur ^= 1;
     h.launches++;
@@ -82,6 +83,15 @@ int earb200_delay_process_device(earb200_delay *d, int64_t nsamples, const float
   return guarded([&] {
     if (!d) throw Error(INVALID_ARGUMENT, "null handle");
     delay_process_device(*d, nsamples, d_in, in_stride, d_out, out_stride, (cudaStream_t)stream);
+  });
+}
+
+int earb200_delay_process_add_device(earb200_delay *d, int64_t nsamples, const float *d_in, int64_t in_stride,
+                                     const float *d_add, int64_t add_stride, float *d_out, int64_t out_stride,
+                                     void *stream) {
+  return guarded([&] {
+    if (!d) throw Error(INVALID_ARGUMENT, "null handle");
+    delay_process_device(*d, nsamples, d_in, in_stride, d_out, out_stride, (cudaStream_t)stream, d_add, add_stride);
   });
 }
 

@@ -18,12 +18,13 @@ namespace earb {
     __global__ void __launch_bounds__(kThreads)
         delay_kernel(int C, long n, long delay, const float *__restrict__ in, long in_stride,
                      float *__restrict__ out, long out_stride, const float *__restrict__ mem,
-                     float *__restrict__ mem_new) {
+                     float *__restrict__ mem_new, const float *__restrict__ add, long add_stride) {
       const int c = blockIdx.y;
       const float *m = mem + (long)c * delay;
       const float *x = in ? in + (long)c * in_stride : nullptr;
       float *y = out + (long)c * out_stride;
       float *mn = mem_new + (long)c * delay;
+      const float *ad = add ? add + (long)c * add_stride : nullptr;  // out = delayed + add
       const long total = n + delay;
       for (long base = ((long)blockIdx.x * kThreads + threadIdx.x) * kPerThread; base < total;
            base += (long)gridDim.x * kThreads * kPerThread) {
@@ -33,6 +34,12 @@ namespace earb {
           v.y = delay_fetch(m, x, base + 1, delay);
           v.z = delay_fetch(m, x, base + 2, delay);
           v.w = delay_fetch(m, x, base + 3, delay);
+          if (ad) {
+            v.x += __ldcs(ad + base);
+            v.y += __ldcs(ad + base + 1);
+            v.z += __ldcs(ad + base + 2);
+            v.w += __ldcs(ad + base + 3);
+          }
           __stcs(reinterpret_cast<float4 *>(y + base), v);
         } else {
 #pragma unroll
@@ -41,7 +48,7 @@ namespace earb {
             if (i >= total) break;
             const float v = delay_fetch(m, x, i, delay);
             if (i < n)
-              y[i] = v;
+              y[i] = ad ? v + ad[i] : v;
             else
               mn[i - n] = v;
           }
@@ -81,10 +88,12 @@ namespace earb {
   }  // namespace
 
   void launch_delay(int C, long n, long delay, const float *in, long in_stride, float *out,
-                    long out_stride, const float *mem, float *mem_new, int n_sms, cudaStream_t stream) {
+                    long out_stride, const float *mem, float *mem_new, const float *add, long add_stride,
+                    int n_sms, cudaStream_t stream) {
     if (C <= 0 || n + delay <= 0) return;
     dim3 grid(grid_x(n + delay, C, n_sms), C);
-    delay_kernel<<<grid, kThreads, 0, stream>>>(C, n, delay, in, in_stride, out, out_stride, mem, mem_new);
+    delay_kernel<<<grid, kThreads, 0, stream>>>(C, n, delay, in, in_stride, out, out_stride, mem, mem_new, add,
+                                                add_stride);
   }
 
   void launch_add(int C, long n, const float *a, long a_stride, const float *b, long b_stride, float *out,

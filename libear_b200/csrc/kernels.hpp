@@ -139,8 +139,10 @@ namespace earb {
   // ---- delay line / bus mix of the Objects signal flow (dsp_kernels.cu)
   // [mem; in] -> [out; mem_new] per channel (mem, mem_new: [C][delay], distinct buffers);
   // in may be null (silence)
+  // add (nullable): out = delayed input + add (the last stage of the Objects signal flow)
   void launch_delay(int C, long n, long delay, const float *in, long in_stride, float *out,
-                    long out_stride, const float *mem, float *mem_new, int n_sms, cudaStream_t stream);
+                    long out_stride, const float *mem, float *mem_new, const float *add, long add_stride,
+                    int n_sms, cudaStream_t stream);
   void launch_add(int C, long n, const float *a, long a_stride, const float *b, long b_stride, float *out,
                   long out_stride, int n_sms, cudaStream_t stream);
 
