@@ -274,6 +274,36 @@ int earb200_objects_renderer_process_device(earb200_objects_renderer *r, int64_t
                                             int64_t n_blocks, const float *d_in, int64_t in_stride,
                                             float *d_out, int64_t out_stride, void *stream);
 
+/* ------------------------------- Cartesian <-> polar metadata conversion (8f.3)
+ * replaces ear::conversion::{pointCartToPolar, pointPolarToCart, extentCartToPolar,
+ * extentPolarToCart} and, through the facade, toPolar / toCartesian
+ * (include/ear/conversion.hpp:14-71, src/conversion.cpp:127-263) for a batch of objects:
+ * a pre-pass that turns Cartesian-authored Objects blocks into the polar blocks
+ * earb200_objects_calculate_* accepts.  pos [n][3] is X, Y, Z on the Cartesian side and
+ * azimuth, elevation, distance on the polar side; extent [n][3] is width, height, depth
+ * (nullable together with extent_out: positions only).  A position libear would throw
+ * ear::internal_error for (no sector found / p out of range: non-finite input) gives NaN
+ * outputs; the _host variants then return EARB200_INTERNAL_ERROR, the asynchronous _device
+ * variants report it at the next earb200_conversion_check (which synchronises). */
+typedef struct earb200_conversion earb200_conversion;
+
+int earb200_conversion_create(int device, earb200_conversion **out);
+void earb200_conversion_destroy(earb200_conversion *conv);
+int earb200_conversion_cart_to_polar_host(earb200_conversion *conv, int64_t n, const double *pos,
+                                          const double *extent, double *pos_out,
+                                          double *extent_out);
+int earb200_conversion_polar_to_cart_host(earb200_conversion *conv, int64_t n, const double *pos,
+                                          const double *extent, double *pos_out,
+                                          double *extent_out);
+int earb200_conversion_cart_to_polar_device(earb200_conversion *conv, int64_t n,
+                                            const double *d_pos, const double *d_extent,
+                                            double *d_pos_out, double *d_extent_out, void *stream);
+int earb200_conversion_polar_to_cart_device(earb200_conversion *conv, int64_t n,
+                                            const double *d_pos, const double *d_extent,
+                                            double *d_pos_out, double *d_extent_out, void *stream);
+int earb200_conversion_check(earb200_conversion *conv, void *stream);
+int64_t earb200_conversion_launch_count(const earb200_conversion *conv);
+
 /* ------------------------------------------------ HOA decoder design (K5)
  * replaces ear::GainCalculatorHOA (include/ear/gain_calculators.hpp:67-82,
  * src/hoa/gain_calculator_hoa.cpp:8-72, src/hoa/hoa.hpp:88-143). */

@@ -30,7 +30,7 @@ _lib.earb200_layout_channel_name.restype = C.c_char_p
 for _f in ("earb200_objects_launch_count", "earb200_interp_launch_count",
            "earb200_convolver_launch_count", "earb200_direct_speakers_launch_count",
            "earb200_delay_launch_count", "earb200_delay_get_delay", "earb200_fft_launch_count",
-           "earb200_fft_size", "earb200_objects_renderer_block_size"):
+           "earb200_fft_size", "earb200_objects_renderer_block_size", "earb200_conversion_launch_count"):
     getattr(_lib, _f).restype = C.c_int64
 
 
@@ -452,6 +452,58 @@ class DelayBuffer:
     def process_device(self, nsamples, d_in, in_stride, d_out, out_stride, stream=0):
         _chk(_lib.earb200_delay_process_device(self.h, C.c_int64(nsamples), _ptr(d_in), C.c_int64(in_stride),
                                                _ptr(d_out), C.c_int64(out_stride), C.c_void_p(int(stream))))
+
+
+class Conversion:
+    """ear::conversion (include/ear/conversion.hpp:14-71) for a batch of objects: positions
+    [n][3] (X, Y, Z <-> azimuth, elevation, distance) and optional extents [n][3]
+    (width, height, depth)."""
+
+    def __init__(self, device=0):
+        self.h = C.c_void_p()
+        _chk(_lib.earb200_conversion_create(device, C.byref(self.h)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            _lib.earb200_conversion_destroy(self.h)
+            self.h = None
+
+    @property
+    def launch_count(self):
+        return _lib.earb200_conversion_launch_count(self.h)
+
+    def _run(self, fn, pos, extent):
+        pos = np.ascontiguousarray(pos, dtype=np.float64).reshape(-1, 3)
+        pos_out = np.zeros_like(pos)
+        ext_out = None
+        if extent is not None:
+            extent = np.ascontiguousarray(extent, dtype=np.float64).reshape(-1, 3)
+            if extent.shape != pos.shape:
+                raise InvalidArgument("extent must have one row per position")
+            ext_out = np.zeros_like(extent)
+        _chk(fn(self.h, C.c_int64(len(pos)), _ptr(pos), _ptr(extent), _ptr(pos_out), _ptr(ext_out)))
+        return (pos_out, ext_out) if extent is not None else pos_out
+
+    def cart_to_polar(self, pos, extent=None):
+        """pointCartToPolar (extent None) / extentCartToPolar per row."""
+        return self._run(_lib.earb200_conversion_cart_to_polar_host, pos, extent)
+
+    def polar_to_cart(self, pos, extent=None):
+        """pointPolarToCart (extent None) / extentPolarToCart per row."""
+        return self._run(_lib.earb200_conversion_polar_to_cart_host, pos, extent)
+
+    def cart_to_polar_device(self, n, d_pos, d_extent, d_pos_out, d_extent_out, stream=0):
+        _chk(_lib.earb200_conversion_cart_to_polar_device(self.h, C.c_int64(n), _ptr(d_pos), _ptr(d_extent),
+                                                          _ptr(d_pos_out), _ptr(d_extent_out),
+                                                          C.c_void_p(int(stream))))
+
+    def polar_to_cart_device(self, n, d_pos, d_extent, d_pos_out, d_extent_out, stream=0):
+        _chk(_lib.earb200_conversion_polar_to_cart_device(self.h, C.c_int64(n), _ptr(d_pos), _ptr(d_extent),
+                                                          _ptr(d_pos_out), _ptr(d_extent_out),
+                                                          C.c_void_p(int(stream))))
+
+    def check(self, stream=0):
+        _chk(_lib.earb200_conversion_check(self.h, C.c_void_p(int(stream))))
 
 
 WARN_HOA_SCREENREF, WARN_HOA_NFCREFDIST = 4, 5

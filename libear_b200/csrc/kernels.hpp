@@ -146,6 +146,21 @@ namespace earb {
   void launch_add(int C, long n, const float *a, long a_stride, const float *b, long b_stride, float *out,
                   long out_stride, int n_sms, cudaStream_t stream);
 
+  // ---- Cartesian <-> polar metadata conversion pre-pass (conversion_kernels.cu)
+  // the five azimuth sectors of ear::conversion (ref src/conversion.cpp:24-73): sector s runs
+  // from corner s to corner (s + 1) % 5
+  struct ConversionSectors {
+    double polar_az[5];     // polar azimuth of the corners
+    double cart_az[5];      // azimuth of the corners' Cartesian positions
+    double cart_pos[5][2];  // Cartesian x, y of the corners
+    double m[5][4];         // inverse of [start; end] per sector, row-major 2x2
+  };
+  // pos / ext: [n][3]; ext / ext_out nullable (positions only); *d_n_failed counts objects the
+  // reference would have thrown on (their outputs are NaN)
+  void launch_conversion(const ConversionSectors &sectors, long n, bool to_polar, const double *d_pos,
+                         const double *d_ext, double *d_pos_out, double *d_ext_out,
+                         unsigned int *d_n_failed, int n_sms, cudaStream_t stream);
+
   // ---- K5: HOA decoder design (hoa_kernels.cu)
   int hoa_power_blocks(int P);
   // Y [C][P], D [S][C], partial [hoa_power_blocks(P)]

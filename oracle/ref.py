@@ -308,3 +308,16 @@ def delay_process(x, delay, call_size=None):
     out = np.zeros_like(x)
     _chk(lib().ref_delay_process(nch, C.c_long(delay), C.c_long(T), C.c_long(call_size or T), _p(x), _p(out)))
     return out
+
+
+def conversion(pos, ext=None, to_polar=True):
+    """ear::conversion::extentCartToPolar / extentPolarToCart (point* when ext is None) per row."""
+    pos = _f64(pos).reshape(-1, 3)
+    pos_out = np.zeros_like(pos)
+    if ext is not None:
+        ext = _f64(ext).reshape(-1, 3)
+        ext_out = np.zeros_like(ext)
+    else:
+        ext_out = None
+    _chk(lib().ref_conversion(C.c_long(len(pos)), int(bool(to_polar)), _p(pos), _p(ext), _p(pos_out), _p(ext_out)))
+    return pos_out, ext_out

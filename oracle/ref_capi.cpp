@@ -35,6 +35,7 @@
 #include "direct_speakers/gain_calculator_direct_speakers.hpp"
 #include "direct_speakers/mapping_rules.hpp"
 #include "ear/bs2051.hpp"
+#include "ear/conversion.hpp"
 #include "ear/decorrelate.hpp"
 #include "ear/dsp/block_convolver.hpp"
 #include "ear/dsp/delay_buffer.hpp"
@@ -627,6 +628,41 @@ int ref_delay_process(int n_channels, long delay, long T, long call_size,
       out_p[c] = out + (size_t)c * T + t;
     }
     db.process(n, in_p.data(), out_p.data());
+  }
+  return 0;
+  REF_CATCH
+}
+
+// ---- ear::conversion ------------------------------------------------------
+// pos / ext [n][3]; ext nullable (point conversion only); to_polar: Cartesian -> polar
+int ref_conversion(long n, int to_polar, const double *pos, const double *ext,
+                   double *pos_out, double *ext_out) {
+  REF_TRY
+  for (long i = 0; i < n; i++) {
+    const double *p = pos + 3 * i;
+    if (to_polar) {
+      CartesianPosition c{p[0], p[1], p[2]};
+      PolarPosition r;
+      if (ext) {
+        conversion::ExtentParams e{ext[3 * i], ext[3 * i + 1], ext[3 * i + 2]}, eo;
+        std::tie(r, eo) = conversion::extentCartToPolar(c, e);
+        ext_out[3 * i] = eo.width, ext_out[3 * i + 1] = eo.height, ext_out[3 * i + 2] = eo.depth;
+      } else {
+        r = conversion::pointCartToPolar(c);
+      }
+      pos_out[3 * i] = r.azimuth, pos_out[3 * i + 1] = r.elevation, pos_out[3 * i + 2] = r.distance;
+    } else {
+      PolarPosition c{p[0], p[1], p[2]};
+      CartesianPosition r;
+      if (ext) {
+        conversion::ExtentParams e{ext[3 * i], ext[3 * i + 1], ext[3 * i + 2]}, eo;
+        std::tie(r, eo) = conversion::extentPolarToCart(c, e);
+        ext_out[3 * i] = eo.width, ext_out[3 * i + 1] = eo.height, ext_out[3 * i + 2] = eo.depth;
+      } else {
+        r = conversion::pointPolarToCart(c);
+      }
+      pos_out[3 * i] = r.X, pos_out[3 * i + 1] = r.Y, pos_out[3 * i + 2] = r.Z;
+    }
   }
   return 0;
   REF_CATCH

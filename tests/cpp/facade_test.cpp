@@ -12,6 +12,7 @@
 #include <numeric>
 #include <sstream>
 
+#include "ear/conversion.hpp"
 #include "ear/dsp/dsp.hpp"
 #include "ear/ear.hpp"
 
@@ -388,6 +389,61 @@ static void test_decorrelators() {
   CHECK(close(e, 1.0, 1e-3));
 }
 
+// ref tests/conversion_tests.cpp:52-90, 162-252
+static void test_conversion() {
+  using namespace ear::conversion;
+  for (double az : {0.0, -10.0, 10.0, 90.0, -90.0, 150.0, -150.0})
+    for (double el : {0.0, -10.0, 10.0, -45.0, 45.0, -90.0, 90.0})
+      for (double dist : {0.5, 1.0}) {
+        PolarPosition back = pointCartToPolar(pointPolarToCart(PolarPosition(az, el, dist)));
+        if (std::abs(el) < 90.0) CHECK(close(back.azimuth, az));
+        CHECK(close(back.elevation, el) && close(back.distance, dist));
+      }
+  {
+    auto res = extentPolarToCart(PolarPosition(10.0, 20.0, 0.3), ExtentParams{40.0, 50.0, 0.6});
+    CHECK(close(res.first.X, -0.08972503721988338) && close(res.first.Y, 0.3) &&
+          close(res.first.Z, 0.1732050807568877));
+    CHECK(close(res.second.width, 0.35166171614357594) && close(res.second.height, 0.4470181645863707) &&
+          close(res.second.depth, 0.5762749096794243));
+  }
+  {
+    auto res = extentCartToPolar(CartesianPosition(0.9, 0.8, 0.1), ExtentParams{0.3, 0.5, 0.4});
+    CHECK(close(res.first.azimuth, -34.85107611658391) && close(res.first.elevation, 4.226794497273273) &&
+          close(res.first.distance, 0.9000000000000001));
+    CHECK(close(res.second.width, 76.50724453298275) && close(res.second.height, 104.9708107421662) &&
+          close(res.second.depth, 0.1756348204517474));
+  }
+  // wrappers: the type held by position decides, the flag is fixed up
+  ObjectsTypeMetadata otm;
+  otm.position = PolarPosition(10.0, 20.0, 0.3);
+  otm.width = 40.0, otm.height = 50.0, otm.depth = 0.6;
+  ObjectsTypeMetadata otm_cart = otm;
+  toCartesian(otm_cart);
+  CHECK(otm_cart.cartesian && otm_cart.position.which() == 0);
+  CHECK(close(compat::get<CartesianPosition>(otm_cart.position).Y, 0.3) && close(otm_cart.depth, 0.5762749096794243));
+  otm.cartesian = true;
+  toPolar(otm);
+  CHECK(!otm.cartesian && close(otm.width, 40.0));
+  toPolar(otm_cart);
+  CHECK(!otm_cart.cartesian && otm_cart.position.which() == 1);
+  // a Cartesian-authored block through the batched pre-pass, then the calculator
+  std::vector<ObjectsTypeMetadata> block(3);
+  block[0].position = CartesianPosition(0.9, 0.8, 0.1);
+  block[0].cartesian = true;
+  block[0].width = 0.3, block[0].height = 0.5, block[0].depth = 0.4;
+  block[1].position = PolarPosition(30.0, 0.0, 1.0);
+  block[2].position = CartesianPosition(-1.0, 1.0, 0.0);
+  block[2].cartesian = true;
+  GainCalculatorObjects gc(getLayout("0+5+0"));
+  std::vector<double> direct(6), diffuse(6);
+  CHECK_THROWS(gc.calculate(block[0], direct, diffuse), not_implemented);
+  toPolar(block);
+  CHECK(close(block[0].width, 76.50724453298275) && close(compat::get<PolarPosition>(block[2].position).azimuth, 30.0));
+  gc.calculate(block[2], direct, diffuse);
+  CHECK(close(direct[0], 1.0));  // M+030
+  CHECK_THROWS(pointPolarToCart(PolarPosition(std::nan(""), 0.0, 1.0)), internal_error);
+}
+
 static int run_objects(const std::string &layout_name) {
   Layout layout = getLayout(layout_name);
   GainCalculatorObjects gc(layout);
@@ -424,6 +480,7 @@ int main(int argc, char **argv) {
     test_block_convolver();
     test_fft_plugin();
     test_delay_and_adapter();
+    test_conversion();
   } catch (const std::exception &e) {
     std::printf("FAIL unexpected exception: %s\n", e.what());
     return 2;

@@ -302,6 +302,45 @@ def gen_delay():
                         y=ref.delay_process(x, 255, call_size=128))
 
 
+def conversion_inputs():
+    """Seeded positions / extents plus the cases of the reference's own conversion tests
+    (tests/conversion_tests.cpp:52-160): the az x el x dist loop, poles, centre, sector corners."""
+    rng = np.random.default_rng(17)
+    n = 400
+    polar = [[az, el, d] for az in (0.0, -10.0, 10.0, 90.0, -90.0, 150.0, -150.0)
+             for el in (0.0, -10.0, 10.0, -45.0, 45.0, -90.0, 90.0) for d in (0.5, 1.0)]
+    polar += [[0.0, s * 90.0, d] for s in (-1.0, 1.0) for d in (0.5, 1.0, 2.0)]
+    polar += [[az, el, 0.0] for az in (-90.0, 0.0, 90.0) for el in (-90.0, 0.0, 90.0)]
+    polar += [[az, el, 1.0] for az in (0.0, -30.0, -110.0, 110.0, 30.0, 180.0, -180.0, 360.0, -400.0)
+              for el in (0.0, 30.0, -30.0, 30.000001)]
+    polar += [[10.0, 20.0, 0.3]]
+    polar = np.array(polar)
+    polar = np.concatenate([polar, np.stack([rng.uniform(-180, 180, n), rng.uniform(-90, 90, n),
+                                             rng.uniform(0, 2, n)], 1)])
+    polar_ext = np.stack([rng.uniform(0, 360, len(polar)), rng.uniform(0, 360, len(polar)),
+                          rng.uniform(0, 1, len(polar))], 1)
+    polar_ext[:20] = 0.0
+    polar_ext[-1 - n] = [40.0, 50.0, 0.6]  # conversion_reference, tests/conversion_tests.cpp:163
+    cartp = [[0.0, 0.0, s * d] for s in (-1.0, 1.0) for d in (0.5, 1.0, 2.0)] + [[0.0, 0.0, 0.0]]
+    cartp += [[x, y, z] for x in (-1.0, 0.0, 1.0) for y in (-1.0, 0.0, 1.0) for z in (-1.0, 0.0, 0.5, 1.0)
+              if (x, y) != (0.0, 0.0)]
+    cartp += [[1e-11, 1e-11, 0.5], [1e-9, 0.0, 0.5], [0.9, 0.8, 0.1]]
+    cartp = np.array(cartp)
+    cartp = np.concatenate([cartp, rng.uniform(-1.2, 1.2, (n, 3))])
+    cart_ext = rng.uniform(0, 1, (len(cartp), 3))
+    cart_ext[:10] = 0.0
+    cart_ext[-1 - n] = [0.3, 0.5, 0.4]  # conversion_reference, tests/conversion_tests.cpp:175
+    return polar, polar_ext, cartp, cart_ext
+
+
+def gen_conversion():
+    polar, polar_ext, cartp, cart_ext = conversion_inputs()
+    p2c_pos, p2c_ext = ref.conversion(polar, polar_ext, to_polar=False)
+    c2p_pos, c2p_ext = ref.conversion(cartp, cart_ext, to_polar=True)
+    np.savez_compressed(os.path.join(HERE, "conversion.npz"), polar=polar, polar_ext=polar_ext, p2c_pos=p2c_pos,
+                        p2c_ext=p2c_ext, cart=cartp, cart_ext=cart_ext, c2p_pos=c2p_pos, c2p_ext=c2p_ext)
+
+
 def gen_kat():
     """Known answers held by the reference's own tests (not produced by running anything)."""
     kat = {
@@ -316,6 +355,12 @@ def gen_kat():
         "hoa_point_first": np.array([-0.007238307489963788, 0.8575241661297168, 0.5143927598714958]),
         "hoa_point_last": np.array([-0.5784605915309438, 0.5246941913018843, -0.6245633271812653]),
         "hoa_n_points": np.array(5200),
+        # tests/conversion_tests.cpp:162-185 -- extentPolarToCart({10, 20, 0.3}, {40, 50, 0.6}) and
+        # extentCartToPolar({0.9, 0.8, 0.1}, {0.3, 0.5, 0.4}): position then extent
+        "conversion_p2c": np.array([-0.08972503721988338, 0.3, 0.1732050807568877, 0.35166171614357594,
+                                    0.4470181645863707, 0.5762749096794243]),
+        "conversion_c2p": np.array([-34.85107611658391, 4.226794497273273, 0.9000000000000001,
+                                    76.50724453298275, 104.9708107421662, 0.1756348204517474]),
     }
     np.savez_compressed(os.path.join(HERE, "kat.npz"), **kat)
 
@@ -324,6 +369,6 @@ if __name__ == "__main__":
     if not ref.available():
         raise SystemExit("build oracle/_ref first: make -C oracle")
     for fn in (gen_psp, gen_extent, gen_objects, gen_interp, gen_convolver, gen_decorrelators, gen_hoa,
-               gen_direct_speakers, gen_delay, gen_kat):
+               gen_direct_speakers, gen_delay, gen_conversion, gen_kat):
         fn()
         print("wrote", fn.__name__[4:])

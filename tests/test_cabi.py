@@ -87,7 +87,7 @@ def test_no_cpu_fallback(eb):
         pytest.skip("a CUDA device is present")
     for make in (lambda: eb.PointSourcePanner("0+5+0"), lambda: eb.GainCalculatorObjects("9+10+3"),
                  lambda: eb.GainInterpolator(4, 2), lambda: eb.BlockConvolver(512, 2, 1),
-                 lambda: eb.GainCalculatorHOA("4+7+0"), lambda: eb.DelayBuffer(2, 255), lambda: eb.FFT(1024),
+                 lambda: eb.GainCalculatorHOA("4+7+0"), lambda: eb.DelayBuffer(2, 255), lambda: eb.FFT(1024), lambda: eb.Conversion(),
                  lambda: eb.GainCalculatorDirectSpeakers("4+7+0").calculate(["foo"], az=12.0, el=5.0)):
         with pytest.raises(eb.CudaError):
             make()

@@ -237,3 +237,53 @@ def test_golden_fixtures_are_current(ref):
             c.get("bounds"), c.get("low_pass"), c.get("high_pass"), c.get("pack"), c.get("substitutions"),
             screen_edge_lock=c.get("screen_edge_lock", 0), codes=True)
         assert np.abs(gains - g[f"{i}/gains"]).max() < 1e-15 and codes == list(g[f"{i}/warnings"])
+
+
+# ------------------------------------------------------------------ Cartesian <-> polar conversion
+def _oracle_conversion(pos, ext, to_polar):
+    fn = eo.extent_cart_to_polar if to_polar else eo.extent_polar_to_cart
+    out = [fn(p, e) for p, e in zip(pos, ext)]
+    return np.array([o[0] for o in out]), np.array([o[1] for o in out])
+
+
+def test_conversion_golden():
+    g = golden("conversion")
+    pos, ext = _oracle_conversion(g["polar"], g["polar_ext"], False)
+    assert np.abs(pos - g["p2c_pos"]).max() < 1e-12
+    assert np.abs(ext - g["p2c_ext"]).max() < 1e-12
+    pos, ext = _oracle_conversion(g["cart"], g["cart_ext"], True)
+    assert np.abs(pos - g["c2p_pos"]).max() < 1e-10  # degrees
+    assert np.abs(ext - g["c2p_ext"]).max() < 1e-10
+
+
+def test_conversion_known_answers():
+    # tests/conversion_tests.cpp:162-185 (margin 1e-6 there)
+    kat = golden("kat")
+    pos, ext = eo.extent_polar_to_cart([10.0, 20.0, 0.3], [40.0, 50.0, 0.6])
+    assert np.abs(np.concatenate([pos, ext]) - kat["conversion_p2c"]).max() < 1e-9
+    pos, ext = eo.extent_cart_to_polar([0.9, 0.8, 0.1], [0.3, 0.5, 0.4])
+    assert np.abs(np.concatenate([pos, ext]) - kat["conversion_c2p"]).max() < 1e-9
+
+
+def test_conversion_round_trip_and_poles():
+    # tests/conversion_tests.cpp:52-90
+    for az in (0.0, -10.0, 10.0, 90.0, -90.0, 150.0, -150.0):
+        for el in (0.0, -10.0, 10.0, -45.0, 45.0, -90.0, 90.0):
+            for dist in (0.5, 1.0):
+                back = eo.point_cart_to_polar(*eo.point_polar_to_cart(az, el, dist))
+                if abs(el) < 90.0:
+                    assert abs(back[0] - az) < 1e-6
+                assert abs(back[1] - el) < 1e-6 and abs(back[2] - dist) < 1e-6
+    for sign in (-1.0, 1.0):
+        for d in (0.5, 1.0, 2.0):
+            assert np.abs(eo.point_polar_to_cart(0.0, sign * 90.0, d) - [0.0, 0.0, sign * d]).max() < 1e-6
+            assert np.abs(eo.point_cart_to_polar(0.0, 0.0, sign * d) - [0.0, sign * 90.0, d]).max() < 1e-6
+
+
+def test_conversion_live(ref):
+    rng = np.random.default_rng(23)
+    n = 300
+    cartp, ext = rng.uniform(-1.5, 1.5, (n, 3)), rng.uniform(0, 1, (n, 3))
+    r_pos, r_ext = ref.conversion(cartp, ext, to_polar=True)
+    pos, e = _oracle_conversion(cartp, ext, True)
+    assert np.abs(pos - r_pos).max() < 1e-10 and np.abs(e - r_ext).max() < 1e-10
