@@ -56,6 +56,23 @@ int earb200_layout_create(const char *name, earb200_layout **out);
  * real_pos is [n][3] = azimuth, elevation, distance per channel, table order. */
 int earb200_layout_create_with_positions(const char *name, int n_channels,
                                          const double *real_pos, earb200_layout **out);
+/* any layout (ear::Layout(name, channels), include/ear/layout.hpp:67-96): channels as given.
+ * A name from the BS.2051 table selects that layout's tabulated hull facets; any other name
+ * makes the panner triangulate the nominal positions itself (convex hull,
+ * src/common/convex_hull.cpp:7-100, src/common/point_source_panner.cpp:484-487).
+ * pos / nominal_pos [n][3] = azimuth, elevation, distance; az_range / el_range [n][2];
+ * nominal_pos, az_range, el_range and is_lfe are nullable (defaults as ear::Channel:
+ * nominal = real position, ranges = the position itself, not LFE). */
+int earb200_layout_create_custom(const char *name, int n_channels,
+                                 const char *const *channel_names, const double *pos,
+                                 const double *nominal_pos, const double *az_range,
+                                 const double *el_range, const int32_t *is_lfe,
+                                 earb200_layout **out);
+/* the triangulation used for such layouts, exposed for inspection (host, setup-time): facets of
+ * the convex hull of n_points unit vectors xyz [n][3], in the order ear::convex_hull finds them;
+ * facets is a flat list, each facet = vertex count followed by its sorted vertex indices. */
+int earb200_convex_hull(int n_points, const double *xyz, int32_t *facets, int capacity,
+                        int *n_written);
 void earb200_layout_destroy(earb200_layout *layout);
 int earb200_layout_num_channels(const earb200_layout *layout);
 const char *earb200_layout_channel_name(const earb200_layout *layout, int i);

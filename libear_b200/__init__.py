@@ -97,10 +97,23 @@ def layout_names():
 class Layout:
     """ear::Layout / ear::getLayout (include/ear/layout.hpp:62-96, src/bs2051.cpp:13-22)."""
 
-    def __init__(self, name, real_positions=None):
+    def __init__(self, name, real_positions=None, channels=None):
+        """channels: dict(names, pos[, nominal, az_range, el_range, is_lfe]) for ear::Layout(name, channels)
+        with arbitrary channels; a name outside BS.2051 makes the panner build its own convex hull."""
         self.h = C.c_void_p()
         self.name = name
-        if real_positions is None:
+        if channels is not None:
+            names = [n.encode() for n in channels["names"]]
+            arr = (C.c_char_p * len(names))(*names)
+            pos = np.ascontiguousarray(channels["pos"], dtype=np.float64).reshape(-1, 3)
+            opt = {k: (None if channels.get(k) is None else np.ascontiguousarray(channels[k], dtype=np.float64))
+                   for k in ("nominal", "az_range", "el_range")}
+            lfe = channels.get("is_lfe")
+            lfe = None if lfe is None else np.ascontiguousarray(lfe, dtype=np.int32)
+            _chk(_lib.earb200_layout_create_custom(name.encode(), len(names), arr, _ptr(pos), _ptr(opt["nominal"]),
+                                                   _ptr(opt["az_range"]), _ptr(opt["el_range"]), _ptr(lfe),
+                                                   C.byref(self.h)))
+        elif real_positions is None:
             _chk(_lib.earb200_layout_create(name.encode(), C.byref(self.h)))
         else:
             rp = np.ascontiguousarray(real_positions, dtype=np.float64).reshape(-1, 3)
@@ -119,6 +132,20 @@ class Layout:
         if getattr(self, "h", None):
             _lib.earb200_layout_destroy(self.h)
             self.h = None
+
+
+def convex_hull(xyz):
+    """ear::convex_hull (src/common/convex_hull.cpp:7-100): facets as sorted vertex index lists."""
+    xyz = np.ascontiguousarray(xyz, dtype=np.float64).reshape(-1, 3)
+    buf = np.zeros(64 * len(xyz) + 64, dtype=np.int32)
+    n = C.c_int(0)
+    _chk(_lib.earb200_convex_hull(len(xyz), _ptr(xyz), _ptr(buf), len(buf), C.byref(n)))
+    out, k = [], 0
+    while k < n.value:
+        c = int(buf[k])
+        out.append([int(v) for v in buf[k + 1:k + 1 + c]])
+        k += 1 + c
+    return out
 
 
 def get_layout(name):

@@ -366,6 +366,45 @@ int earb200_layout_create_with_positions(const char *name, int n_channels,
     *out = l.release();
   });
 }
+int earb200_layout_create_custom(const char *name, int n_channels, const char *const *channel_names,
+                                 const double *pos, const double *nominal_pos, const double *az_range,
+                                 const double *el_range, const int32_t *is_lfe, earb200_layout **out) {
+  return guarded([&] {
+    if (!name || !out || !pos || !channel_names) throw Error(INVALID_ARGUMENT, "null argument");
+    if (n_channels < 0) throw Error(INVALID_ARGUMENT, "negative channel count");
+    auto l = std::make_unique<earb200_layout>();
+    l->layout.name = name;
+    for (int i = 0; i < n_channels; i++) {
+      if (!channel_names[i]) throw Error(INVALID_ARGUMENT, "null channel name");
+      HostChannel c;
+      c.name = channel_names[i];
+      c.pos = {pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]};
+      // defaults as ear::Channel (ref src/layout.cpp:27-45): nominal = real, ranges = the position
+      c.nominal = nominal_pos ? Polar{nominal_pos[3 * i], nominal_pos[3 * i + 1], nominal_pos[3 * i + 2]} : c.pos;
+      c.az_lo = az_range ? az_range[2 * i] : c.pos.az;
+      c.az_hi = az_range ? az_range[2 * i + 1] : c.pos.az;
+      c.el_lo = el_range ? el_range[2 * i] : c.pos.el;
+      c.el_hi = el_range ? el_range[2 * i + 1] : c.pos.el;
+      c.lfe = is_lfe && is_lfe[i];
+      l->layout.channels.push_back(c);
+    }
+    *out = l.release();
+  });
+}
+int earb200_convex_hull(int n_points, const double *xyz, int32_t *facets, int capacity, int *n_written) {
+  return guarded([&] {
+    if (!xyz || !facets || !n_written) throw Error(INVALID_ARGUMENT, "null argument");
+    std::vector<Vec3> pts;
+    for (int i = 0; i < n_points; i++) pts.push_back({xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]});
+    int k = 0;
+    for (const auto &f : convexHull(pts)) {
+      if (k + 1 + (int)f.size() > capacity) throw Error(INVALID_ARGUMENT, "facet buffer too small");
+      facets[k++] = (int32_t)f.size();
+      for (int v : f) facets[k++] = v;
+    }
+    *n_written = k;
+  });
+}
 void earb200_layout_destroy(earb200_layout *layout) { delete layout; }
 int earb200_layout_num_channels(const earb200_layout *layout) {
   return layout ? (int)layout->layout.channels.size() : 0;

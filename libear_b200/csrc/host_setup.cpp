@@ -45,12 +45,14 @@ namespace earb {
       return nullptr;
     }
 
+    bool hasFacetTable(const std::string &name) {
+      const LayoutSpec *spec = findSpec(name);
+      return spec && spec->facets;
+    }
+
     std::vector<std::vector<int>> facetsFor(const std::string &name) {
       const LayoutSpec *spec = findSpec(name);
-      if (!spec || !spec->facets)
-        throw Error(NOT_IMPLEMENTED,
-                    "layouts without tabulated convex-hull facets (custom layout names) "
-                    "are not supported: " + name);
+      if (!spec || !spec->facets) throw Error(INTERNAL_ERROR, "no facet table for layout " + name);
       std::vector<std::vector<int>> out;
       std::vector<int> cur;
       for (const int *p = spec->facets; *p != -2; ++p) {
@@ -153,7 +155,18 @@ namespace earb {
         real.push_back({0.0, 0.0, 1.0});
       }
 
-      std::vector<std::vector<int>> facets = facetsFor(layout.name);
+      // hull facets: tabulated for the BS.2051 layout names, else the convex hull of the
+      // *nominal* positions (ref point_source_panner.cpp:484-487)
+      std::vector<std::vector<int>> facets;
+      if (hasFacetTable(layout.name)) {
+        facets = facetsFor(layout.name);
+      } else {
+        std::vector<Vec3> nominal;
+        for (const auto &ch : layout.channels) nominal.push_back(cart(ch.nominal.az, ch.nominal.el, 1.0));
+        for (const auto &ch : extra.channels) nominal.push_back(cart(ch.nominal.az, ch.nominal.el, 1.0));
+        for (int vv : virtual_verts) nominal.push_back(real[vv]);
+        facets = convexHull(nominal);
+      }
       for (const auto &f : facets)
         for (int v : f)
           if (v < 0 || v >= (int)real.size())
@@ -383,6 +396,60 @@ namespace earb {
       return r;
     }
   }  // namespace
+
+  // Facets of the convex hull of a handful of points, brute force (ref src/common/convex_hull.cpp:7-100;
+  // same acceptance tests and tolerance, so the same facets in the same order): every triangle
+  // (i < j < k) whose plane has all points on the side of the centroid is a hull triangle;
+  // coplanar hull triangles merge into one facet (sorted vertex set) in order of first appearance.
+  std::vector<std::vector<int>> convexHull(const std::vector<Vec3> &pts, double tol) {
+    const int n = (int)pts.size();
+    if (n < 4) throw Error(INVALID_ARGUMENT, "convex hull needs at least 4 loudspeaker positions");
+    Vec3 inside = {0.0, 0.0, 0.0};
+    for (const Vec3 &p : pts) inside = inside + p;
+    inside = {inside.x / (double)n, inside.y / (double)n, inside.z / (double)n};
+
+    struct HullFacet {
+      std::set<int> verts;
+      Vec3 normal;
+    };
+    std::vector<HullFacet> hull;
+    for (int i = 0; i < n; i++)
+      for (int j = i + 1; j < n; j++)
+        for (int k = j + 1; k < n; k++) {
+          Vec3 nrm = cross(pts[j] - pts[i], pts[k] - pts[i]);
+          const double sq = dot(nrm, nrm);
+          if (!(sq > tol)) throw Error(INTERNAL_ERROR, "collinear points in convex hull");
+          const double len = std::sqrt(sq);
+          nrm = {nrm.x / len, nrm.y / len, nrm.z / len};
+          const double d_inside = dot(nrm, inside - pts[i]);
+          if (std::abs(d_inside) < tol) continue;  // plane through the centroid: not a hull face
+          bool all_inside = true;
+          for (const Vec3 &q : pts) {
+            const double d = dot(nrm, q - pts[i]);
+            if (!(d_inside > 0 ? d > -tol : d < tol)) {
+              all_inside = false;
+              break;
+            }
+          }
+          if (!all_inside) continue;
+          // same plane as an earlier facet? (its lowest vertex lies in this plane and the
+          // normals are parallel)
+          bool merged = false;
+          for (HullFacet &f : hull) {
+            const Vec3 &fp = pts[*f.verts.begin()];
+            const Vec3 c = cross(f.normal, nrm);
+            if (std::abs(dot(pts[i] - fp, f.normal)) < tol && dot(c, c) < tol) {
+              f.verts.insert({i, j, k});
+              merged = true;
+              break;
+            }
+          }
+          if (!merged) hull.push_back({{i, j, k}, nrm});
+        }
+    std::vector<std::vector<int>> out;
+    for (const HullFacet &f : hull) out.emplace_back(f.verts.begin(), f.verts.end());
+    return out;
+  }
 
   std::vector<int> ngonVertexOrder(const std::vector<Vec3> &verts) {
     const int n = (int)verts.size();

@@ -66,6 +66,10 @@ namespace earb {
   // order of the vertices of a convex, roughly planar polygon (ref geom.cpp:38-69)
   std::vector<int> ngonVertexOrder(const std::vector<Vec3> &verts);
 
+  // facets (sorted vertex index lists) of the convex hull of unit vectors, for layouts without a
+  // tabulated hull (ref src/common/convex_hull.cpp:7-100)
+  std::vector<std::vector<int>> convexHull(const std::vector<Vec3> &positions, double tolerance = 1e-5);
+
   // build the point-source panner tables for a layout (LFE channels are dropped
   // first, as every libear calculator does: ref gain_calculator_objects.cpp:28)
   void buildPspTables(const HostLayout &layout, PspTables &out);

@@ -129,25 +129,28 @@ namespace ear {
       return Layout(name, channels);
     }
 
-    // ear::Layout -> C-ABI layout: the tabulated BS.2051 layout of that name with the real
-    // loudspeaker positions of `layout` (the panner range-checks them, as libear does:
-    // ref src/common/point_source_panner.cpp:560-578)
+    // ear::Layout -> C-ABI layout: the channels exactly as the Layout holds them.  A BS.2051
+    // name selects the tabulated hull, any other name makes the panner triangulate the nominal
+    // positions itself (ref src/common/point_source_panner.cpp:484-487); the panner range-checks
+    // the screen loudspeakers as libear does (:560-578)
     inline LayoutHandle toHandle(const Layout &layout) {
-      std::vector<double> pos;
-      for (const Channel &c : layout.channels()) {
-        const PolarPosition p = c.polarPosition();
-        pos.push_back(p.azimuth);
-        pos.push_back(p.elevation);
-        pos.push_back(p.distance);
+      const std::vector<Channel> &ch = layout.channels();
+      std::vector<const char *> names;
+      std::vector<double> pos, nominal, az, el;
+      std::vector<int32_t> lfe;
+      for (const Channel &c : ch) {
+        names.push_back(c.name().c_str());
+        const PolarPosition p = c.polarPosition(), q = c.polarPositionNominal();
+        pos.insert(pos.end(), {p.azimuth, p.elevation, p.distance});
+        nominal.insert(nominal.end(), {q.azimuth, q.elevation, q.distance});
+        az.insert(az.end(), {c.azimuthRange().first, c.azimuthRange().second});
+        el.insert(el.end(), {c.elevationRange().first, c.elevationRange().second});
+        lfe.push_back(c.isLfe() ? 1 : 0);
       }
       earb200_layout *h = nullptr;
-      check(earb200_layout_create_with_positions(layout.name().c_str(), (int)layout.channels().size(), pos.data(), &h));
-      LayoutHandle out(h);
-      for (size_t i = 0; i < layout.channels().size(); i++)
-        if (layout.channels()[i].name() != earb200_layout_channel_name(h, (int)i))
-          throw invalid_argument("channel " + layout.channels()[i].name() + " does not match BS.2051 layout " +
-                                 layout.name());
-      return out;
+      check(earb200_layout_create_custom(layout.name().c_str(), (int)ch.size(), names.data(), pos.data(),
+                                         nominal.data(), az.data(), el.data(), lfe.data(), &h));
+      return LayoutHandle(h);
     }
   }  // namespace b200
 

@@ -99,7 +99,10 @@ class PointSourcePanner:
 
     def __init__(self, layout):
         self.h = C.c_void_p()
-        _chk(lib().ref_psp_new(layout.encode(), C.byref(self.h)))
+        if isinstance(layout, dict):  # custom layout, see custom_layout()
+            _chk(lib().ref_psp_new_custom(*_custom_args(layout), C.byref(self.h)))
+        else:
+            _chk(lib().ref_psp_new(layout.encode(), C.byref(self.h)))
         self.S = lib().ref_psp_num_channels(self.h)
         self.n_regions = lib().ref_psp_num_regions(self.h)
 
@@ -147,8 +150,12 @@ class Objects:
 
     def __init__(self, layout):
         self.h = C.c_void_p()
-        _chk(lib().ref_objects_new(layout.encode(), C.byref(self.h)))
-        self.n_out = len(layout_info(layout)["names"])
+        if isinstance(layout, dict):
+            _chk(lib().ref_objects_new_custom(*_custom_args(layout), C.byref(self.h)))
+            self.n_out = len(layout["names"])
+        else:
+            _chk(lib().ref_objects_new(layout.encode(), C.byref(self.h)))
+            self.n_out = len(layout_info(layout)["names"])
 
     def __del__(self):
         if getattr(self, "h", None):
@@ -321,3 +328,33 @@ def conversion(pos, ext=None, to_polar=True):
         ext_out = None
     _chk(lib().ref_conversion(C.c_long(len(pos)), int(bool(to_polar)), _p(pos), _p(ext), _p(pos_out), _p(ext_out)))
     return pos_out, ext_out
+
+
+def custom_layout(name, names, pos, nominal=None, az_range=None, el_range=None, is_lfe=None):
+    """Flat description of an ear::Layout(name, channels); defaults as ear::Channel."""
+    pos = _f64(pos).reshape(-1, 3)
+    nominal = pos.copy() if nominal is None else _f64(nominal).reshape(-1, 3)
+    az_range = np.stack([pos[:, 0], pos[:, 0]], 1) if az_range is None else _f64(az_range).reshape(-1, 2)
+    el_range = np.stack([pos[:, 1], pos[:, 1]], 1) if el_range is None else _f64(el_range).reshape(-1, 2)
+    is_lfe = np.zeros(len(pos), np.int32) if is_lfe is None else np.ascontiguousarray(is_lfe, dtype=np.int32)
+    return dict(name=name, names=list(names), pos=pos, nominal=nominal, az_range=np.ascontiguousarray(az_range),
+                el_range=np.ascontiguousarray(el_range), is_lfe=is_lfe)
+
+
+def _custom_args(lay):
+    return (lay["name"].encode(), len(lay["names"]), "\n".join(lay["names"]).encode(), _p(lay["pos"]),
+            _p(lay["nominal"]), _p(lay["az_range"]), _p(lay["el_range"]), _p(lay["is_lfe"]))
+
+
+def convex_hull(xyz):
+    """ear::convex_hull: list of facets (sorted vertex index lists) in the reference's order."""
+    xyz = _f64(xyz).reshape(-1, 3)
+    buf = np.zeros(8 * len(xyz) * 8 + 64, dtype=np.int32)
+    n = C.c_int(0)
+    _chk(lib().ref_convex_hull(len(xyz), _p(xyz), _p(buf), len(buf), C.byref(n)))
+    out, k = [], 0
+    while k < n.value:
+        c = int(buf[k])
+        out.append([int(v) for v in buf[k + 1:k + 1 + c]])
+        k += 1 + c
+    return out

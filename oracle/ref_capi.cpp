@@ -29,6 +29,7 @@
 #include "common/point_source_panner.hpp"
 #undef private
 
+#include "common/convex_hull.hpp"
 #include "common/facets.hpp"
 #include "common/geom.hpp"
 #include "common/helpers/eigen_helpers.hpp"
@@ -155,9 +156,61 @@ int ref_facets(const char *layout_name, int *out, int cap, int *n) {
 }
 
 // ---- point source panner + region index --------------------------------
+// a Layout from flat arrays: names separated by '\n'; pos / nominal [n][3]; ranges [n][2]
+static Layout make_custom_layout(const char *name, int n, const char *names, const double *pos,
+                                 const double *nominal, const double *az_range,
+                                 const double *el_range, const int *is_lfe) {
+  std::vector<Channel> channels;
+  std::string all(names);
+  size_t start = 0;
+  for (int i = 0; i < n; i++) {
+    size_t end = all.find('\n', start);
+    std::string cname = all.substr(start, end == std::string::npos ? std::string::npos : end - start);
+    start = end == std::string::npos ? all.size() : end + 1;
+    channels.emplace_back(
+        cname, PolarPosition{pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]},
+        PolarPosition{nominal[3 * i], nominal[3 * i + 1], nominal[3 * i + 2]},
+        std::make_pair(az_range[2 * i], az_range[2 * i + 1]),
+        std::make_pair(el_range[2 * i], el_range[2 * i + 1]), is_lfe[i] != 0);
+  }
+  return Layout(name, channels);
+}
+
+static int build_psp(Layout layout, void **out);
+
 int ref_psp_new(const char *layout_name, void **out) {
   REF_TRY
-  Layout layout = getLayout(layout_name).withoutLfe();
+  return build_psp(getLayout(layout_name).withoutLfe(), out);
+  REF_CATCH
+}
+
+// custom layout (any name): the hull comes from convex_hull when the name has no FACETS entry
+int ref_psp_new_custom(const char *name, int n, const char *names, const double *pos,
+                       const double *nominal, const double *az_range, const double *el_range,
+                       const int *is_lfe, void **out) {
+  REF_TRY
+  return build_psp(make_custom_layout(name, n, names, pos, nominal, az_range, el_range, is_lfe).withoutLfe(), out);
+  REF_CATCH
+}
+
+// ear::convex_hull on n points; out: flat int array, each facet = [count, v0, v1, ...]
+int ref_convex_hull(int n, const double *xyz, int *out, int cap, int *n_out) {
+  REF_TRY
+  std::vector<Eigen::Vector3d> pts;
+  for (int i = 0; i < n; i++) pts.emplace_back(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]);
+  int k = 0;
+  for (const auto &facet : convex_hull(pts)) {
+    if (k + 1 + (int)facet.size() > cap) return 8;
+    out[k++] = (int)facet.size();
+    for (int v : facet) out[k++] = v;
+  }
+  *n_out = k;
+  return 0;
+  REF_CATCH
+}
+
+static int build_psp(Layout layout, void **out) {
+  {
   auto h = std::make_unique<RefPsp>();
   h->psp = configurePolarPanner(layout);
   if (layout.name() != "0+2+0") {
@@ -165,7 +218,9 @@ int ref_psp_new(const char *layout_name, void **out) {
     std::set<int> virtualVerts;
     std::tie(positionsReal, positionsNominal, virtualVerts, h->downmix) =
         getAugmentedLayout(layout);
-    std::vector<Facet> facets = FACETS.at(layout.name());
+    auto facets_it = FACETS.find(layout.name());
+    std::vector<Facet> facets =
+        facets_it != FACETS.end() ? facets_it->second : convex_hull(positionsNominal);
     for (int virtualVert : virtualVerts) {
       Facet realVerts = _adjacent_verts(facets, virtualVert);
       std::vector<int> realVertsVec(realVerts.begin(), realVerts.end());
@@ -200,7 +255,7 @@ int ref_psp_new(const char *layout_name, void **out) {
   }
   *out = h.release();
   return 0;
-  REF_CATCH
+  }
 }
 void ref_psp_free(void *h) { delete (RefPsp *)h; }
 int ref_psp_num_channels(void *h) {
@@ -299,6 +354,14 @@ const char *ref_extent_isa() {
 int ref_objects_new(const char *layout_name, void **out) {
   REF_TRY
   *out = new GainCalculatorObjects(getLayout(layout_name));
+  return 0;
+  REF_CATCH
+}
+int ref_objects_new_custom(const char *name, int n, const char *names, const double *pos,
+                           const double *nominal, const double *az_range, const double *el_range,
+                           const int *is_lfe, void **out) {
+  REF_TRY
+  *out = new GainCalculatorObjects(make_custom_layout(name, n, names, pos, nominal, az_range, el_range, is_lfe));
   return 0;
   REF_CATCH
 }

@@ -341,6 +341,77 @@ def gen_conversion():
                         p2c_ext=p2c_ext, cart=cartp, cart_ext=cart_ext, c2p_pos=c2p_pos, c2p_ext=c2p_ext)
 
 
+def custom_layouts():
+    """Layouts whose names are not in BS.2051 (ear::Layout(name, channels)): the panner builds
+    their hull itself (convex_hull).  Channel names still follow BS.2051 (the extra-speaker rule
+    reads the layers from them); LFE channels are dropped by every calculator."""
+    out = {}
+    # 4+5+0's channels under another name, real positions moved inside the allowed ranges
+    info = ref.layout_info("4+5+0")
+    pos = info["pos"].copy()
+    pos[0, 0], pos[1, 0], pos[4, 0], pos[6, 1] = 25.0, -35.0, 118.0, 38.0
+    out["renamed_4+5+0"] = ref.custom_layout("renamed_4+5+0", info["names"], pos, info["nominal"],
+                                             info["ranges"][:, :2], info["ranges"][:, 2:], info["is_lfe"])
+    # mid ring of five at non-standard azimuths + four upper speakers; nominal = real
+    names = ["M+000", "M+045", "M-045", "M+135", "M-135", "U+045", "U-045", "U+135", "U-135"]
+    pos = [[0, 0, 1], [45, 0, 1], [-45, 0, 1], [135, 0, 1], [-135, 0, 1],
+           [45, 35, 1], [-45, 35, 1], [135, 35, 1], [-135, 35, 1]]
+    out["ring5_upper4"] = ref.custom_layout("ring5_upper4", names, pos)
+    # seven mid, two upper (extra upper speakers appear at the back), three bottom, one LFE
+    names = ["M+000", "M+030", "M-030", "M+090", "M-090", "M+135", "M-135", "U+045", "U-045",
+             "B+000", "B+045", "B-045", "LFE1"]
+    pos = [[0, 0, 1], [30, 0, 1], [-30, 0, 1], [90, 0, 1], [-90, 0, 1], [135, 0, 1], [-135, 0, 1],
+           [45, 30, 1], [-45, 30, 1], [0, -30, 1], [45, -30, 1], [-45, -30, 1], [45, -30, 1]]
+    lfe = [0] * 12 + [1]
+    out["mid7_upper2_bottom3"] = ref.custom_layout("mid7_upper2_bottom3", names, pos, is_lfe=lfe)
+    return out
+
+
+def gen_custom():
+    """Custom-layout path (SURVEY 8f.4): ear::convex_hull facets for a set of point clouds, and
+    point-source gains / region indices / Objects gains on layouts with non-BS.2051 names."""
+    out = {}
+    rng = np.random.default_rng(18)
+    clouds = []
+    for name in LAYOUTS[1:]:
+        info = ref.layout_info(name)
+        nom = info["nominal"][~info["is_lfe"]]
+        pts = [cart(nom[:, 0], nom[:, 1]), [[0.0, 0.0, -1.0]]]
+        if "T+000" not in info["names"] and "UH+180" not in info["names"]:
+            pts.append([[0.0, 0.0, 1.0]])
+        clouds.append(np.concatenate(pts))
+    clouds += [sphere(rng, n) for n in (4, 5, 6, 9, 14, 20)]
+    clouds.append(cart(np.array([45.0, -45, 135, -135, 45, -45, 135, -135]),
+                       np.array([35.0, 35, 35, 35, -35, -35, -35, -35])))  # a box: six quads
+    out["n_clouds"] = np.array(len(clouds))
+    for k, pts in enumerate(clouds):
+        facets = ref.convex_hull(pts)
+        out[f"hull{k}/xyz"] = pts
+        out[f"hull{k}/facets"] = np.array([x for f in facets for x in [len(f)] + f], dtype=np.int32)
+    az, el = np.meshgrid(np.linspace(-180, 180, 21), np.linspace(-90, 90, 11))
+    grid = cart(az.ravel(), el.ravel())
+    lays = custom_layouts()
+    out["layouts"] = np.array(sorted(lays))
+    for key, lay in lays.items():
+        for f in ("pos", "nominal", "az_range", "el_range", "is_lfe"):
+            out[f"{key}/{f}"] = lay[f]
+        out[f"{key}/names"] = np.array(lay["names"])
+        keep = lay["is_lfe"] == 0
+        spk = cart(lay["pos"][keep, 0], lay["pos"][keep, 1])
+        xyz = np.concatenate([grid, spk, sphere(rng, 300) * rng.uniform(0.1, 2.0, (300, 1))])
+        g, reg, inner = ref.PointSourcePanner(lay).handle(xyz)
+        out[f"{key}/xyz"], out[f"{key}/gains"], out[f"{key}/region"], out[f"{key}/inner"] = xyz, g, reg, inner
+        n = 48
+        obj = np.stack([rng.uniform(-180, 180, n), np.degrees(np.arcsin(rng.uniform(-1, 1, n))),
+                        rng.uniform(0.2, 1.5, n), rng.uniform(0, 360, n), rng.uniform(0, 360, n),
+                        np.where(rng.uniform(size=n) < 0.5, 0.0, rng.uniform(0, 1, n)),
+                        rng.uniform(0, 1, n), rng.uniform(0, 1, n)])
+        obj[3:6, :8] = 0.0  # some point sources
+        d, f = ref.Objects(lay).calculate(*obj, dtype=np.float32)
+        out[f"{key}/obj_in"], out[f"{key}/obj_direct"], out[f"{key}/obj_diffuse"] = obj, d, f
+    np.savez_compressed(os.path.join(HERE, "custom.npz"), **out)
+
+
 def gen_kat():
     """Known answers held by the reference's own tests (not produced by running anything)."""
     kat = {
@@ -369,6 +440,6 @@ if __name__ == "__main__":
     if not ref.available():
         raise SystemExit("build oracle/_ref first: make -C oracle")
     for fn in (gen_psp, gen_extent, gen_objects, gen_interp, gen_convolver, gen_decorrelators, gen_hoa,
-               gen_direct_speakers, gen_delay, gen_conversion, gen_kat):
+               gen_direct_speakers, gen_delay, gen_conversion, gen_custom, gen_kat):
         fn()
         print("wrote", fn.__name__[4:])

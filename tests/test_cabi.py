@@ -100,3 +100,29 @@ def test_product_does_not_import_the_oracle():
             src = open(path, errors="ignore").read()
             assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), path
             assert "libear_ref" not in src and "ear_oracle" not in src, path
+
+
+def test_convex_hull_matches_reference_golden(eb):
+    # host-side triangulation of custom layouts (ear::convex_hull, ref src/common/convex_hull.cpp:7-100):
+    # same facets in the same order as the compiled reference
+    g = np.load(os.path.join(GOLDEN, "custom.npz"))
+    for k in range(int(g["n_clouds"])):
+        flat, exp, i = g[f"hull{k}/facets"], [], 0
+        while i < len(flat):
+            exp.append([int(v) for v in flat[i + 1:i + 1 + flat[i]]])
+            i += 1 + flat[i]
+        assert eb.convex_hull(g[f"hull{k}/xyz"]) == exp, k
+    with pytest.raises(eb.InternalError):  # "collinear points in convex hull"
+        eb.convex_hull([[0, 0, 1.0], [0, 0, 1.0], [0, 1.0, 0], [1.0, 0, 0]])
+    with pytest.raises(eb.InvalidArgument):
+        eb.convex_hull([[0, 0, 1.0], [0, 1.0, 0], [1.0, 0, 0]])
+
+
+def test_custom_layout_handle_round_trip(eb):
+    g = np.load(os.path.join(GOLDEN, "custom.npz"))
+    key = "mid7_upper2_bottom3"
+    lay = eb.Layout(key, channels=dict(names=[str(n) for n in g[f"{key}/names"]], pos=g[f"{key}/pos"],
+                                       is_lfe=g[f"{key}/is_lfe"]))
+    assert lay.channel_names[-1] == "LFE1" and lay.is_lfe[-1] and not lay.is_lfe[:-1].any()
+    assert np.array_equal(lay.positions, g[f"{key}/pos"])
+    assert np.array_equal(lay.nominal_positions, g[f"{key}/pos"])  # nominal defaults to the real position

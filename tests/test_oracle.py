@@ -287,3 +287,34 @@ def test_conversion_live(ref):
     r_pos, r_ext = ref.conversion(cartp, ext, to_polar=True)
     pos, e = _oracle_conversion(cartp, ext, True)
     assert np.abs(pos - r_pos).max() < 1e-10 and np.abs(e - r_ext).max() < 1e-10
+
+
+# ------------------------------------------------------------------ custom layouts / convex hull
+def _golden_facets(g, k):
+    flat, out, i = g[f"hull{k}/facets"], [], 0
+    while i < len(flat):
+        out.append([int(v) for v in flat[i + 1:i + 1 + flat[i]]])
+        i += 1 + flat[i]
+    return out
+
+
+def test_convex_hull_golden():
+    g = golden("custom")
+    for k in range(int(g["n_clouds"])):
+        assert eo.convex_hull(g[f"hull{k}/xyz"]) == _golden_facets(g, k)
+
+
+def _custom_layout(g, key):
+    return dict(name=key, names=[str(n) for n in g[f"{key}/names"]], pos=g[f"{key}/pos"],
+                nominal=g[f"{key}/nominal"], az_range=g[f"{key}/az_range"], el_range=g[f"{key}/el_range"],
+                is_lfe=g[f"{key}/is_lfe"])
+
+
+def test_custom_layout_psp_golden():
+    g = golden("custom")
+    for key in g["layouts"]:
+        key = str(key)
+        gains, reg, inner = eo.PointSourcePanner(_custom_layout(g, key)).handle(g[f"{key}/xyz"])
+        assert np.array_equal(reg, g[f"{key}/region"]), key
+        assert np.array_equal(inner, g[f"{key}/inner"]), key
+        assert np.abs(gains - g[f"{key}/gains"]).max() < 1e-12, key
