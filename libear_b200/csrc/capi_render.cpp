@@ -208,7 +208,7 @@ int earb200_interp_set_points(earb200_interp *interp, int64_t n_points,
       EARB_CUDA(cudaMemcpy(h.d_gains.ptr, gains, sizeof(float) * mat * n_points,
                            cudaMemcpyHostToDevice));
       if (h.use_tc) {
-        h.d_images.reserve(render_tc_image_floats(h.N) * n_points);
+        h.d_images.reserve(render_tc_image_floats(h.N, h.M) * n_points);
         launch_render_prepare_points(h.N, h.M, (long)n_points, h.d_gains.ptr, h.d_images.ptr, 0);
         EARB_CUDA(cudaGetLastError());
         EARB_CUDA(cudaStreamSynchronize(0));

@@ -90,7 +90,7 @@ namespace earb {
                         const RenderSegment *d_segs, const float *d_images, int n_sms, int accumulate,
                         cudaStream_t stream);
   // per-point gain-matrix images for the tcgen05 kernel (TF32 hi/lo split in UMMA layout)
-  size_t render_tc_image_floats(int N);
+  size_t render_tc_image_floats(int N, int M);
   void launch_render_prepare_points(int N, int M, long n_points, const float *d_gains, float *d_images,
                                     cudaStream_t stream);
   int render_tile_samples(int M);

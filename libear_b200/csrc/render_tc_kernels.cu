@@ -192,10 +192,15 @@ namespace earb {
                                     float *__restrict__ out, long out_stride,
                                     const RenderItem *__restrict__ items, int n_tiles,
                                     const RenderSegment *__restrict__ segs,
-                                    const float *__restrict__ images, int n_stages, int accumulate) {
+                                    const float *__restrict__ images, int n_stages, int accumulate,
+                                    int n_groups) {
       extern __shared__ __align__(128) unsigned char smem_raw[];
       const int Kp = (N + kCh - 1) / kCh * kCh;  // K padded to whole stages
       const int n_iters = Kp / kCh;
+      // a work unit = one 256-sample tile x one group of 16 output channels; the groups of a tile
+      // are adjacent units, so they run on neighbouring CTAs at the same time and the second read
+      // of the tile's input is served by L2
+      const int n_units = n_tiles * n_groups;
       float *sB = reinterpret_cast<float *>(smem_raw);       // [2 tiles][8 groups][Kp/4][8][4]
       float *sx = sB + (size_t)kBBufs * 2 * Kp * kNP;        // [n_stages][kCh][kTile]
       __shared__ __align__(8) uint64_t full[kMaxStages], empty[kMaxStages];
@@ -241,7 +246,9 @@ namespace earb {
           int slot = 0, L = 0;
           uint32_t phase = 0;  // parity of the `empty` completion to wait for, once the ring wrapped
           bool wrapped = false;
-          for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
+          for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, L++) {
+          const int tile = unit / n_groups, grp = unit - tile * n_groups;
+          (void)grp;
             const int t0 = (int)items[tile].t0;
             for (int it = 0; it < n_iters; it++) {
               if (wrapped) mbar_wait(&empty[slot], phase);
@@ -264,11 +271,14 @@ namespace earb {
           const uint32_t quarter = (uint32_t)(Kp * 16 * sizeof(float));  // 2 row groups x Kp/4 x 128 B
           const size_t img = (size_t)Kp * 32;                            // floats per point image
           int L = 0;
-          for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
+          for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, L++) {
+          const int tile = unit / n_groups, grp = unit - tile * n_groups;
+          (void)grp;
             const int ab = L & 1;
             if (L >= 2) mbar_wait(&acc_full[ab], (uint32_t)(((L >> 1) - 1) & 1));
             const RenderSegment seg = segs[items[tile].seg];
-            const float *pa = images + (size_t)seg.pa * img, *pb = images + (size_t)seg.pb * img;
+            const float *pa = images + ((size_t)seg.pa * n_groups + grp) * img,
+                        *pb = images + ((size_t)seg.pb * n_groups + grp) * img;
             float *dst = sB + (size_t)ab * 2 * Kp * kNP;
             mbar_expect_tx(&b_full[ab], 4 * quarter);
             bulk_g2s(dst, pa, quarter, &b_full[ab]);
@@ -292,7 +302,9 @@ namespace earb {
         const uint64_t bdesc_base = b_desc(smem_u32(sB), Kp);
         const uint32_t b_tile_step = (uint32_t)((2 * Kp * kNP * sizeof(float)) >> 4);  // next B buffer
         int g = 0, L = 0;
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
+        for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, L++) {
+          const int tile = unit / n_groups, grp = unit - tile * n_groups;
+          (void)grp;
           const int ab = L & 1;
           // B of this tile: rows 0..31 = [a | b] hi, 32..63 = [a | b] lo
           const int bb = L & 1;
@@ -328,7 +340,7 @@ namespace earb {
         const int row = j * 128 + q * 32 + lane;
         int g = 0, slot = 0;
         uint32_t full_phase = 0;
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
           for (int it = 0; it < n_iters; it++, g++) {
             const int abuf = g & (kABufs - 1);
             mbar_wait(&full[slot], full_phase);
@@ -350,7 +362,9 @@ namespace earb {
 #pragma unroll
             for (int c = 0; c < kCh; c++) {
               // hi = x truncated to TF32, lo = x - hi exactly (13 significant bits; the tensor core
-              // reads the top 19 bits of each operand).  Split error <= 2^-21 |x|, see DESIGN.md
+              // reads the top 19 bits of each operand).  Split error <= 2^-21 |x|, see DESIGN.md.
+              // (Rounding hi instead was measured: -2.7 % throughput, same error against libear --
+              // at N >= 128 the difference is dominated by the fp32 summation order on both sides.)
               const float x = src[c * kTile];
               hi[c] = __uint_as_float(__float_as_uint(x) & 0xffffe000u);
               lo[c] = x - hi[c];
@@ -381,11 +395,15 @@ namespace earb {
         const int q = warp & 3;
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
         int L = 0;
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
+        for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, L++) {
+          const int tile = unit / n_groups, grp = unit - tile * n_groups;
+          (void)grp;
           const int ab = L & 1;
           const RenderItem item = items[tile];
           const RenderSegment seg = segs[item.seg];
           const bool ramp = seg.ramp != 0;
+          const int Mg = min(16, M - grp * 16);  // output channels of this group
+          float *const og = out + (long)grp * 16 * out_stride;
           // accumulate mode: the bus values this thread will add to are fetched before waiting for
           // the accumulators, so their latency hides behind the MMAs of this tile
           float prev[kMT][16];
@@ -394,7 +412,7 @@ namespace earb {
             for (int j = 0; j < kMT; j++) {
               const long tp = item.t0 + j * 128 + q * 32 + lane;
 #pragma unroll
-              for (int m = 0; m < 16; m++) prev[j][m] = (m < M) ? __ldcs(out + (long)m * out_stride + tp) : 0.0f;
+              for (int m = 0; m < 16; m++) prev[j][m] = (m < Mg) ? __ldcs(og + (long)m * out_stride + tp) : 0.0f;
             }
           }
           mbar_wait(&acc_full[ab], (uint32_t)((L >> 1) & 1));
@@ -409,13 +427,13 @@ namespace earb {
             const float p = ramp ? (float)(t - seg.ramp_start) * seg.scale : 0.0f;
 #pragma unroll
             for (int m = 0; m < 16; m++) {
-              if (m < M) {
+              if (m < Mg) {
                 // columns 0..15: sum_n x * g_a (start point), 16..31: sum_n x * g_b (end point)
                 const float sa = a[m] + b[m];
                 const float sb = a[16 + m] + b[16 + m];
                 float r = ramp ? fmaf(p, sb - sa, sa) : sa;
                 if (accumulate) r += prev[j][m];  // mix into the bus
-                if (EARB_RENDER_EXPERIMENT < 3) __stcs(out + (long)m * out_stride + t, r);
+                if (EARB_RENDER_EXPERIMENT < 3) __stcs(og + (long)m * out_stride + t, r);
               }
             }
           }
@@ -437,42 +455,46 @@ namespace earb {
     // Per-point image of a gain matrix g[N][M] in the layout the UMMA reads (see b_desc):
     // [hi | lo][2 row groups][Kp/4][8 rows][4], hi = g rounded to TF32, lo = TF32(g - hi); rows
     // m >= M and channels k >= N are zero.  Written once per set_points.
-    __global__ void render_prepare_points_kernel(int N, int M, int Kp, long n_points,
+    __global__ void render_prepare_points_kernel(int N, int M, int Kp, int n_groups, long n_points,
                                                  const float *__restrict__ gains,
                                                  float *__restrict__ images) {
-      const long total = n_points * Kp * 16;
+      const long total = n_points * n_groups * Kp * 16;
       for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-        // i enumerates (point, group, chunk, row-in-group, k-in-chunk) of the hi half
+        // i enumerates (point, output group, row group, chunk, row-in-group, k-in-chunk) of the hi half
         const int e = (int)(i % ((long)Kp * 16));
-        const long p = i / ((long)Kp * 16);
+        const long pg = i / ((long)Kp * 16);  // point * n_groups + output group
+        const long p = pg / n_groups;
+        const int og = (int)(pg - p * n_groups);
         const int grp = e / (Kp * 8), rem = e % (Kp * 8);
         const int chunk = rem / 32, r8 = (rem % 32) / 4, k4 = rem % 4;
-        const int m = grp * 8 + r8, k = chunk * 4 + k4;
+        const int m = og * 16 + grp * 8 + r8, k = chunk * 4 + k4;
         float hi = 0.0f, lo = 0.0f;
         if (m < M && k < N) {
           const float g = gains[(p * N + k) * M + m];
           hi = round_tf32(g);
           lo = round_tf32(g - hi);
         }
-        float *img = images + p * ((long)Kp * 32);
+        float *img = images + pg * ((long)Kp * 32);
         img[e] = hi;
         img[Kp * 16 + e] = lo;
       }
     }
   }  // namespace
 
-  size_t render_tc_image_floats(int N) {
+  // floats per interpolation point: one image per group of 16 output channels
+  size_t render_tc_image_floats(int N, int M) {
     const int Kp = (N + kCh - 1) / kCh * kCh;
-    return (size_t)Kp * 32;
+    return (size_t)Kp * 32 * ((M + 15) / 16);
   }
 
   void launch_render_prepare_points(int N, int M, long n_points, const float *d_gains, float *d_images,
                                     cudaStream_t stream) {
     if (n_points <= 0) return;
     const int Kp = (N + kCh - 1) / kCh * kCh;
-    const long total = n_points * Kp * 16;
+    const int n_groups = (M + 15) / 16;
+    const long total = n_points * n_groups * Kp * 16;
     const unsigned blocks = (unsigned)std::min<long>((total + 255) / 256, 148 * 16);
-    render_prepare_points_kernel<<<blocks, 256, 0, stream>>>(N, M, Kp, n_points, d_gains, d_images);
+    render_prepare_points_kernel<<<blocks, 256, 0, stream>>>(N, M, Kp, n_groups, n_points, d_gains, d_images);
   }
 
   namespace {
@@ -494,7 +516,9 @@ namespace earb {
     return b_bytes(N, M) + sizeof(float) * (size_t)stages_for(N, M) * kCh * kTile;
   }
 
-  bool render_tc_supported(int N, int M) { return M <= 16 && N <= 256; }
+  // M > 16 runs as ceil(M / 16) output groups per tile (same kernel, the input tile is read once
+  // from HBM and again from L2)
+  bool render_tc_supported(int N, int M) { return M <= EARB_MAX_OUT && N <= 256; }
 
   namespace {
     typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
@@ -541,9 +565,11 @@ namespace earb {
                            (int)kSmemBudget);
       configured = true;
     }
-    const unsigned grid = (unsigned)std::min<long>(n_tiles, n_sms > 0 ? n_sms : 148);
-    render_tc_persistent_kernel<<<grid, kThreadsP, smem, stream>>>(
-        map, N, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(N, M), accumulate);
+    const int n_groups = (M + 15) / 16;
+    const unsigned grid = (unsigned)std::min<long>(n_tiles * n_groups, n_sms > 0 ? n_sms : 148);
+    render_tc_persistent_kernel<<<grid, kThreadsP, smem, stream>>>(map, N, M, out, out_stride, d_items, (int)n_tiles,
+                                                                   d_segs, d_images, stages_for(N, M), accumulate,
+                                                                   n_groups);
     return true;
   }
 }  // namespace earb

@@ -59,17 +59,45 @@ def test_one_point_and_only_step(eb, ref):
     assert peak_err(out, exp) < 1e-6
 
 
-@pytest.mark.parametrize("N,M", [(1, 1), (1, 7), (16, 12), (32, 24), (7, 9), (3, 17), (2, 32), (128, 14)])
+def exact_render(x, samples, gains):
+    """float64 evaluation of LinearInterpMatrix (ref include/ear/dsp/gain_interpolator.hpp:248-300) for
+    strictly increasing sample indices that cover the whole call."""
+    x, gains = x.astype(np.float64), gains.astype(np.float64)
+    T = x.shape[1]
+    out = np.zeros((gains.shape[2], T))
+    for i in range(len(samples) - 1):
+        a, b = int(samples[i]), int(samples[i + 1])
+        t = np.arange(max(a, 0), min(b, T))
+        if len(t) == 0:
+            continue
+        p = (t - a) / float(b - a)
+        out[:, t] = (np.einsum("nm,nt->mt", gains[i], x[:, t]) * (1.0 - p) +
+                     np.einsum("nm,nt->mt", gains[i + 1], x[:, t]) * p)
+    return out
+
+
+@pytest.mark.parametrize("N,M", [(1, 1), (1, 7), (16, 12), (32, 24), (7, 9), (3, 17), (2, 32), (128, 14),
+                                 (128, 24), (20, 31), (256, 22)])
 def test_channel_shapes(eb, ref, N, M):
     # (1,1) = LinearInterpSingle, (1,M) = LinearInterpVector, (16,12) = HOA order 3 -> 4+7+0,
-    # (32,24) = the reference's matrix_benchmark shape, (128,14) = BASELINE config 2 shape
+    # (32,24) = the reference's matrix_benchmark shape, (128,14) = BASELINE config 2 shape;
+    # M > 16 runs as two groups of output channels per tile on the tensor-core path
     rng = np.random.default_rng(N * 100 + M)
     T = 4096 + 37
     x = np.clip(rng.normal(0, 0.25, size=(N, T)), -1, 1).astype(np.float32)
     samples = np.arange(0, T + 512, 512)
     gains = (rng.uniform(0, 1, size=(len(samples), N, M)) / np.sqrt(N)).astype(np.float32)
     out, exp = run_both(eb, ref, x, samples, gains)
-    assert peak_err(out, exp) < 1e-6
+    if N < 128:
+        assert peak_err(out, exp) < 1e-6
+    else:
+        # 128+ products per sample: libear's sequential fp32 sum and the tensor-core fp32 sum each sit
+        # ~5e-7 of peak away from the exact result, so the bar is 1e-6 against the float64 evaluation
+        # of the same formula and 2e-6 between the two fp32 paths
+        exact = exact_render(x, samples, gains)
+        assert peak_err(out, exact) < 1e-6
+        assert peak_err(exp, exact) < 1.5e-6  # the reference's own fp32 rounding
+        assert peak_err(out, exp) < 2e-6
     if N == 1:
         v = ref.interp_vector(x[0], samples, gains[:, 0, :])
         assert peak_err(out, v) < 1e-6
@@ -115,12 +143,13 @@ def test_linearity_full_size_channels(eb):
     assert np.abs(rxy - (0.5 * rx + ry)).max() / np.abs(rxy).max() < 1e-5
 
 
+@pytest.mark.parametrize("M", [12, 24])
 @pytest.mark.parametrize("T,call", [(4096 + 37, None), (3000, 700)])
-def test_accumulate_mixes_channel_groups(eb, ref, T, call):
+def test_accumulate_mixes_channel_groups(eb, ref, T, call, M):
     """Extension earb200_interp_set_accumulate: two groups of objects rendered one after the other
     into the same bus equal one interpolator over all of them (the reference on the full matrix)."""
     rng = np.random.default_rng(21)
-    N, M = 48, 12
+    N = 48
     x = rng.normal(0, 0.25, (N, T)).astype(np.float32)
     samples = np.arange(-100, T + 512, 512)
     g = (rng.uniform(0, 1, (len(samples), N, M)) / 4).astype(np.float32)
