@@ -121,14 +121,14 @@ namespace {
       align = (int)((ia / 4) & 3);
     build_plan(h, block_start, nsamples, align);
     RenderPlan plan{h.d_items.ptr, h.n_items[0], h.n_items[1], h.n_items[2], h.n_items[3], h.use_tc,
-                    h.n_sms, (long)nsamples, h.d_images.ptr, h.accumulate};
+                    h.n_sms, (long)nsamples, h.d_images.ptr, h.accumulate, (long)h.n_points};
     h.timer.start(stream);
     launch_render(h.N, h.M, d_in, (long)in_stride, d_out, (long)out_stride, plan, h.d_segs.ptr,
                   h.d_gains.ptr, stream);
     h.timer.stop(stream);
     EARB_CUDA(cudaGetLastError());
     if (h.use_tc) {
-      h.launches += (h.n_items[0] + h.n_items[1]) > 0;
+      if (h.n_items[0] + h.n_items[1] > 0) h.launches += (h.N + 255) / 256;  // one per group of 256 inputs
       h.launches += (h.n_items[2] > 0) + (h.n_items[3] > 0);
     } else {
       for (int k = 0; k < 4; k++) h.launches += h.n_items[k] > 0;

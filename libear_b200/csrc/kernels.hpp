@@ -78,6 +78,7 @@ namespace earb {
     long n_samples;  // samples per channel of this call (extent of the TMA descriptor)
     const float *d_images;  // per-point gain-matrix images (tcgen05 path)
     int accumulate;         // out += result instead of out = result (mixing channel groups)
+    long n_points;          // interpolation points behind d_images
   };
   // tcgen05 / TMEM variant of the fast path (render_tc_kernels.cu)
   bool render_tc_supported(int N, int M);
@@ -87,8 +88,8 @@ namespace earb {
   // could not be encoded, nothing launched
   bool launch_render_tc(int N, int M, const float *in, long in_stride, long n_samples, float *out,
                         long out_stride, const RenderItem *d_items, long n_tiles,
-                        const RenderSegment *d_segs, const float *d_images, int n_sms, int accumulate,
-                        cudaStream_t stream);
+                        const RenderSegment *d_segs, const float *d_images, long n_points, int n_sms,
+                        int accumulate, cudaStream_t stream);
   // per-point gain-matrix images for the tcgen05 kernel (TF32 hi/lo split in UMMA layout)
   size_t render_tc_image_floats(int N, int M);
   void launch_render_prepare_points(int N, int M, long n_points, const float *d_gains, float *d_images,

@@ -386,7 +386,7 @@ namespace earb {
     if (plan.use_tc) {
       // the ramp and constant tiles are adjacent in the item list: one persistent launch
       if (!launch_render_tc(N, M, in, in_stride, plan.n_samples, out, out_stride, fast_ramp,
-                            n_fast_ramp + n_fast_const, d_segs, plan.d_images, plan.n_sms,
+                            n_fast_ramp + n_fast_const, d_segs, plan.d_images, plan.n_points, plan.n_sms,
                             plan.accumulate, stream))
         throw std::runtime_error("cuTensorMapEncodeTiled failed for the render input");
       n_fast_ramp = n_fast_const = 0;

@@ -455,7 +455,8 @@ namespace earb {
     // Per-point image of a gain matrix g[N][M] in the layout the UMMA reads (see b_desc):
     // [hi | lo][2 row groups][Kp/4][8 rows][4], hi = g rounded to TF32, lo = TF32(g - hi); rows
     // m >= M and channels k >= N are zero.  Written once per set_points.
-    __global__ void render_prepare_points_kernel(int N, int M, int Kp, int n_groups, long n_points,
+    __global__ void render_prepare_points_kernel(int N_total, int k0, int N, int M, int Kp, int n_groups,
+                                                 long n_points,
                                                  const float *__restrict__ gains,
                                                  float *__restrict__ images) {
       const long total = n_points * n_groups * Kp * 16;
@@ -470,7 +471,7 @@ namespace earb {
         const int m = og * 16 + grp * 8 + r8, k = chunk * 4 + k4;
         float hi = 0.0f, lo = 0.0f;
         if (m < M && k < N) {
-          const float g = gains[(p * N + k) * M + m];
+          const float g = gains[(p * N_total + k0 + k) * M + m];
           hi = round_tf32(g);
           lo = round_tf32(g - hi);
         }
@@ -481,20 +482,32 @@ namespace earb {
     }
   }  // namespace
 
-  // floats per interpolation point: one image per group of 16 output channels
+  // N > 256 runs as groups of up to 256 input channels, one launch each, the later ones
+  // accumulating into the output (the gain matrices of 256 channels fill the shared memory)
+  constexpr int kMaxInGroup = 256;
+  static int padded_k(int n) { return (n + kCh - 1) / kCh * kCh; }
+
+  // floats per interpolation point: one image per (input group, group of 16 output channels)
   size_t render_tc_image_floats(int N, int M) {
-    const int Kp = (N + kCh - 1) / kCh * kCh;
-    return (size_t)Kp * 32 * ((M + 15) / 16);
+    size_t total = 0;
+    for (int k0 = 0; k0 < N; k0 += kMaxInGroup)
+      total += (size_t)padded_k(std::min(kMaxInGroup, N - k0)) * 32 * ((M + 15) / 16);
+    return total;
   }
 
+  // image layout: [input group][point][output group][Kp_g * 32]
   void launch_render_prepare_points(int N, int M, long n_points, const float *d_gains, float *d_images,
                                     cudaStream_t stream) {
     if (n_points <= 0) return;
-    const int Kp = (N + kCh - 1) / kCh * kCh;
     const int n_groups = (M + 15) / 16;
-    const long total = n_points * n_groups * Kp * 16;
-    const unsigned blocks = (unsigned)std::min<long>((total + 255) / 256, 148 * 16);
-    render_prepare_points_kernel<<<blocks, 256, 0, stream>>>(N, M, Kp, n_groups, n_points, d_gains, d_images);
+    for (int k0 = 0; k0 < N; k0 += kMaxInGroup) {
+      const int Ng = std::min(kMaxInGroup, N - k0), Kp = padded_k(Ng);
+      const long total = n_points * n_groups * Kp * 16;
+      const unsigned blocks = (unsigned)std::min<long>((total + 255) / 256, 148 * 16);
+      render_prepare_points_kernel<<<blocks, 256, 0, stream>>>(N, k0, Ng, M, Kp, n_groups, n_points, d_gains,
+                                                                d_images);
+      d_images += (size_t)n_points * n_groups * Kp * 32;
+    }
   }
 
   namespace {
@@ -518,7 +531,7 @@ namespace earb {
 
   // M > 16 runs as ceil(M / 16) output groups per tile (same kernel, the input tile is read once
   // from HBM and again from L2)
-  bool render_tc_supported(int N, int M) { return M <= EARB_MAX_OUT && N <= 256; }
+  bool render_tc_supported(int N, int M) { return M <= EARB_MAX_OUT && N >= 1; }
 
   namespace {
     typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
@@ -543,22 +556,11 @@ namespace earb {
   // Returns false when the TMA descriptor cannot be built (the caller then uses the FFMA path).
   bool launch_render_tc(int N, int M, const float *in, long in_stride, long n_samples, float *out,
                         long out_stride, const RenderItem *d_items, long n_tiles,
-                        const RenderSegment *d_segs, const float *d_images, int n_sms, int accumulate,
-                        cudaStream_t stream) {
+                        const RenderSegment *d_segs, const float *d_images, long n_points, int n_sms,
+                        int accumulate, cudaStream_t stream) {
     if (n_tiles <= 0) return true;
     EncodeTiledFn encode = encode_tiled();
     if (!encode) return false;
-    // the input as a [N channels][n_samples] float tensor with a row pitch of in_stride floats
-    CUtensorMap map;
-    const cuuint64_t dims[2] = {(cuuint64_t)n_samples, (cuuint64_t)N};
-    const cuuint64_t strides[1] = {(cuuint64_t)in_stride * sizeof(float)};
-    const cuuint32_t box[2] = {(cuuint32_t)kTile, (cuuint32_t)kCh};
-    const cuuint32_t estr[2] = {1, 1};
-    if (encode(&map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(in), dims, strides, box, estr,
-               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
-      return false;
-    const size_t smem = render_tc_smem_bytes(N, M);
     static bool configured = false;
     if (!configured) {
       cudaFuncSetAttribute(render_tc_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -567,9 +569,23 @@ namespace earb {
     }
     const int n_groups = (M + 15) / 16;
     const unsigned grid = (unsigned)std::min<long>(n_tiles * n_groups, n_sms > 0 ? n_sms : 148);
-    render_tc_persistent_kernel<<<grid, kThreadsP, smem, stream>>>(map, N, M, out, out_stride, d_items, (int)n_tiles,
-                                                                   d_segs, d_images, stages_for(N, M), accumulate,
-                                                                   n_groups);
+    for (int k0 = 0; k0 < N; k0 += kMaxInGroup) {
+      const int Ng = std::min(kMaxInGroup, N - k0);
+      // the input group as a [Ng channels][n_samples] float tensor with a row pitch of in_stride floats
+      CUtensorMap map;
+      const cuuint64_t dims[2] = {(cuuint64_t)n_samples, (cuuint64_t)Ng};
+      const cuuint64_t strides[1] = {(cuuint64_t)in_stride * sizeof(float)};
+      const cuuint32_t box[2] = {(cuuint32_t)kTile, (cuuint32_t)kCh};
+      const cuuint32_t estr[2] = {1, 1};
+      if (encode(&map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(in + (size_t)k0 * in_stride), dims,
+                 strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+        return false;
+      render_tc_persistent_kernel<<<grid, kThreadsP, render_tc_smem_bytes(Ng, M), stream>>>(
+          map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, M),
+          (accumulate || k0 > 0) ? 1 : 0, n_groups);
+      d_images += (size_t)n_points * n_groups * padded_k(Ng) * 32;
+    }
     return true;
   }
 }  // namespace earb

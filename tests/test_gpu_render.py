@@ -77,11 +77,12 @@ def exact_render(x, samples, gains):
 
 
 @pytest.mark.parametrize("N,M", [(1, 1), (1, 7), (16, 12), (32, 24), (7, 9), (3, 17), (2, 32), (128, 14),
-                                 (128, 24), (20, 31), (256, 22)])
+                                 (128, 24), (20, 31), (256, 22), (300, 12), (520, 24)])
 def test_channel_shapes(eb, ref, N, M):
     # (1,1) = LinearInterpSingle, (1,M) = LinearInterpVector, (16,12) = HOA order 3 -> 4+7+0,
     # (32,24) = the reference's matrix_benchmark shape, (128,14) = BASELINE config 2 shape;
-    # M > 16 runs as two groups of output channels per tile on the tensor-core path
+    # M > 16 runs as two groups of output channels per tile on the tensor-core path, N > 256 as
+    # groups of 256 inputs accumulated into the output
     rng = np.random.default_rng(N * 100 + M)
     T = 4096 + 37
     x = np.clip(rng.normal(0, 0.25, size=(N, T)), -1, 1).astype(np.float32)
