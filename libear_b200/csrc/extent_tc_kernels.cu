@@ -143,7 +143,6 @@ namespace earb {
       float sin_thr;  // straight-line part when circle_test_dot >= sin_thr (0, or +inf if circular)
       float m, c;     // fade: weight = m * angle + c between the start and end angles
       float a_sin;    // m * pi/2 + c
-      float a_neg;    // m * pi + c
     };
 
     // Weight of one virtual source (ref polar_extent_simd.hpp:39-95), branch-free.
@@ -155,9 +154,10 @@ namespace earb {
     // two selects (weights differ from the reference's by rounding at the fade ends only).
     // angle = acos(v) on the circle part, asin(|z'|) on the straight part, both from
     // r = acos(|v|) = sqrt(1 - |v|) * P7(|v|) (Abramowitz & Stegun 4.4.46, |error| <= 2e-8):
-    //   circle, v >= 0:  angle = r            weight = sat( m r + c)
-    //   circle, v <  0:  angle = pi - r       weight = sat(-m r + (m pi + c))
-    //   straight:        angle = pi/2 - r     weight = sat(-m r + (m pi/2 + c))
+    // With q = pi/2 - r = asin(|v|) (folded into the last FMA) the three cases
+    //   straight:        angle = q                         weight = sat(m q + c)
+    //   circle:          angle = pi/2 - copysign(q, v)     weight = sat(m (-copysign(q, v)) + (m pi/2 + c))
+    // share one saturating FMA whose operand is q with the inverted sign of v (one LOP3).
     __device__ __forceinline__ float point_weight(const PassRegs &c, float x, float y, float z) {
       const float xt = fmaf(x, c.b[0], fmaf(y, c.b[1], __fmul_rn(z, c.b[2])));
       const float yt = fmaf(x, c.b[3], fmaf(y, c.b[4], __fmul_rn(z, c.b[5])));
@@ -167,7 +167,7 @@ namespace earb {
       const float circle_dot = fmaf(ax, c.cc0, __fmul_rn(yt, c.cc1));
       const bool is_sin = circle_test_dot >= c.sin_thr;
       const float v = is_sin ? zt : circle_dot;
-      const float av = fminf(fabsf(v), 1.0f);  // rounding can leave |v| a few ulp above 1
+      const float av = fabsf(v);  // rounding can leave |v| a few ulp above 1: the square root's argument saturates
       float p = -0.0012624911f;
       p = fmaf(p, av, 0.0066700901f);
       p = fmaf(p, av, -0.0170881256f);
@@ -177,12 +177,11 @@ namespace earb {
       p = fmaf(p, av, -0.2145988016f);
       p = fmaf(p, av, 1.5707963050f);
       float sq;
-      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(__fsub_rn(1.0f, av)));
-      const float r = __fmul_rn(sq, p);
-      const bool neg = circle_dot < 0.0f;
-      const float slope = (is_sin || neg) ? -c.m : c.m;
-      const float offs = is_sin ? c.a_sin : (neg ? c.a_neg : c.c);
-      return __saturatef(fmaf(slope, r, offs));
+      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(__saturatef(__fsub_rn(1.0f, av))));
+      const float q = fmaf(-sq, p, 1.57079632679490f);
+      // q carrying the inverted sign bit of circle_dot
+      const float qs = __uint_as_float(__float_as_uint(q) | (~__float_as_uint(circle_dot) & 0x80000000u));
+      return __saturatef(fmaf(c.m, is_sin ? q : qs, is_sin ? c.c : c.a_sin));
     }
 
     // Barriers
@@ -322,7 +321,6 @@ namespace earb {
             c.m = e.m;
             c.c = e.c;
             c.a_sin = fmaf(e.m, 1.57079632679490f, e.c);
-            c.a_neg = fmaf(e.m, 3.14159265358979f, e.c);
             c.sin_thr = 0.0f;
             if (e.is_circular) {
               c.sin_thr = __int_as_float(0x7f800000);
