@@ -184,6 +184,77 @@ namespace earb {
       return __saturatef(fmaf(c.m, is_sin ? q : qs, is_sin ? c.c : c.a_sin));
     }
 
+    // ---- packed fp32 (sm_100 FFMA2 / FMUL2 / FADD2: two FMAs per lane per issue slot).  The kernel
+    // is issue-bound, so the weights of two virtual sources are evaluated side by side: the FMA-pipe
+    // work keeps its cost, the issue slots it needs halve.  Scalar operands (the pass constants)
+    // are given as broadcast pairs, which ptxas folds into the instruction's scalar-operand form.
+    typedef unsigned long long f32x2;
+    __device__ __forceinline__ f32x2 pk(float a, float b) {
+      f32x2 r;
+      asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+      return r;
+    }
+    __device__ __forceinline__ void upk(f32x2 v, float &a, float &b) {
+      asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+    }
+    __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+      f32x2 r;
+      asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+      return r;
+    }
+    __device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+      f32x2 r;
+      asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+      return r;
+    }
+    __device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) {
+      f32x2 r;
+      asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+      return r;
+    }
+    __device__ __forceinline__ f32x2 bc(float a) { return pk(a, a); }
+    __device__ __forceinline__ f32x2 abs2(f32x2 v) { return v & 0x7fffffff7fffffffull; }
+
+    // point_weight for two virtual sources at once: X, Y, Z hold the coordinates of both; the same
+    // operations in the same order per half, so each weight is bit-identical to point_weight's.
+    __device__ __forceinline__ void point_weight2(const PassRegs &c, f32x2 X, f32x2 Y, f32x2 Z, float &w0,
+                                                  float &w1) {
+      const f32x2 xt = fma2(X, bc(c.b[0]), fma2(Y, bc(c.b[1]), mul2(Z, bc(c.b[2]))));
+      const f32x2 yt = fma2(X, bc(c.b[3]), fma2(Y, bc(c.b[4]), mul2(Z, bc(c.b[5]))));
+      const f32x2 zt = fma2(X, bc(c.b[6]), fma2(Y, bc(c.b[7]), mul2(Z, bc(c.b[8]))));
+      const f32x2 ax = abs2(xt);
+      const f32x2 ctd = fma2(ax, bc(c.ct0), mul2(yt, bc(c.ct1)));
+      const f32x2 cd = fma2(ax, bc(c.cc0), mul2(yt, bc(c.cc1)));
+      float ctd0, ctd1, cd0, cd1, z0, z1;
+      upk(ctd, ctd0, ctd1);
+      upk(cd, cd0, cd1);
+      upk(zt, z0, z1);
+      const bool s0 = ctd0 >= c.sin_thr, s1 = ctd1 >= c.sin_thr;
+      const float v0 = s0 ? z0 : cd0, v1 = s1 ? z1 : cd1;
+      const f32x2 av = abs2(pk(v0, v1));
+      f32x2 p = fma2(bc(-0.0012624911f), av, bc(0.0066700901f));
+      p = fma2(p, av, bc(-0.0170881256f));
+      p = fma2(p, av, bc(0.0308918810f));
+      p = fma2(p, av, bc(-0.0501743046f));
+      p = fma2(p, av, bc(0.0889789874f));
+      p = fma2(p, av, bc(-0.2145988016f));
+      p = fma2(p, av, bc(1.5707963050f));
+      float q0, q1;
+      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(q0) : "f"(__saturatef(__fsub_rn(1.0f, fabsf(v0)))));
+      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(q1) : "f"(__saturatef(__fsub_rn(1.0f, fabsf(v1)))));
+      // nq = sq * p - pi/2 = -asin(|v|)
+      const f32x2 nq = fma2(pk(q0, q1), p, bc(-1.57079632679490f));
+      float n0, n1;
+      upk(nq, n0, n1);
+      // asin(|v|) carrying the inverted sign of the circle dot product (plain on the straight part)
+      const float t0 = __uint_as_float((__float_as_uint(n0) & 0x7fffffffu) |
+                                       (~__float_as_uint(s0 ? -0.0f : cd0) & 0x80000000u));
+      const float t1 = __uint_as_float((__float_as_uint(n1) & 0x7fffffffu) |
+                                       (~__float_as_uint(s1 ? -0.0f : cd1) & 0x80000000u));
+      w0 = __saturatef(fmaf(c.m, t0, s0 ? c.c : c.a_sin));
+      w1 = __saturatef(fmaf(c.m, t1, s1 ? c.c : c.a_sin));
+    }
+
     // Barriers
     //   a_full[mt][b]  generators -> MMA         A buffer b of M-tile mt is complete (4 warps)
     //   a_free[mt][b]  MMA commit -> generators  the UMMAs reading it have finished
@@ -199,7 +270,9 @@ namespace earb {
       const int Pp = grid.n_points_pad;  // multiple of kKC
       const int S = grid.n_spk;
       float *sB = reinterpret_cast<float *>(smem_raw);                 // [kBStages][kStageFloats]
-      float4 *spts = reinterpret_cast<float4 *>(sB + kBStages * kStageFloats);  // [Pp]
+      // virtual sources in pairs: sxy[j] = (x, x', y, y'), sz[j] = (z, z') of points 2j and 2j + 1
+      float4 *sxy = reinterpret_cast<float4 *>(sB + kBStages * kStageFloats);  // [Pp / 2]
+      float2 *sz = reinterpret_cast<float2 *>(sxy + Pp / 2);                     // [Pp / 2]
       __shared__ __align__(8) uint64_t a_full[kMTiles][2], a_free[kMTiles][2];
       __shared__ __align__(8) uint64_t b_full[kBStages], b_empty[kBStages], acc_full;
       __shared__ uint32_t tmem_base_s;
@@ -209,7 +282,11 @@ namespace earb {
       const int n_tiles = (n_active + kMTiles * 128 - 1) / (kMTiles * 128);
       const int n_chunks = Pp / kChunk, n_stages = Pp / kKC;
 
-      for (int i = tid; i < Pp; i += kThreads) spts[i] = g_points[i];
+      for (int j = tid; j < Pp / 2; j += kThreads) {
+        const float4 a = g_points[2 * j], b = g_points[2 * j + 1];
+        sxy[j] = make_float4(a.x, b.x, a.y, b.y);
+        sz[j] = make_float2(a.z, b.z);
+      }
       if (tid == 0) {
         for (int m = 0; m < kMTiles; m++)
           for (int b = 0; b < 2; b++) {
@@ -333,11 +410,14 @@ namespace earb {
             const int buf = gc & 1;
             float hi[kChunk], lo[kChunk];
 #pragma unroll
-            for (int i = 0; i < kChunk; i++) {
-              const float4 p = spts[ch * kChunk + i];  // warp-uniform broadcast
-              const float w = point_weight(c, p.x, p.y, p.z);
-              hi[i] = __uint_as_float(__float_as_uint(w) & 0xffffe000u);
-              lo[i] = __fsub_rn(w, hi[i]);
+            for (int i = 0; i < kChunk; i += 2) {
+              const float4 xy = sxy[(ch * kChunk + i) >> 1];  // warp-uniform broadcasts
+              const float2 zz = sz[(ch * kChunk + i) >> 1];
+              float w0, w1;
+              point_weight2(c, pk(xy.x, xy.y), pk(xy.z, xy.w), pk(zz.x, zz.y), w0, w1);
+              hi[i] = __uint_as_float(__float_as_uint(w0) & 0xffffe000u);
+              hi[i + 1] = __uint_as_float(__float_as_uint(w1) & 0xffffe000u);
+              upk(sub2(pk(w0, w1), pk(hi[i], hi[i + 1])), lo[i], lo[i + 1]);
             }
             if (gc >= 2) {
               mbar_wait(&a_free[mt][buf], (uint32_t)(((gc >> 1) - 1) & 1));
