@@ -31,6 +31,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cstdlib>
 
 #include "kernels.hpp"
 
@@ -39,7 +40,9 @@ namespace earb {
     constexpr int kTile = RENDER_TC_TILE;  // samples per CTA (2 UMMA M-tiles)
     constexpr int kMT = kTile / 128;       // M-tiles
     constexpr int kCh = 16;                // channels per stage = two K = 8 UMMA steps
-    constexpr int kNP = 32;                // UMMA N: 16 columns for S, 16 for D
+    // NP = UMMA N of one product: NP/2 columns for S, NP/2 for D.  NP = 32: up to 16 outputs per
+    // work unit, separate main / correction accumulators; NP = 64 ("wide"): up to 32 outputs, the
+    // three products into one accumulator
 
     __device__ __forceinline__ uint32_t smem_u32(const void *p) {
       return (uint32_t)__cvta_generic_to_shared(p);
@@ -181,12 +184,14 @@ namespace earb {
     constexpr int kTmemColsP = 512;
     // TMEM columns: accumulators [2 tiles][main: kMT x 32 | corr: kMT x 32], then
     // A [2 buffers][kMT][hi 16 | lo 16]
-    constexpr int kAccStride = 2 * kMT * kNP;
+    constexpr int kAccCols = 64;  // TMEM columns per M-tile: [main 32 | corr 32] or one 64-wide accumulator
+    constexpr int kAccStride = kMT * kAccCols;
     constexpr int kColAP = 2 * kAccStride;
     constexpr int kBBufs = 2;  // gain-matrix buffers in shared memory
     constexpr int kABufs = 4;  // A-operand ring in TMEM (power of two)
     static_assert(kColAP + kABufs * kMT * 2 * kCh <= kTmemColsP, "TMEM budget");
 
+    template <int NP>
     __global__ void __launch_bounds__(kThreadsP, 1)
         render_tc_persistent_kernel(const __grid_constant__ CUtensorMap in_map, int N, int M,
                                     float *__restrict__ out, long out_stride,
@@ -202,7 +207,7 @@ namespace earb {
       // of the tile's input is served by L2
       const int n_units = n_tiles * n_groups;
       float *sB = reinterpret_cast<float *>(smem_raw);       // [2 tiles][8 groups][Kp/4][8][4]
-      float *sx = sB + (size_t)kBBufs * 2 * Kp * kNP;        // [n_stages][kCh][kTile]
+      float *sx = sB + (size_t)kBBufs * 2 * Kp * NP;         // [n_stages][kCh][kTile]
       __shared__ __align__(8) uint64_t full[kMaxStages], empty[kMaxStages];
       __shared__ __align__(8) uint64_t a_full[kABufs], a_free[kABufs], b_full[kBBufs], acc_full[2], acc_free[2];
       __shared__ uint32_t tmem_base_s;
@@ -268,8 +273,9 @@ namespace earb {
         // copied verbatim from the per-point images.  Buffer L & 1 is free once every UMMA of tile
         // L - 2 has finished (acc_full).
         if (lane == 0) {
-          const uint32_t quarter = (uint32_t)(Kp * 16 * sizeof(float));  // 2 row groups x Kp/4 x 128 B
-          const size_t img = (size_t)Kp * 32;                            // floats per point image
+          const int qf = Kp * (NP / 2);                                  // floats per quarter: NP/16 row groups
+          const uint32_t quarter = (uint32_t)(qf * sizeof(float));
+          const size_t img = (size_t)Kp * NP;                            // floats per point image
           int L = 0;
           for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, L++) {
           const int tile = unit / n_groups, grp = unit - tile * n_groups;
@@ -279,12 +285,12 @@ namespace earb {
             const RenderSegment seg = segs[items[tile].seg];
             const float *pa = images + ((size_t)seg.pa * n_groups + grp) * img,
                         *pb = images + ((size_t)seg.pb * n_groups + grp) * img;
-            float *dst = sB + (size_t)ab * 2 * Kp * kNP;
+            float *dst = sB + (size_t)ab * 2 * Kp * NP;
             mbar_expect_tx(&b_full[ab], 4 * quarter);
             bulk_g2s(dst, pa, quarter, &b_full[ab]);
-            bulk_g2s(dst + Kp * 16, pb, quarter, &b_full[ab]);
-            bulk_g2s(dst + 2 * Kp * 16, pa + Kp * 16, quarter, &b_full[ab]);
-            bulk_g2s(dst + 3 * Kp * 16, pb + Kp * 16, quarter, &b_full[ab]);
+            bulk_g2s(dst + qf, pb, quarter, &b_full[ab]);
+            bulk_g2s(dst + 2 * qf, pa + qf, quarter, &b_full[ab]);
+            bulk_g2s(dst + 3 * qf, pb + qf, quarter, &b_full[ab]);
           }
         }
       } else if (warp >= kMmaWarp) {
@@ -297,10 +303,11 @@ namespace earb {
         asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(leader));
         // instruction descriptors: D f32, A/B tf32, both K-major, M = 128, N = 64 / 32
         const uint32_t idesc_base = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 4) << 24);
-        const uint32_t idesc64 = idesc_base | ((uint32_t)(2 * kNP >> 3) << 17);
-        const uint32_t idesc32 = idesc_base | ((uint32_t)(kNP >> 3) << 17);
+        const uint32_t idesc64 = idesc_base | ((uint32_t)(64 >> 3) << 17);
+        const uint32_t idesc32 = idesc_base | ((uint32_t)(32 >> 3) << 17);
+        const uint32_t b_lo_step = (uint32_t)((Kp * NP * sizeof(float)) >> 4);  // hi rows -> lo rows
         const uint64_t bdesc_base = b_desc(smem_u32(sB), Kp);
-        const uint32_t b_tile_step = (uint32_t)((2 * Kp * kNP * sizeof(float)) >> 4);  // next B buffer
+        const uint32_t b_tile_step = (uint32_t)((2 * Kp * NP * sizeof(float)) >> 4);  // next B buffer
         int g = 0, L = 0;
         for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, L++) {
           const int tile = unit / n_groups, grp = unit - tile * n_groups;
@@ -309,7 +316,7 @@ namespace earb {
           // B of this tile: rows 0..31 = [a | b] hi, 32..63 = [a | b] lo
           const int bb = L & 1;
           uint64_t bd = bdesc_base + (uint64_t)(bb * b_tile_step);
-          const uint32_t acc = tm + ab * kAccStride + j * 2 * kNP;  // [main 32 | corr 32]
+          const uint32_t acc = tm + ab * kAccStride + j * kAccCols;
           mbar_wait(&b_full[bb], (uint32_t)((L >> 1) & 1));
           if (L >= 2) mbar_wait(&acc_free[ab], (uint32_t)(((L >> 1) - 1) & 1));
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -323,8 +330,15 @@ namespace earb {
               for (int ks = 0; ks < (EARB_RENDER_EXPERIMENT >= 2 ? 0 : kCh / 8); ks++) {
                 // one K = 8 step covers two 4-wide chunks of B (2 x 128 bytes within a row group)
                 // [main | corr] (+)= x_hi * [g_hi | g_lo];  corr += x_lo * g_hi
-                umma_tf32_ts(acc, a_hi + ks * 8, bd, idesc64, (it | ks) != 0);
-                umma_tf32_ts(acc + kNP, a_hi + kCh + ks * 8, bd, idesc32, 1);
+                if (NP == 32) {
+                  umma_tf32_ts(acc, a_hi + ks * 8, bd, idesc64, (it | ks) != 0);
+                  umma_tf32_ts(acc + 32, a_hi + kCh + ks * 8, bd, idesc32, 1);
+                } else {
+                  // wide: acc (64 columns) (+)= x_hi * g_hi + x_hi * g_lo + x_lo * g_hi
+                  umma_tf32_ts(acc, a_hi + ks * 8, bd, idesc64, (it | ks) != 0);
+                  umma_tf32_ts(acc, a_hi + ks * 8, bd + b_lo_step, idesc64, 1);
+                  umma_tf32_ts(acc, a_hi + kCh + ks * 8, bd, idesc64, 1);
+                }
                 bd += (2 * 128) >> 4;
               }
               umma_commit(&a_free[abuf]);  // arrives when every UMMA issued so far has finished
@@ -402,12 +416,14 @@ namespace earb {
           const RenderItem item = items[tile];
           const RenderSegment seg = segs[item.seg];
           const bool ramp = seg.ramp != 0;
-          const int Mg = min(16, M - grp * 16);  // output channels of this group
-          float *const og = out + (long)grp * 16 * out_stride;
+          constexpr int MO = NP / 2;               // output channels per work unit
+          const int Mg = min(MO, M - grp * MO);    // output channels of this group
+          float *const og = out + (long)grp * MO * out_stride;
           // accumulate mode: the bus values this thread will add to are fetched before waiting for
           // the accumulators, so their latency hides behind the MMAs of this tile
+          // (wide units read the bus inside the loop instead: 64 more registers would not fit)
           float prev[kMT][16];
-          if (accumulate) {
+          if (accumulate && NP == 32) {
 #pragma unroll
             for (int j = 0; j < kMT; j++) {
               const long tp = item.t0 + j * 128 + q * 32 + lane;
@@ -421,18 +437,19 @@ namespace earb {
 #pragma unroll
           for (int j = 0; j < kMT; j++) {
             float a[32], b[32];
-            tmem_ld32(acc + j * 2 * kNP, a);
-            tmem_ld32(acc + j * 2 * kNP + kNP, b);
+            tmem_ld32(acc + j * kAccCols, a);
+            tmem_ld32(acc + j * kAccCols + 32, b);
             const long t = item.t0 + j * 128 + q * 32 + lane;
             const float p = ramp ? (float)(t - seg.ramp_start) * seg.scale : 0.0f;
 #pragma unroll
-            for (int m = 0; m < 16; m++) {
+            for (int m = 0; m < MO; m++) {
               if (m < Mg) {
-                // columns 0..15: sum_n x * g_a (start point), 16..31: sum_n x * g_b (end point)
-                const float sa = a[m] + b[m];
-                const float sb = a[16 + m] + b[16 + m];
+                // NP = 32: main and correction accumulators, each [16 x g_a (start point) | 16 x g_b
+                // (end point)]; wide: one accumulator [32 x g_a | 32 x g_b]
+                const float sa = NP == 32 ? a[m & 15] + b[m & 15] : a[m];
+                const float sb = NP == 32 ? a[16 + (m & 15)] + b[16 + (m & 15)] : b[m];
                 float r = ramp ? fmaf(p, sb - sa, sa) : sa;
-                if (accumulate) r += prev[j][m];  // mix into the bus
+                if (accumulate) r += NP == 32 ? prev[j][m & 15] : __ldcs(og + (long)m * out_stride + t);
                 if (EARB_RENDER_EXPERIMENT < 3) __stcs(og + (long)m * out_stride + t, r);
               }
             }
@@ -455,82 +472,100 @@ namespace earb {
     // Per-point image of a gain matrix g[N][M] in the layout the UMMA reads (see b_desc):
     // [hi | lo][2 row groups][Kp/4][8 rows][4], hi = g rounded to TF32, lo = TF32(g - hi); rows
     // m >= M and channels k >= N are zero.  Written once per set_points.
-    __global__ void render_prepare_points_kernel(int N_total, int k0, int N, int M, int Kp, int n_groups,
+    __global__ void render_prepare_points_kernel(int N_total, int k0, int N, int M, int Kp, int NP, int n_groups,
                                                  long n_points,
                                                  const float *__restrict__ gains,
                                                  float *__restrict__ images) {
-      const long total = n_points * n_groups * Kp * 16;
+      const int half = Kp * (NP / 2);  // floats of the hi (or lo) part of one image
+      const long total = n_points * n_groups * half;
       for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
         // i enumerates (point, output group, row group, chunk, row-in-group, k-in-chunk) of the hi half
-        const int e = (int)(i % ((long)Kp * 16));
-        const long pg = i / ((long)Kp * 16);  // point * n_groups + output group
+        const int e = (int)(i % half);
+        const long pg = i / half;  // point * n_groups + output group
         const long p = pg / n_groups;
         const int og = (int)(pg - p * n_groups);
         const int grp = e / (Kp * 8), rem = e % (Kp * 8);
         const int chunk = rem / 32, r8 = (rem % 32) / 4, k4 = rem % 4;
-        const int m = og * 16 + grp * 8 + r8, k = chunk * 4 + k4;
+        const int m = og * (NP / 2) + grp * 8 + r8, k = chunk * 4 + k4;
         float hi = 0.0f, lo = 0.0f;
         if (m < M && k < N) {
           const float g = gains[(p * N_total + k0 + k) * M + m];
           hi = round_tf32(g);
           lo = round_tf32(g - hi);
         }
-        float *img = images + pg * ((long)Kp * 32);
+        float *img = images + pg * ((long)Kp * NP);
         img[e] = hi;
-        img[Kp * 16 + e] = lo;
+        img[half + e] = lo;
       }
     }
   }  // namespace
 
-  // N > 256 runs as groups of up to 256 input channels, one launch each, the later ones
-  // accumulating into the output (the gain matrices of 256 channels fill the shared memory)
-  constexpr int kMaxInGroup = 256;
-  static int padded_k(int n) { return (n + kCh - 1) / kCh * kCh; }
+  // How a render of N inputs into M outputs is cut up for the kernel:
+  //   M <= 16: NP = 32 units (main + correction accumulators), input groups of up to 256 channels;
+  //   M  > 16: NP = 64 "wide" units (up to 32 outputs, one accumulator, the input is converted
+  //            once), input groups of up to 128 channels -- the gain matrices of one tile are
+  //            2 * Kp * NP floats and two of them must leave room for the input ring.
+  // Input groups run as one launch each, the later ones accumulating into the output.
+  // EARB200_RENDER_WIDE=0 keeps NP = 32 for M > 16 (two output groups per tile, the second read of
+  // the input served by L2; kept for comparison).
+  namespace {
+    struct TcShape {
+      int NP, max_in, n_out_groups;
+    };
+    TcShape tc_shape(int M) {
+      static const bool wide_ok = [] {
+        const char *e = std::getenv("EARB200_RENDER_WIDE");
+        return !(e && e[0] == '0');
+      }();
+      if (M > 16 && wide_ok) return {64, 128, (M + 31) / 32};
+      return {32, 256, (M + 15) / 16};
+    }
+    int padded_k(int n) { return (n + kCh - 1) / kCh * kCh; }
+  }  // namespace
 
-  // floats per interpolation point: one image per (input group, group of 16 output channels)
+  // floats per interpolation point: one image per (input group, output group)
   size_t render_tc_image_floats(int N, int M) {
+    const TcShape sh = tc_shape(M);
     size_t total = 0;
-    for (int k0 = 0; k0 < N; k0 += kMaxInGroup)
-      total += (size_t)padded_k(std::min(kMaxInGroup, N - k0)) * 32 * ((M + 15) / 16);
+    for (int k0 = 0; k0 < N; k0 += sh.max_in)
+      total += (size_t)padded_k(std::min(sh.max_in, N - k0)) * sh.NP * sh.n_out_groups;
     return total;
   }
 
-  // image layout: [input group][point][output group][Kp_g * 32]
+  // image layout: [input group][point][output group][Kp_g * NP]
   void launch_render_prepare_points(int N, int M, long n_points, const float *d_gains, float *d_images,
                                     cudaStream_t stream) {
     if (n_points <= 0) return;
-    const int n_groups = (M + 15) / 16;
-    for (int k0 = 0; k0 < N; k0 += kMaxInGroup) {
-      const int Ng = std::min(kMaxInGroup, N - k0), Kp = padded_k(Ng);
-      const long total = n_points * n_groups * Kp * 16;
+    const TcShape sh = tc_shape(M);
+    for (int k0 = 0; k0 < N; k0 += sh.max_in) {
+      const int Ng = std::min(sh.max_in, N - k0), Kp = padded_k(Ng);
+      const long total = n_points * sh.n_out_groups * Kp * (sh.NP / 2);
       const unsigned blocks = (unsigned)std::min<long>((total + 255) / 256, 148 * 16);
-      render_prepare_points_kernel<<<blocks, 256, 0, stream>>>(N, k0, Ng, M, Kp, n_groups, n_points, d_gains,
-                                                                d_images);
-      d_images += (size_t)n_points * n_groups * Kp * 32;
+      render_prepare_points_kernel<<<blocks, 256, 0, stream>>>(N, k0, Ng, M, Kp, sh.NP, sh.n_out_groups, n_points,
+                                                                d_gains, d_images);
+      d_images += (size_t)n_points * sh.n_out_groups * Kp * sh.NP;
     }
   }
 
   namespace {
     constexpr size_t kSmemBudget = 224 * 1024;  // dynamic shared memory we ask for at most
-    // gain matrices: kBBufs tiles x 64 rows x Kp
-    size_t b_bytes(int N, int M) {
-      (void)M;
-      const int Kp = (N + kCh - 1) / kCh * kCh;
-      return sizeof(float) * (size_t)kBBufs * 2 * Kp * kNP;
-    }
-    int stages_for(int N, int M) {
+    // gain matrices of one input group: kBBufs tiles x 2 NP rows x Kp
+    size_t b_bytes(int Ng, int NP) { return sizeof(float) * (size_t)kBBufs * 2 * padded_k(Ng) * NP; }
+    int stages_for(int Ng, int NP) {
       const size_t stage = sizeof(float) * kCh * kTile;
-      const size_t left = kSmemBudget - b_bytes(N, M);
+      const size_t left = kSmemBudget - b_bytes(Ng, NP);
       return (int)std::min<size_t>(kMaxStages, left / stage);
+    }
+    size_t smem_for(int Ng, int NP) {
+      return b_bytes(Ng, NP) + sizeof(float) * (size_t)stages_for(Ng, NP) * kCh * kTile;
     }
   }  // namespace
 
   size_t render_tc_smem_bytes(int N, int M) {
-    return b_bytes(N, M) + sizeof(float) * (size_t)stages_for(N, M) * kCh * kTile;
+    const TcShape sh = tc_shape(M);
+    return smem_for(std::min(N, sh.max_in), sh.NP);
   }
 
-  // M > 16 runs as ceil(M / 16) output groups per tile (same kernel, the input tile is read once
-  // from HBM and again from L2)
   bool render_tc_supported(int N, int M) { return M <= EARB_MAX_OUT && N >= 1; }
 
   namespace {
@@ -563,14 +598,16 @@ namespace earb {
     if (!encode) return false;
     static bool configured = false;
     if (!configured) {
-      cudaFuncSetAttribute(render_tc_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      cudaFuncSetAttribute(render_tc_persistent_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)kSmemBudget);
+      cudaFuncSetAttribute(render_tc_persistent_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)kSmemBudget);
       configured = true;
     }
-    const int n_groups = (M + 15) / 16;
-    const unsigned grid = (unsigned)std::min<long>(n_tiles * n_groups, n_sms > 0 ? n_sms : 148);
-    for (int k0 = 0; k0 < N; k0 += kMaxInGroup) {
-      const int Ng = std::min(kMaxInGroup, N - k0);
+    const TcShape sh = tc_shape(M);
+    const unsigned grid = (unsigned)std::min<long>(n_tiles * sh.n_out_groups, n_sms > 0 ? n_sms : 148);
+    for (int k0 = 0; k0 < N; k0 += sh.max_in) {
+      const int Ng = std::min(sh.max_in, N - k0);
       // the input group as a [Ng channels][n_samples] float tensor with a row pitch of in_stride floats
       CUtensorMap map;
       const cuuint64_t dims[2] = {(cuuint64_t)n_samples, (cuuint64_t)Ng};
@@ -581,10 +618,16 @@ namespace earb {
                  strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return false;
-      render_tc_persistent_kernel<<<grid, kThreadsP, render_tc_smem_bytes(Ng, M), stream>>>(
-          map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, M),
-          (accumulate || k0 > 0) ? 1 : 0, n_groups);
-      d_images += (size_t)n_points * n_groups * padded_k(Ng) * 32;
+      const int acc_mode = (accumulate || k0 > 0) ? 1 : 0;
+      if (sh.NP == 64)
+        render_tc_persistent_kernel<64><<<grid, kThreadsP, smem_for(Ng, 64), stream>>>(
+            map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 64), acc_mode,
+            sh.n_out_groups);
+      else
+        render_tc_persistent_kernel<32><<<grid, kThreadsP, smem_for(Ng, 32), stream>>>(
+            map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 32), acc_mode,
+            sh.n_out_groups);
+      d_images += (size_t)n_points * sh.n_out_groups * padded_k(Ng) * sh.NP;
     }
     return true;
   }
