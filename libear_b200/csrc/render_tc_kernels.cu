@@ -106,6 +106,32 @@ namespace earb {
           "r"(__float_as_uint(v[15]))
           : "memory");
     }
+    // two 16-column loads in flight, one wait
+    __device__ __forceinline__ void tmem_ld16x2(uint32_t ta, uint32_t tb, float (&a)[16], float (&b)[16]) {
+      uint32_t r[16], q[16];
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+            "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
+            "=r"(r[15])
+          : "r"(ta)
+          : "memory");
+      asm volatile(
+          "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+          : "=r"(q[0]), "=r"(q[1]), "=r"(q[2]), "=r"(q[3]), "=r"(q[4]), "=r"(q[5]), "=r"(q[6]), "=r"(q[7]),
+            "=r"(q[8]), "=r"(q[9]), "=r"(q[10]), "=r"(q[11]), "=r"(q[12]), "=r"(q[13]), "=r"(q[14]),
+            "=r"(q[15])
+          : "r"(tb)
+          : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+      for (int i = 0; i < 16; i++) {
+        a[i] = __uint_as_float(r[i]);
+        b[i] = __uint_as_float(q[i]);
+      }
+    }
     __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
       uint32_t r[32];
       asm volatile(
@@ -184,9 +210,13 @@ namespace earb {
     constexpr int kTmemColsP = 512;
     // TMEM columns: accumulators [2 tiles][main: kMT x 32 | corr: kMT x 32], then
     // A [2 buffers][kMT][hi 16 | lo 16]
-    constexpr int kAccCols = 64;  // TMEM columns per M-tile: [main 32 | corr 32] or one 64-wide accumulator
-    constexpr int kAccStride = kMT * kAccCols;
-    constexpr int kColAP = 2 * kAccStride;
+    // TMEM accumulator columns.  NP = 32: per M-tile [main 32 | corr 32], two tile buffers.
+    // NP = 64: per M-tile [main 64 | corr 64], ONE tile buffer (the MMAs of a tile then wait for the
+    // epilogue of the tile before; keeping the two small cross terms out of the main accumulator is
+    // what holds the 1e-6 bar -- accumulating all three products into one accumulator measured
+    // 1.7e-6 of peak at N = 128).  Either way 256 columns, and the A ring takes the other 256.
+    constexpr int kAccRegion = 256;
+    constexpr int kColAP = kAccRegion;
     constexpr int kBBufs = 2;  // gain-matrix buffers in shared memory
     constexpr int kABufs = 4;  // A-operand ring in TMEM (power of two)
     static_assert(kColAP + kABufs * kMT * 2 * kCh <= kTmemColsP, "TMEM budget");
@@ -316,9 +346,13 @@ namespace earb {
           // B of this tile: rows 0..31 = [a | b] hi, 32..63 = [a | b] lo
           const int bb = L & 1;
           uint64_t bd = bdesc_base + (uint64_t)(bb * b_tile_step);
-          const uint32_t acc = tm + ab * kAccStride + j * kAccCols;
+          const uint32_t acc = NP == 32 ? tm + ab * 128 + j * 64 : tm + j * 128;
           mbar_wait(&b_full[bb], (uint32_t)((L >> 1) & 1));
-          if (L >= 2) mbar_wait(&acc_free[ab], (uint32_t)(((L >> 1) - 1) & 1));
+          if (NP == 32) {
+            if (L >= 2) mbar_wait(&acc_free[ab], (uint32_t)(((L >> 1) - 1) & 1));  // tile L - 2 read out
+          } else {
+            if (L >= 1) mbar_wait(&acc_free[(L - 1) & 1], (uint32_t)(((L - 1) >> 1) & 1));  // tile L - 1
+          }
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           for (int it = 0; it < n_iters; it++, g++) {
             const int abuf = g & (kABufs - 1);
@@ -334,10 +368,10 @@ namespace earb {
                   umma_tf32_ts(acc, a_hi + ks * 8, bd, idesc64, (it | ks) != 0);
                   umma_tf32_ts(acc + 32, a_hi + kCh + ks * 8, bd, idesc32, 1);
                 } else {
-                  // wide: acc (64 columns) (+)= x_hi * g_hi + x_hi * g_lo + x_lo * g_hi
+                  // wide: main (64 columns) (+)= x_hi * g_hi;  corr (+)= x_hi * g_lo + x_lo * g_hi
                   umma_tf32_ts(acc, a_hi + ks * 8, bd, idesc64, (it | ks) != 0);
-                  umma_tf32_ts(acc, a_hi + ks * 8, bd + b_lo_step, idesc64, 1);
-                  umma_tf32_ts(acc, a_hi + kCh + ks * 8, bd, idesc64, 1);
+                  umma_tf32_ts(acc + 64, a_hi + ks * 8, bd + b_lo_step, idesc64, (it | ks) != 0);
+                  umma_tf32_ts(acc + 64, a_hi + kCh + ks * 8, bd, idesc64, 1);
                 }
                 bd += (2 * 128) >> 4;
               }
@@ -433,24 +467,49 @@ namespace earb {
           }
           mbar_wait(&acc_full[ab], (uint32_t)((L >> 1) & 1));
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint32_t acc = lane_base + ab * kAccStride;
+          const uint32_t acc = NP == 32 ? lane_base + ab * 128 : lane_base;
 #pragma unroll
           for (int j = 0; j < kMT; j++) {
-            float a[32], b[32];
-            tmem_ld32(acc + j * kAccCols, a);
-            tmem_ld32(acc + j * kAccCols + 32, b);
             const long t = item.t0 + j * 128 + q * 32 + lane;
             const float p = ramp ? (float)(t - seg.ramp_start) * seg.scale : 0.0f;
+            if (NP == 32) {
+              // main and correction accumulators, each [16 x g_a (start point) | 16 x g_b (end point)]
+              float a[32], b[32];
+              tmem_ld32(acc + j * 64, a);
+              tmem_ld32(acc + j * 64 + 32, b);
 #pragma unroll
-            for (int m = 0; m < MO; m++) {
-              if (m < Mg) {
-                // NP = 32: main and correction accumulators, each [16 x g_a (start point) | 16 x g_b
-                // (end point)]; wide: one accumulator [32 x g_a | 32 x g_b]
-                const float sa = NP == 32 ? a[m & 15] + b[m & 15] : a[m];
-                const float sb = NP == 32 ? a[16 + (m & 15)] + b[16 + (m & 15)] : b[m];
-                float r = ramp ? fmaf(p, sb - sa, sa) : sa;
-                if (accumulate) r += NP == 32 ? prev[j][m & 15] : __ldcs(og + (long)m * out_stride + t);
-                if (EARB_RENDER_EXPERIMENT < 3) __stcs(og + (long)m * out_stride + t, r);
+              for (int m = 0; m < 16; m++) {
+                if (m < Mg) {
+                  const float sa = a[m] + b[m];
+                  const float sb = a[16 + m] + b[16 + m];
+                  float r = ramp ? fmaf(p, sb - sa, sa) : sa;
+                  if (accumulate) r += prev[j][m];  // mix into the bus
+                  if (EARB_RENDER_EXPERIMENT < 3) __stcs(og + (long)m * out_stride + t, r);
+                }
+              }
+            } else {
+              // wide: main and correction accumulators, each [32 x g_a | 32 x g_b], read out 16 output
+              // channels at a time
+#pragma unroll
+              for (int h = 0; h < 2; h++) {
+                float bus[16];
+                if (accumulate) {
+#pragma unroll
+                  for (int m = 0; m < 16; m++)
+                    bus[m] = (h * 16 + m < Mg) ? __ldcs(og + (long)(h * 16 + m) * out_stride + t) : 0.0f;
+                }
+                float sa[16], sb[16], ca[16], cb[16];
+                tmem_ld16x2(acc + j * 128 + h * 16, acc + j * 128 + 32 + h * 16, sa, sb);
+                tmem_ld16x2(acc + j * 128 + 64 + h * 16, acc + j * 128 + 96 + h * 16, ca, cb);
+#pragma unroll
+                for (int m = 0; m < 16; m++) {
+                  if (h * 16 + m < Mg) {
+                    const float va = sa[m] + ca[m], vb = sb[m] + cb[m];
+                    float r = ramp ? fmaf(p, vb - va, va) : va;
+                    if (accumulate) r += bus[m];
+                    if (EARB_RENDER_EXPERIMENT < 3) __stcs(og + (long)(h * 16 + m) * out_stride + t, r);
+                  }
+                }
               }
             }
           }
@@ -502,22 +561,24 @@ namespace earb {
 
   // How a render of N inputs into M outputs is cut up for the kernel:
   //   M <= 16: NP = 32 units (main + correction accumulators), input groups of up to 256 channels;
-  //   M  > 16: NP = 64 "wide" units (up to 32 outputs, one accumulator, the input is converted
-  //            once), input groups of up to 128 channels -- the gain matrices of one tile are
-  //            2 * Kp * NP floats and two of them must leave room for the input ring.
+  //   M  > 16 and N <= 128: NP = 64 "wide" units (up to 32 outputs, the input is converted once; the
+  //            gain matrices of one tile are 2 * Kp * NP floats and two of them must leave room for
+  //            the input ring, hence N <= 128);
+  //   M  > 16 and N > 128: NP = 32 with two output groups per tile, the second read of the input
+  //            served by L2 (measured faster than wide units over several accumulating launches:
+  //            N = 256, M = 24: 1.06 vs 1.09 ms; N = 512: 2.14 vs 2.47 ms).
   // Input groups run as one launch each, the later ones accumulating into the output.
-  // EARB200_RENDER_WIDE=0 keeps NP = 32 for M > 16 (two output groups per tile, the second read of
-  // the input served by L2; kept for comparison).
+  // EARB200_RENDER_WIDE=0 keeps NP = 32 for every shape (for comparison).
   namespace {
     struct TcShape {
       int NP, max_in, n_out_groups;
     };
-    TcShape tc_shape(int M) {
+    TcShape tc_shape(int N, int M) {
       static const bool wide_ok = [] {
         const char *e = std::getenv("EARB200_RENDER_WIDE");
         return !(e && e[0] == '0');
       }();
-      if (M > 16 && wide_ok) return {64, 128, (M + 31) / 32};
+      if (M > 16 && N <= 128 && wide_ok) return {64, 128, (M + 31) / 32};
       return {32, 256, (M + 15) / 16};
     }
     int padded_k(int n) { return (n + kCh - 1) / kCh * kCh; }
@@ -525,7 +586,7 @@ namespace earb {
 
   // floats per interpolation point: one image per (input group, output group)
   size_t render_tc_image_floats(int N, int M) {
-    const TcShape sh = tc_shape(M);
+    const TcShape sh = tc_shape(N, M);
     size_t total = 0;
     for (int k0 = 0; k0 < N; k0 += sh.max_in)
       total += (size_t)padded_k(std::min(sh.max_in, N - k0)) * sh.NP * sh.n_out_groups;
@@ -536,7 +597,7 @@ namespace earb {
   void launch_render_prepare_points(int N, int M, long n_points, const float *d_gains, float *d_images,
                                     cudaStream_t stream) {
     if (n_points <= 0) return;
-    const TcShape sh = tc_shape(M);
+    const TcShape sh = tc_shape(N, M);
     for (int k0 = 0; k0 < N; k0 += sh.max_in) {
       const int Ng = std::min(sh.max_in, N - k0), Kp = padded_k(Ng);
       const long total = n_points * sh.n_out_groups * Kp * (sh.NP / 2);
@@ -562,7 +623,7 @@ namespace earb {
   }  // namespace
 
   size_t render_tc_smem_bytes(int N, int M) {
-    const TcShape sh = tc_shape(M);
+    const TcShape sh = tc_shape(N, M);
     return smem_for(std::min(N, sh.max_in), sh.NP);
   }
 
@@ -604,7 +665,7 @@ namespace earb {
                            (int)kSmemBudget);
       configured = true;
     }
-    const TcShape sh = tc_shape(M);
+    const TcShape sh = tc_shape(N, M);
     const unsigned grid = (unsigned)std::min<long>(n_tiles * sh.n_out_groups, n_sms > 0 ? n_sms : 148);
     for (int k0 = 0; k0 < N; k0 += sh.max_in) {
       const int Ng = std::min(sh.max_in, N - k0);
