@@ -278,6 +278,7 @@ void earb200_objects_renderer_destroy(earb200_objects_renderer *r);
 int earb200_objects_renderer_num_outputs(const earb200_objects_renderer *r);
 int64_t earb200_objects_renderer_block_size(const earb200_objects_renderer *r); /* 512 */
 int earb200_objects_renderer_delay(const earb200_objects_renderer *r);          /* 255 */
+int64_t earb200_objects_renderer_launch_count(const earb200_objects_renderer *r);
 /* interpolation points: direct / diffuse gains [n_points][n_objects][C_out] (e.g. the output of
  * earb200_objects_calculate_* per metadata block), host buffers */
 int earb200_objects_renderer_set_gains(earb200_objects_renderer *r, int64_t n_points,

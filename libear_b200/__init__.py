@@ -30,7 +30,8 @@ _lib.earb200_layout_channel_name.restype = C.c_char_p
 for _f in ("earb200_objects_launch_count", "earb200_interp_launch_count",
            "earb200_convolver_launch_count", "earb200_direct_speakers_launch_count",
            "earb200_delay_launch_count", "earb200_delay_get_delay", "earb200_fft_launch_count",
-           "earb200_fft_size", "earb200_objects_renderer_block_size", "earb200_conversion_launch_count"):
+           "earb200_fft_size", "earb200_objects_renderer_block_size", "earb200_conversion_launch_count",
+           "earb200_objects_renderer_launch_count"):
     getattr(_lib, _f).restype = C.c_int64
 
 
@@ -391,6 +392,10 @@ class ObjectsRenderer:
         if getattr(self, "h", None):
             _lib.earb200_objects_renderer_destroy(self.h)
             self.h = None
+
+    @property
+    def launch_count(self):
+        return _lib.earb200_objects_renderer_launch_count(self.h)
 
     def set_gains(self, sample_idx, direct, diffuse):
         s = np.ascontiguousarray(sample_idx, dtype=np.int64)

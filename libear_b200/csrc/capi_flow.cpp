@@ -84,6 +84,11 @@ int earb200_objects_renderer_create(const earb200_layout *layout, int n_objects,
 void earb200_objects_renderer_destroy(earb200_objects_renderer *r) { delete r; }
 
 int earb200_objects_renderer_num_outputs(const earb200_objects_renderer *r) { return r ? r->C : 0; }
+int64_t earb200_objects_renderer_launch_count(const earb200_objects_renderer *r) {
+  if (!r) return 0;
+  return earb200_interp_launch_count(r->direct) + earb200_interp_launch_count(r->diffuse) +
+         earb200_convolver_launch_count(r->conv) + earb200_delay_launch_count(r->delay);
+}
 int64_t earb200_objects_renderer_block_size(const earb200_objects_renderer *r) { return r ? r->B : 0; }
 int earb200_objects_renderer_delay(const earb200_objects_renderer *r) {
   return r ? earb200_decorrelator_compensation_delay() : 0;
