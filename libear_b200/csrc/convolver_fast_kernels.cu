@@ -61,36 +61,83 @@ namespace earb {
     }
     __device__ __forceinline__ float sin32(int k) { return cos32(k - 8); }
 
+    // ---- complex numbers as packed fp32 pairs (sm_100 FADD2 / FMUL2 / FFMA2: one issue slot for
+    // the real and the imaginary part; swapping the halves and negating either one are operand
+    // modifiers of those instructions, so the "multiply by i" patterns below cost nothing extra).
+    // The kernel is bound by instruction issue in the butterflies, not by HBM.
+    typedef unsigned long long cx;
+    __device__ __forceinline__ cx mk(float re, float im) {
+      cx r;
+      asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(re), "f"(im));
+      return r;
+    }
+    __device__ __forceinline__ float re(cx v) {
+      float a, b;
+      asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+      return a;
+    }
+    __device__ __forceinline__ float im(cx v) {
+      float a, b;
+      asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
+      return b;
+    }
+    __device__ __forceinline__ cx add2(cx a, cx b) {
+      cx r;
+      asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+      return r;
+    }
+    __device__ __forceinline__ cx sub2(cx a, cx b) {
+      cx r;
+      asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+      return r;
+    }
+    __device__ __forceinline__ cx mul2(cx a, cx b) {
+      cx r;
+      asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+      return r;
+    }
+    __device__ __forceinline__ cx fma2(cx a, cx b, cx c) {
+      cx r;
+      asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+      return r;
+    }
+    __device__ __forceinline__ cx bc(float a) { return mk(a, a); }
+    __device__ __forceinline__ cx mul_i(cx a) { return mk(-im(a), re(a)); }    // i a
+    __device__ __forceinline__ cx mul_mi(cx a) { return mk(im(a), -re(a)); }   // -i a
+    __device__ __forceinline__ cx neg(cx a) { return mk(-re(a), -im(a)); }
+    // a * (c + i s), c and s scalars: (a.x c - a.y s, a.y c + a.x s)
+    __device__ __forceinline__ cx cmul_cs(cx a, float c, float s) { return fma2(a, bc(c), mul2(mul_i(a), bc(s))); }
+
     // a * exp(-+ 2 pi i k / 32): forward uses the negative exponent
     template <bool INV>
-    __device__ __forceinline__ float2 mul_w32(float2 a, int k) {
+    __device__ __forceinline__ cx mul_w32(cx a, int k) {
       k &= 31;
       if (k == 0) return a;
-      if (k == 8) return INV ? make_float2(-a.y, a.x) : make_float2(a.y, -a.x);
-      if (k == 16) return make_float2(-a.x, -a.y);
-      if (k == 24) return INV ? make_float2(a.y, -a.x) : make_float2(-a.y, a.x);
+      if (k == 8) return INV ? mul_i(a) : mul_mi(a);
+      if (k == 16) return neg(a);
+      if (k == 24) return INV ? mul_mi(a) : mul_i(a);
       const float c = cos32(k), s = INV ? sin32(k) : -sin32(k);  // w = c + i s
       if (k == 4 || k == 12 || k == 20 || k == 28) {
-        // |c| == |s|: two multiplies
+        // |c| == |s|: one addition and one multiplication
         const float m = 0.70710678118654752f;
-        const float sc = c > 0.0f ? 1.0f : -1.0f, ss = s > 0.0f ? 1.0f : -1.0f;
-        return make_float2((sc * a.x - ss * a.y) * m, (ss * a.x + sc * a.y) * m);
+        const cx t = (c > 0.0f) == (s > 0.0f) ? add2(a, mul_i(a)) : sub2(a, mul_i(a));  // a (1 +- i)
+        return mul2(t, bc(c > 0.0f ? m : -m));
       }
-      return make_float2(fmaf(a.x, c, -a.y * s), fmaf(a.x, s, a.y * c));
+      return cmul_cs(a, c, s);
     }
 
     // 32-point transform in registers, decimation in frequency: natural order in, v[br5(k)] = X[k] out.
     // UPPER_ZERO: v[16..31] are known to be zero on entry (zero-padded block), first stage pruned.
     template <bool INV, bool UPPER_ZERO>
-    __device__ __forceinline__ void dif32(float2 (&v)[32]) {
+    __device__ __forceinline__ void dif32(cx (&v)[32]) {
 #pragma unroll
       for (int i = 0; i < 16; i++) {
         if (UPPER_ZERO) {
           v[i + 16] = mul_w32<INV>(v[i], i);
         } else {
-          const float2 a = v[i], b = v[i + 16];
-          v[i] = make_float2(a.x + b.x, a.y + b.y);
-          v[i + 16] = mul_w32<INV>(make_float2(a.x - b.x, a.y - b.y), i);
+          const cx a = v[i], b = v[i + 16];
+          v[i] = add2(a, b);
+          v[i + 16] = mul_w32<INV>(sub2(a, b), i);
         }
       }
 #pragma unroll
@@ -99,53 +146,52 @@ namespace earb {
         for (int g = 0; g < 32; g += 2 * s) {
 #pragma unroll
           for (int i = 0; i < s; i++) {
-            const float2 a = v[g + i], b = v[g + i + s];
-            v[g + i] = make_float2(a.x + b.x, a.y + b.y);
-            v[g + i + s] = mul_w32<INV>(make_float2(a.x - b.x, a.y - b.y), i * (16 / s));
+            const cx a = v[g + i], b = v[g + i + s];
+            v[g + i] = add2(a, b);
+            v[g + i + s] = mul_w32<INV>(sub2(a, b), i * (16 / s));
           }
         }
       }
     }
 
-    // (a, b) <- (a + w b, a - w b), w = exp(-+ 2 pi i k / 32), in six FMAs: the complex product is
-    // written as c (b - t i b) with t = s / c (or with the roles of c and s swapped when |s| > |c|),
-    // so that the scaling by c folds into the two additions (Linzer-Feig).
+    // (a, b) <- (a + w b, a - w b), w = exp(-+ 2 pi i k / 32), in three packed FMAs: the complex
+    // product is written as c (b + t i b) with t = s / c (or with the roles of c and s swapped when
+    // |s| > |c|), so that the scaling by c folds into the two additions (Linzer-Feig).
     template <bool INV>
-    __device__ __forceinline__ void bfly_dit(float2 &a, float2 &b, int k) {
+    __device__ __forceinline__ void bfly_dit(cx &a, cx &b, int k) {
       k &= 15;
-      float2 a0 = a, b0 = b;
+      const cx a0 = a, b0 = b;
       if (k == 0) {
-        a = make_float2(a0.x + b0.x, a0.y + b0.y);
-        b = make_float2(a0.x - b0.x, a0.y - b0.y);
+        a = add2(a0, b0);
+        b = sub2(a0, b0);
         return;
       }
       if (k == 8) {  // w = -i (forward), +i (inverse)
-        const float2 wb = INV ? make_float2(-b0.y, b0.x) : make_float2(b0.y, -b0.x);
-        a = make_float2(a0.x + wb.x, a0.y + wb.y);
-        b = make_float2(a0.x - wb.x, a0.y - wb.y);
+        const cx wb = INV ? mul_i(b0) : mul_mi(b0);
+        a = add2(a0, wb);
+        b = sub2(a0, wb);
         return;
       }
       const float c = cos32(k), sn = INV ? sin32(k) : -sin32(k);  // w = c + i sn
-      float u, v, scale;
+      cx uv;
+      float scale;
       if (fabsf(c) >= fabsf(sn)) {
-        const float t = sn / c;       // compile-time constant
-        u = fmaf(-t, b0.y, b0.x);     // Re(w b) / c
-        v = fmaf(t, b0.x, b0.y);      // Im(w b) / c
+        const float t = sn / c;                 // compile-time constant
+        uv = fma2(mul_i(b0), bc(t), b0);        // w b / c  = b + t i b
         scale = c;
       } else {
         const float t = c / sn;
-        u = fmaf(t, b0.x, -b0.y);     // Re(w b) / sn
-        v = fmaf(t, b0.y, b0.x);      // Im(w b) / sn
+        uv = fma2(b0, bc(t), mul_i(b0));        // w b / sn = t b + i b
         scale = sn;
       }
-      a = make_float2(fmaf(scale, u, a0.x), fmaf(scale, v, a0.y));
-      b = make_float2(fmaf(-scale, u, a0.x), fmaf(-scale, v, a0.y));
+      a = fma2(uv, bc(scale), a0);
+      b = fma2(uv, bc(-scale), a0);
     }
 
     // decimation in time: v[br5(a)] = x[a] in, natural order out.
     // ODD_ZERO: the odd slots (inputs a >= 16) are known to be zero: first stage pruned.
     template <bool INV, bool ODD_ZERO>
-    __device__ __forceinline__ void dit32(float2 (&v)[32]) {
+    __device__ __forceinline__ void dit32(cx (&v)[32]) {
       if (ODD_ZERO) {
 #pragma unroll
         for (int g = 0; g < 32; g += 2) v[g + 1] = v[g];
@@ -160,12 +206,9 @@ namespace earb {
       }
     }
 
-    __device__ __forceinline__ float2 cmulf(float2 a, float2 b) {
-      return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
-    }
-    __device__ __forceinline__ float2 cmulcf(float2 a, float2 b) {  // a * conj(b)
-      return make_float2(fmaf(a.x, b.x, a.y * b.y), fmaf(a.y, b.x, -a.x * b.y));
-    }
+    // a * (bx + i by) and a * conj(bx + i by), the second factor given as two scalars
+    __device__ __forceinline__ cx cmulf(cx a, float bx, float by) { return fma2(a, bc(bx), mul2(mul_i(a), bc(by))); }
+    __device__ __forceinline__ cx cmulcf(cx a, float bx, float by) { return fma2(a, bc(bx), mul2(mul_mi(a), bc(by))); }
 
     struct FastArgs {
       long K;         // blocks per channel in this call
@@ -187,30 +230,30 @@ namespace earb {
     // zero), filter multiply, inverse transform.  On return v[n2] = y[lane + 32 n2] (real part:
     // first block of the pair, imaginary part: second block).
     // tw_s / H_s hold two consecutive slots per float4: [slot / 2][lane] = (slot, slot + 1).
-    __device__ __forceinline__ void convolve_pair(float2 (&v)[32], float2 *tile, const float4 *tw_s,
-                                                  const float4 *H_s, int lane) {
+    __device__ __forceinline__ void convolve_pair(cx (&v)[32], cx *tile, const float4 *tw_s, const float4 *H_s,
+                                                  int lane) {
       dit32<false, true>(v);  // over a: v[k1] = A_lane[k1]
 #pragma unroll
       for (int k1 = 0; k1 < 32; k1 += 2) {
         const float4 t = tw_s[(k1 >> 1) * 32 + lane];
-        tile[k1 * kRow + lane] = cmulf(v[k1], make_float2(t.x, t.y));
-        tile[(k1 + 1) * kRow + lane] = cmulf(v[k1 + 1], make_float2(t.z, t.w));
+        tile[k1 * kRow + lane] = cmulf(v[k1], t.x, t.y);
+        tile[(k1 + 1) * kRow + lane] = cmulf(v[k1 + 1], t.z, t.w);
       }
       __syncwarp();
-      const float4 *row = reinterpret_cast<const float4 *>(tile + lane * kRow);
+      const ulonglong2 *row = reinterpret_cast<const ulonglong2 *>(tile + lane * kRow);
 #pragma unroll
       for (int b = 0; b < 32; b += 2) {
-        const float4 t = row[b >> 1];
-        v[br5(b)] = make_float2(t.x, t.y);
-        v[br5(b + 1)] = make_float2(t.z, t.w);
+        const ulonglong2 t = row[b >> 1];
+        v[br5(b)] = t.x;
+        v[br5(b + 1)] = t.y;
       }
       __syncwarp();
       dit32<false, false>(v);  // over b: v[k2] = Z[lane + 32 k2]
 #pragma unroll
       for (int k2 = 0; k2 < 32; k2 += 2) {
         const float4 h = H_s[(k2 >> 1) * 32 + lane];
-        v[k2] = cmulf(v[k2], make_float2(h.x, h.y));
-        v[k2 + 1] = cmulf(v[k2 + 1], make_float2(h.z, h.w));
+        v[k2] = cmulf(v[k2], h.x, h.y);
+        v[k2 + 1] = cmulf(v[k2 + 1], h.z, h.w);
       }
       dif32<true, false>(v);  // inverse over k2: v[br5(n1)]
 #pragma unroll
@@ -218,17 +261,15 @@ namespace earb {
         // slots q, q + 1 hold n1 = br5(q), br5(q) + 16
         const int n1 = br5(q);
         const float4 ta = tw_s[(n1 >> 1) * 32 + lane], tb = tw_s[((n1 + 16) >> 1) * 32 + lane];
-        const float2 wa = (n1 & 1) ? make_float2(ta.z, ta.w) : make_float2(ta.x, ta.y);
-        const float2 wb = (n1 & 1) ? make_float2(tb.z, tb.w) : make_float2(tb.x, tb.y);
-        tile[n1 * kRow + lane] = cmulcf(v[q], wa);
-        tile[(n1 + 16) * kRow + lane] = cmulcf(v[q + 1], wb);
+        tile[n1 * kRow + lane] = (n1 & 1) ? cmulcf(v[q], ta.z, ta.w) : cmulcf(v[q], ta.x, ta.y);
+        tile[(n1 + 16) * kRow + lane] = (n1 & 1) ? cmulcf(v[q + 1], tb.z, tb.w) : cmulcf(v[q + 1], tb.x, tb.y);
       }
       __syncwarp();
 #pragma unroll
       for (int b = 0; b < 32; b += 2) {
-        const float4 t = row[b >> 1];
-        v[br5(b)] = make_float2(t.x, t.y);
-        v[br5(b + 1)] = make_float2(t.z, t.w);
+        const ulonglong2 t = row[b >> 1];
+        v[br5(b)] = t.x;
+        v[br5(b + 1)] = t.y;
       }
       __syncwarp();
       dit32<true, false>(v);  // inverse over b: v[n2] = y[lane + 32 n2]
@@ -238,7 +279,7 @@ namespace earb {
       extern __shared__ float4 fsm[];
       float4 *tw_s = fsm;        // [16][32]: (tw[2j][lane], tw[2j + 1][lane])
       float4 *H_s = tw_s + 512;  // [16][32]: (H[lane + 32 (2j)], H[lane + 32 (2j + 1)])
-      float2 *tiles = reinterpret_cast<float2 *>(H_s + 512);  // kWarps x 32 x kRow
+      cx *tiles = reinterpret_cast<cx *>(H_s + 512);  // kWarps x 32 x kRow complex numbers
       const int c = blockIdx.y;
       const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
       const int f = a.filter_of[c];
@@ -261,12 +302,12 @@ namespace earb {
       const long p0 = ((long)blockIdx.x * kWarps + warp) * a.run_pairs;
       if (p0 >= a.n_pairs) return;
       const long p1 = min(a.n_pairs, p0 + a.run_pairs);
-      float2 *tile = tiles + (size_t)warp * 32 * kRow;
+      cx *tile = tiles + (size_t)warp * 32 * kRow;
       const float *x = a.in + (size_t)c * a.in_stride;
       float *y = a.out + (size_t)c * a.out_stride;
       const float norm = 1.0f / (float)(2 * kFastB);
 
-      float2 v[32];
+      cx v[32];
       float tail[16];
       if (p0 == 0) {
 #pragma unroll
@@ -275,36 +316,34 @@ namespace earb {
         // halo: the block before the run as the imaginary part of a pair
         const float *xb = x + (size_t)(2 * p0 - 1) * kFastB;
 #pragma unroll
-        for (int r = 0; r < 16; r++) v[br5(r)] = make_float2(0.0f, __ldg(xb + lane + 32 * r));
+        for (int r = 0; r < 16; r++) v[br5(r)] = mk(0.0f, __ldg(xb + lane + 32 * r));
         convolve_pair(v, tile, tw_s, H_s, lane);
 #pragma unroll
-        for (int r = 0; r < 16; r++) tail[r] = v[r + 16].y;
+        for (int r = 0; r < 16; r++) tail[r] = im(v[r + 16]);
       }
       for (long p = p0; p < p1; p++) {
         const bool has_second = 2 * p + 1 < a.K;
         const float *x0 = x + (size_t)(2 * p) * kFastB;
+        float xr[16], xi[16];
 #pragma unroll
-        for (int r = 0; r < 16; r++) v[br5(r)].x = __ldcs(x0 + lane + 32 * r);
-        if (has_second) {
+        for (int r = 0; r < 16; r++) xr[r] = __ldcs(x0 + lane + 32 * r);
 #pragma unroll
-          for (int r = 0; r < 16; r++) v[br5(r)].y = __ldcs(x0 + kFastB + lane + 32 * r);
-        } else {
+        for (int r = 0; r < 16; r++) xi[r] = has_second ? __ldcs(x0 + kFastB + lane + 32 * r) : 0.0f;
 #pragma unroll
-          for (int r = 0; r < 16; r++) v[br5(r)].y = 0.0f;
-        }
+        for (int r = 0; r < 16; r++) v[br5(r)] = mk(xr[r], xi[r]);
         convolve_pair(v, tile, tw_s, H_s, lane);
         float *y0 = y + (size_t)(2 * p) * kFastB;
 #pragma unroll
-        for (int r = 0; r < 16; r++) __stcs(y0 + lane + 32 * r, (v[r].x + tail[r]) * norm);
+        for (int r = 0; r < 16; r++) __stcs(y0 + lane + 32 * r, (re(v[r]) + tail[r]) * norm);
         if (has_second) {
 #pragma unroll
           for (int r = 0; r < 16; r++) {
-            __stcs(y0 + kFastB + lane + 32 * r, (v[r].y + v[r + 16].x) * norm);
-            tail[r] = v[r + 16].y;
+            __stcs(y0 + kFastB + lane + 32 * r, (im(v[r]) + re(v[r + 16])) * norm);
+            tail[r] = im(v[r + 16]);
           }
         } else {
 #pragma unroll
-          for (int r = 0; r < 16; r++) tail[r] = v[r + 16].x;
+          for (int r = 0; r < 16; r++) tail[r] = re(v[r + 16]);
         }
       }
       if (p1 == a.n_pairs) {
