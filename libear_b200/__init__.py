@@ -131,7 +131,8 @@ class Layout:
 
     def __del__(self):
         if getattr(self, "h", None):
-            _lib.earb200_layout_destroy(self.h)
+            if _lib is not None:  # None while the interpreter shuts down
+                _lib.earb200_layout_destroy(self.h)
             self.h = None
 
 
@@ -169,7 +170,8 @@ class PointSourcePanner:
 
     def __del__(self):
         if getattr(self, "h", None):
-            _lib.earb200_panner_destroy(self.h)
+            if _lib is not None:  # None while the interpreter shuts down
+                _lib.earb200_panner_destroy(self.h)
             self.h = None
 
     def handle(self, xyz, regions=False):
@@ -204,7 +206,8 @@ class GainCalculatorObjects:
 
     def __del__(self):
         if getattr(self, "h", None):
-            _lib.earb200_objects_destroy(self.h)
+            if _lib is not None:  # None while the interpreter shuts down
+                _lib.earb200_objects_destroy(self.h)
             self.h = None
 
     @property
@@ -271,7 +274,8 @@ class GainInterpolator:
 
     def __del__(self):
         if getattr(self, "h", None):
-            _lib.earb200_interp_destroy(self.h)
+            if _lib is not None:  # None while the interpreter shuts down
+                _lib.earb200_interp_destroy(self.h)
             self.h = None
 
     @property
@@ -325,7 +329,8 @@ class BlockConvolver:
 
     def __del__(self):
         if getattr(self, "h", None):
-            _lib.earb200_convolver_destroy(self.h)
+            if _lib is not None:  # None while the interpreter shuts down
+                _lib.earb200_convolver_destroy(self.h)
             self.h = None
 
     @property
@@ -390,7 +395,8 @@ class ObjectsRenderer:
 
     def __del__(self):
         if getattr(self, "h", None):
-            _lib.earb200_objects_renderer_destroy(self.h)
+            if _lib is not None:  # None while the interpreter shuts down
+                _lib.earb200_objects_renderer_destroy(self.h)
             self.h = None
 
     @property
@@ -431,7 +437,8 @@ class FFT:
 
     def __del__(self):
         if getattr(self, "h", None):
-            _lib.earb200_fft_destroy(self.h)
+            if _lib is not None:  # None while the interpreter shuts down
+                _lib.earb200_fft_destroy(self.h)
             self.h = None
 
     @property
@@ -463,7 +470,8 @@ class DelayBuffer:
 
     def __del__(self):
         if getattr(self, "h", None):
-            _lib.earb200_delay_destroy(self.h)
+            if _lib is not None:  # None while the interpreter shuts down
+                _lib.earb200_delay_destroy(self.h)
             self.h = None
 
     @property
@@ -497,7 +505,8 @@ class Conversion:
 
     def __del__(self):
         if getattr(self, "h", None):
-            _lib.earb200_conversion_destroy(self.h)
+            if _lib is not None:  # None while the interpreter shuts down
+                _lib.earb200_conversion_destroy(self.h)
             self.h = None
 
     @property
@@ -551,7 +560,8 @@ class GainCalculatorHOA:
 
     def __del__(self):
         if getattr(self, "h", None):
-            _lib.earb200_hoa_destroy(self.h)
+            if _lib is not None:  # None while the interpreter shuts down
+                _lib.earb200_hoa_destroy(self.h)
             self.h = None
 
     def calculate(self, orders, degrees, normalization="SN3D", nfc_ref_dist=0.0, screen_ref=False):
@@ -597,7 +607,8 @@ class GainCalculatorDirectSpeakers:
 
     def __del__(self):
         if getattr(self, "h", None):
-            _lib.earb200_direct_speakers_destroy(self.h)
+            if _lib is not None:  # None while the interpreter shuts down
+                _lib.earb200_direct_speakers_destroy(self.h)
             self.h = None
 
     @property
