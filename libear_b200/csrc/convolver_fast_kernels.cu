@@ -324,6 +324,9 @@ namespace earb {
       for (long p = p0; p < p1; p++) {
         const bool has_second = 2 * p + 1 < a.K;
         const float *x0 = x + (size_t)(2 * p) * kFastB;
+        // the next pair's 4 KB (32 lines) on their way into L2 while this pair is transformed
+        if (p + 1 < p1 && 2 * p + 3 < a.K)
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(x0 + 2 * kFastB + lane * 32));
         float xr[16], xi[16];
 #pragma unroll
         for (int r = 0; r < 16; r++) xr[r] = __ldcs(x0 + lane + 32 * r);
