@@ -131,6 +131,15 @@ class ClockSampler:
                 "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
+def ncu_traffic(kernel):
+    """DRAM bytes per launch of `kernel` from the committed ncu capture (profiles/traffic.json), or None."""
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "traffic.json")) as f:
+            return json.load(f)[kernel]["bytes"]
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -382,7 +391,9 @@ def run_ours(args):
                                    f"{R['ramp']}-sample linear gain ramps; inputs 1.6 GB/step > L2",
                        "bus_reduce": "nccl all_reduce(sum, f32) of the [M x T] bus" if world > 1 else "none"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / hbm_peak,
+                         "traffic": ncu_traffic("render_tc_persistent_kernel") if (N, M, T) == (128, 14, 2_880_000) else None,
+                         "peak_source": peak_src,
                          "kernel": "render_kernel<16,4,true>", "kernel_ms": k_ms / max(1, k_launches),
                          "algorithmic_bytes_per_launch": alg_bytes},
         }
@@ -451,7 +462,9 @@ def run_ours(args):
                                    f"designDecorrelators({LAYOUT}) 512-tap filters, block size {Bc}; "
                                    "5.5 GB/step > L2", "sharding": "replicated channels per GPU, no collective"},
             "roofline": {"bound": "hbm", "achieved": c_achieved, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": c_achieved / hbm_peak, "traffic": None, "peak_source": peak_src,
+                         "frac": c_achieved / hbm_peak,
+                         "traffic": ncu_traffic("convolver_fast_kernel") if (Cc, Kc) == (24, 56250) else None,
+                         "peak_source": peak_src,
                          "kernel": "convolver_fast_kernel", "kernel_ms": ck_ms / max(1, ck_n),
                          "algorithmic_bytes_per_launch": c_bytes,
                          "note": "8 B/sample; the FP32 butterflies (about 2,300 warp instructions per pair of "
@@ -647,8 +660,10 @@ def run_ours(args):
                        "layout": LAYOUT, "objects_per_gpu": n, "passes_per_step_per_gpu": n_passes,
                        "l2": "inputs+outputs 256 MB/step/GPU > 126 MB L2", "sharding": "objects, no collective"},
             "roofline": {"bound": "tensor", "achieved": core_tflops, "peak": bf16_peak, "unit": "TFLOP/s",
-                         "frac": core_tflops / bf16_peak, "traffic": None, "peak_source": peak_src,
-                         "kernel": "extent_core_kernel", "kernel_ms": core_ms / max(1, core_launches),
+                         "frac": core_tflops / bf16_peak,
+                         "traffic": ncu_traffic("extent_core_tc_kernel") if n >= 131072 else None,
+                         "peak_source": peak_src,
+                         "kernel": "extent_core_tc_kernel", "kernel_ms": core_ms / max(1, core_launches),
                          "algorithmic_flop_per_pass": FLOP_PER_PASS,
                          "note": "contraction flops only; the kernel is FP32-ALU bound by the 1,652 weight "
                                  "evaluations per pass (DESIGN.md section 4)",
