@@ -23,12 +23,19 @@ struct earb200_interp {
   DeviceBuffer<float> d_gains;
   DeviceBuffer<float> d_images;  // tcgen05 path: per-point TF32 hi/lo images in UMMA layout
   int64_t n_points = 0;
-  // plan cache for the last (block_start, nsamples, buffer alignment)
-  int64_t plan_start = 0, plan_n = -1;
-  int plan_align = -1;
-  long n_items[4] = {0, 0, 0, 0};  // fast ramp, fast const, slow ramp, slow const
-  DeviceBuffer<RenderItem> d_items;
-  DeviceBuffer<RenderSegment> d_segs;
+  // plan cache keyed by (block_start, nsamples, buffer alignment): a caller that walks the same
+  // chunks every pass (chunked mixing with the bus reduce of chunk k behind the render of chunk
+  // k + 1) pays the host-side segmentation and its upload once per chunk, not once per call
+  struct Plan {
+    int64_t start = 0, n = -1;
+    int align = -1;
+    long n_items[4] = {0, 0, 0, 0};  // fast ramp, fast const, slow ramp, slow const
+    DeviceBuffer<RenderItem> d_items;
+    DeviceBuffer<RenderSegment> d_segs;
+    uint64_t last_use = 0;
+  };
+  std::vector<std::unique_ptr<Plan>> plans;
+  uint64_t plan_clock = 0;
   // staging for process_host
   DeviceBuffer<float> d_in, d_out;
   int64_t launches = 0;
@@ -41,8 +48,14 @@ struct earb200_interp {
 namespace {
   // align: sample phase p in [0, 4) such that call-relative samples t with (t + p) % 4 == 0
   // are 16-byte aligned in both buffers, or -1 when no such phase exists
-  void build_plan(earb200_interp &h, int64_t block_start, int64_t nsamples, int align) {
-    if (h.plan_n == nsamples && h.plan_start == block_start && h.plan_align == align) return;
+  constexpr size_t kMaxPlans = 64;
+
+  earb200_interp::Plan &build_plan(earb200_interp &h, int64_t block_start, int64_t nsamples, int align) {
+    for (auto &p : h.plans)
+      if (p->n == nsamples && p->start == block_start && p->align == align) {
+        p->last_use = ++h.plan_clock;
+        return *p;
+      }
     const int fast_tile = h.use_tc ? RENDER_TC_TILE : RENDER_PIPE_TILE;
     const int64_t P = h.n_points;
     if (P == 0) throw Error(INVALID_ARGUMENT, "no interpolation points");
@@ -91,20 +104,35 @@ namespace {
       for (; t < end; t += tile) emit(t, std::min<int64_t>(tile, end - t), false);
       cur = end;
     }
+    // a streaming caller never repeats a key: the least recently used plan is recycled together with
+    // its device buffers (grow-only), so steady state allocates nothing
+    std::unique_ptr<earb200_interp::Plan> plan;
+    if (h.plans.size() >= kMaxPlans) {
+      size_t lru = 0;
+      for (size_t i = 1; i < h.plans.size(); i++)
+        if (h.plans[i]->last_use < h.plans[lru]->last_use) lru = i;
+      plan = std::move(h.plans[lru]);
+      h.plans.erase(h.plans.begin() + lru);
+    } else {
+      plan = std::make_unique<earb200_interp::Plan>();
+    }
     std::vector<RenderItem> all;
     for (int k = 0; k < 4; k++) {
-      h.n_items[k] = (long)items[k].size();
+      plan->n_items[k] = (long)items[k].size();
       all.insert(all.end(), items[k].begin(), items[k].end());
     }
-    h.d_items.reserve(std::max<size_t>(all.size(), 1));
-    h.d_segs.reserve(std::max<size_t>(segs.size(), 1));
-    EARB_CUDA(cudaMemcpy(h.d_items.ptr, all.data(), sizeof(RenderItem) * all.size(),
+    plan->d_items.reserve(std::max<size_t>(all.size(), 1));
+    plan->d_segs.reserve(std::max<size_t>(segs.size(), 1));
+    EARB_CUDA(cudaMemcpy(plan->d_items.ptr, all.data(), sizeof(RenderItem) * all.size(),
                          cudaMemcpyHostToDevice));
-    EARB_CUDA(cudaMemcpy(h.d_segs.ptr, segs.data(), sizeof(RenderSegment) * segs.size(),
+    EARB_CUDA(cudaMemcpy(plan->d_segs.ptr, segs.data(), sizeof(RenderSegment) * segs.size(),
                          cudaMemcpyHostToDevice));
-    h.plan_start = block_start;
-    h.plan_n = nsamples;
-    h.plan_align = align;
+    plan->start = block_start;
+    plan->n = nsamples;
+    plan->align = align;
+    plan->last_use = ++h.plan_clock;
+    h.plans.push_back(std::move(plan));
+    return *h.plans.back();
   }
 
   void process_device(earb200_interp &h, int64_t block_start, int64_t nsamples, const float *d_in,
@@ -119,19 +147,19 @@ namespace {
     if (ia % 4 == 0 && oa % 4 == 0 && in_stride % 4 == 0 && out_stride % 4 == 0 &&
         ((ia / 4) & 3) == ((oa / 4) & 3))
       align = (int)((ia / 4) & 3);
-    build_plan(h, block_start, nsamples, align);
-    RenderPlan plan{h.d_items.ptr, h.n_items[0], h.n_items[1], h.n_items[2], h.n_items[3], h.use_tc,
+    const earb200_interp::Plan &pl = build_plan(h, block_start, nsamples, align);
+    RenderPlan plan{pl.d_items.ptr, pl.n_items[0], pl.n_items[1], pl.n_items[2], pl.n_items[3], h.use_tc,
                     h.n_sms, (long)nsamples, h.d_images.ptr, h.accumulate, (long)h.n_points};
     h.timer.start(stream);
-    launch_render(h.N, h.M, d_in, (long)in_stride, d_out, (long)out_stride, plan, h.d_segs.ptr,
+    launch_render(h.N, h.M, d_in, (long)in_stride, d_out, (long)out_stride, plan, pl.d_segs.ptr,
                   h.d_gains.ptr, stream);
     h.timer.stop(stream);
     EARB_CUDA(cudaGetLastError());
     if (h.use_tc) {
-      if (h.n_items[0] + h.n_items[1] > 0) h.launches += (h.N + 255) / 256;  // one per group of 256 inputs
-      h.launches += (h.n_items[2] > 0) + (h.n_items[3] > 0);
+      if (pl.n_items[0] + pl.n_items[1] > 0) h.launches += (h.N + 255) / 256;  // one per group of 256 inputs
+      h.launches += (pl.n_items[2] > 0) + (pl.n_items[3] > 0);
     } else {
-      for (int k = 0; k < 4; k++) h.launches += h.n_items[k] > 0;
+      for (int k = 0; k < 4; k++) h.launches += pl.n_items[k] > 0;
     }
   }
 }  // namespace
@@ -202,7 +230,7 @@ int earb200_interp_set_points(earb200_interp *interp, int64_t n_points,
       h.same_as_prev[i] = same;
     }
     h.n_points = n_points;
-    h.plan_n = -1;
+    h.plans.clear();
     if (n_points > 0) {
       h.d_gains.reserve(mat * n_points);
       EARB_CUDA(cudaMemcpy(h.d_gains.ptr, gains, sizeof(float) * mat * n_points,

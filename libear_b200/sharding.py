@@ -28,3 +28,56 @@ def reduce_bus(bus, group=None):
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(bus, op=dist.ReduceOp.SUM, group=group)
     return bus
+
+
+def chunk_ranges(n_samples, n_chunks, align=512):
+    """[start, end) sample ranges of at most n_chunks chunks whose boundaries are multiples of
+    `align` (whole render tiles / convolver blocks); the last chunk takes the remainder."""
+    n_samples, n_chunks = int(n_samples), max(1, int(n_chunks))
+    per = -(-n_samples // n_chunks)
+    per = max(align, -(-per // align) * align)
+    return [(t, min(n_samples, t + per)) for t in range(0, n_samples, per)]
+
+
+def reduce_bus_rows(bus, t0, t1, group=None):
+    """All-reduce the columns [t0, t1) of a planar [M x T] bus in place: the M row slices are
+    contiguous, so they go out as one coalesced NCCL group (one fused launch)."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1):
+        return
+    rows = [bus[m, t0:t1] for m in range(bus.shape[0])]
+    if bus.is_cuda and hasattr(dist, "_coalescing_manager"):
+        with dist._coalescing_manager(group=group, device=bus.device):
+            for r in rows:
+                dist.all_reduce(r, op=dist.ReduceOp.SUM, group=group)
+    else:
+        for r in rows:
+            dist.all_reduce(r, op=dist.ReduceOp.SUM, group=group)
+
+
+def mix_pipelined(bus, render_chunk, n_chunks=8, group=None, reduce_stream=None, align=512):
+    """Object-sharded mixing with the exchange step hidden behind the rendering: the bus is cut
+    into time chunks; chunk k is rendered on the current stream (`render_chunk(t0, t1)` must write
+    bus[:, t0:t1]) and summed over the ranks on `reduce_stream` while chunk k + 1 renders.  On one
+    rank (or without a process group) it only renders.  Returns when both streams are joined."""
+    import torch
+    import torch.distributed as dist
+    sharded = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+    chunks = chunk_ranges(bus.shape[1], n_chunks if sharded else 1, align)
+    if not (sharded and bus.is_cuda):
+        for t0, t1 in chunks:
+            render_chunk(t0, t1)
+            if sharded:
+                reduce_bus_rows(bus, t0, t1, group)
+        return bus
+    main = torch.cuda.current_stream(bus.device)
+    side = reduce_stream or torch.cuda.Stream(bus.device)
+    for t0, t1 in chunks:
+        render_chunk(t0, t1)
+        done = torch.cuda.Event()
+        done.record(main)
+        side.wait_event(done)
+        with torch.cuda.stream(side):
+            reduce_bus_rows(bus, t0, t1, group)
+    main.wait_stream(side)
+    return bus

@@ -11,7 +11,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from libear_b200.sharding import object_groups, reduce_bus, shard_range
+from libear_b200.sharding import chunk_ranges, mix_pipelined, object_groups, reduce_bus, shard_range
 
 
 def test_shard_range_is_a_partition():
@@ -30,6 +30,16 @@ def test_object_groups():
     assert object_groups(512) == [(0, 256), (256, 512)]
     assert object_groups(300) == [(0, 256), (256, 300)]
     assert object_groups(0) == []
+
+
+def test_chunk_ranges():
+    assert chunk_ranges(2_880_000, 8) == [(t, min(2_880_000, t + 360_448)) for t in range(0, 2_880_000, 360_448)]
+    assert chunk_ranges(1000, 4) == [(0, 512), (512, 1000)]
+    assert chunk_ranges(100, 8) == [(0, 100)]
+    for T, k in ((4096 + 37, 3), (512 * 7, 7), (1, 1)):
+        c = chunk_ranges(T, k)
+        assert c[0][0] == 0 and c[-1][1] == T and len(c) <= k
+        assert all(a[1] == b[0] for a, b in zip(c, c[1:])) and all(a % 512 == 0 for a, _ in c)
 
 
 def _free_port():
@@ -57,6 +67,13 @@ def _worker(rank, world, port, out_dir):
         reduce_bus(bus)
         full = eo.interp_matrix(x, samples, gains)
         err = float(np.abs(bus.numpy() - full).max() / np.abs(full).max())
+        # the same mix chunk by chunk, each chunk summed over the ranks as soon as it is rendered
+        bus2 = torch.zeros((M, T), dtype=torch.float32)
+
+        def render_chunk(t0, t1):
+            bus2[:, t0:t1] = torch.from_numpy(eo.interp_matrix(x[a:b, t0:t1], samples, gains[:, a:b], block_start=t0))
+        mix_pipelined(bus2, render_chunk, n_chunks=3)
+        err = max(err, float(np.abs(bus2.numpy() - full).max() / np.abs(full).max()))
         # gains shard with no collective: each rank's rows are just a slice of the global answer
         pan = eo.PointSourcePanner("0+5+0")
         dirs = rng.normal(size=(64, 3))
