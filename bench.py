@@ -358,16 +358,23 @@ def run_ours(args):
         gi = eb.GainInterpolator(N, M, device=local_rank)
         gi.set_points(samples, gains)
 
-        from libear_b200.sharding import mix_pipelined
+        from libear_b200.sharding import chunked_bus, mix_pipelined
         side_stream = torch.cuda.Stream(dev) if world > 1 else None
+        if world > 1:
+            # object-sharded mixing: the bus is kept chunk-major so that each time chunk is summed
+            # over the GPUs by one contiguous all-reduce on a side stream while the next one renders
+            del y
+            y, y_ranges = chunked_bus(M, T, args.mix_chunks, device=dev)
+            y_per = y.shape[2]
 
-        def render_chunk(t0, t1):
-            gi.process_device(t0, t1 - t0, x.data_ptr() + 4 * t0, T, y.data_ptr() + 4 * t0, T, stream=stream)
+            def render_chunk(k, t0, t1):
+                gi.process_device(t0, t1 - t0, x.data_ptr() + 4 * t0, T, y[k].data_ptr(), y_per, stream=stream)
 
-        def step_render():
-            # object-sharded mixing: the per-GPU partial loudspeaker buses are summed chunk by chunk
-            # on a side stream while the next chunk renders (one rank: a single full-length render)
-            mix_pipelined(y, render_chunk, n_chunks=args.mix_chunks, reduce_stream=side_stream)
+            def step_render():
+                mix_pipelined(y, render_chunk, reduce_stream=side_stream, ranges=y_ranges)
+        else:
+            def step_render():
+                gi.process_device(0, T, x.data_ptr(), T, y.data_ptr(), T, stream=stream)
 
         for _ in range(args.warmup):
             step_render()
@@ -394,8 +401,7 @@ def run_ours(args):
             "ms_per_step": r_ms / args.steps,
             "config": {"workload": f"cfg2: {N} objects/GPU x 60 s x 48 kHz into {R['layout']} (M={M}), "
                                    f"{R['ramp']}-sample linear gain ramps; inputs 1.6 GB/step > L2",
-                       "bus_reduce": (f"nccl all_reduce(sum, f32) of the [M x T] bus in {args.mix_chunks} time chunks, "
-                                      "chunk k reduced on a side stream while chunk k + 1 renders")
+                       "bus_reduce": (f"nccl all_reduce(sum, f32) of the [M x T] bus, {args.mix_chunks} time chunk(s)")
                        if world > 1 else "none"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                          "frac": achieved / hbm_peak,
@@ -551,7 +557,7 @@ def run_ours(args):
         lay5 = "4+7+0"
         T5 = args.mix_samples
         n_total = args.mix_objects
-        from libear_b200.sharding import object_groups, reduce_bus, shard_range
+        from libear_b200.sharding import chunked_bus, mix_pipelined, object_groups, reduce_bus, shard_range
         obj_a, obj_b = shard_range(n_total, rank, world)
         n_local = obj_b - obj_a
         # HOA order 3 (ACN 0..15, SN3D): design on the device, apply as a static 16 -> 12 matrix
@@ -607,20 +613,23 @@ def run_ours(args):
         red0, red1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
         mix_side = torch.cuda.Stream(dev) if world > 1 else None
+        cbus, cranges = chunked_bus(M5, T5, args.mix_chunks if world > 1 else 1, device=dev)
+        c_per = cbus.shape[2]
 
-        def mix_chunk(t0, t1):
+        def mix_chunk(k, t0, t1):
             for g0, g1, gi in groups:
-                gi.process_device(t0, t1 - t0, xo[g0].data_ptr() + 4 * t0, T5, bus.data_ptr() + 4 * t0, T5,
+                gi.process_device(t0, t1 - t0, xo[g0].data_ptr() + 4 * t0, T5, cbus[k].data_ptr(), c_per,
                                   stream=stream)
 
         def step_mix(timed_reduce=False):
             if timed_reduce:  # the exchange step on its own: render everything, then one all-reduce
-                mix_chunk(0, T5)
+                for g0, g1, gi in groups:
+                    gi.process_device(0, T5, xo[g0].data_ptr(), T5, bus.data_ptr(), T5, stream=stream)
                 red0.record()
                 reduce_bus(bus)
                 red1.record()
             else:             # the one collective, chunked and hidden behind the rendering
-                mix_pipelined(bus, mix_chunk, n_chunks=args.mix_chunks, reduce_stream=mix_side)
+                mix_pipelined(cbus, mix_chunk, reduce_stream=mix_side, ranges=cranges)
 
         for _ in range(args.warmup):
             step_mix()
@@ -649,8 +658,8 @@ def run_ours(args):
             "config": {"workload": f"cfg5: {n_total} extent objects x {T5 / 48000:.0f} s x 48 kHz into {lay5} (M={M5}), "
                                    f"{n_local} objects/GPU in groups of 256, gains from GainCalculatorObjects at "
                                    f"{n_pts} points; HOA order 3 (16 ch) decode alongside",
-                       "bus_reduce": (f"nccl all_reduce(sum, f32) of the [M x T] bus in {args.mix_chunks} time chunks behind "
-                                      "the rendering; bus_reduce_ms is the same reduce unchunked and exposed")
+                       "bus_reduce": (f"nccl all_reduce(sum, f32) of the [M x T] bus, {args.mix_chunks} time chunk(s); "
+                                      "bus_reduce_ms is the reduce on its own")
                        if world > 1 else "none (1 GPU)"},
             "roofline": {"bound": "hbm", "achieved": mix_bytes / (mix_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                          "frac": mix_bytes / (mix_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None,
@@ -662,7 +671,7 @@ def run_ours(args):
                     "apply_msamples_per_s": 16 * T5 / (hoa_ms * 1e-3) / 1e6,
                     "apply_gbs": 4.0 * T5 * (16 + M5) / (hoa_ms * 1e-3) / 1e9},
         }
-        del xo, bus, groups
+        del xo, bus, cbus, groups
 
     if rank == 0:
         line = {
@@ -730,7 +739,10 @@ def main():
     ap.add_argument("--conv-blocks", type=int, default=56250, help="blocks per channel (cfg4: 10 min)")
     ap.add_argument("--mix-objects", type=int, default=4096, help="objects of the whole job (cfg5)")
     ap.add_argument("--mix-samples", type=int, default=2_880_000)
-    ap.add_argument("--mix-chunks", type=int, default=8, help="time chunks of the pipelined bus reduce (N > 1)")
+    ap.add_argument("--mix-chunks", type=int, default=1,
+                    help="time chunks of the bus reduce at N > 1 (chunk k reduced on a side stream while chunk "
+                         "k + 1 renders); 1 = render, then one all-reduce -- the faster form as measured, see "
+                         "DESIGN.md section 7")
     ap.add_argument("--no-render-e2e", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiler runs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")

@@ -186,6 +186,12 @@ int earb200_interp_create(int n_in, int n_out, int device, earb200_interp **out)
     cudaDeviceProp prop;
     EARB_CUDA(cudaGetDeviceProperties(&prop, device));
     h->n_sms = prop.multiProcessorCount;
+    // EARB200_RENDER_SM_RESERVE=k leaves k SMs free of the persistent render CTAs (each takes a
+    // whole SM), e.g. for a collective running next to the render on another stream
+    if (const char *r = std::getenv("EARB200_RENDER_SM_RESERVE")) {
+      const int k = std::atoi(r);
+      if (k > 0 && k < h->n_sms) h->n_sms -= k;
+    }
     h->N = n_in;
     h->M = n_out;
     const char *path = std::getenv("EARB200_RENDER_PATH");

@@ -55,29 +55,65 @@ def reduce_bus_rows(bus, t0, t1, group=None):
             dist.all_reduce(r, op=dist.ReduceOp.SUM, group=group)
 
 
-def mix_pipelined(bus, render_chunk, n_chunks=8, group=None, reduce_stream=None, align=512):
+def chunked_bus(n_out, n_samples, n_chunks, device=None, dtype=None, align=512):
+    """A loudspeaker bus stored chunk-major, [n_chunks][n_out][chunk_samples]: every time chunk is
+    one contiguous block, so its all-reduce is a single collective.  Returns (bus, ranges); chunk k
+    holds the samples ranges[k] = [t0, t1) in bus[k, :, :t1 - t0]."""
+    import torch
+    ranges = chunk_ranges(n_samples, n_chunks, align)
+    per = ranges[0][1] - ranges[0][0]
+    bus = torch.zeros((len(ranges), n_out, per), device=device, dtype=dtype or torch.float32)
+    return bus, ranges
+
+
+def mix_pipelined(bus, render_chunk, n_chunks=8, group=None, reduce_stream=None, align=512, ranges=None):
     """Object-sharded mixing with the exchange step hidden behind the rendering: the bus is cut
-    into time chunks; chunk k is rendered on the current stream (`render_chunk(t0, t1)` must write
-    bus[:, t0:t1]) and summed over the ranks on `reduce_stream` while chunk k + 1 renders.  On one
-    rank (or without a process group) it only renders.  Returns when both streams are joined."""
+    into time chunks; chunk k is rendered on the current stream and summed over the ranks on
+    `reduce_stream` while chunk k + 1 renders.  Two bus layouts:
+      * chunk-major (3-D, from chunked_bus; pass its `ranges`): render_chunk(k, t0, t1) writes
+        bus[k, :, :t1 - t0]; one contiguous all-reduce per chunk -- the fast form;
+      * planar [M x T] (2-D): render_chunk(t0, t1) writes bus[:, t0:t1]; a chunk is M row slices,
+        reduced as one coalesced group of M collectives (measured latency-bound: 112 small
+        all-reduces per 60 s bus cost more than the single unchunked one).
+    On one rank (or without a process group) it only renders.  Returns with both streams joined."""
     import torch
     import torch.distributed as dist
     sharded = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
-    chunks = chunk_ranges(bus.shape[1], n_chunks if sharded else 1, align)
-    if not (sharded and bus.is_cuda):
-        for t0, t1 in chunks:
+    chunk_major = bus.dim() == 3
+    if chunk_major:
+        if ranges is None or len(ranges) != bus.shape[0]:
+            raise ValueError("a chunk-major bus needs the ranges chunked_bus returned")
+        chunks = list(ranges)
+    else:
+        chunks = chunk_ranges(bus.shape[1], n_chunks if sharded else 1, align)
+
+    def render(k):
+        t0, t1 = chunks[k]
+        if chunk_major:
+            render_chunk(k, t0, t1)
+        else:
             render_chunk(t0, t1)
+
+    def reduce(k):
+        if chunk_major:
+            dist.all_reduce(bus[k], op=dist.ReduceOp.SUM, group=group)
+        else:
+            reduce_bus_rows(bus, chunks[k][0], chunks[k][1], group)
+
+    if not (sharded and bus.is_cuda):
+        for k in range(len(chunks)):
+            render(k)
             if sharded:
-                reduce_bus_rows(bus, t0, t1, group)
+                reduce(k)
         return bus
     main = torch.cuda.current_stream(bus.device)
     side = reduce_stream or torch.cuda.Stream(bus.device)
-    for t0, t1 in chunks:
-        render_chunk(t0, t1)
+    for k in range(len(chunks)):
+        render(k)
         done = torch.cuda.Event()
         done.record(main)
         side.wait_event(done)
         with torch.cuda.stream(side):
-            reduce_bus_rows(bus, t0, t1, group)
+            reduce(k)
     main.wait_stream(side)
     return bus

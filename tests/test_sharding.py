@@ -11,7 +11,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from libear_b200.sharding import chunk_ranges, mix_pipelined, object_groups, reduce_bus, shard_range
+from libear_b200.sharding import chunk_ranges, chunked_bus, mix_pipelined, object_groups, reduce_bus, shard_range
 
 
 def test_shard_range_is_a_partition():
@@ -74,6 +74,15 @@ def _worker(rank, world, port, out_dir):
             bus2[:, t0:t1] = torch.from_numpy(eo.interp_matrix(x[a:b, t0:t1], samples, gains[:, a:b], block_start=t0))
         mix_pipelined(bus2, render_chunk, n_chunks=3)
         err = max(err, float(np.abs(bus2.numpy() - full).max() / np.abs(full).max()))
+        # and with the chunk-major bus (one contiguous all-reduce per chunk)
+        bus3, ranges = chunked_bus(M, T, 3)
+
+        def render_chunk3(k, t0, t1):
+            bus3[k, :, :t1 - t0] = torch.from_numpy(
+                eo.interp_matrix(x[a:b, t0:t1], samples, gains[:, a:b], block_start=t0))
+        mix_pipelined(bus3, render_chunk3, ranges=ranges)
+        planar = np.concatenate([bus3[k, :, :t1 - t0].numpy() for k, (t0, t1) in enumerate(ranges)], axis=1)
+        err = max(err, float(np.abs(planar - full).max() / np.abs(full).max()))
         # gains shard with no collective: each rank's rows are just a slice of the global answer
         pan = eo.PointSourcePanner("0+5+0")
         dirs = rng.normal(size=(64, 3))
