@@ -431,6 +431,42 @@ def run_ours(args):
         del x, y
 
 
+    # ---------------- point sources: BASELINE configs[0] (1,024 objects on 0+5+0, no extent) as the
+    # reference's own CPU-runnable case -- latency-bound -- and the same kernels at 10^6 objects
+    point_block = None
+    if not args.no_points:
+        gcp = eb.GainCalculatorObjects("0+5+0", device=local_rank)
+        Cp = gcp.num_outputs
+        point_block = {"metric": "point-source gain vectors/s (0+5+0, no extent)", "unit": "vectors/s"}
+        for label, npts in (("n1024", 1024), ("n1M", 1_000_000)):
+            rp = np.random.default_rng(1 + rank)
+            cols = [rp.uniform(-180, 180, npts), np.degrees(np.arcsin(rp.uniform(-1, 1, npts))), np.ones(npts),
+                    np.zeros(npts), np.zeros(npts), np.zeros(npts), rp.uniform(0, 1, npts), rp.uniform(0, 1, npts)]
+            dp_in = torch.from_numpy(np.stack(cols)).to(dev)
+            dp_d = torch.empty((npts, Cp), dtype=torch.float32, device=dev)
+            dp_f = torch.empty((npts, Cp), dtype=torch.float32, device=dev)
+            soap = [dp_in[k].data_ptr() for k in range(8)]
+            for _ in range(args.warmup):
+                gcp.calculate_device(npts, soap, dp_d.data_ptr(), dp_f.data_ptr(), stream=stream)
+            barrier()
+            pl0 = gcp.launch_count
+            p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            p0.record()
+            for _ in range(args.steps):
+                gcp.calculate_device(npts, soap, dp_d.data_ptr(), dp_f.data_ptr(), stream=stream)
+            p1.record()
+            barrier()
+            p_ms = max_over_ranks(p0.elapsed_time(p1)) / args.steps
+            gpu_launches += gcp.launch_count - pl0
+            p_bytes = npts * (64.0 + 2 * 4 * Cp)
+            point_block[label] = {"objects_per_gpu": npts, "value": npts * world / (p_ms * 1e-3), "us_per_call": p_ms * 1e3,
+                                  "algorithmic_gbs": p_bytes / (p_ms * 1e-3) / 1e9,
+                                  "hbm_frac": p_bytes / (p_ms * 1e-3) / 1e9 / hbm_peak}
+            del dp_in, dp_d, dp_f
+        point_block["note"] = ("n1024 is launch-latency-bound (three small kernels per call); n1M runs the FP64 "
+                               "region scan at 112 algorithmic bytes per object")
+        del gcp
+
     # ---------------- convolver: BASELINE config 4 (24 channels x 10 min, 512-tap decorrelators, B = 512)
     conv_block = None
     if not args.no_convolver:
@@ -698,6 +734,8 @@ def run_ours(args):
             "gpu_launches": int(gpu_launches),
             "clocks": sampler.summary(),
         }
+        if point_block is not None:
+            line["point_sources"] = point_block
         if render is not None:
             line["render"] = render
         if conv_block is not None:
@@ -736,6 +774,7 @@ def main():
     ap.add_argument("--no-convolver", action="store_true")
     ap.add_argument("--no-mix", action="store_true")
     ap.add_argument("--no-flow", action="store_true")
+    ap.add_argument("--no-points", action="store_true")
     ap.add_argument("--conv-blocks", type=int, default=56250, help="blocks per channel (cfg4: 10 min)")
     ap.add_argument("--mix-objects", type=int, default=4096, help="objects of the whole job (cfg5)")
     ap.add_argument("--mix-samples", type=int, default=2_880_000)
