@@ -223,7 +223,7 @@ def run_reference(args):
         "unit": "vectors/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"cfg1 sample: {step_n} extent objects/step on {LAYOUT} "
+        "config": {"workload": f"configs[1] (SURVEY cfg 2) sample: {step_n} extent objects/step on {LAYOUT} "
                                "(same distribution as the GPU arm's 1M objects/GPU)",
                    "layout": LAYOUT},
         "cpu_baseline": {"value": value, "unit": "vectors/s", "cores": threads, "kind": "reference",
@@ -399,7 +399,7 @@ def run_ours(args):
             "metric": "render Msamples/s (input object-samples)",
             "value": N * T * world * args.steps / (r_ms * 1e-3) / 1e6, "unit": "Msamples/s",
             "ms_per_step": r_ms / args.steps,
-            "config": {"workload": f"cfg2: {N} objects/GPU x 60 s x 48 kHz into {R['layout']} (M={M}), "
+            "config": {"workload": f"configs[2] (SURVEY cfg 3): {N} objects/GPU x 60 s x 48 kHz into {R['layout']} (M={M}), "
                                    f"{R['ramp']}-sample linear gain ramps; inputs 1.6 GB/step > L2",
                        "bus_reduce": (f"nccl all_reduce(sum, f32) of the [M x T] bus, {args.mix_chunks} time chunk(s)")
                        if world > 1 else "none"},
@@ -407,7 +407,7 @@ def run_ours(args):
                          "frac": achieved / hbm_peak,
                          "traffic": ncu_traffic("render_tc_persistent_kernel") if (N, M, T) == (128, 14, 2_880_000) else None,
                          "peak_source": peak_src,
-                         "kernel": "render_kernel<16,4,true>", "kernel_ms": k_ms / max(1, k_launches),
+                         "kernel": "render_tc_persistent_kernel<32>", "kernel_ms": k_ms / max(1, k_launches),
                          "algorithmic_bytes_per_launch": alg_bytes},
         }
         # end to end: pinned host input/output through the C-ABI host entry point
@@ -437,7 +437,7 @@ def run_ours(args):
     if not args.no_points:
         gcp = eb.GainCalculatorObjects("0+5+0", device=local_rank)
         Cp = gcp.num_outputs
-        point_block = {"metric": "point-source gain vectors/s (0+5+0, no extent)", "unit": "vectors/s"}
+        point_block = {"metric": "point-source gain vectors/s (0+5+0, no extent): configs[0] (SURVEY cfg 1)", "unit": "vectors/s"}
         for label, npts in (("n1024", 1024), ("n1M", 1_000_000)):
             rp = np.random.default_rng(1 + rank)
             cols = [rp.uniform(-180, 180, npts), np.degrees(np.arcsin(rp.uniform(-1, 1, npts))), np.ones(npts),
@@ -507,7 +507,7 @@ def run_ours(args):
         conv_block = {
             "metric": "decorrelation convolver Msamples/s", "value": Cc * Tc * world * args.steps / (c_ms * 1e-3) / 1e6,
             "unit": "Msamples/s", "ms_per_step": c_ms / args.steps,
-            "config": {"workload": f"cfg4: {Cc} channels/GPU x {Tc} samples ({Tc / 48000 / 60:.1f} min at 48 kHz), "
+            "config": {"workload": f"configs[3] (SURVEY cfg 4): {Cc} channels/GPU x {Tc} samples ({Tc / 48000 / 60:.1f} min at 48 kHz), "
                                    f"designDecorrelators({LAYOUT}) 512-tap filters, block size {Bc}; "
                                    "5.5 GB/step > L2", "sharding": "replicated channels per GPU, no collective"},
             "roofline": {"bound": "hbm", "achieved": c_achieved, "peak": hbm_peak, "unit": "GB/s",
@@ -691,7 +691,7 @@ def run_ours(args):
             "metric": "object mixing Msamples/s (input object-samples, whole job)",
             "value": n_total * T5 / (mix_ms * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": mix_ms,
             "scaling": "strong",
-            "config": {"workload": f"cfg5: {n_total} extent objects x {T5 / 48000:.0f} s x 48 kHz into {lay5} (M={M5}), "
+            "config": {"workload": f"configs[4] (SURVEY cfg 5): {n_total} extent objects x {T5 / 48000:.0f} s x 48 kHz into {lay5} (M={M5}), "
                                    f"{n_local} objects/GPU in groups of 256, gains from GainCalculatorObjects at "
                                    f"{n_pts} points; HOA order 3 (16 ch) decode alongside",
                        "bus_reduce": (f"nccl all_reduce(sum, f32) of the [M x T] bus, {args.mix_chunks} time chunk(s); "
@@ -715,7 +715,7 @@ def run_ours(args):
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"cfg1: {n} extent objects/GPU on {LAYOUT} via the batched "
+            "config": {"workload": f"configs[1] (SURVEY cfg 2): {n} extent objects/GPU on {LAYOUT} via the batched "
                                    "GainCalculatorObjects C-ABI (1,652-point spreading grid, depth != 0 for half)",
                        "layout": LAYOUT, "objects_per_gpu": n, "passes_per_step_per_gpu": n_passes,
                        "l2": "inputs+outputs 256 MB/step/GPU > 126 MB L2", "sharding": "objects, no collective"},
