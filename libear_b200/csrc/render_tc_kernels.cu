@@ -200,12 +200,14 @@ namespace earb {
     //   b_full[t]   epilogue   -> MMA         gain matrix buffer t is built   (4 warps)
     //   acc_full[t] MMA commit -> epilogue    accumulators t are complete (B buffer t is free too)
     //   acc_free[t] epilogue   -> MMA         accumulators t have been read out (4 warps)
-    constexpr int kConvWarps = 8, kEpiWarps = 4;
+    // EPI epilogue warps: 4 (one per TMEM lane quarter, draining both M-tiles of a tile in turn) or 8
+    // (one per lane quarter and M-tile).  The read-out is a fixed cost per tile, so with few input
+    // channels it sets the pace and the second set of warps pays (N = 16: 0.148 -> 0.102 ms); at
+    // N >= 128 the 96-register cap of 640 threads costs 2 %, and the wide units spill under it.
+    constexpr int kConvWarps = 8;
     // two MMA issuer warps, one per M-tile: a single thread cannot issue the UMMAs of both fast
     // enough (each tcgen05.mma costs the issuing thread ~100 cycles of scalar work)
-    constexpr int kProducerWarp = kConvWarps + kEpiWarps, kMmaWarp = kProducerWarp + 1;
-    constexpr int kBLoadWarp = kMmaWarp + kMT;        // streams the gain-matrix images
-    constexpr int kThreadsP = (kBLoadWarp + 1) * 32;  // 512
+    constexpr int threads_for(int epi) { return (kConvWarps + epi + 1 + kMT + 1) * 32; }  // 512 or 640
     constexpr int kMaxStages = 10;
     constexpr int kTmemColsP = 512;
     // TMEM columns: accumulators [2 tiles][main: kMT x 32 | corr: kMT x 32], then
@@ -221,8 +223,8 @@ namespace earb {
     constexpr int kABufs = 4;  // A-operand ring in TMEM (power of two)
     static_assert(kColAP + kABufs * kMT * 2 * kCh <= kTmemColsP, "TMEM budget");
 
-    template <int NP>
-    __global__ void __launch_bounds__(kThreadsP, 1)
+    template <int NP, int EPI>
+    __global__ void __launch_bounds__(threads_for(EPI), 1)
         render_tc_persistent_kernel(const __grid_constant__ CUtensorMap in_map, int N, int M,
                                     float *__restrict__ out, long out_stride,
                                     const RenderItem *__restrict__ items, int n_tiles,
@@ -230,6 +232,9 @@ namespace earb {
                                     const float *__restrict__ images, int n_stages, int accumulate,
                                     int n_groups) {
       extern __shared__ __align__(128) unsigned char smem_raw[];
+      constexpr int kEpiWarps = EPI;
+      constexpr int kProducerWarp = kConvWarps + kEpiWarps, kMmaWarp = kProducerWarp + 1;
+      constexpr int kBLoadWarp = kMmaWarp + kMT;  // streams the gain-matrix images
       const int Kp = (N + kCh - 1) / kCh * kCh;  // K padded to whole stages
       const int n_iters = Kp / kCh;
       // a work unit = one 256-sample tile x one group of 16 output channels; the groups of a tile
@@ -440,7 +445,9 @@ namespace earb {
         }
       } else {
         // ------------------------------------------------------------ epilogue + gain matrices
-        const int q = warp & 3;
+        // EPI == 8: this warp drains M-tile j0 only; EPI == 4: both, one after the other
+        const int q = warp & 3, j0 = (warp - kConvWarps) >> 2;
+        constexpr int kJ = kMT * 4 / EPI;  // M-tiles per epilogue warp
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
         int L = 0;
         for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, L++) {
@@ -456,20 +463,21 @@ namespace earb {
           // accumulate mode: the bus values this thread will add to are fetched before waiting for
           // the accumulators, so their latency hides behind the MMAs of this tile
           // (wide units read the bus inside the loop instead: 64 more registers would not fit)
-          float prev[kMT][16];
+          float prev[kJ][16];
           if (accumulate && NP == 32) {
 #pragma unroll
-            for (int j = 0; j < kMT; j++) {
-              const long tp = item.t0 + j * 128 + q * 32 + lane;
+            for (int jj = 0; jj < kJ; jj++) {
+              const long tp = item.t0 + (j0 + jj) * 128 + q * 32 + lane;
 #pragma unroll
-              for (int m = 0; m < 16; m++) prev[j][m] = (m < Mg) ? __ldcs(og + (long)m * out_stride + tp) : 0.0f;
+              for (int m = 0; m < 16; m++) prev[jj][m] = (m < Mg) ? __ldcs(og + (long)m * out_stride + tp) : 0.0f;
             }
           }
           mbar_wait(&acc_full[ab], (uint32_t)((L >> 1) & 1));
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint32_t acc = NP == 32 ? lane_base + ab * 128 : lane_base;
 #pragma unroll
-          for (int j = 0; j < kMT; j++) {
+          for (int jj = 0; jj < kJ; jj++) {
+            const int j = j0 + jj;
             const long t = item.t0 + j * 128 + q * 32 + lane;
             const float p = ramp ? (float)(t - seg.ramp_start) * seg.scale : 0.0f;
             if (NP == 32) {
@@ -483,7 +491,7 @@ namespace earb {
                   const float sa = a[m] + b[m];
                   const float sb = a[16 + m] + b[16 + m];
                   float r = ramp ? fmaf(p, sb - sa, sa) : sa;
-                  if (accumulate) r += prev[j][m];  // mix into the bus
+                  if (accumulate) r += prev[jj][m];  // mix into the bus
                   if (EARB_RENDER_EXPERIMENT < 3) __stcs(og + (long)m * out_stride + t, r);
                 }
               }
@@ -659,9 +667,11 @@ namespace earb {
     if (!encode) return false;
     static bool configured = false;
     if (!configured) {
-      cudaFuncSetAttribute(render_tc_persistent_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      cudaFuncSetAttribute(render_tc_persistent_kernel<32, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)kSmemBudget);
-      cudaFuncSetAttribute(render_tc_persistent_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      cudaFuncSetAttribute(render_tc_persistent_kernel<32, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)kSmemBudget);
+      cudaFuncSetAttribute(render_tc_persistent_kernel<64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)kSmemBudget);
       configured = true;
     }
@@ -681,11 +691,15 @@ namespace earb {
         return false;
       const int acc_mode = (accumulate || k0 > 0) ? 1 : 0;
       if (sh.NP == 64)
-        render_tc_persistent_kernel<64><<<grid, kThreadsP, smem_for(Ng, 64), stream>>>(
+        render_tc_persistent_kernel<64, 4><<<grid, threads_for(4), smem_for(Ng, 64), stream>>>(
             map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 64), acc_mode,
             sh.n_out_groups);
+      else if (Ng <= 64)  // few input channels: the read-out sets the pace, eight epilogue warps
+        render_tc_persistent_kernel<32, 8><<<grid, threads_for(8), smem_for(Ng, 32), stream>>>(
+            map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 32), acc_mode,
+            sh.n_out_groups);
       else
-        render_tc_persistent_kernel<32><<<grid, kThreadsP, smem_for(Ng, 32), stream>>>(
+        render_tc_persistent_kernel<32, 4><<<grid, threads_for(4), smem_for(Ng, 32), stream>>>(
             map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 32), acc_mode,
             sh.n_out_groups);
       d_images += (size_t)n_points * sh.n_out_groups * padded_k(Ng) * sh.NP;
