@@ -106,6 +106,27 @@ namespace earb {
           "r"(__float_as_uint(v[15]))
           : "memory");
     }
+    // four 8-column loads in flight, one wait
+    __device__ __forceinline__ void tmem_ld8x4(uint32_t ta, uint32_t tb, uint32_t tc, uint32_t td, float (&a)[8],
+                                               float (&b)[8], float (&c)[8], float (&d)[8]) {
+      uint32_t r[4][8];
+      const uint32_t addr[4] = {ta, tb, tc, td};
+#pragma unroll
+      for (int k = 0; k < 4; k++)
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                     : "=r"(r[k][0]), "=r"(r[k][1]), "=r"(r[k][2]), "=r"(r[k][3]), "=r"(r[k][4]), "=r"(r[k][5]),
+                       "=r"(r[k][6]), "=r"(r[k][7])
+                     : "r"(addr[k])
+                     : "memory");
+      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        a[i] = __uint_as_float(r[0][i]);
+        b[i] = __uint_as_float(r[1][i]);
+        c[i] = __uint_as_float(r[2][i]);
+        d[i] = __uint_as_float(r[3][i]);
+      }
+    }
     // two 16-column loads in flight, one wait
     __device__ __forceinline__ void tmem_ld16x2(uint32_t ta, uint32_t tb, float (&a)[16], float (&b)[16]) {
       uint32_t r[16], q[16];
@@ -496,26 +517,28 @@ namespace earb {
                 }
               }
             } else {
-              // wide: main and correction accumulators, each [32 x g_a | 32 x g_b], read out 16 output
-              // channels at a time
+              // wide: main and correction accumulators, each [32 x g_a | 32 x g_b], read out 8 output
+              // channels at a time (32 live values: the 96-register form of the kernel has room for it)
 #pragma unroll
-              for (int h = 0; h < 2; h++) {
-                float bus[16];
-                if (accumulate) {
+              for (int h = 0; h < 4; h++) {
+                if (h * 8 < Mg) {
+                  float bus[8];
+                  if (accumulate) {
 #pragma unroll
-                  for (int m = 0; m < 16; m++)
-                    bus[m] = (h * 16 + m < Mg) ? __ldcs(og + (long)(h * 16 + m) * out_stride + t) : 0.0f;
-                }
-                float sa[16], sb[16], ca[16], cb[16];
-                tmem_ld16x2(acc + j * 128 + h * 16, acc + j * 128 + 32 + h * 16, sa, sb);
-                tmem_ld16x2(acc + j * 128 + 64 + h * 16, acc + j * 128 + 96 + h * 16, ca, cb);
+                    for (int m = 0; m < 8; m++)
+                      bus[m] = (h * 8 + m < Mg) ? __ldcs(og + (long)(h * 8 + m) * out_stride + t) : 0.0f;
+                  }
+                  float sa[8], sb[8], ca[8], cb[8];
+                  tmem_ld8x4(acc + j * 128 + h * 8, acc + j * 128 + 32 + h * 8, acc + j * 128 + 64 + h * 8,
+                             acc + j * 128 + 96 + h * 8, sa, sb, ca, cb);
 #pragma unroll
-                for (int m = 0; m < 16; m++) {
-                  if (h * 16 + m < Mg) {
-                    const float va = sa[m] + ca[m], vb = sb[m] + cb[m];
-                    float r = ramp ? fmaf(p, vb - va, va) : va;
-                    if (accumulate) r += bus[m];
-                    if (EARB_RENDER_EXPERIMENT < 3) __stcs(og + (long)(h * 16 + m) * out_stride + t, r);
+                  for (int m = 0; m < 8; m++) {
+                    if (h * 8 + m < Mg) {
+                      const float va = sa[m] + ca[m], vb = sb[m] + cb[m];
+                      float r = ramp ? fmaf(p, vb - va, va) : va;
+                      if (accumulate) r += bus[m];
+                      if (EARB_RENDER_EXPERIMENT < 3) __stcs(og + (long)(h * 8 + m) * out_stride + t, r);
+                    }
                   }
                 }
               }
@@ -673,6 +696,8 @@ namespace earb {
                            (int)kSmemBudget);
       cudaFuncSetAttribute(render_tc_persistent_kernel<64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)kSmemBudget);
+      cudaFuncSetAttribute(render_tc_persistent_kernel<64, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)kSmemBudget);
       configured = true;
     }
     const TcShape sh = tc_shape(N, M);
@@ -690,7 +715,11 @@ namespace earb {
                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return false;
       const int acc_mode = (accumulate || k0 > 0) ? 1 : 0;
-      if (sh.NP == 64)
+      if (sh.NP == 64 && Ng <= 64)
+        render_tc_persistent_kernel<64, 8><<<grid, threads_for(8), smem_for(Ng, 64), stream>>>(
+            map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 64), acc_mode,
+            sh.n_out_groups);
+      else if (sh.NP == 64)
         render_tc_persistent_kernel<64, 4><<<grid, threads_for(4), smem_for(Ng, 64), stream>>>(
             map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 64), acc_mode,
             sh.n_out_groups);
