@@ -592,12 +592,11 @@ namespace earb {
 
   // How a render of N inputs into M outputs is cut up for the kernel:
   //   M <= 16: NP = 32 units (main + correction accumulators), input groups of up to 256 channels;
-  //   M  > 16 and N <= 128: NP = 64 "wide" units (up to 32 outputs, the input is converted once; the
-  //            gain matrices of one tile are 2 * Kp * NP floats and two of them must leave room for
-  //            the input ring, hence N <= 128);
-  //   M  > 16 and N > 128: NP = 32 with two output groups per tile, the second read of the input
-  //            served by L2 (measured faster than wide units over several accumulating launches:
-  //            N = 256, M = 24: 1.06 vs 1.09 ms; N = 512: 2.14 vs 2.47 ms).
+  //   M  > 16: NP = 64 "wide" units (up to 32 outputs, the input is converted once; the gain
+  //            matrices of one tile are 2 * Kp * NP floats and two of them must leave room for the
+  //            input ring, hence input groups of up to 128 channels).  With eight epilogue warps
+  //            this beats NP = 32 with two output groups at every N (N = 256, M = 24: 0.80 vs
+  //            1.07 ms; N = 512: 1.78 vs 2.15 ms).
   // Input groups run as one launch each, the later ones accumulating into the output.
   // EARB200_RENDER_WIDE=0 keeps NP = 32 for every shape (for comparison).
   namespace {
@@ -605,11 +604,11 @@ namespace earb {
       int NP, max_in, n_out_groups;
     };
     TcShape tc_shape(int N, int M) {
-      static const bool wide_ok = [] {
+      static const int wide = [] {
         const char *e = std::getenv("EARB200_RENDER_WIDE");
-        return !(e && e[0] == '0');
+        return e ? std::atoi(e) : 1;
       }();
-      if (M > 16 && N <= 128 && wide_ok) return {64, 128, (M + 31) / 32};
+      if (M > 16 && wide > 0) return {64, 128, (M + 31) / 32};
       return {32, 256, (M + 15) / 16};
     }
     int padded_k(int n) { return (n + kCh - 1) / kCh * kCh; }
@@ -694,8 +693,6 @@ namespace earb {
                            (int)kSmemBudget);
       cudaFuncSetAttribute(render_tc_persistent_kernel<32, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)kSmemBudget);
-      cudaFuncSetAttribute(render_tc_persistent_kernel<64, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           (int)kSmemBudget);
       cudaFuncSetAttribute(render_tc_persistent_kernel<64, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)kSmemBudget);
       configured = true;
@@ -715,12 +712,8 @@ namespace earb {
                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return false;
       const int acc_mode = (accumulate || k0 > 0) ? 1 : 0;
-      if (sh.NP == 64 && Ng <= 64)
+      if (sh.NP == 64)  // wide units: the read-out of 2 x 64 accumulator columns always wants eight warps
         render_tc_persistent_kernel<64, 8><<<grid, threads_for(8), smem_for(Ng, 64), stream>>>(
-            map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 64), acc_mode,
-            sh.n_out_groups);
-      else if (sh.NP == 64)
-        render_tc_persistent_kernel<64, 4><<<grid, threads_for(4), smem_for(Ng, 64), stream>>>(
             map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 64), acc_mode,
             sh.n_out_groups);
       else if (Ng <= 64)  // few input channels: the read-out sets the pace, eight epilogue warps
