@@ -229,9 +229,11 @@ namespace earb {
     // forward transform of the pair held in v (v[br5(a)] = z[lane + 32 a] for a < 16, odd slots
     // zero), filter multiply, inverse transform.  On return v[n2] = y[lane + 32 n2] (real part:
     // first block of the pair, imaginary part: second block).
-    // tw_s / H_s hold two consecutive slots per float4: [slot / 2][lane] = (slot, slot + 1).
-    __device__ __forceinline__ void convolve_pair(cx (&v)[32], cx *tile, const float4 *tw_s, const float4 *H_s,
-                                                  int lane) {
+    // tw_s / H_s hold two consecutive slots per float4: [slot / 2][lane] = (slot, slot + 1);
+    // twi_s pairs the slots the inverse needs together: [n1][lane] = (n1, n1 + 16).  H_s carries the
+    // 1 / (2B) scale (a power of two: exact), so v comes back normalised.
+    __device__ __forceinline__ void convolve_pair(cx (&v)[32], cx *tile, const float4 *tw_s, const float4 *twi_s,
+                                                  const float4 *H_s, int lane) {
       dit32<false, true>(v);  // over a: v[k1] = A_lane[k1]
 #pragma unroll
       for (int k1 = 0; k1 < 32; k1 += 2) {
@@ -260,9 +262,9 @@ namespace earb {
       for (int q = 0; q < 32; q += 2) {
         // slots q, q + 1 hold n1 = br5(q), br5(q) + 16
         const int n1 = br5(q);
-        const float4 ta = tw_s[(n1 >> 1) * 32 + lane], tb = tw_s[((n1 + 16) >> 1) * 32 + lane];
-        tile[n1 * kRow + lane] = (n1 & 1) ? cmulcf(v[q], ta.z, ta.w) : cmulcf(v[q], ta.x, ta.y);
-        tile[(n1 + 16) * kRow + lane] = (n1 & 1) ? cmulcf(v[q + 1], tb.z, tb.w) : cmulcf(v[q + 1], tb.x, tb.y);
+        const float4 t = twi_s[n1 * 32 + lane];
+        tile[n1 * kRow + lane] = cmulcf(v[q], t.x, t.y);
+        tile[(n1 + 16) * kRow + lane] = cmulcf(v[q + 1], t.z, t.w);
       }
       __syncwarp();
 #pragma unroll
@@ -279,15 +281,21 @@ namespace earb {
       extern __shared__ float4 fsm[];
       float4 *tw_s = fsm;        // [16][32]: (tw[2j][lane], tw[2j + 1][lane])
       float4 *H_s = tw_s + 512;  // [16][32]: (H[lane + 32 (2j)], H[lane + 32 (2j + 1)])
-      cx *tiles = reinterpret_cast<cx *>(H_s + 512);  // kWarps x 32 x kRow complex numbers
+      float4 *twi_s = H_s + 512;  // [16][32]: (tw[n1][lane], tw[n1 + 16][lane])
+      cx *tiles = reinterpret_cast<cx *>(twi_s + 512);  // kWarps x 32 x kRow complex numbers
       const int c = blockIdx.y;
       const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
       const int f = a.filter_of[c];
+      // the carried tails stay unnormalised in global memory (shared with the generic kernel): scaled
+      // by the power of two on the way in and out, which is exact
+      const float norm = 1.0f / (float)(2 * kFastB);
       for (int i = threadIdx.x; i < 1024; i += kWarps * 32) {
         const int slot = i >> 5, L = i & 31;
         float2 *tw_dst = reinterpret_cast<float2 *>(tw_s) + ((slot >> 1) * 32 + L) * 2 + (slot & 1);
         float2 *H_dst = reinterpret_cast<float2 *>(H_s) + ((slot >> 1) * 32 + L) * 2 + (slot & 1);
-        *tw_dst = a.tw[i];
+        const float2 w = a.tw[i];
+        *tw_dst = w;
+        reinterpret_cast<float2 *>(twi_s)[((slot & 15) * 32 + L) * 2 + (slot >> 4)] = w;
         const int k = L + 32 * slot;
         float2 h = make_float2(0.0f, 0.0f);
         if (f >= 0) {
@@ -295,7 +303,7 @@ namespace earb {
           h = k <= kFastB ? a.filt[(size_t)f * (kFastB + 1) + k] : a.filt[(size_t)f * (kFastB + 1) + (2 * kFastB - k)];
           if (k > kFastB) h.y = -h.y;
         }
-        *H_dst = h;
+        *H_dst = make_float2(h.x * norm, h.y * norm);
       }
       __syncthreads();
 
@@ -305,19 +313,18 @@ namespace earb {
       cx *tile = tiles + (size_t)warp * 32 * kRow;
       const float *x = a.in + (size_t)c * a.in_stride;
       float *y = a.out + (size_t)c * a.out_stride;
-      const float norm = 1.0f / (float)(2 * kFastB);
 
       cx v[32];
       float tail[16];
       if (p0 == 0) {
 #pragma unroll
-        for (int r = 0; r < 16; r++) tail[r] = a.tail[(size_t)c * kFastB + lane + 32 * r];
+        for (int r = 0; r < 16; r++) tail[r] = a.tail[(size_t)c * kFastB + lane + 32 * r] * norm;
       } else {
         // halo: the block before the run as the imaginary part of a pair
         const float *xb = x + (size_t)(2 * p0 - 1) * kFastB;
 #pragma unroll
         for (int r = 0; r < 16; r++) v[br5(r)] = mk(0.0f, __ldg(xb + lane + 32 * r));
-        convolve_pair(v, tile, tw_s, H_s, lane);
+        convolve_pair(v, tile, tw_s, twi_s, H_s, lane);
 #pragma unroll
         for (int r = 0; r < 16; r++) tail[r] = im(v[r + 16]);
       }
@@ -334,14 +341,14 @@ namespace earb {
         for (int r = 0; r < 16; r++) xi[r] = has_second ? __ldcs(x0 + kFastB + lane + 32 * r) : 0.0f;
 #pragma unroll
         for (int r = 0; r < 16; r++) v[br5(r)] = mk(xr[r], xi[r]);
-        convolve_pair(v, tile, tw_s, H_s, lane);
+        convolve_pair(v, tile, tw_s, twi_s, H_s, lane);
         float *y0 = y + (size_t)(2 * p) * kFastB;
 #pragma unroll
-        for (int r = 0; r < 16; r++) __stcs(y0 + lane + 32 * r, (re(v[r]) + tail[r]) * norm);
+        for (int r = 0; r < 16; r++) __stcs(y0 + lane + 32 * r, re(v[r]) + tail[r]);
         if (has_second) {
 #pragma unroll
           for (int r = 0; r < 16; r++) {
-            __stcs(y0 + kFastB + lane + 32 * r, (im(v[r]) + re(v[r + 16])) * norm);
+            __stcs(y0 + kFastB + lane + 32 * r, im(v[r]) + re(v[r + 16]));
             tail[r] = im(v[r + 16]);
           }
         } else {
@@ -351,7 +358,7 @@ namespace earb {
       }
       if (p1 == a.n_pairs) {
 #pragma unroll
-        for (int r = 0; r < 16; r++) a.tail_new[(size_t)c * kFastB + lane + 32 * r] = tail[r];
+        for (int r = 0; r < 16; r++) a.tail_new[(size_t)c * kFastB + lane + 32 * r] = tail[r] * (float)(2 * kFastB);
       }
     }
   }  // namespace
@@ -390,7 +397,7 @@ namespace earb {
     a.filt = reinterpret_cast<const float2 *>(L.filt);
     a.filter_of = d_filter_of;
     a.tw = reinterpret_cast<const float2 *>(d_tw_fast);
-    const size_t smem = sizeof(float2) * (2048 + (size_t)kWarps * 32 * kRow);
+    const size_t smem = sizeof(float2) * (3072 + (size_t)kWarps * 32 * kRow);
     cudaFuncSetAttribute(convolver_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     const long warps = (a.n_pairs + run - 1) / run;
     dim3 grid((unsigned)((warps + kWarps - 1) / kWarps), (unsigned)L.C);
