@@ -230,7 +230,9 @@ namespace earb {
       upk(cd, cd0, cd1);
       upk(zt, z0, z1);
       const bool s0 = ctd0 >= c.sin_thr, s1 = ctd1 >= c.sin_thr;
-      const float v0 = s0 ? z0 : cd0, v1 = s1 ? z1 : cd1;
+      // the straight part enters as -|z'|: with the inverted sign of v on q below, both parts are
+      // weight = sat(m * (-copysign(q, v)) + k)
+      const float v0 = s0 ? -fabsf(z0) : cd0, v1 = s1 ? -fabsf(z1) : cd1;
       const f32x2 av = abs2(pk(v0, v1));
       f32x2 p = fma2(bc(-0.0012624911f), av, bc(0.0066700901f));
       p = fma2(p, av, bc(-0.0170881256f));
@@ -246,11 +248,9 @@ namespace earb {
       const f32x2 nq = fma2(pk(q0, q1), p, bc(-1.57079632679490f));
       float n0, n1;
       upk(nq, n0, n1);
-      // asin(|v|) carrying the inverted sign of the circle dot product (plain on the straight part)
-      const float t0 = __uint_as_float((__float_as_uint(n0) & 0x7fffffffu) |
-                                       (~__float_as_uint(s0 ? -0.0f : cd0) & 0x80000000u));
-      const float t1 = __uint_as_float((__float_as_uint(n1) & 0x7fffffffu) |
-                                       (~__float_as_uint(s1 ? -0.0f : cd1) & 0x80000000u));
+      // asin(|v|) carrying the inverted sign of v
+      const float t0 = __uint_as_float((__float_as_uint(n0) & 0x7fffffffu) | (~__float_as_uint(v0) & 0x80000000u));
+      const float t1 = __uint_as_float((__float_as_uint(n1) & 0x7fffffffu) | (~__float_as_uint(v1) & 0x80000000u));
       w0 = __saturatef(fmaf(c.m, t0, s0 ? c.c : c.a_sin));
       w1 = __saturatef(fmaf(c.m, t1, s1 ? c.c : c.a_sin));
     }
@@ -279,7 +279,14 @@ namespace earb {
 
       const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
       const int n_active = (int)*n_active_ptr;
-      const int n_tiles = (n_active + kMTiles * 128 - 1) / (kMTiles * 128);
+      // every CTA owns one contiguous range of passes, equal to within one warp (32 passes): the
+      // CTAs finish together whatever n_active is (whole 512-pass tiles dealt out round-robin left
+      // 2.6 tiles per CTA at the 131,072-object chunk of the batched path, i.e. 3 for most).  Only
+      // the last tile of a CTA is partial: its empty M-tiles are skipped, its empty warps only keep
+      // the barriers moving.
+      const int per_cta = (((n_active + (int)gridDim.x - 1) / (int)gridDim.x) + 31) & ~31;
+      const int p_begin = min(n_active, (int)blockIdx.x * per_cta), p_end = min(n_active, p_begin + per_cta);
+      const int n_tiles = (p_end - p_begin + kMTiles * 128 - 1) / (kMTiles * 128);
       const int n_chunks = Pp / kChunk, n_stages = Pp / kKC;
 
       for (int j = tid; j < Pp / 2; j += kThreads) {
@@ -316,7 +323,7 @@ namespace earb {
         // ------------------------------------------------------------ B producer
         if (lane == 0) {
           int g = 0;
-          for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
+          for (int tile = 0; tile < n_tiles; tile++)
             for (int s = 0; s < n_stages; s++, g++) {
               const int bs = g % kBStages;
               if (g >= kBStages) mbar_wait(&b_empty[bs], (uint32_t)(((g / kBStages) - 1) & 1));
@@ -337,7 +344,9 @@ namespace earb {
         const uint32_t idesc32 = idesc_base | ((uint32_t)(32 >> 3) << 17);
         const uint64_t bdesc0 = b_desc(smem_u32(sB));
         int gs = 0, gc = 0;  // B stage / chunk counters, continuous across tiles
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (int tile = 0; tile < n_tiles; tile++) {
+          // M-tiles of this tile that hold passes
+          const int n_mt = min(kMTiles, (p_end - (p_begin + tile * (kMTiles * 128)) + 127) / 128);
           for (int c = 0; c < n_chunks; c++, gc++) {
             const int sub = c % (kKC / kChunk);
             const int bs = gs % kBStages;
@@ -347,6 +356,7 @@ namespace earb {
             const uint64_t bd = bdesc0 + (uint64_t)((bs * kStageFloats * 4 + sub * (kChunk / 4) * 128) >> 4);
 #pragma unroll
             for (int mt = 0; mt < kMTiles; mt++) {
+              if (mt >= n_mt) break;
               mbar_wait(&a_full[mt][buf], (uint32_t)((gc >> 1) & 1));
               asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
               if (leader) {
@@ -377,9 +387,21 @@ namespace earb {
         const int mt = warp >> 2, q = warp & 3;
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
         int gc = 0, L = 0;
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, L++) {
-          const int idx = tile * (kMTiles * 128) + mt * 128 + q * 32 + lane;
-          const bool valid = idx < n_active;
+        for (int tile = 0; tile < n_tiles; tile++, L++) {
+          const int base = p_begin + tile * (kMTiles * 128) + mt * 128;
+          if (base >= p_end) break;  // an empty M-tile (last tile of the CTA only)
+          const int idx = base + q * 32 + lane;
+          const bool valid = idx < p_end;
+          if (base + q * 32 >= p_end) {
+            // no passes in this warp (last tile of the CTA only): keep a_full / a_free in step
+            for (int ch = 0; ch < n_chunks; ch++, gc++) {
+              const int buf = gc & 1;
+              if (gc >= 2) mbar_wait(&a_free[mt][buf], (uint32_t)(((gc >> 1) - 1) & 1));
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&a_full[mt][buf]);
+            }
+            break;
+          }
           const ExtentPass *pp = passes + (valid ? idx : n_active - 1);
           PassRegs c;
           int slot;
