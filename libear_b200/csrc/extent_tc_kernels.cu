@@ -153,7 +153,10 @@ namespace earb {
     // function is clamp(m * angle + c, 0, 1) -- one saturating FMA instead of two comparisons and
     // two selects (weights differ from the reference's by rounding at the fade ends only).
     // angle = acos(v) on the circle part, asin(|z'|) on the straight part, both from
-    // r = acos(|v|) = sqrt(1 - |v|) * P7(|v|) (Abramowitz & Stegun 4.4.46, |error| <= 2e-8):
+    // r = acos(|v|) = sqrt(u) * Q7(u), u = 1 - |v|: Abramowitz & Stegun 4.4.46 (|error| <= 2.2e-8)
+    // re-expanded in u, so that |v| is only ever an operand modifier of the subtraction -- a
+    // separate |.| is an ALU instruction, and those hold the dispatch port two cycles
+    // (tools/ubench_fp32x2.cu):
     // With q = pi/2 - r = asin(|v|) (folded into the last FMA) the three cases
     //   straight:        angle = q                         weight = sat(m q + c)
     //   circle:          angle = pi/2 - copysign(q, v)     weight = sat(m (-copysign(q, v)) + (m pi/2 + c))
@@ -167,17 +170,18 @@ namespace earb {
       const float circle_dot = fmaf(ax, c.cc0, __fmul_rn(yt, c.cc1));
       const bool is_sin = circle_test_dot >= c.sin_thr;
       const float v = is_sin ? zt : circle_dot;
-      const float av = fabsf(v);  // rounding can leave |v| a few ulp above 1: the square root's argument saturates
-      float p = -0.0012624911f;
-      p = fmaf(p, av, 0.0066700901f);
-      p = fmaf(p, av, -0.0170881256f);
-      p = fmaf(p, av, 0.0308918810f);
-      p = fmaf(p, av, -0.0501743046f);
-      p = fmaf(p, av, 0.0889789874f);
-      p = fmaf(p, av, -0.2145988016f);
-      p = fmaf(p, av, 1.5707963050f);
+      // rounding can leave |v| a few ulp above 1: u saturates
+      const float u = __saturatef(__fsub_rn(1.0f, fabsf(v)));
+      float p = 0.0012628264f;
+      p = fmaf(p, u, -0.0021685062f);
+      p = fmaf(p, u, 0.0035814755f);
+      p = fmaf(p, u, 0.0013143348f);
+      p = fmaf(p, u, 0.0082738195f);
+      p = fmaf(p, u, 0.0264650658f);
+      p = fmaf(p, u, 0.1178537458f);
+      p = fmaf(p, u, 1.4142135382f);
       float sq;
-      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(__saturatef(__fsub_rn(1.0f, av))));
+      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(u));
       const float q = fmaf(-sq, p, 1.57079632679490f);
       // q carrying the inverted sign bit of circle_dot
       const float qs = __uint_as_float(__float_as_uint(q) | (~__float_as_uint(circle_dot) & 0x80000000u));
@@ -222,28 +226,30 @@ namespace earb {
       const f32x2 xt = fma2(X, bc(c.b[0]), fma2(Y, bc(c.b[1]), mul2(Z, bc(c.b[2]))));
       const f32x2 yt = fma2(X, bc(c.b[3]), fma2(Y, bc(c.b[4]), mul2(Z, bc(c.b[5]))));
       const f32x2 zt = fma2(X, bc(c.b[6]), fma2(Y, bc(c.b[7]), mul2(Z, bc(c.b[8]))));
-      const f32x2 ax = abs2(xt);
-      const f32x2 ctd = fma2(ax, bc(c.ct0), mul2(yt, bc(c.ct1)));
-      const f32x2 cd = fma2(ax, bc(c.cc0), mul2(yt, bc(c.cc1)));
-      float ctd0, ctd1, cd0, cd1, z0, z1;
-      upk(ctd, ctd0, ctd1);
-      upk(cd, cd0, cd1);
+      // |x'| rides as an operand modifier of scalar FMAs (same operations as point_weight)
+      float x0, x1, ty0, ty1, tc0, tc1, z0, z1;
+      upk(xt, x0, x1);
+      upk(mul2(yt, bc(c.ct1)), ty0, ty1);
+      upk(mul2(yt, bc(c.cc1)), tc0, tc1);
       upk(zt, z0, z1);
+      const float ctd0 = fmaf(fabsf(x0), c.ct0, ty0), ctd1 = fmaf(fabsf(x1), c.ct0, ty1);
+      const float cd0 = fmaf(fabsf(x0), c.cc0, tc0), cd1 = fmaf(fabsf(x1), c.cc0, tc1);
       const bool s0 = ctd0 >= c.sin_thr, s1 = ctd1 >= c.sin_thr;
       // the straight part enters as -|z'|: with the inverted sign of v on q below, both parts are
       // weight = sat(m * (-copysign(q, v)) + k)
       const float v0 = s0 ? -fabsf(z0) : cd0, v1 = s1 ? -fabsf(z1) : cd1;
-      const f32x2 av = abs2(pk(v0, v1));
-      f32x2 p = fma2(bc(-0.0012624911f), av, bc(0.0066700901f));
-      p = fma2(p, av, bc(-0.0170881256f));
-      p = fma2(p, av, bc(0.0308918810f));
-      p = fma2(p, av, bc(-0.0501743046f));
-      p = fma2(p, av, bc(0.0889789874f));
-      p = fma2(p, av, bc(-0.2145988016f));
-      p = fma2(p, av, bc(1.5707963050f));
+      const float u0 = __saturatef(__fsub_rn(1.0f, fabsf(v0))), u1 = __saturatef(__fsub_rn(1.0f, fabsf(v1)));
+      const f32x2 U = pk(u0, u1);
+      f32x2 p = fma2(bc(0.0012628264f), U, bc(-0.0021685062f));
+      p = fma2(p, U, bc(0.0035814755f));
+      p = fma2(p, U, bc(0.0013143348f));
+      p = fma2(p, U, bc(0.0082738195f));
+      p = fma2(p, U, bc(0.0264650658f));
+      p = fma2(p, U, bc(0.1178537458f));
+      p = fma2(p, U, bc(1.4142135382f));
       float q0, q1;
-      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(q0) : "f"(__saturatef(__fsub_rn(1.0f, fabsf(v0)))));
-      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(q1) : "f"(__saturatef(__fsub_rn(1.0f, fabsf(v1)))));
+      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(q0) : "f"(u0));
+      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(q1) : "f"(u1));
       // nq = sq * p - pi/2 = -asin(|v|)
       const f32x2 nq = fma2(pk(q0, q1), p, bc(-1.57079632679490f));
       float n0, n1;
