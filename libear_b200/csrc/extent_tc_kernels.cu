@@ -254,9 +254,11 @@ namespace earb {
       const f32x2 nq = fma2(pk(q0, q1), p, bc(-1.57079632679490f));
       float n0, n1;
       upk(nq, n0, n1);
-      // asin(|v|) carrying the inverted sign of v
-      const float t0 = __uint_as_float((__float_as_uint(n0) & 0x7fffffffu) | (~__float_as_uint(v0) & 0x80000000u));
-      const float t1 = __uint_as_float((__float_as_uint(n1) & 0x7fffffffu) | (~__float_as_uint(v1) & 0x80000000u));
+      // asin(|v|) carrying the inverted sign of v: n = -asin(|v|) has its sign bit set, so one
+      // XOR with the sign of v does it (n can round to +1e-7 at |v| < 2^-25, where the sign of an
+      // angle of 1e-7 does not matter)
+      const float t0 = __uint_as_float(__float_as_uint(n0) ^ (__float_as_uint(v0) & 0x80000000u));
+      const float t1 = __uint_as_float(__float_as_uint(n1) ^ (__float_as_uint(v1) & 0x80000000u));
       w0 = __saturatef(fmaf(c.m, t0, s0 ? c.c : c.a_sin));
       w1 = __saturatef(fmaf(c.m, t1, s1 ? c.c : c.a_sin));
     }
