@@ -155,6 +155,11 @@ int earb200_objects_extent_host(earb200_objects *calc, int64_t n, const double *
                                 const double *depth, double *out);
 /* number of kernels this handle has launched so far (bench bookkeeping) */
 int64_t earb200_objects_launch_count(const earb200_objects *calc);
+/* self-test hook (no reference counterpart): the gain epilogue takes its FP64 square roots on a
+ * branch-free path that must equal sqrt() bit for bit; this runs that path over x[n] (host) on
+ * `device` and returns the number of elements that differ (arguments outside the fast range fall
+ * back to sqrt() in the product and are not counted). */
+int earb200_selftest_fast_sqrt(int device, int64_t n, const double *x, int64_t *n_mismatch);
 /* measurement hooks: with profiling on, every launch of the dominant kernel (the extent
  * core) is bracketed by CUDA events on the launching stream; _kernel_time synchronises,
  * returns the summed device time [ms] and launch count since the last query and the

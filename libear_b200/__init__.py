@@ -150,6 +150,15 @@ def convex_hull(xyz):
     return out
 
 
+def selftest_fast_sqrt(x, device=0):
+    """Number of elements of x where the gain epilogue's branch-free FP64 square root differs from
+    sqrt() (self-test hook of the C ABI; must be 0)."""
+    x = np.ascontiguousarray(x, dtype=np.float64).ravel()
+    n = C.c_int64(0)
+    _chk(_lib.earb200_selftest_fast_sqrt(int(device), C.c_int64(len(x)), _ptr(x), C.byref(n)))
+    return n.value
+
+
 def get_layout(name):
     return Layout(name)
 

@@ -502,6 +502,25 @@ int64_t earb200_objects_launch_count(const earb200_objects *calc) {
   return calc ? calc->launches : 0;
 }
 
+int earb200_selftest_fast_sqrt(int device, int64_t n, const double *x, int64_t *n_mismatch) {
+  return guarded([&] {
+    if (n < 0 || (n > 0 && !x) || !n_mismatch) throw Error(INVALID_ARGUMENT, "invalid argument");
+    use_device(device);
+    DeviceBuffer<double> d_x;
+    DeviceBuffer<unsigned long long> d_count;
+    double *dx = d_x.reserve((size_t)std::max<int64_t>(n, 1));
+    unsigned long long *dc = d_count.reserve(1);
+    EARB_CUDA(cudaMemsetAsync(dc, 0, sizeof(unsigned long long), 0));
+    if (n > 0) EARB_CUDA(cudaMemcpyAsync(dx, x, sizeof(double) * (size_t)n, cudaMemcpyHostToDevice, 0));
+    launch_selftest_fast_sqrt(dx, (long)n, dc, 0);
+    EARB_CUDA(cudaGetLastError());
+    unsigned long long h = 0;
+    EARB_CUDA(cudaMemcpyAsync(&h, dc, sizeof(h), cudaMemcpyDeviceToHost, 0));
+    EARB_CUDA(cudaStreamSynchronize(0));
+    *n_mismatch = (int64_t)h;
+  });
+}
+
 int earb200_objects_set_profiling(earb200_objects *calc, int enable) {
   return guarded([&] {
     if (!calc) throw Error(INVALID_ARGUMENT, "null argument");

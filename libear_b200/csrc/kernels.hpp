@@ -41,6 +41,8 @@ namespace earb {
                           const float *d_block_sums, const unsigned int *d_n_active,
                           const ExtentPass *d_passes, float *d_results,
                           unsigned long long *d_counter, int n_sms, cudaStream_t stream);
+  // self-test: counts the elements where the epilogue's branch-free square root differs from sqrt()
+  void launch_selftest_fast_sqrt(const double *d_x, long n, unsigned long long *d_n_mismatch, cudaStream_t stream);
   template <typename OutT>
   void launch_objects_epilogue(const PspTables *d_tables, long n, const ObjectsSoA &in,
                                const ExtentPass *d_passes, const ObjectAux *d_aux,

@@ -173,3 +173,18 @@ def test_empty_batch(eb):
     gc = eb.GainCalculatorObjects("0+5+0")
     d, f = gc.calculate(np.zeros(0), np.zeros(0))
     assert d.shape == (0, 6)
+
+
+def test_epilogue_square_root_is_ieee(eb):
+    # the epilogue's branch-free FP64 square root (fast path of the IEEE algorithm) against sqrt():
+    # bit-equal over the ranges the gains live in, over the whole fast range and at awkward values
+    rng = np.random.default_rng(77)
+    xs = [rng.uniform(0, 4, 2_000_000), rng.uniform(0, 1, 1_000_000) ** 8,
+          np.exp(rng.uniform(np.log(1e-290), np.log(1e300), 2_000_000)),
+          (rng.uniform(0, 1, 500_000).astype(np.float32) ** 2).astype(np.float64),
+          np.array([0.0, 1.0, 2.0, 4.0, 0.25, 1.0 - 2.0 ** -53, 1.0 + 2.0 ** -52, 2.0 - 2.0 ** -52, 1e-300, 1e-320,
+                    np.inf, np.nan, 3.0, 0.5])]
+    # perfect squares and their neighbours (halfway cases of the final rounding)
+    k = rng.integers(1, 2 ** 26, 500_000).astype(np.float64)
+    xs += [k * k, np.nextafter(k * k, 0), np.nextafter(k * k, np.inf)]
+    assert eb.selftest_fast_sqrt(np.concatenate(xs)) == 0
