@@ -83,6 +83,7 @@ struct earb200_objects {
     DeviceBuffer<ExtentPass> d_passes;
     DeviceBuffer<ObjectAux> d_aux;
     DeviceBuffer<float> d_results;
+    DeviceBuffer<double> d_point_gains;  // point source panner gains of the small-extent objects
     DeviceBuffer<unsigned int> d_n_active;
     cudaEvent_t ev_core = nullptr, ev_epi = nullptr;
   } scratch[2];
@@ -198,6 +199,7 @@ namespace {
       sc.d_passes.reserve(2 * earb200_objects::kChunk);
       sc.d_aux.reserve(earb200_objects::kChunk);
       sc.d_results.reserve(2 * earb200_objects::kChunk * EARB_MAX_SPK);
+      sc.d_point_gains.reserve(earb200_objects::kChunk * EARB_MAX_SPK);
       sc.d_n_active.reserve(1);
       EARB_CUDA(cudaEventCreateWithFlags(&sc.ev_core, cudaEventDisableTiming));
       EARB_CUDA(cudaEventCreateWithFlags(&sc.ev_epi, cudaEventDisableTiming));
@@ -259,11 +261,12 @@ namespace {
     if (o.timer.enabled) o.timed_passes += 2 * m;
     EARB_CUDA(cudaEventRecord(sc.ev_core, stream));
     EARB_CUDA(cudaStreamWaitEvent(o.s_epi, sc.ev_core, 0));
-    launch_objects_epilogue<OutT>(o.panner.d_tables, m, c, sc.d_passes.ptr, sc.d_aux.ptr, sc.d_results.ptr, n_out,
-                                  d_out_index, d_direct + start * n_out, d_diffuse + start * n_out,
+    launch_objects_epilogue<OutT>(o.panner.d_tables, o.grid.n_spk, m, c, sc.d_passes.ptr, sc.d_aux.ptr,
+                                  sc.d_results.ptr, sc.d_point_gains.ptr, n_out, d_out_index,
+                                  d_direct + start * n_out, d_diffuse + start * n_out,
                                   d_region ? d_region + start : nullptr, o.s_epi);
     EARB_CUDA(cudaEventRecord(sc.ev_epi, o.s_epi));
-    o.launches += 3;
+    o.launches += 4;
     return sc.ev_epi;
   }
 

@@ -43,12 +43,14 @@ namespace earb {
                           unsigned long long *d_counter, int n_sms, cudaStream_t stream);
   // self-test: counts the elements where the epilogue's branch-free square root differs from sqrt()
   void launch_selftest_fast_sqrt(const double *d_x, long n, unsigned long long *d_n_mismatch, cudaStream_t stream);
+  // two launches: the point source gains of the objects that need them (d_point_gains
+  // [n][EARB_MAX_SPK] scratch, and the region indices when d_region is given), then the gains
   template <typename OutT>
-  void launch_objects_epilogue(const PspTables *d_tables, long n, const ObjectsSoA &in,
+  void launch_objects_epilogue(const PspTables *d_tables, int n_real, long n, const ObjectsSoA &in,
                                const ExtentPass *d_passes, const ObjectAux *d_aux,
-                               const float *d_results, int n_out, const int32_t *d_out_index,
-                               OutT *d_direct, OutT *d_diffuse, int32_t *d_region,
-                               cudaStream_t stream);
+                               const float *d_results, double *d_point_gains, int n_out,
+                               const int32_t *d_out_index, OutT *d_direct, OutT *d_diffuse,
+                               int32_t *d_region, cudaStream_t stream);
 
   // ---- K3: interpolated mixing (render_kernels.cu)
 #define RENDER_THREADS 128
