@@ -76,7 +76,21 @@ struct earb200_objects {
   DeviceBuffer<unsigned int> d_n_active;
   int use_tc = 1;  // EARB200_EXTENT_PATH=cuda selects the FFMA warp-per-pass core
   // per-chunk scratch
-  static constexpr int64_t kChunk = 131072;
+  // Scratch capacity in objects.  A call is cut into chunks sized so that every CTA of the extent
+  // core gets whole rounds of 512 passes (its time goes with the number of rounds, not with how
+  // full the last one is): chunk = rounds * 512 * SMs / (passes per object), see pick_chunk.
+  // EARB200_OBJECTS_CHUNK fixes the chunk size instead (tuning).
+  static const int64_t kChunk;
+  static const int64_t kChunkFixed;
+  // passes per object: sampled from the depth column on the host path, fed back from the
+  // previous call's pass counts on the device path (2 = every object has depth: never too small)
+  double passes_per_object = 2.0;
+  static constexpr int kFeedbackSlots = 64;
+  unsigned int *h_active = nullptr;  // pinned: n_active of the chunks of the last device call
+  int64_t fb_objects[kFeedbackSlots] = {};
+  int fb_count = 0;
+  bool fb_pending = false;
+  cudaEvent_t ev_fb = nullptr;
   // two scratch sets: the FP64 epilogue of chunk k runs on a side stream while the extent core of
   // chunk k + 1 (a different pipe mix: FP32 issue + tensor) already occupies the SMs
   struct Scratch {
@@ -107,12 +121,20 @@ struct earb200_objects {
       if (sc.ev_core) cudaEventDestroy(sc.ev_core);
       if (sc.ev_epi) cudaEventDestroy(sc.ev_epi);
     }
+    if (ev_fb) cudaEventDestroy(ev_fb);
+    if (h_active) cudaFreeHost(h_active);
     if (s_epi) cudaStreamDestroy(s_epi);
     if (s_in) cudaStreamDestroy(s_in);
     if (s_compute) cudaStreamDestroy(s_compute);
     if (s_out) cudaStreamDestroy(s_out);
   }
 };
+const int64_t earb200_objects::kChunk = 262144;
+const int64_t earb200_objects::kChunkFixed = [] {
+  const char *e = std::getenv("EARB200_OBJECTS_CHUNK");
+  const long long v = e ? std::atoll(e) : 0;
+  return (int64_t)(v >= 1024 && v <= earb200_objects::kChunk ? v : 0);
+}();
 
 namespace {
   void objects_init(earb200_objects &o, const HostLayout &layout, int device) {
@@ -204,6 +226,8 @@ namespace {
       EARB_CUDA(cudaEventCreateWithFlags(&sc.ev_core, cudaEventDisableTiming));
       EARB_CUDA(cudaEventCreateWithFlags(&sc.ev_epi, cudaEventDisableTiming));
     }
+    EARB_CUDA(cudaEventCreateWithFlags(&o.ev_fb, cudaEventDisableTiming));
+    EARB_CUDA(cudaHostAlloc((void **)&o.h_active, sizeof(unsigned int) * earb200_objects::kFeedbackSlots, cudaHostAllocDefault));
     EARB_CUDA(cudaStreamCreateWithFlags(&o.s_epi, cudaStreamNonBlocking));
     o.d_counter.reserve(1);
   }
@@ -226,12 +250,24 @@ namespace {
     }
   }
 
+  // Objects per chunk for `rounds` whole rounds of 512 passes per CTA of the extent core (0: as
+  // many as the scratch holds), with 2.5 % of slack: one pass too many costs a whole round.
+  int64_t pick_chunk(const earb200_objects &o, double passes_per_object, int rounds) {
+    if (earb200_objects::kChunkFixed) return earb200_objects::kChunkFixed;
+    const double ppo = std::min(2.0, std::max(0.05, passes_per_object));
+    const double per_round = 0.975 * 512.0 * (double)o.n_sms / ppo;
+    if (rounds <= 0) rounds = std::max(1, (int)((double)earb200_objects::kChunk / per_round));
+    int64_t chunk = (int64_t)(per_round * rounds);
+    chunk = std::min<int64_t>(earb200_objects::kChunk, std::max<int64_t>(8192, chunk / 128 * 128));
+    return chunk;
+  }
+
   // one chunk (<= kChunk objects starting at `start`): prelude -> extent core on `stream`, the
   // epilogue on the side stream.  Returns the event that marks the chunk's outputs complete.
   template <typename OutT>
   cudaEvent_t objects_run_chunk(earb200_objects &o, int64_t start, int64_t m, const ObjectsSoA &in, int n_out,
                                 const int32_t *d_out_index, OutT *d_direct, OutT *d_diffuse, int32_t *d_region,
-                                cudaStream_t stream) {
+                                cudaStream_t stream, int fb_slot = -1) {
     ObjectsSoA c = in;
     if (c.xyz) {
       c.xyz += 3 * start;
@@ -250,6 +286,12 @@ namespace {
     EARB_CUDA(cudaStreamWaitEvent(stream, sc.ev_epi, 0));
     EARB_CUDA(cudaMemsetAsync(sc.d_n_active.ptr, 0, sizeof(unsigned int), stream));
     launch_objects_prelude(m, c, sc.d_passes.ptr, sc.d_aux.ptr, sc.d_n_active.ptr, stream);
+    if (fb_slot >= 0 && fb_slot < earb200_objects::kFeedbackSlots) {
+      EARB_CUDA(cudaMemcpyAsync(o.h_active + fb_slot, sc.d_n_active.ptr, sizeof(unsigned int), cudaMemcpyDeviceToHost,
+                                stream));
+      o.fb_objects[fb_slot] = m;
+      o.fb_count = fb_slot + 1;
+    }
     o.timer.start(stream);
     if (o.use_tc)
       launch_extent_core_tc(o.grid, o.d_grid_points.ptr, o.d_grid_bimage.ptr, sc.d_n_active.ptr, sc.d_passes.ptr,
@@ -279,9 +321,27 @@ namespace {
   void objects_run(earb200_objects &o, int64_t n, const ObjectsSoA &in, int n_out,
                    const int32_t *d_out_index, OutT *d_direct, OutT *d_diffuse,
                    int32_t *d_region, cudaStream_t stream) {
-    for (int64_t start = 0; start < n; start += earb200_objects::kChunk)
-      objects_run_chunk<OutT>(o, start, std::min<int64_t>(earb200_objects::kChunk, n - start), in, n_out,
-                              d_out_index, d_direct, d_diffuse, d_region, stream);
+    // passes per object as the previous call measured them (if its counters have arrived)
+    if (o.fb_pending && cudaEventQuery(o.ev_fb) == cudaSuccess) {
+      double active = 0.0, objects = 0.0;
+      for (int k = 0; k < o.fb_count; k++) {
+        active += o.h_active[k];
+        objects += (double)o.fb_objects[k];
+      }
+      if (objects > 0) o.passes_per_object = active / objects;
+      o.fb_pending = false;
+    }
+    const int64_t chunk = pick_chunk(o, o.passes_per_object, 0);
+    const bool feed = !o.fb_pending && n > chunk;  // a call of one chunk has nothing to size
+    if (feed) o.fb_count = 0;
+    int slot = 0;
+    for (int64_t start = 0; start < n; start += chunk, slot++)
+      objects_run_chunk<OutT>(o, start, std::min<int64_t>(chunk, n - start), in, n_out, d_out_index, d_direct,
+                              d_diffuse, d_region, stream, feed ? slot : -1);
+    if (feed && o.fb_count > 0) {
+      EARB_CUDA(cudaEventRecord(o.ev_fb, stream));
+      o.fb_pending = true;
+    }
     objects_join(o, stream);
     EARB_CUDA(cudaGetLastError());
   }
@@ -297,7 +357,16 @@ namespace {
       EARB_CUDA(cudaStreamCreateWithFlags(&o.s_compute, cudaStreamNonBlocking));
       EARB_CUDA(cudaStreamCreateWithFlags(&o.s_out, cudaStreamNonBlocking));
     }
-    const int64_t n_chunks = (n + earb200_objects::kChunk - 1) / earb200_objects::kChunk;
+    // passes per object from a strided sample of the depth column (depth != 0: two passes)
+    {
+      const int64_t samples = std::min<int64_t>(n, 4096), stride = std::max<int64_t>(1, n / samples);
+      int64_t deep = 0;
+      for (int64_t k = 0; k < samples; k++) deep += src[5][k * stride] != 0.0;
+      o.passes_per_object = 1.0 + (double)deep / (double)samples;
+    }
+    // two rounds per chunk: small enough for the copies of neighbouring chunks to hide behind it
+    const int64_t chunk = pick_chunk(o, o.passes_per_object, 2);
+    const int64_t n_chunks = (n + chunk - 1) / chunk;
     while ((int64_t)o.ev_in.size() < n_chunks) {
       cudaEvent_t a, b;
       EARB_CUDA(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
@@ -313,8 +382,8 @@ namespace {
                                                               : (void *)o.d_out_f.reserve(2 * n_el));
     OutT *d_direct = d_out, *d_diffuse = d_out + n_el;
     for (int64_t k = 0; k < n_chunks; k++) {
-      const int64_t start = k * earb200_objects::kChunk;
-      const int64_t m = std::min<int64_t>(earb200_objects::kChunk, n - start);
+      const int64_t start = k * chunk;
+      const int64_t m = std::min<int64_t>(chunk, n - start);
       for (int f = 0; f < 8; f++)
         EARB_CUDA(cudaMemcpyAsync(d + (size_t)f * n + start, src[f] + start, sizeof(double) * m,
                                   cudaMemcpyHostToDevice, o.s_in));
