@@ -721,7 +721,7 @@ def run_ours(args):
                        "l2": "inputs+outputs 256 MB/step/GPU > 126 MB L2", "sharding": "objects, no collective"},
             "roofline": {"bound": "tensor", "achieved": core_tflops, "peak": bf16_peak, "unit": "TFLOP/s",
                          "frac": core_tflops / bf16_peak,
-                         "traffic": ncu_traffic("extent_core_tc_kernel") if n >= 131072 else None,
+                         "traffic": ncu_traffic("extent_core_tc_kernel") if n >= 262144 else None,
                          "peak_source": peak_src,
                          "kernel": "extent_core_tc_kernel", "kernel_ms": core_ms / max(1, core_launches),
                          "algorithmic_flop_per_pass": FLOP_PER_PASS,
