@@ -285,7 +285,7 @@ namespace {
     // the epilogue of the chunk that used this scratch set two chunks ago must have read it
     EARB_CUDA(cudaStreamWaitEvent(stream, sc.ev_epi, 0));
     EARB_CUDA(cudaMemsetAsync(sc.d_n_active.ptr, 0, sizeof(unsigned int), stream));
-    launch_objects_prelude(m, c, sc.d_passes.ptr, sc.d_aux.ptr, sc.d_n_active.ptr, stream);
+    launch_objects_prelude(m, c, sc.d_passes.ptr, sc.d_aux.ptr, sc.d_n_active.ptr, !o.use_tc, stream);
     if (fb_slot >= 0 && fb_slot < earb200_objects::kFeedbackSlots) {
       EARB_CUDA(cudaMemcpyAsync(o.h_active + fb_slot, sc.d_n_active.ptr, sizeof(unsigned int), cudaMemcpyDeviceToHost,
                                 stream));

@@ -25,8 +25,9 @@ namespace earb {
                         double *d_gains, int32_t *d_region, int32_t *d_inner,
                         cudaStream_t stream);
   // writes the active passes compacted to d_passes[0 .. *d_n_active) (d_n_active must be zero)
-  void launch_objects_prelude(long n, const ObjectsSoA &in, ExtentPass *d_passes,
-                              ObjectAux *d_aux, unsigned int *d_n_active, cudaStream_t stream);
+  // (thresholds: also the fade's start / end cos and sin, which only the FFMA core reads)
+  void launch_objects_prelude(long n, const ObjectsSoA &in, ExtentPass *d_passes, ObjectAux *d_aux,
+                              unsigned int *d_n_active, bool thresholds, cudaStream_t stream);
   size_t extent_core_smem_bytes(const ExtentGrid &grid);
 #define EXTENT_TC_STAGE_POINTS 64
   // tcgen05 extent core (extent_tc_kernels.cu): thread-per-pass weights feeding 3xTF32 UMMAs
