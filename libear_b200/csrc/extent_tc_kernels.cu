@@ -296,6 +296,7 @@ namespace earb {
       const int p_begin = min(n_active, (int)blockIdx.x * per_cta), p_end = min(n_active, p_begin + per_cta);
       const int n_tiles = (p_end - p_begin + kMTiles * 128 - 1) / (kMTiles * 128);
       const int n_chunks = Pp / kChunk, n_stages = Pp / kKC;
+      if (n_tiles == 0) return;  // no passes for this CTA (small batches): nothing to set up
 
       for (int j = tid; j < Pp / 2; j += kThreads) {
         const float4 a = g_points[2 * j], b = g_points[2 * j + 1];
