@@ -73,6 +73,15 @@ int earb200_layout_create_custom(const char *name, int n_channels,
  * facets is a flat list, each facet = vertex count followed by its sorted vertex indices. */
 int earb200_convex_hull(int n_points, const double *xyz, int32_t *facets, int capacity,
                         int *n_written);
+/* the clustering of the extent panner's virtual sources into cells of 16 that the extent core
+ * culls by (K2; the reference's per-batch all-ones / all-zeros shortcut,
+ * src/object_based/polar_extent_simd.hpp:111-126, decided per cell), exposed for inspection (host,
+ * setup-time): grid = the reference's generatePanningPositionsEven(n_rows)
+ * (polar_extent.cpp:15-39).  order [n_cells][16]: grid point of every slot (-1: padding),
+ * centre [n_cells][3] and radius [n_cells] (radians): the bounding cap of each cell.  Buffers sized
+ * for `capacity` cells; *n_cells_out / *n_points_out receive the counts. */
+int earb200_extent_cells(int n_rows, int capacity, int32_t *order, float *centre, double *radius,
+                         double *grid_xyz, int *n_cells_out, int *n_points_out);
 void earb200_layout_destroy(earb200_layout *layout);
 int earb200_layout_num_channels(const earb200_layout *layout);
 const char *earb200_layout_channel_name(const earb200_layout *layout, int i);

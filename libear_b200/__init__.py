@@ -150,6 +150,20 @@ def convex_hull(xyz):
     return out
 
 
+def extent_cells(n_rows=37):
+    """The extent core's clustering of the virtual-source grid into cells of 16 (host, setup-time):
+    (grid_xyz [P][3], order [n_cells][16], centre [n_cells][3], radius [n_cells] in radians)."""
+    cap = 1024
+    order = np.full((cap, 16), -1, dtype=np.int32)
+    centre = np.zeros((cap, 3), dtype=np.float32)
+    radius = np.zeros(cap)
+    grid = np.zeros((cap * 16, 3))
+    nc, npts = C.c_int(0), C.c_int(0)
+    _chk(_lib.earb200_extent_cells(int(n_rows), cap, _ptr(order), _ptr(centre), _ptr(radius), _ptr(grid),
+                                   C.byref(nc), C.byref(npts)))
+    return grid[:npts.value], order[:nc.value], centre[:nc.value], radius[:nc.value]
+
+
 def selftest_fast_sqrt(x, device=0):
     """Number of elements of x where the gain epilogue's branch-free FP64 square root differs from
     sqrt() (self-test hook of the C ABI; must be 0)."""

@@ -75,6 +75,12 @@ struct earb200_objects {
   DeviceBuffer<float> d_grid_bimage;
   DeviceBuffer<unsigned int> d_n_active;
   int use_tc = 1;  // EARB200_EXTENT_PATH=cuda selects the FFMA warp-per-pass core
+  // cell-culled tcgen05 extent core: per-cell stream [fp16 gain image | point coordinates],
+  // cell centres + class thresholds
+  DeviceBuffer<unsigned char> d_cell_stream;
+  DeviceBuffer<float> d_cell_centres;
+  int n_cells = 0;
+  int use_cells = 1;  // EARB200_EXTENT_PATH=tf32 selects the first-generation tcgen05 core
   // per-chunk scratch
   // Scratch capacity in objects.  A call is cut into chunks sized so that every CTA of the extent
   // core gets whole rounds of 512 passes (its time goes with the number of rounds, not with how
@@ -216,6 +222,19 @@ namespace {
                            cudaMemcpyHostToDevice));
       const char *path = std::getenv("EARB200_EXTENT_PATH");
       o.use_tc = !(path && std::string(path) == "cuda");
+      o.use_cells = o.use_tc && !(path && std::string(path) == "tf32");
+      ExtentCells cells;
+      extent_cells_build(P, fxyz.data(), Pp, cells);
+      o.n_cells = cells.n_cells;
+      if (extent_cell_smem_bytes(o.n_cells) > 227 * 1024)
+        throw Error(INTERNAL_ERROR, "extent cell tables do not fit in shared memory");
+      std::vector<unsigned char> cs(extent_cell_stream_bytes(cells));
+      extent_cell_build_stream(cells, o.S, Pp, fxyz.data(), fg.data(), cs.data());
+      EARB_CUDA(cudaMemcpy(o.d_cell_stream.reserve(cs.size()), cs.data(), cs.size(), cudaMemcpyHostToDevice));
+      std::vector<float> cc(extent_cell_centre_floats(cells));
+      extent_cell_build_centres(cells, cc.data());
+      EARB_CUDA(cudaMemcpy(o.d_cell_centres.reserve(cc.size()), cc.data(), sizeof(float) * cc.size(),
+                           cudaMemcpyHostToDevice));
     }
     for (earb200_objects::Scratch &sc : o.scratch) {
       sc.d_passes.reserve(2 * earb200_objects::kChunk);
@@ -293,7 +312,10 @@ namespace {
       o.fb_count = fb_slot + 1;
     }
     o.timer.start(stream);
-    if (o.use_tc)
+    if (o.use_cells)
+      launch_extent_cell(o.n_cells, o.grid.n_spk, o.d_cell_stream.ptr, o.d_cell_centres.ptr, sc.d_n_active.ptr,
+                         sc.d_passes.ptr, sc.d_results.ptr, o.n_sms, stream);
+    else if (o.use_tc)
       launch_extent_core_tc(o.grid, o.d_grid_points.ptr, o.d_grid_bimage.ptr, sc.d_n_active.ptr, sc.d_passes.ptr,
                             sc.d_results.ptr, o.n_sms, stream);
     else
@@ -475,6 +497,41 @@ int earb200_convex_hull(int n_points, const double *xyz, int32_t *facets, int ca
       for (int v : f) facets[k++] = v;
     }
     *n_written = k;
+  });
+}
+int earb200_extent_cells(int n_rows, int capacity, int32_t *order, float *centre, double *radius,
+                         double *grid_xyz, int *n_cells_out, int *n_points_out) {
+  return guarded([&] {
+    if (!n_cells_out || !n_points_out) throw Error(INVALID_ARGUMENT, "null argument");
+    if (n_rows < 2) throw Error(INVALID_ARGUMENT, "the grid needs at least two rows");
+    std::vector<Vec3> pts = extentGridPositions(n_rows);
+    const int P = (int)pts.size();
+    const int Pp = (P + EXTENT_TC_STAGE_POINTS - 1) / EXTENT_TC_STAGE_POINTS * EXTENT_TC_STAGE_POINTS;
+    std::vector<float> fxyz(3 * (size_t)Pp, 0.0f);
+    for (int p = 0; p < P; p++) {
+      fxyz[p] = (float)pts[p].x;
+      fxyz[Pp + p] = (float)pts[p].y;
+      fxyz[2 * Pp + p] = (float)pts[p].z;
+    }
+    ExtentCells cells;
+    extent_cells_build(P, fxyz.data(), Pp, cells);
+    *n_cells_out = cells.n_cells;
+    *n_points_out = P;
+    if (cells.n_cells > capacity) throw Error(INVALID_ARGUMENT, "cell buffers too small");
+    for (int c = 0; c < cells.n_cells; c++) {
+      if (order)
+        for (int i = 0; i < EXTENT_CELL_POINTS; i++)
+          order[c * EXTENT_CELL_POINTS + i] = cells.order[(size_t)c * EXTENT_CELL_POINTS + i];
+      if (centre)
+        for (int i = 0; i < 3; i++) centre[3 * c + i] = cells.centre[3 * (size_t)c + i];
+      if (radius) radius[c] = cells.radius[c];
+    }
+    if (grid_xyz)
+      for (int p = 0; p < P; p++) {
+        grid_xyz[3 * p] = pts[p].x;
+        grid_xyz[3 * p + 1] = pts[p].y;
+        grid_xyz[3 * p + 2] = pts[p].z;
+      }
   });
 }
 void earb200_layout_destroy(earb200_layout *layout) { delete layout; }

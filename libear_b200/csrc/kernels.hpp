@@ -3,6 +3,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <vector>
+
 #include "tables.h"
 
 #define EARB_CORE_THREADS 1024
@@ -37,6 +39,27 @@ namespace earb {
   void launch_extent_core_tc(const ExtentGrid &grid, const float4 *d_points, const float *d_bimage,
                              const unsigned int *d_n_active, const ExtentPass *d_passes,
                              float *d_results, int n_sms, cudaStream_t stream);
+  // cell-culled tcgen05 extent core (extent_cell_kernels.cu): the virtual sources clustered into
+  // compact cells of 16, uniform (pass, cell) pairs decided from the cell centre, the rest
+  // evaluated in batches; fp16 hi/lo UMMAs with the weights staged in shared memory
+#define EXTENT_CELL_POINTS 16
+  struct ExtentCells {
+    int n_cells = 0;
+    std::vector<int> order;      // [n_cells][16] grid point of every slot, -1: padding
+    std::vector<float> centre;   // [n_cells][3] bounding-cap centre as the kernel sees it
+    std::vector<double> radius;  // [n_cells] bounding-cap radius, radians
+  };
+  // xyz: [3][n_points_pad] float (the grid as the reference's float core sees it)
+  void extent_cells_build(int n_points, const float *xyz, int n_points_pad, ExtentCells &out);
+  size_t extent_cell_stream_bytes(const ExtentCells &cells);
+  size_t extent_cell_centre_floats(const ExtentCells &cells);
+  void extent_cell_build_stream(const ExtentCells &cells, int n_spk, int n_points_pad, const float *xyz,
+                                const float *gains, unsigned char *stream);
+  void extent_cell_build_centres(const ExtentCells &cells, float *out);
+  size_t extent_cell_smem_bytes(int n_cells);
+  void launch_extent_cell(int n_cells, int n_spk, const unsigned char *d_stream, const float *d_centres,
+                          const unsigned int *d_n_active, const ExtentPass *d_passes, float *d_results,
+                          int n_sms, cudaStream_t stream);
   // FFMA extent core (objects_kernels.cu), warp per pass
   void launch_extent_core(const ExtentGrid &grid, const float *d_xyz, const float *d_gains,
                           const float *d_block_sums, const unsigned int *d_n_active,
