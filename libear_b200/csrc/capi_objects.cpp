@@ -77,8 +77,8 @@ struct earb200_objects {
   int use_tc = 1;  // EARB200_EXTENT_PATH=cuda selects the FFMA warp-per-pass core
   // cell-culled tcgen05 extent core: per-cell stream [fp16 gain image | point coordinates],
   // cell centres + class thresholds
-  DeviceBuffer<unsigned char> d_cell_stream;
-  DeviceBuffer<float> d_cell_centres;
+  DeviceBuffer<unsigned char> d_cell_stream, d_cell_sums;
+  DeviceBuffer<float> d_cell_centres, d_cell_points;
   int n_cells = 0;
   int use_cells = 1;  // EARB200_EXTENT_PATH=tf32 selects the first-generation tcgen05 core
   // per-chunk scratch
@@ -104,7 +104,8 @@ struct earb200_objects {
     DeviceBuffer<ObjectAux> d_aux;
     DeviceBuffer<float> d_results;
     DeviceBuffer<double> d_point_gains;  // point source panner gains of the small-extent objects
-    DeviceBuffer<unsigned int> d_n_active;
+    DeviceBuffer<int32_t> d_point_list;  // the objects that need them, compacted by the prelude
+    DeviceBuffer<unsigned int> d_n_active;  // [0] active passes, [1] length of d_point_list
     cudaEvent_t ev_core = nullptr, ev_epi = nullptr;
   } scratch[2];
   cudaStream_t s_epi = nullptr;
@@ -226,14 +227,19 @@ namespace {
       ExtentCells cells;
       extent_cells_build(P, fxyz.data(), Pp, cells);
       o.n_cells = cells.n_cells;
-      if (extent_cell_smem_bytes(o.n_cells) > 227 * 1024)
-        throw Error(INTERNAL_ERROR, "extent cell tables do not fit in shared memory");
-      std::vector<unsigned char> cs(extent_cell_stream_bytes(cells));
-      extent_cell_build_stream(cells, o.S, Pp, fxyz.data(), fg.data(), cs.data());
+      if (!extent_cell_supported(cells))
+        throw Error(INTERNAL_ERROR, "extent cell tables do not fit the extent core");
+      std::vector<unsigned char> cs(extent_cell_stream_bytes(cells)), sums(extent_cell_sum_bytes(cells));
+      extent_cell_build_stream(cells, o.S, Pp, fg.data(), cs.data());
+      extent_cell_build_sums(cells, o.S, Pp, fg.data(), sums.data());
       EARB_CUDA(cudaMemcpy(o.d_cell_stream.reserve(cs.size()), cs.data(), cs.size(), cudaMemcpyHostToDevice));
-      std::vector<float> cc(extent_cell_centre_floats(cells));
+      EARB_CUDA(cudaMemcpy(o.d_cell_sums.reserve(sums.size()), sums.data(), sums.size(), cudaMemcpyHostToDevice));
+      std::vector<float> cc(extent_cell_centre_floats(cells)), cpnt(extent_cell_point_floats(cells));
       extent_cell_build_centres(cells, cc.data());
+      extent_cell_build_points(cells, Pp, fxyz.data(), cpnt.data());
       EARB_CUDA(cudaMemcpy(o.d_cell_centres.reserve(cc.size()), cc.data(), sizeof(float) * cc.size(),
+                           cudaMemcpyHostToDevice));
+      EARB_CUDA(cudaMemcpy(o.d_cell_points.reserve(cpnt.size()), cpnt.data(), sizeof(float) * cpnt.size(),
                            cudaMemcpyHostToDevice));
     }
     for (earb200_objects::Scratch &sc : o.scratch) {
@@ -241,7 +247,8 @@ namespace {
       sc.d_aux.reserve(earb200_objects::kChunk);
       sc.d_results.reserve(2 * earb200_objects::kChunk * EARB_MAX_SPK);
       sc.d_point_gains.reserve(earb200_objects::kChunk * EARB_MAX_SPK);
-      sc.d_n_active.reserve(1);
+      sc.d_point_list.reserve(earb200_objects::kChunk);
+      sc.d_n_active.reserve(2);
       EARB_CUDA(cudaEventCreateWithFlags(&sc.ev_core, cudaEventDisableTiming));
       EARB_CUDA(cudaEventCreateWithFlags(&sc.ev_epi, cudaEventDisableTiming));
     }
@@ -303,8 +310,9 @@ namespace {
     earb200_objects::Scratch &sc = o.scratch[o.chunk_counter++ & 1];
     // the epilogue of the chunk that used this scratch set two chunks ago must have read it
     EARB_CUDA(cudaStreamWaitEvent(stream, sc.ev_epi, 0));
-    EARB_CUDA(cudaMemsetAsync(sc.d_n_active.ptr, 0, sizeof(unsigned int), stream));
-    launch_objects_prelude(m, c, sc.d_passes.ptr, sc.d_aux.ptr, sc.d_n_active.ptr, !o.use_tc, stream);
+    EARB_CUDA(cudaMemsetAsync(sc.d_n_active.ptr, 0, 2 * sizeof(unsigned int), stream));
+    launch_objects_prelude(m, c, sc.d_passes.ptr, sc.d_aux.ptr, sc.d_n_active.ptr, sc.d_point_list.ptr,
+                           d_region != nullptr, !o.use_tc, stream);
     if (fb_slot >= 0 && fb_slot < earb200_objects::kFeedbackSlots) {
       EARB_CUDA(cudaMemcpyAsync(o.h_active + fb_slot, sc.d_n_active.ptr, sizeof(unsigned int), cudaMemcpyDeviceToHost,
                                 stream));
@@ -313,8 +321,9 @@ namespace {
     }
     o.timer.start(stream);
     if (o.use_cells)
-      launch_extent_cell(o.n_cells, o.grid.n_spk, o.d_cell_stream.ptr, o.d_cell_centres.ptr, sc.d_n_active.ptr,
-                         sc.d_passes.ptr, sc.d_results.ptr, o.n_sms, stream);
+      launch_extent_cell(o.n_cells, o.grid.n_spk, o.d_cell_stream.ptr, o.d_cell_sums.ptr, o.d_cell_centres.ptr,
+                         o.d_cell_points.ptr, sc.d_n_active.ptr, sc.d_passes.ptr, sc.d_results.ptr, o.n_sms,
+                         stream);
     else if (o.use_tc)
       launch_extent_core_tc(o.grid, o.d_grid_points.ptr, o.d_grid_bimage.ptr, sc.d_n_active.ptr, sc.d_passes.ptr,
                             sc.d_results.ptr, o.n_sms, stream);
@@ -326,7 +335,8 @@ namespace {
     EARB_CUDA(cudaEventRecord(sc.ev_core, stream));
     EARB_CUDA(cudaStreamWaitEvent(o.s_epi, sc.ev_core, 0));
     launch_objects_epilogue<OutT>(o.panner.d_tables, o.grid.n_spk, m, c, sc.d_passes.ptr, sc.d_aux.ptr,
-                                  sc.d_results.ptr, sc.d_point_gains.ptr, n_out, d_out_index,
+                                  sc.d_results.ptr, sc.d_point_gains.ptr, sc.d_n_active.ptr, sc.d_point_list.ptr,
+                                  o.n_sms, n_out, d_out_index,
                                   d_direct + start * n_out, d_diffuse + start * n_out,
                                   d_region ? d_region + start : nullptr, o.s_epi);
     EARB_CUDA(cudaEventRecord(sc.ev_epi, o.s_epi));

@@ -12,31 +12,39 @@
 // host) into compact CELLS of 16 with a bounding cap (centre, radius r): if the weight function
 // evaluated at the centre is >= 1 + |m| r every weight of the cell is exactly 1, if it is
 // <= -|m| r every weight is exactly 0 -- the reference's own all-ones / all-zeros block shortcut
-// (polar_extent_simd.hpp:111-126), decided from one evaluation instead of sixteen.  On random
-// metadata three quarters of all (pass, cell) pairs are uniform (tools/exp_cells.py).
+// (polar_extent_simd.hpp:111-126, with its pre-summed gains of a block), decided from one
+// evaluation instead of sixteen.  On random metadata three quarters of all (pass, cell) pairs are
+// uniform (tools/exp_cells.py), and only the MIXED quarter is evaluated point by point.
 //
 // One persistent CTA per SM walks its passes in tiles of 512 (four M = 128 UMMA tiles):
-//   warps 0..15  phase 1  thread = pass: pass constants -> shared memory, the weight function at
-//                         the 104 cell centres -> per-cell bit masks (mixed / all-ones) by ballot.
-//                phase 2  "evaluators": a batch = 32 (pass, cell) items of ONE cell whose class is
-//                         mixed (lane = pass, taken from the cell's list); 16 weights per lane,
-//                         split into fp16 hi + lo and stored into the A stage of the cell in
-//                         shared memory (UMMA canonical K-major layout).
-//                epilogue thread = pass: tcgen05.ld of the accumulator row, normalise, store.
-//   warps 16,17  fillers  per cell: write the rows of the uniform passes (0 or 1) into the A
-//                         stage and the list of mixed passes for the evaluators.
-//   warp  18     MMA      per cell and M-tile: [main | corr] (+)= A_hi * [G_hi | G_lo]  (N = 48)
-//                                              corr          +=  A_lo * G_hi           (N = 32)
-//   warp  19     producer streams [gain image | point coordinates] per cell through a ring
-//                         (cp.async.bulk); evaluators read the coordinates from the same stage.
+//   warps 0..15  phase 1   thread = pass: pass constants -> shared memory; the weight function at
+//                          the cell centres -> class of every (pass, cell): mixed -> bit masks by
+//                          ballot; all-ones -> an fp16 0/1 INDICATOR row written to TMEM.
+//                phase 1.5 per-cell counts and prefix sums; the lists of mixed passes of every
+//                          cell, compacted into one pool (in rounds of cells if it overflows).
+//                phase 2   "evaluators": a batch = 32 mixed (pass, cell) items of ONE cell, lane =
+//                          pass; 16 weights per lane, split into fp16 hi + lo and stored into the
+//                          A stage of the cell in shared memory (UMMA K-major layout).  Batches are
+//                          dealt round-robin; a warp only touches the barriers of its own batches
+//                          and runs ahead of the tensor pipe by the depth of the A ring.
+//                epilogue  thread = pass: tcgen05.ld of the accumulator row, normalise, store.
+//   warps 16..18 cleaners  one per A stage; after the UMMAs of a cell: zeroes the rows its batches
+//                          wrote (an A stage is all zeros except the mixed rows) and arms the stage
+//                          for its next cell.
+//   warp  19     MMA       per tile:  acc  = indicator[passes x cells] * Gsum[cells x S]  (fp16 hi +
+//                                     mid + lo of the per-cell gain sums: the all-ones cells)
+//                          per cell:  [main | corr] += A_hi * [G_hi | G_lo]   (N = 48)
+//                                     corr          += A_lo * G_hi            (N = 32)
+//   warp  20     producer  streams the per-cell gain image through a ring (cp.async.bulk).
 // fp16 hi + lo carries 22 bits of the weight and of the gain (|error| <= 6e-8 absolute; weights
-// and gains lie in [0, 1]); the three products accumulate in fp32 in TMEM.
+// and gains lie in [0, 1]); all products accumulate in fp32 in TMEM.
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
 
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -48,24 +56,25 @@ namespace earb {
     constexpr int kMT = 4;                     // M-tiles per tile
     constexpr int kTileRows = kMT * 128;
     constexpr int kEvalWarps = kTileRows / 32;  // 16
-    constexpr int kFillWarps = 2;
-    constexpr int kMmaWarp = kEvalWarps + kFillWarps, kProdWarp = kMmaWarp + 1;
-    constexpr int kThreads = (kProdWarp + 1) * 32;  // 640
-    constexpr int kD = 4;                            // A ring depth in cells
+    constexpr int kD = 3;                            // A ring depth in cells
+    constexpr int kCleanWarp = kEvalWarps;           // kD cleaner warps, one per A stage
+    constexpr int kMmaWarp = kEvalWarps + kD, kProdWarp = kMmaWarp + 1;
+    constexpr int kThreads = (kProdWarp + 1) * 32;  // 672
     constexpr int kBCells = 4;                       // cells per stream stage
     constexpr int kBStages = 4;
     constexpr int kRows = 48;                        // B rows: 24 G_hi + 24 G_lo
     constexpr int kCellBBytes = kRows * kCell * 2;   // 1536
-    constexpr int kCellPtBytes = (kCell / 2) * 24;   // 8 x (float4 xy pair + float2 z pair) = 192
-    constexpr int kCellBytes = kCellBBytes + kCellPtBytes;  // 1728
-    constexpr int kBStageBytes = kBCells * kCellBytes;      // 6912
+    constexpr int kBStageBytes = kBCells * kCellBBytes;     // 6144
     constexpr int kAPlaneBytes = 128 * kCell * 2;           // one M-tile, one plane: 4096
     constexpr int kAStageBytes = kMT * 2 * kAPlaneBytes;    // 32768
     constexpr int kConstBytes = 64;                         // pass constants per row
     constexpr int kAccCols = 64;                            // per M-tile: [main 24 | corr 24 | spill 8 | -]
-    constexpr int kTmemCols = kMT * kAccCols;               // 256
+    constexpr int kColInd = kMT * kAccCols;                 // indicator A: [M-tile][n_cells_pad / 2]
+    constexpr int kTmemCols = 512;
+    constexpr int kMaxCellsPad = (kTmemCols - kColInd) / kMT * 2;  // 128
+    constexpr int kSum1Bytes = 48 * 16 * 2, kSum2Bytes = 32 * 16 * 2;  // per 16 cells: [hi | mid], [lo | 0]
+    constexpr int kPoolCap = 20480;                         // entries of the mixed-pass lists
     static_assert(EARB_MAX_SPK <= 24, "B row packing assumes at most 24 loudspeakers");
-    static_assert(kCellBytes % 16 == 0, "stage pieces must stay 16-byte aligned");
     static_assert(EXTENT_TC_STAGE_POINTS % (kBCells * kCell) == 0, "grid padding covers whole stages");
     // classification margin in weight units (|m| * 0.1 degree): covers the float rounding of the
     // centre evaluation, which is worst where acos is steep (angle ~ 0 or pi: 4.5e-4 rad)
@@ -81,8 +90,8 @@ namespace earb {
       asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                    : "memory");
     }
-    __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
-      asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+    __device__ __forceinline__ void mbar_arrive(uint64_t *bar, uint32_t count = 1) {
+      asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
     }
     __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
       asm volatile(
@@ -91,29 +100,37 @@ namespace earb {
           "l"(src), "r"(bytes), "r"(smem_u32(bar))
           : "memory");
     }
-    // waits for the phase with the given parity; a protocol error traps after ~2 s instead of
-    // hanging the GPU
+    // waits for the phase with the given parity (the waiter follows every phase of the barrier); a
+    // protocol error traps after ~2 s instead of hanging the GPU
     __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
       uint32_t done;
-      asm volatile(
-          "{\n\t.reg .pred p;\n\t"
-          "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-          "selp.u32 %0, 1, 0, p;\n\t}"
-          : "=r"(done)
-          : "r"(smem_u32(bar)), "r"(parity)
-          : "memory");
-      if (done) return;
-      const long long t0 = clock64();
+      uint32_t spins = 0;
       do {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, 0x989680;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
             "selp.u32 %0, 1, 0, p;\n\t}"
             : "=r"(done)
             : "r"(smem_u32(bar)), "r"(parity)
             : "memory");
-        if (!done && clock64() - t0 > 4000000000LL) __trap();
+        if (!done && ++spins > 20000000u) __trap();
       } while (!done);
+    }
+    // monotone progress counters in shared memory (waiters may skip values, unlike barrier phases)
+    __device__ __forceinline__ void counter_publish(uint32_t *ctr, uint32_t v) {
+      asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_u32(ctr)), "r"(v) : "memory");
+    }
+    // polls with a short sleep in between: a spinning warp would take issue slots from the warps
+    // it is waiting for
+    __device__ __forceinline__ void counter_wait(uint32_t *ctr, uint32_t at_least) {
+      uint32_t v;
+      uint32_t spins = 0;
+      while (true) {
+        asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(ctr)) : "memory");
+        if (v >= at_least) break;
+        __nanosleep(100);
+        if (++spins > 20000000u) __trap();
+      }
     }
     __device__ __forceinline__ void fence_proxy_async() {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -132,7 +149,13 @@ namespace earb {
 #pragma unroll
       for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
     }
-    // D[tmem] (+)= A[smem desc] * B[smem desc], kind::f16 (fp16 operands, fp32 accumulate)
+    __device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8]) {
+      asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr),
+                   "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+                   : "memory");
+    }
+    // D[tmem] (+)= A * B[smem desc], kind::f16 (fp16 operands, fp32 accumulate); A from shared
+    // memory (descriptor) or from TMEM (two K elements per 32-bit column)
     __device__ __forceinline__ void umma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
                                                 uint32_t idesc, uint32_t accumulate) {
       asm volatile(
@@ -142,6 +165,15 @@ namespace earb {
           ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
           : "memory");
     }
+    __device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc,
+                                                uint32_t idesc, uint32_t accumulate) {
+      asm volatile(
+          "{\n\t.reg .pred p;\n\t"
+          "setp.ne.b32 p, %4, 0;\n\t"
+          "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+          ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+          : "memory");
+    }
     __device__ __forceinline__ void umma_commit(uint64_t *bar) {
       asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
                        smem_u32(bar))
@@ -149,7 +181,7 @@ namespace earb {
     }
     // K-major, no swizzle, 16-bit elements: a core matrix is 8 rows x 16 bytes (8 elements of K);
     // the two core matrices of one K = 16 step are 128 bytes apart (LBO), 8-row groups 256 bytes
-    // (SBO).  Same layout for A (128 rows) and B (48 rows).
+    // (SBO).  Same layout for A (128 rows) and the B images (48 / 32 rows).
     __device__ __forceinline__ uint64_t kmajor_desc(uint32_t smem_addr) {
       const uint64_t lbo = 128 >> 4, sbo = 256 >> 4;
       return (uint64_t)((smem_addr >> 4) & 0x3FFF) | (lbo << 16) | (sbo << 32) | (1ull << 46);
@@ -193,7 +225,8 @@ namespace earb {
     // angle >= end and the fade m * angle + c in between; the fade is 1 at `start`, 0 at `end`
     // and monotone, and the sentinels libear uses when an angle passes pi (pi/2 for the sine test)
     // only ever disable a comparison whose fade value is already inside [0, 1]
-    // (polar_extent.cpp:176-199), so the whole function is clamp(m * angle + c, 0, 1).
+    // (polar_extent.cpp:176-199), so the whole function is clamp(m * angle + c, 0, 1) (weights
+    // differ from the reference's by rounding at the fade ends only).
     // angle = acos(v) on the circle part, asin(|z'|) on the straight part, both from
     // acos(|v|) = sqrt(u) * Q7(u), u = 1 - |v| (Abramowitz & Stegun 4.4.46 re-expanded in u,
     // |error| <= 2.2e-8); the straight part enters as v = -|z'| so that both parts are
@@ -242,30 +275,73 @@ namespace earb {
     __device__ __forceinline__ uint32_t const_piece(uint32_t row, uint32_t i) {
       return row * kConstBytes + ((i ^ ((row >> 1) & 3u)) << 4);
     }
+    // byte offset of row `row` of the tile inside an A stage (hi plane, K-chunk 0)
+    __device__ __forceinline__ uint32_t a_row_offset(uint32_t row) {
+      return (row >> 7) * (2 * kAPlaneBytes) + ((row & 127u) >> 3) * 256 + (row & 7u) * 16;
+    }
 
-    // Barriers (parities follow counters that run on across tiles)
-    //   filled[s]    filler -> evaluators        uniform rows written, list of mixed passes ready
-    //   a_full[s]    16 evaluator warps -> MMA   every mixed row of the cell is in the A stage
-    //   a_free[s]    MMA commit -> filler        the UMMAs reading the A stage have finished
-    //   b_full[t]    producer -> MMA, evaluators stream stage t has landed (tx bytes)
-    //   b_empty[t]   MMA commit -> producer      the UMMAs reading stream stage t have finished
-    //   acc_full     MMA commit -> epilogue      every UMMA of the tile has finished
-    //   masks_ready  16 evaluator warps -> fillers  phase 1 of the tile is complete
+    // dynamic shared memory layout
+    struct Smem {
+      unsigned char *A, *B, *consts, *sum1, *sum2;
+      uint32_t *mixed;        // [NC][16] ballot masks: bit = pass is mixed for the cell
+      unsigned short *pw;     // [NC][16] list position of the first mixed pass of (cell, warp)
+      float *ctr;             // [NC / 2][12] centre pairs + class thresholds
+      uint32_t *off;          // [NC + 1] list start of every cell in the tile-wide numbering
+      unsigned short *nmixed; // [NC]
+      unsigned short *nbp;    // [NC + 1] batch prefix
+      unsigned short *round_end;  // [NC] last cell (exclusive) of every round; [NC] = number of rounds
+      unsigned short *pool;   // [kPoolCap]
+    };
+    __host__ __device__ inline size_t smem_layout(int NC, unsigned char *base, Smem *s) {
+      size_t o = 0;
+      auto take = [&](size_t bytes) {
+        unsigned char *p = base + o;
+        o += (bytes + 127) & ~(size_t)127;
+        return p;
+      };
+      unsigned char *A = take((size_t)kD * kAStageBytes), *B = take((size_t)kBStages * kBStageBytes);
+      unsigned char *consts = take((size_t)kTileRows * kConstBytes);
+      unsigned char *sum1 = take((size_t)(NC / 16) * kSum1Bytes), *sum2 = take((size_t)(NC / 16) * kSum2Bytes);
+      unsigned char *mixed = take((size_t)NC * kEvalWarps * 4), *pw = take((size_t)NC * kEvalWarps * 2);
+      unsigned char *ctr = take((size_t)(NC / 2) * 48), *off = take((size_t)(NC + 1) * 4);
+      unsigned char *nmixed = take((size_t)NC * 2), *nbp = take((size_t)(NC + 1) * 2);
+      unsigned char *round_end = take((size_t)(NC + 1) * 2), *pool = take((size_t)kPoolCap * 2);
+      if (s) {
+        s->A = A, s->B = B, s->consts = consts, s->sum1 = sum1, s->sum2 = sum2;
+        s->mixed = reinterpret_cast<uint32_t *>(mixed);
+        s->pw = reinterpret_cast<unsigned short *>(pw);
+        s->ctr = reinterpret_cast<float *>(ctr);
+        s->off = reinterpret_cast<uint32_t *>(off);
+        s->nmixed = reinterpret_cast<unsigned short *>(nmixed);
+        s->nbp = reinterpret_cast<unsigned short *>(nbp);
+        s->round_end = reinterpret_cast<unsigned short *>(round_end);
+        s->pool = reinterpret_cast<unsigned short *>(pool);
+      }
+      return o;
+    }
+
+    // Barriers and counters (barrier parities follow counters that run on across tiles; every
+    // waiter of a barrier follows each of its phases)
+    //   tables_ready  16 evaluator warps -> cleaner, MMA   phase 1 / 1.5 of the tile are complete
+    //   a_full[s]     cleaner (17 - batches) + one per batch -> MMA   all mixed rows of the cell stored
+    //   a_free[s]     MMA commit -> cleaner                 the UMMAs reading the A stage have finished
+    //   b_full[t]     producer -> MMA                       stream stage t has landed (tx bytes)
+    //   b_empty[t]    MMA commit -> producer                the UMMAs reading stream stage t have finished
+    //   acc_full      MMA commit -> epilogue                every UMMA of the tile has finished
+    //   armed_uses[s]    cleaner s -> evaluators   uses of A stage s that are clean and armed
+    //   cleaned_uses[s]  cleaner s -> evaluators   uses of A stage s whose rows are zero again
     __global__ void __launch_bounds__(kThreads, 1)
-        extent_cell_kernel(int n_cells, int n_spk, const unsigned char *__restrict__ g_stream,
-                           const float *__restrict__ g_centres, const unsigned int *__restrict__ n_active_ptr,
-                           const ExtentPass *__restrict__ passes, float *__restrict__ results) {
+        extent_cell_kernel(int n_cells, int NC, int n_spk, const unsigned char *__restrict__ g_stream,
+                           const unsigned char *__restrict__ g_sums, const float *__restrict__ g_centres,
+                           const float4 *__restrict__ g_points, const unsigned int *__restrict__ n_active_ptr,
+                           const ExtentPass *__restrict__ passes, float *__restrict__ results, int dbg) {
       extern __shared__ __align__(128) unsigned char smem_raw[];
-      unsigned char *sA = smem_raw;                                       // [kD][kAStageBytes]
-      unsigned char *sB = sA + kD * kAStageBytes;                         // [kBStages][kBStageBytes]
-      unsigned char *sConst = sB + kBStages * kBStageBytes;               // [kTileRows][64]
-      uint32_t *sMixed = reinterpret_cast<uint32_t *>(sConst + kTileRows * kConstBytes);  // [n_cells][16]
-      uint32_t *sOnes = sMixed + n_cells * kEvalWarps;                    // [n_cells][16]
-      float *sCtr = reinterpret_cast<float *>(sOnes + n_cells * kEvalWarps);  // [n_cells / 2][12]
-      unsigned short *sList = reinterpret_cast<unsigned short *>(sCtr + (n_cells / 2) * 12);  // [kD][kTileRows]
-      __shared__ __align__(8) uint64_t filled[kD], a_full[kD], a_free[kD];
-      __shared__ __align__(8) uint64_t b_full[kBStages], b_empty[kBStages], acc_full, masks_ready;
-      __shared__ uint32_t s_nmixed[kD];
+      Smem sm;
+      smem_layout(NC, smem_raw, &sm);
+      __shared__ __align__(8) uint64_t a_full[kD], a_free[kD];
+      __shared__ __align__(8) uint64_t b_full[kBStages], b_empty[kBStages], acc_full, tables_ready;
+      // per A stage: number of uses armed / cleaned so far (use u of stage s = cell u * kD + s)
+      __shared__ uint32_t armed_uses[kD], cleaned_uses[kD];
       __shared__ uint32_t tmem_base_s;
 
       const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -277,11 +353,21 @@ namespace earb {
       const int n_bstages = n_cells / kBCells;
       if (n_tiles == 0) return;  // no passes for this CTA (small batches): nothing to set up
 
-      for (int j = tid; j < (n_cells / 2) * 12; j += kThreads) sCtr[j] = g_centres[j];
+      for (int j = tid; j < (NC / 2) * 12; j += kThreads) sm.ctr[j] = g_centres[j];
+      {
+        const uint4 *src = reinterpret_cast<const uint4 *>(g_sums);
+        uint4 *d1 = reinterpret_cast<uint4 *>(sm.sum1), *d2 = reinterpret_cast<uint4 *>(sm.sum2);
+        const int n1 = (NC / 16) * kSum1Bytes / 16, n2 = (NC / 16) * kSum2Bytes / 16;
+        for (int j = tid; j < n1; j += kThreads) d1[j] = src[j];
+        for (int j = tid; j < n2; j += kThreads) d2[j] = src[n1 + j];
+        // the A ring starts all zeros
+        uint4 *a = reinterpret_cast<uint4 *>(sm.A);
+        for (int j = tid; j < kD * kAStageBytes / 16; j += kThreads) a[j] = make_uint4(0u, 0u, 0u, 0u);
+      }
+      fence_proxy_async();
       if (tid == 0) {
         for (int s = 0; s < kD; s++) {
-          mbar_init(&filled[s], 1);
-          mbar_init(&a_full[s], kEvalWarps);
+          mbar_init(&a_full[s], kEvalWarps + 1);
           mbar_init(&a_free[s], 1);
         }
         for (int s = 0; s < kBStages; s++) {
@@ -289,7 +375,8 @@ namespace earb {
           mbar_init(&b_empty[s], 1);
         }
         mbar_init(&acc_full, 1);
-        mbar_init(&masks_ready, kEvalWarps);
+        mbar_init(&tables_ready, kEvalWarps);
+        for (int s = 0; s < kD; s++) armed_uses[s] = cleaned_uses[s] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       }
       if (warp == kMmaWarp) {
@@ -313,7 +400,7 @@ namespace earb {
               const int bs = g % kBStages;
               if (g >= kBStages) mbar_wait(&b_empty[bs], (uint32_t)(((g / kBStages) - 1) & 1));
               mbar_expect_tx(&b_full[bs], (uint32_t)kBStageBytes);
-              bulk_g2s(sB + bs * kBStageBytes, g_stream + (size_t)st * kBStageBytes, (uint32_t)kBStageBytes,
+              bulk_g2s(sm.B + bs * kBStageBytes, g_stream + (size_t)st * kBStageBytes, (uint32_t)kBStageBytes,
                        &b_full[bs]);
             }
         }
@@ -326,24 +413,46 @@ namespace earb {
         const uint32_t idesc_base = (1u << 4) | ((uint32_t)(128 >> 4) << 24);
         const uint32_t idesc48 = idesc_base | ((uint32_t)(48 >> 3) << 17);
         const uint32_t idesc32 = idesc_base | ((uint32_t)(32 >> 3) << 17);
-        const uint32_t sA_addr = smem_u32(sA), sB_addr = smem_u32(sB);
+        const uint32_t sA_addr = smem_u32(sm.A), sB_addr = smem_u32(sm.B);
+        const uint32_t s1_addr = smem_u32(sm.sum1), s2_addr = smem_u32(sm.sum2);
         int g = 0;  // cell counter, continuous across tiles
         for (int tile = 0; tile < n_tiles; tile++) {
           const int n_mt = min(kMT, (p_end - (p_begin + tile * kTileRows) + 127) / 128);
+          mbar_wait(&tables_ready, (uint32_t)(tile & 1));
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          if (leader) {
+            // the all-ones cells: acc = indicator * [Gsum_hi | Gsum_mid], corr += indicator * Gsum_lo
+            for (int ks = 0; ks < NC / 16; ks++) {
+              const uint64_t d1 = kmajor_desc(s1_addr + ks * kSum1Bytes), d2 = kmajor_desc(s2_addr + ks * kSum2Bytes);
+#pragma unroll
+              for (int mt = 0; mt < kMT; mt++) {
+                if (mt >= n_mt) break;
+                const uint32_t acc = tm + mt * kAccCols;
+                const uint32_t a_ind = tm + kColInd + mt * (NC / 2) + ks * 8;
+                umma_f16_ts(acc, a_ind, d1, idesc48, ks != 0);
+                umma_f16_ts(acc + 24, a_ind, d2, idesc32, 1);
+              }
+            }
+          }
+          __syncwarp();
           for (int k = 0; k < n_cells; k++, g++) {
             const int s = g % kD, bsg = g / kBCells, bs = bsg % kBStages, sub = g % kBCells;
             if (sub == 0) mbar_wait(&b_full[bs], (uint32_t)((bsg / kBStages) & 1));
             mbar_wait(&a_full[s], (uint32_t)((g / kD) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const bool any = sm.nmixed[k] != 0;
             if (leader) {
-              const uint64_t bd = kmajor_desc(sB_addr + bs * kBStageBytes + sub * kCellBytes);
+              if (any) {
+                const uint64_t bd = kmajor_desc(sB_addr + bs * kBStageBytes + sub * kCellBBytes);
 #pragma unroll
-              for (int mt = 0; mt < kMT; mt++) {
-                if (mt >= n_mt) break;
-                const uint32_t acc = tm + mt * kAccCols;
-                const uint32_t a_hi = sA_addr + s * kAStageBytes + mt * 2 * kAPlaneBytes;
-                umma_f16_ss(acc, kmajor_desc(a_hi), bd, idesc48, k != 0);
-                umma_f16_ss(acc + 24, kmajor_desc(a_hi + kAPlaneBytes), bd, idesc32, 1);
+                for (int mt = 0; mt < kMT; mt++) {
+                  if (mt >= n_mt) break;
+                  const uint32_t acc = tm + mt * kAccCols;
+                  const uint32_t a_hi = sA_addr + s * kAStageBytes + mt * 2 * kAPlaneBytes;
+                  if (dbg & 1) continue;
+                  umma_f16_ss(acc, kmajor_desc(a_hi), bd, idesc48, 1);
+                  umma_f16_ss(acc + 24, kmajor_desc(a_hi + kAPlaneBytes), bd, idesc32, 1);
+                }
               }
               umma_commit(&a_free[s]);
               if (sub == kBCells - 1) umma_commit(&b_empty[bs]);
@@ -352,48 +461,58 @@ namespace earb {
             __syncwarp();
           }
         }
-      } else if (warp >= kEvalWarps) {
-        // ------------------------------------------------------------ fillers
-        const int f = warp - kEvalWarps;
-        const uint32_t lt_mask = (1u << lane) - 1u;
+      } else if (warp >= kCleanWarp) {
+        // ------------------------------------------------------------ cleaners (one per A stage)
+        const uint32_t s = (uint32_t)(warp - kCleanWarp);
+        unsigned char *stage = sm.A + s * kAStageBytes;
+        uint32_t use = 0;  // uses of this stage so far (continuous across tiles)
         for (int tile = 0; tile < n_tiles; tile++) {
-          mbar_wait(&masks_ready, (uint32_t)(tile & 1));
-          for (int k = f; k < n_cells; k += kFillWarps) {
-            const int g = tile * n_cells + k, s = g % kD, u = g / kD;
-            if (u >= 1) mbar_wait(&a_free[s], (uint32_t)((u - 1) & 1));
-            unsigned char *stage = sA + s * kAStageBytes;
-            unsigned short *list = sList + s * kTileRows;
-            uint32_t base = 0;
-#pragma unroll 4
-            for (int w = 0; w < kEvalWarps; w++) {
-              const uint32_t mm = sMixed[k * kEvalWarps + w], mo = sOnes[k * kEvalWarps + w];
-              const uint32_t row = (uint32_t)(w * 32 + lane);
-              if ((mm >> lane) & 1u) {
-                list[base + __popc(mm & lt_mask)] = (unsigned short)row;
-              } else {
-                const uint32_t v = ((mo >> lane) & 1u) ? 0x3C003C00u : 0u;  // fp16 1.0 twice, or zeros
-                unsigned char *hi = stage + (row >> 7) * (2 * kAPlaneBytes) + ((row & 127u) >> 3) * 256 +
-                                    (row & 7u) * 16;
-                *reinterpret_cast<uint4 *>(hi) = make_uint4(v, v, v, v);
-                *reinterpret_cast<uint4 *>(hi + 128) = make_uint4(v, v, v, v);
-                *reinterpret_cast<uint4 *>(hi + kAPlaneBytes) = make_uint4(0u, 0u, 0u, 0u);
-                *reinterpret_cast<uint4 *>(hi + kAPlaneBytes + 128) = make_uint4(0u, 0u, 0u, 0u);
-              }
-              base += (uint32_t)__popc(mm);
+          const uint32_t gbase = (uint32_t)(tile * n_cells);
+          mbar_wait(&tables_ready, (uint32_t)(tile & 1));
+          // first cell of this stage in the tile; its stage is clean (end of the previous tile): arm it
+          int k = (int)((s + kD - gbase % kD) % kD);
+          if (k < n_cells) {
+            if (lane == 0) {
+              mbar_arrive(&a_full[s], (uint32_t)(kEvalWarps + 1 - ((sm.nmixed[k] + 31) >> 5)));
+              counter_publish(&armed_uses[s], use + 1);
             }
-            if (lane == 0) s_nmixed[s] = base;
+          }
+          int r = 0;
+          uint32_t round_off = 0;
+          for (; k < n_cells; k += kD, use++) {
+            while (k >= (int)sm.round_end[r]) {
+              round_off = sm.off[sm.round_end[r]];
+              r++;
+            }
+            const uint32_t n = sm.nmixed[k], base = sm.off[k] - round_off;
+            mbar_wait(&a_free[s], use & 1);
+            for (uint32_t i = (uint32_t)lane; i < n && !(dbg & 2); i += 32) {
+              unsigned char *dst = stage + a_row_offset(sm.pool[base + i]);
+              *reinterpret_cast<uint4 *>(dst) = make_uint4(0u, 0u, 0u, 0u);
+              *reinterpret_cast<uint4 *>(dst + 128) = make_uint4(0u, 0u, 0u, 0u);
+              *reinterpret_cast<uint4 *>(dst + kAPlaneBytes) = make_uint4(0u, 0u, 0u, 0u);
+              *reinterpret_cast<uint4 *>(dst + kAPlaneBytes + 128) = make_uint4(0u, 0u, 0u, 0u);
+            }
             fence_proxy_async();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&filled[s]);
+            if (lane == 0) {
+              if (k + kD < n_cells) {
+                mbar_arrive(&a_full[s], (uint32_t)(kEvalWarps + 1 - ((sm.nmixed[k + kD] + 31) >> 5)));
+                counter_publish(&armed_uses[s], use + 2);
+              }
+              counter_publish(&cleaned_uses[s], use + 1);
+            }
           }
         }
       } else {
-        // ------------------------------------------------------------ evaluators (phase 1, 2, epilogue)
+        // ------------------------------------------------------------ evaluators (phase 1, 1.5, 2, epilogue)
         const int mt = warp >> 2, q = warp & 3;
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
         const uint32_t row_own = (uint32_t)(warp * 32 + lane);
-        const uint32_t sConst_addr = smem_u32(sConst);
+        const uint32_t sConst_addr = smem_u32(sm.consts);
+        const uint32_t lt_mask = (1u << lane) - 1u;
         for (int tile = 0; tile < n_tiles; tile++) {
+          const uint32_t gbase = (uint32_t)(tile * n_cells);
           const int idx = p_begin + tile * kTileRows + (int)row_own;
           const bool valid = idx < p_end;
           int slot;
@@ -435,41 +554,114 @@ namespace earb {
             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(sConst_addr + const_piece(row_own, 3)),
                          "f"(c.cc1), "f"(c.sin_thr), "f"(c.m), "f"(c.c)
                          : "memory");
-            for (int cp = 0; cp < n_cells / 2; cp++) {
-              // centres of cells 2cp, 2cp + 1: (x0, x1, y0, y1), (z0, z1, -, -), (one0, zero0, one1, zero1)
-              const float4 xy = *reinterpret_cast<const float4 *>(sCtr + cp * 12);
-              const float4 zz = *reinterpret_cast<const float4 *>(sCtr + cp * 12 + 4);
-              const float4 th = *reinterpret_cast<const float4 *>(sCtr + cp * 12 + 8);
-              float t0, t1;
-              weight_fn2(c, pk(xy.x, xy.y), pk(xy.z, xy.w), pk(zz.x, zz.y), t0, t1);
-              const unsigned one0 = __ballot_sync(0xffffffffu, valid && t0 >= th.x);
-              const unsigned zero0 = __ballot_sync(0xffffffffu, !valid || t0 <= th.y);
-              const unsigned one1 = __ballot_sync(0xffffffffu, valid && t1 >= th.z);
-              const unsigned zero1 = __ballot_sync(0xffffffffu, !valid || t1 <= th.w);
-              if (lane == 0) {
-                sMixed[(2 * cp) * kEvalWarps + warp] = ~(one0 | zero0);
-                sOnes[(2 * cp) * kEvalWarps + warp] = one0;
-                sMixed[(2 * cp + 1) * kEvalWarps + warp] = ~(one1 | zero1);
-                sOnes[(2 * cp + 1) * kEvalWarps + warp] = one1;
+            for (int cp0 = 0; cp0 < NC / 2; cp0 += 8) {
+              uint32_t ind[8];
+#pragma unroll
+              for (int i = 0; i < 8; i++) {
+                const int cp = cp0 + i;
+                // centres of cells 2cp, 2cp + 1: (x0, x1, y0, y1), (z0, z1, -, -), (one0, zero0, one1, zero1)
+                const float4 xy = *reinterpret_cast<const float4 *>(sm.ctr + cp * 12);
+                const float4 zz = *reinterpret_cast<const float4 *>(sm.ctr + cp * 12 + 4);
+                const float4 th = *reinterpret_cast<const float4 *>(sm.ctr + cp * 12 + 8);
+                float t0, t1;
+                weight_fn2(c, pk(xy.x, xy.y), pk(xy.z, xy.w), pk(zz.x, zz.y), t0, t1);
+                const bool real0 = valid && 2 * cp < n_cells, real1 = valid && 2 * cp + 1 < n_cells;
+                const bool one0 = real0 && t0 >= th.x, one1 = real1 && t1 >= th.z;
+                const unsigned mix0 = __ballot_sync(0xffffffffu, real0 && !one0 && !(t0 <= th.y) && !(dbg & 16));
+                const unsigned mix1 = __ballot_sync(0xffffffffu, real1 && !one1 && !(t1 <= th.w) && !(dbg & 16));
+                if (lane == 0) {
+                  sm.mixed[(2 * cp) * kEvalWarps + warp] = mix0;
+                  sm.mixed[(2 * cp + 1) * kEvalWarps + warp] = mix1;
+                }
+                ind[i] = (one0 ? 0x00003C00u : 0u) | (one1 ? 0x3C000000u : 0u);  // fp16 1.0 per cell
               }
+              tmem_st8(lane_base + kColInd + mt * (NC / 2) + cp0, ind);
+            }
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          }
+          asm volatile("bar.sync 1, %0;" ::"n"(kEvalWarps * 32) : "memory");
+          // ---- phase 1.5: counts, prefix sums, rounds
+          if ((int)row_own < NC) {
+            const int k = (int)row_own;
+            uint32_t run = 0;
+#pragma unroll
+            for (int w = 0; w < kEvalWarps; w++) {
+              sm.pw[k * kEvalWarps + w] = (unsigned short)run;
+              run += (uint32_t)__popc(sm.mixed[k * kEvalWarps + w]);
+            }
+            sm.nmixed[k] = (unsigned short)run;
+          }
+          asm volatile("bar.sync 1, %0;" ::"n"(kEvalWarps * 32) : "memory");
+          if (warp == 0) {
+            // exclusive scans over the cells (one warp, 32 cells at a time), then the rounds: as
+            // many cells as the pool holds
+            uint32_t carry_off = 0, carry_nb = 0;
+            for (int k0 = 0; k0 < NC; k0 += 32) {
+              const int k = k0 + lane;
+              const uint32_t n = k < NC ? sm.nmixed[k] : 0u, nb = (n + 31u) >> 5;
+              uint32_t io = n, ib = nb;
+#pragma unroll
+              for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t to = __shfl_up_sync(0xffffffffu, io, o), tb = __shfl_up_sync(0xffffffffu, ib, o);
+                if (lane >= o) io += to, ib += tb;
+              }
+              if (k < NC) {
+                sm.off[k] = carry_off + io - n;
+                sm.nbp[k] = (unsigned short)(carry_nb + ib - nb);
+              }
+              carry_off += __shfl_sync(0xffffffffu, io, 31);
+              carry_nb += __shfl_sync(0xffffffffu, ib, 31);
+            }
+            if (lane == 0) {
+              sm.off[NC] = carry_off;
+              sm.nbp[NC] = (unsigned short)carry_nb;
+            }
+            __syncwarp();
+            if (lane == 0) {
+              int n_rounds = 0, k = 0;
+              while (k < n_cells) {
+                const uint32_t start = sm.off[k];
+                int e = k + 1;  // a cell holds at most 512 entries: always fits
+                while (e < n_cells && sm.off[e + 1] - start <= (uint32_t)kPoolCap) e++;
+                sm.round_end[n_rounds++] = (unsigned short)e;
+                k = e;
+              }
+              sm.round_end[NC] = (unsigned short)n_rounds;
             }
           }
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&masks_ready);
-          // every evaluator's constants are in shared memory before any batch reads them
           asm volatile("bar.sync 1, %0;" ::"n"(kEvalWarps * 32) : "memory");
+          if (lane == 0) mbar_arrive(&tables_ready);
 
-          // ---- phase 2: batches of mixed (pass, cell) items
-          for (int k = 0; k < n_cells; k++) {
-            const int g = tile * n_cells + k, s = g % kD, bsg = g / kBCells, bs = bsg % kBStages;
-            if ((g % kBCells) == 0) mbar_wait(&b_full[bs], (uint32_t)((bsg / kBStages) & 1));
-            mbar_wait(&filled[s], (uint32_t)((g / kD) & 1));
-            const uint32_t n_mixed = s_nmixed[s];
-            const uint32_t first = (uint32_t)((warp - 5 * k) & (kEvalWarps - 1)) * 32u;
-            if (first < n_mixed) {
+          // ---- phase 2: rounds of cells; lists of the round, then its batches
+          const int n_rounds = sm.round_end[NC];
+          int k_lo = 0;
+          for (int r = 0; r < n_rounds; r++) {
+            const int k_hi = sm.round_end[r];
+            const uint32_t round_off = sm.off[k_lo];
+            // the pool is free once the cleaner is through with the cells before this round
+            if (r > 0) {
+              // every cell before k_lo cleaned: stage s has been used for the cells g < gbase + k_lo
+              // with g % kD == s
+              const uint32_t g_lo = gbase + (uint32_t)k_lo;
+#pragma unroll
+              for (uint32_t s = 0; s < (uint32_t)kD; s++) counter_wait(&cleaned_uses[s], (g_lo + kD - 1 - s) / kD);
+            }
+            for (int k = k_lo; k < k_hi; k++) {
+              const uint32_t mm = sm.mixed[k * kEvalWarps + warp];
+              if ((mm >> lane) & 1u)
+                sm.pool[sm.off[k] - round_off + sm.pw[k * kEvalWarps + warp] + __popc(mm & lt_mask)] =
+                    (unsigned short)row_own;
+            }
+            asm volatile("bar.sync 1, %0;" ::"n"(kEvalWarps * 32) : "memory");
+            int k = k_lo;
+            const int b_end = sm.nbp[k_hi];
+            for (int b = (int)sm.nbp[k_lo] + warp; b < b_end; b += kEvalWarps) {
+              while ((int)sm.nbp[k + 1] <= b) k++;
+              const uint32_t n_mixed = sm.nmixed[k], first = (uint32_t)(b - (int)sm.nbp[k]) * 32u;
               const uint32_t item = first + (uint32_t)lane;
               const bool active = item < n_mixed;
-              const uint32_t row = sList[s * kTileRows + (active ? item : first)];
+              const uint32_t row = sm.pool[sm.off[k] - round_off + (active ? item : first)];
               PassRegs c;
               {
                 float4 p0, p1, p2, p3;
@@ -491,33 +683,44 @@ namespace earb {
                 c.cc1 = p3.x, c.sin_thr = p3.y, c.m = p3.z, c.c = p3.w;
                 c.a_sin = fmaf(c.m, 1.57079632679490f, c.c);
               }
-              const unsigned char *pts = sB + bs * kBStageBytes + (g % kBCells) * kCellBytes + kCellBBytes;
+              // the 16 points of the cell: eight (x, x', y, y') then four (z, z', z'', z''')
+              // (warp-uniform loads through L1)
+              const float4 *pts = g_points + (size_t)k * 12;
               uint32_t hi[kCell / 2], lo[kCell / 2];
 #pragma unroll
-              for (int i = 0; i < kCell / 2; i++) {
-                const float4 xy = reinterpret_cast<const float4 *>(pts)[i];  // warp-uniform broadcasts
-                const float2 zz = reinterpret_cast<const float2 *>(pts + 128)[i];
-                float t0, t1;
-                weight_fn2(c, pk(xy.x, xy.y), pk(xy.z, xy.w), pk(zz.x, zz.y), t0, t1);
-                const float w0 = __saturatef(t0), w1 = __saturatef(t1);
-                const __half2 h = __floats2half2_rn(w0, w1);
-                const float2 hf = __half22float2(h);
-                const __half2 l = __floats2half2_rn(__fsub_rn(w0, hf.x), __fsub_rn(w1, hf.y));
-                hi[i] = *reinterpret_cast<const uint32_t *>(&h);
-                lo[i] = *reinterpret_cast<const uint32_t *>(&l);
+              for (int i = 0; i < kCell / 2; i++) hi[i] = lo[i] = 0u;
+              if (!(dbg & 4))
+#pragma unroll
+              for (int i = 0; i < kCell / 2; i += 2) {
+                const float4 xy0 = __ldg(pts + i), xy1 = __ldg(pts + i + 1), zz = __ldg(pts + 8 + i / 2);
+                float t[4];
+                weight_fn2(c, pk(xy0.x, xy0.y), pk(xy0.z, xy0.w), pk(zz.x, zz.y), t[0], t[1]);
+                weight_fn2(c, pk(xy1.x, xy1.y), pk(xy1.z, xy1.w), pk(zz.z, zz.w), t[2], t[3]);
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                  const float w0 = __saturatef(t[2 * h]), w1 = __saturatef(t[2 * h + 1]);
+                  const __half2 hh = __floats2half2_rn(w0, w1);
+                  const float2 hf = __half22float2(hh);
+                  const __half2 ll = __floats2half2_rn(__fsub_rn(w0, hf.x), __fsub_rn(w1, hf.y));
+                  hi[i + h] = *reinterpret_cast<const uint32_t *>(&hh);
+                  lo[i + h] = *reinterpret_cast<const uint32_t *>(&ll);
+                }
               }
-              if (active) {
-                unsigned char *dst = sA + s * kAStageBytes + (row >> 7) * (2 * kAPlaneBytes) +
-                                     ((row & 127u) >> 3) * 256 + (row & 7u) * 16;
+              // the A stage of the cell must be clean and armed
+              const uint32_t g = gbase + (uint32_t)k, s = g % kD;
+              if (!(dbg & 32)) counter_wait(&armed_uses[s], g / kD + 1);
+              if (active && !(dbg & 8)) {
+                unsigned char *dst = sm.A + s * kAStageBytes + a_row_offset(row);
                 *reinterpret_cast<uint4 *>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
                 *reinterpret_cast<uint4 *>(dst + 128) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
                 *reinterpret_cast<uint4 *>(dst + kAPlaneBytes) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
                 *reinterpret_cast<uint4 *>(dst + kAPlaneBytes + 128) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
               }
-              fence_proxy_async();
+              if (!(dbg & 8)) fence_proxy_async();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&a_full[s]);
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&a_full[s]);
+            k_lo = k_hi;
           }
 
           // ---- epilogue: this thread's row of [main | corr]; results /= ||results|| in float
@@ -552,6 +755,12 @@ namespace earb {
             }
           }
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+          // the cleaner is through with the tile: tables, pool and constants may be overwritten
+          {
+            const uint32_t g_hi = gbase + (uint32_t)n_cells;
+#pragma unroll
+            for (uint32_t s = 0; s < (uint32_t)kD; s++) counter_wait(&cleaned_uses[s], (g_hi + kD - 1 - s) / kD);
+          }
         }
       }
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -665,34 +874,24 @@ namespace earb {
     }
   }
 
-  size_t extent_cell_stream_bytes(const ExtentCells &cells) { return (size_t)cells.n_cells * kCellBytes; }
-  size_t extent_cell_centre_floats(const ExtentCells &cells) { return (size_t)(cells.n_cells / 2) * 12; }
+  size_t extent_cell_stream_bytes(const ExtentCells &cells) { return (size_t)cells.n_cells * kCellBBytes; }
+  int extent_cell_pad(const ExtentCells &cells) { return (cells.n_cells + 15) / 16 * 16; }
+  size_t extent_cell_centre_floats(const ExtentCells &cells) { return (size_t)(extent_cell_pad(cells) / 2) * 12; }
+  size_t extent_cell_sum_bytes(const ExtentCells &cells) {
+    return (size_t)(extent_cell_pad(cells) / 16) * (kSum1Bytes + kSum2Bytes);
+  }
+  size_t extent_cell_point_floats(const ExtentCells &cells) { return (size_t)cells.n_cells * 48; }
 
   // per cell: the UMMA B image of [G_hi (24 rows) | G_lo (24 rows)] x 16 points in fp16 --
-  // [6 row groups][2 K-chunks][8 rows][8 halves] -- followed by the point coordinates as eight
-  // (x, x', y, y') and eight (z, z') pairs.  gains is speaker-major [S][Pp] float in grid order.
-  void extent_cell_build_stream(const ExtentCells &cells, int n_spk, int n_points_pad, const float *xyz,
-                                const float *gains, unsigned char *stream) {
+  // [6 row groups][2 K-chunks][8 rows][8 halves].  gains is speaker-major [S][Pp] float in grid order.
+  void extent_cell_build_stream(const ExtentCells &cells, int n_spk, int n_points_pad, const float *gains,
+                                unsigned char *stream) {
     memset(stream, 0, extent_cell_stream_bytes(cells));
     for (int c = 0; c < cells.n_cells; c++) {
-      unsigned char *cell = stream + (size_t)c * kCellBytes;
-      __half *b = reinterpret_cast<__half *>(cell);
-      float *pxy = reinterpret_cast<float *>(cell + kCellBBytes);
-      float *pz = reinterpret_cast<float *>(cell + kCellBBytes + 128);
-      // padding slots repeat a real point of the cell (or the cell's centre), with zero gains
-      int fallback = -1;
-      for (int i = 0; i < kCell; i++)
-        if (cells.order[(size_t)c * kCell + i] >= 0) fallback = cells.order[(size_t)c * kCell + i];
+      __half *b = reinterpret_cast<__half *>(stream + (size_t)c * kCellBBytes);
       for (int i = 0; i < kCell; i++) {
         const int p = cells.order[(size_t)c * kCell + i];
-        const int q = p >= 0 ? p : fallback;
-        const float x = q >= 0 ? xyz[q] : cells.centre[3 * c];
-        const float y = q >= 0 ? xyz[n_points_pad + q] : cells.centre[3 * c + 1];
-        const float z = q >= 0 ? xyz[2 * n_points_pad + q] : cells.centre[3 * c + 2];
-        pxy[(i / 2) * 4 + (i & 1)] = x;
-        pxy[(i / 2) * 4 + 2 + (i & 1)] = y;
-        pz[(i / 2) * 2 + (i & 1)] = z;
-        if (p < 0) continue;
+        if (p < 0) continue;  // padding slots: zero gains
         for (int s = 0; s < n_spk; s++) {
           const float g = gains[(size_t)s * n_points_pad + p];
           const __half hi = __float2half_rn(g);
@@ -705,38 +904,100 @@ namespace earb {
     }
   }
 
+  // the gain sums of every cell (what an all-ones cell adds to a pass: the reference's
+  // summed_panning_results, polar_extent.cpp:146-152) as fp16 hi + mid + lo, K = cell index:
+  // image 1 [K / 16][6 row groups][2][8][8] = [Gsum_hi (24 rows) | Gsum_mid (24 rows)],
+  // image 2 [K / 16][4 row groups][2][8][8] = [Gsum_lo (24 rows) | 8 zero rows]
+  void extent_cell_build_sums(const ExtentCells &cells, int n_spk, int n_points_pad, const float *gains,
+                              unsigned char *sums) {
+    const int NC = extent_cell_pad(cells);
+    memset(sums, 0, extent_cell_sum_bytes(cells));
+    __half *img1 = reinterpret_cast<__half *>(sums);
+    __half *img2 = reinterpret_cast<__half *>(sums + (size_t)(NC / 16) * kSum1Bytes);
+    for (int c = 0; c < cells.n_cells; c++)
+      for (int s = 0; s < n_spk; s++) {
+        double sum = 0.0;
+        for (int i = 0; i < kCell; i++) {
+          const int p = cells.order[(size_t)c * kCell + i];
+          if (p >= 0) sum += (double)gains[(size_t)s * n_points_pad + p];
+        }
+        const __half hi = __float2half_rn((float)sum);
+        const double r1 = sum - (double)__half2float(hi);
+        const __half mid = __float2half_rn((float)r1);
+        const __half lo = __float2half_rn((float)(r1 - (double)__half2float(mid)));
+        const int ks = c / 16, k = c % 16;
+        auto at = [&](int row) { return (row / 8) * 128 + (k / 8) * 64 + (row % 8) * 8 + (k % 8); };
+        img1[(size_t)ks * (kSum1Bytes / 2) + at(s)] = hi;
+        img1[(size_t)ks * (kSum1Bytes / 2) + at(24 + s)] = mid;
+        img2[(size_t)ks * (kSum2Bytes / 2) + at(s)] = lo;
+      }
+  }
+
+  // the 16 points of every cell for the evaluators: eight float4 (x, x', y, y') -- points 2i and
+  // 2i + 1 -- then four float4 (z, z', z'', z''') -- points 4j .. 4j + 3.  Padding slots repeat a
+  // real point of the cell (their gains are zero).  xyz: [3][Pp] float.
+  void extent_cell_build_points(const ExtentCells &cells, int n_points_pad, const float *xyz, float *out) {
+    for (int c = 0; c < cells.n_cells; c++) {
+      float *o = out + (size_t)c * 48;
+      int fallback = -1;
+      for (int i = 0; i < kCell; i++)
+        if (cells.order[(size_t)c * kCell + i] >= 0) fallback = cells.order[(size_t)c * kCell + i];
+      for (int i = 0; i < kCell; i++) {
+        const int p = cells.order[(size_t)c * kCell + i];
+        const int q = p >= 0 ? p : fallback;
+        const float x = q >= 0 ? xyz[q] : cells.centre[3 * c];
+        const float y = q >= 0 ? xyz[n_points_pad + q] : cells.centre[3 * c + 1];
+        const float z = q >= 0 ? xyz[2 * n_points_pad + q] : cells.centre[3 * c + 2];
+        o[(i / 2) * 4 + (i & 1)] = x;
+        o[(i / 2) * 4 + 2 + (i & 1)] = y;
+        o[32 + i] = z;
+      }
+    }
+  }
+
   // centres of cells 2j, 2j + 1 as (x0, x1, y0, y1), (z0, z1, 0, 0) and the class thresholds
   // (one0, zero0, one1, zero1): all weights are 1 when the weight function at the centre is
   // >= one, all 0 when it is <= zero (|m| = 1 / radians(10), ref polar_extent.cpp:194)
   void extent_cell_build_centres(const ExtentCells &cells, float *out) {
     const double M = 1.0 / (10.0 * 3.141592653589793238462643383279502884 / 180.0);
-    for (int j = 0; j < cells.n_cells / 2; j++) {
+    const int NC = extent_cell_pad(cells);
+    for (int j = 0; j < NC / 2; j++) {
       float *o = out + (size_t)j * 12;
       for (int h = 0; h < 2; h++) {
         const int c = 2 * j + h;
-        o[h] = cells.centre[3 * c];
-        o[2 + h] = cells.centre[3 * c + 1];
-        o[4 + h] = cells.centre[3 * c + 2];
-        o[8 + 2 * h] = (float)(1.0 + M * cells.radius[c] + kClassMargin);
-        o[9 + 2 * h] = (float)(-(M * cells.radius[c] + kClassMargin));
+        const bool real = c < cells.n_cells;
+        o[h] = real ? cells.centre[3 * c] : 0.0f;
+        o[2 + h] = real ? cells.centre[3 * c + 1] : 1.0f;
+        o[4 + h] = real ? cells.centre[3 * c + 2] : 0.0f;
+        const double r = real ? cells.radius[c] : 0.0;
+        o[8 + 2 * h] = (float)(1.0 + M * r + kClassMargin);
+        o[9 + 2 * h] = (float)(-(M * r + kClassMargin));
       }
       o[6] = o[7] = 0.0f;
     }
   }
 
-  size_t extent_cell_smem_bytes(int n_cells) {
-    return (size_t)kD * kAStageBytes + (size_t)kBStages * kBStageBytes + (size_t)kTileRows * kConstBytes +
-           (size_t)n_cells * kEvalWarps * 2 * sizeof(uint32_t) + (size_t)(n_cells / 2) * 12 * sizeof(float) +
-           (size_t)kD * kTileRows * sizeof(unsigned short);
+  size_t extent_cell_smem_bytes(const ExtentCells &cells) {
+    return smem_layout(extent_cell_pad(cells), nullptr, nullptr);
+  }
+  bool extent_cell_supported(const ExtentCells &cells) {
+    return extent_cell_pad(cells) <= kMaxCellsPad && cells.n_cells % kBCells == 0 &&
+           extent_cell_smem_bytes(cells) + 1024 <= 227 * 1024;
   }
 
-  void launch_extent_cell(int n_cells, int n_spk, const unsigned char *d_stream, const float *d_centres,
-                          const unsigned int *d_n_active, const ExtentPass *d_passes, float *d_results,
-                          int n_sms, cudaStream_t stream) {
-    const size_t smem = extent_cell_smem_bytes(n_cells);
+  void launch_extent_cell(int n_cells, int n_spk, const unsigned char *d_stream, const unsigned char *d_sums,
+                          const float *d_centres, const float *d_points, const unsigned int *d_n_active,
+                          const ExtentPass *d_passes, float *d_results, int n_sms, cudaStream_t stream) {
+    const int NC = (n_cells + 15) / 16 * 16;
+    const size_t smem = smem_layout(NC, nullptr, nullptr);
     // the attribute is per device: set it on every launch (a few hundred nanoseconds)
     cudaFuncSetAttribute(extent_cell_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    extent_cell_kernel<<<(unsigned)n_sms, kThreads, smem, stream>>>(n_cells, n_spk, d_stream, d_centres,
-                                                                      d_n_active, d_passes, d_results);
+    static const int dbg = [] {
+      const char *e = std::getenv("EARB200_CELL_DBG");
+      return e ? std::atoi(e) : 0;
+    }();
+    extent_cell_kernel<<<(unsigned)n_sms, kThreads, smem, stream>>>(
+        n_cells, NC, n_spk, d_stream, d_sums, d_centres, reinterpret_cast<const float4 *>(d_points), d_n_active,
+        d_passes, d_results, dbg);
   }
 }  // namespace earb

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <vector>
 
 #include "tables.h"
@@ -10,6 +11,16 @@
 #define EARB_CORE_THREADS 1024
 
 namespace earb {
+
+  // Kernel attributes (the opt-in to more than 48 KB of dynamic shared memory) are per DEVICE:
+  // a process may hold handles on several GPUs, so "configured once" is tracked per device.
+  // Returns true the first time it is called for the current device with this mask.
+  inline bool first_use_on_current_device(std::atomic<unsigned long long> &mask) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const unsigned long long bit = 1ull << (dev & 63);
+    return !(mask.fetch_or(bit) & bit);
+  }
 
   // device-resident struct-of-arrays form of ear::ObjectsTypeMetadata
   // (ref include/ear/metadata.hpp:127-145): the eight fields the polar path reads
@@ -26,10 +37,13 @@ namespace earb {
   void launch_psp_batch(const PspTables *d_tables, long n, const double *d_xyz,
                         double *d_gains, int32_t *d_region, int32_t *d_inner,
                         cudaStream_t stream);
-  // writes the active passes compacted to d_passes[0 .. *d_n_active) (d_n_active must be zero)
-  // (thresholds: also the fade's start / end cos and sin, which only the FFMA core reads)
+  // writes the active passes compacted to d_passes[0 .. d_counters[0]) and the objects that need the
+  // point source panner (all of them with all_points) to d_point_list[0 .. d_counters[1]); both
+  // counters must be zero (thresholds: also the fade's start / end cos and sin, which only the FFMA
+  // core reads)
   void launch_objects_prelude(long n, const ObjectsSoA &in, ExtentPass *d_passes, ObjectAux *d_aux,
-                              unsigned int *d_n_active, bool thresholds, cudaStream_t stream);
+                              unsigned int *d_counters, int32_t *d_point_list, bool all_points,
+                              bool thresholds, cudaStream_t stream);
   size_t extent_core_smem_bytes(const ExtentGrid &grid);
 #define EXTENT_TC_STAGE_POINTS 64
   // tcgen05 extent core (extent_tc_kernels.cu): thread-per-pass weights feeding 3xTF32 UMMAs
@@ -53,13 +67,20 @@ namespace earb {
   void extent_cells_build(int n_points, const float *xyz, int n_points_pad, ExtentCells &out);
   size_t extent_cell_stream_bytes(const ExtentCells &cells);
   size_t extent_cell_centre_floats(const ExtentCells &cells);
-  void extent_cell_build_stream(const ExtentCells &cells, int n_spk, int n_points_pad, const float *xyz,
-                                const float *gains, unsigned char *stream);
+  size_t extent_cell_sum_bytes(const ExtentCells &cells);
+  size_t extent_cell_point_floats(const ExtentCells &cells);
+  // gains: speaker-major [S][Pp] float in grid order; xyz: [3][Pp] float
+  void extent_cell_build_stream(const ExtentCells &cells, int n_spk, int n_points_pad, const float *gains,
+                                unsigned char *stream);
+  void extent_cell_build_sums(const ExtentCells &cells, int n_spk, int n_points_pad, const float *gains,
+                              unsigned char *sums);
+  void extent_cell_build_points(const ExtentCells &cells, int n_points_pad, const float *xyz, float *out);
   void extent_cell_build_centres(const ExtentCells &cells, float *out);
-  size_t extent_cell_smem_bytes(int n_cells);
-  void launch_extent_cell(int n_cells, int n_spk, const unsigned char *d_stream, const float *d_centres,
-                          const unsigned int *d_n_active, const ExtentPass *d_passes, float *d_results,
-                          int n_sms, cudaStream_t stream);
+  size_t extent_cell_smem_bytes(const ExtentCells &cells);
+  bool extent_cell_supported(const ExtentCells &cells);
+  void launch_extent_cell(int n_cells, int n_spk, const unsigned char *d_stream, const unsigned char *d_sums,
+                          const float *d_centres, const float *d_points, const unsigned int *d_n_active,
+                          const ExtentPass *d_passes, float *d_results, int n_sms, cudaStream_t stream);
   // FFMA extent core (objects_kernels.cu), warp per pass
   void launch_extent_core(const ExtentGrid &grid, const float *d_xyz, const float *d_gains,
                           const float *d_block_sums, const unsigned int *d_n_active,
@@ -72,7 +93,8 @@ namespace earb {
   template <typename OutT>
   void launch_objects_epilogue(const PspTables *d_tables, int n_real, long n, const ObjectsSoA &in,
                                const ExtentPass *d_passes, const ObjectAux *d_aux,
-                               const float *d_results, double *d_point_gains, int n_out,
+                               const float *d_results, double *d_point_gains, const unsigned int *d_counters,
+                               const int32_t *d_point_list, int n_sms, int n_out,
                                const int32_t *d_out_index, OutT *d_direct, OutT *d_diffuse,
                                int32_t *d_region, cudaStream_t stream);
 

@@ -687,15 +687,14 @@ namespace earb {
     if (n_tiles <= 0) return true;
     EncodeTiledFn encode = encode_tiled();
     if (!encode) return false;
-    static bool configured = false;
-    if (!configured) {
+    static std::atomic<unsigned long long> configured{0};
+    if (first_use_on_current_device(configured)) {
       cudaFuncSetAttribute(render_tc_persistent_kernel<32, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)kSmemBudget);
       cudaFuncSetAttribute(render_tc_persistent_kernel<32, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)kSmemBudget);
       cudaFuncSetAttribute(render_tc_persistent_kernel<64, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)kSmemBudget);
-      configured = true;
     }
     const TcShape sh = tc_shape(N, M);
     const unsigned grid = (unsigned)std::min<long>(n_tiles * sh.n_out_groups, n_sms > 0 ? n_sms : 148);
