@@ -20,22 +20,29 @@
 //   warps 0..15  phase 1   thread = pass: pass constants -> shared memory; the weight function at
 //                          the cell centres -> class of every (pass, cell): mixed -> bit masks by
 //                          ballot; all-ones -> an fp16 0/1 INDICATOR row written to TMEM.
-//                phase 1.5 per-cell counts and prefix sums; the lists of mixed passes of every
-//                          cell, compacted into one pool (in rounds of cells if it overflows).
+//                phase 1.5 per-cell counts and prefix sums (one warp); the lists of mixed passes of
+//                          every cell, compacted into one pool (thread = one ballot word; in rounds
+//                          of cells if the pool overflows).
 //                phase 2   "evaluators": a batch = 32 mixed (pass, cell) items of ONE cell, lane =
-//                          pass; 16 weights per lane, split into fp16 hi + lo and stored into the
-//                          A stage of the cell in shared memory (UMMA K-major layout).  Batches are
-//                          dealt round-robin; a warp only touches the barriers of its own batches
-//                          and runs ahead of the tensor pipe by the depth of the A ring.
+//                          pass; 16 weights per lane (point coordinates: warp-uniform shared-memory
+//                          broadcasts), split into fp16 hi + lo and stored into the A stage of the
+//                          cell in shared memory (UMMA K-major layout).  Batches are dealt
+//                          round-robin; a warp only touches the barriers of its own batches and
+//                          runs ahead of the tensor pipe by the depth of the A ring.
 //                epilogue  thread = pass: tcgen05.ld of the accumulator row, normalise, store.
-//   warps 16..18 cleaners  one per A stage; after the UMMAs of a cell: zeroes the rows its batches
-//                          wrote (an A stage is all zeros except the mixed rows) and arms the stage
-//                          for its next cell.
-//   warp  19     MMA       per tile:  acc  = indicator[passes x cells] * Gsum[cells x S]  (fp16 hi +
+//   warp  16     MMA       per tile:  acc  = indicator[passes x cells] * Gsum[cells x S]  (fp16 hi +
 //                                     mid + lo of the per-cell gain sums: the all-ones cells)
 //                          per cell:  [main | corr] += A_hi * [G_hi | G_lo]   (N = 48)
 //                                     corr          += A_lo * G_hi            (N = 32)
-//   warp  20     producer  streams the per-cell gain image through a ring (cp.async.bulk).
+//                          with the rows that are NOT mixed for the cell switched off through the
+//                          disable-output-lane mask of tcgen05.mma (the ballot masks of phase 1,
+//                          inverted): an A stage only ever holds valid data in the mixed rows of its
+//                          current cell, whatever else it holds never reaches an accumulator, so a
+//                          stage needs no cleaning between cells.
+//   warp  17     producer  streams the per-cell gain image through a ring (cp.async.bulk).
+// Every cell has its own pair of mbarriers (a_full: its mixed rows are stored; a_free: the UMMAs
+// that read them have finished), each completing once per tile, so a warp that only visits some
+// of the cells can wait for any of them by the parity of the tile.
 // fp16 hi + lo carries 22 bits of the weight and of the gain (|error| <= 6e-8 absolute; weights
 // and gains lie in [0, 1]); all products accumulate in fp32 in TMEM.
 #include <cuda_fp16.h>
@@ -45,6 +52,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdlib>
+#include <cstdio>
 #include <cstring>
 #include <vector>
 
@@ -56,10 +64,16 @@ namespace earb {
     constexpr int kMT = 4;                     // M-tiles per tile
     constexpr int kTileRows = kMT * 128;
     constexpr int kEvalWarps = kTileRows / 32;  // 16
-    constexpr int kD = 3;                            // A ring depth in cells
-    constexpr int kCleanWarp = kEvalWarps;           // kD cleaner warps, one per A stage
-    constexpr int kMmaWarp = kEvalWarps + kD, kProdWarp = kMmaWarp + 1;
-    constexpr int kThreads = (kProdWarp + 1) * 32;  // 672
+    // A ring depth in cells.  Measured (r2h): depth 2 and 3 run at the same speed, depth 1 14 %
+    // slower -- the UMMAs of a cell (8 of them, each reading 4 KB of A for 25 cycles of math) and
+    // their issue by one thread set the pace, not the time a stage waits for them -- so the third
+    // stage's 32 KB hold the point table instead.
+    constexpr int kD = 2;
+    // One issuer (a single thread).  Four issuer warps, one per M-tile, were measured slower
+    // (0.441 against 0.406 ms per launch): the per-cell waits, fences and commits are paid four
+    // times and the polling warps take issue slots from the evaluators.
+    constexpr int kMmaWarp = kEvalWarps, kMmaWarps = 1, kProdWarp = kMmaWarp + kMmaWarps;
+    constexpr int kThreads = (kProdWarp + 1) * 32;  // 576
     constexpr int kBCells = 4;                       // cells per stream stage
     constexpr int kBStages = 4;
     constexpr int kRows = 48;                        // B rows: 24 G_hi + 24 G_lo
@@ -116,22 +130,6 @@ namespace earb {
         if (!done && ++spins > 20000000u) __trap();
       } while (!done);
     }
-    // monotone progress counters in shared memory (waiters may skip values, unlike barrier phases)
-    __device__ __forceinline__ void counter_publish(uint32_t *ctr, uint32_t v) {
-      asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_u32(ctr)), "r"(v) : "memory");
-    }
-    // polls with a short sleep in between: a spinning warp would take issue slots from the warps
-    // it is waiting for
-    __device__ __forceinline__ void counter_wait(uint32_t *ctr, uint32_t at_least) {
-      uint32_t v;
-      uint32_t spins = 0;
-      while (true) {
-        asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(v) : "r"(smem_u32(ctr)) : "memory");
-        if (v >= at_least) break;
-        __nanosleep(100);
-        if (++spins > 20000000u) __trap();
-      }
-    }
     __device__ __forceinline__ void fence_proxy_async() {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -155,14 +153,16 @@ namespace earb {
                    : "memory");
     }
     // D[tmem] (+)= A * B[smem desc], kind::f16 (fp16 operands, fp32 accumulate); A from shared
-    // memory (descriptor) or from TMEM (two K elements per 32-bit column)
-    __device__ __forceinline__ void umma_f16_ss(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
-                                                uint32_t idesc, uint32_t accumulate) {
+    // memory (descriptor) or from TMEM (two K elements per 32-bit column).
+    // A from shared memory, with a disable-output-lane mask: bit i of mask word j set = row
+    // 32 j + i of D is left as it is
+    __device__ __forceinline__ void umma_f16_ss_masked(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc,
+                                                       uint32_t idesc, const uint4 &mask) {
       asm volatile(
           "{\n\t.reg .pred p;\n\t"
-          "setp.ne.b32 p, %4, 0;\n\t"
-          "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-          ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+          "setp.ne.b32 p, 1, 0;\n\t"
+          "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, {%4, %5, %6, %7}, p;\n\t}"
+          ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(mask.x), "r"(mask.y), "r"(mask.z), "r"(mask.w)
           : "memory");
     }
     __device__ __forceinline__ void umma_f16_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc,
@@ -291,6 +291,8 @@ namespace earb {
       unsigned short *nbp;    // [NC + 1] batch prefix
       unsigned short *round_end;  // [NC] last cell (exclusive) of every round; [NC] = number of rounds
       unsigned short *pool;   // [kPoolCap]
+      uint64_t *a_full, *a_free;  // [NC] mbarriers, one pair per cell
+      float4 *points;             // [n_cells][12] the 16 points of every cell (evaluator layout)
     };
     __host__ __device__ inline size_t smem_layout(int NC, unsigned char *base, Smem *s) {
       size_t o = 0;
@@ -306,7 +308,11 @@ namespace earb {
       unsigned char *ctr = take((size_t)(NC / 2) * 48), *off = take((size_t)(NC + 1) * 4);
       unsigned char *nmixed = take((size_t)NC * 2), *nbp = take((size_t)(NC + 1) * 2);
       unsigned char *round_end = take((size_t)(NC + 1) * 2), *pool = take((size_t)kPoolCap * 2);
+      unsigned char *a_full = take((size_t)NC * 8), *a_free = take((size_t)NC * 8);
+      unsigned char *points = take((size_t)NC * 12 * 16);
       if (s) {
+        s->points = reinterpret_cast<float4 *>(points);
+        s->a_full = reinterpret_cast<uint64_t *>(a_full), s->a_free = reinterpret_cast<uint64_t *>(a_free);
         s->A = A, s->B = B, s->consts = consts, s->sum1 = sum1, s->sum2 = sum2;
         s->mixed = reinterpret_cast<uint32_t *>(mixed);
         s->pw = reinterpret_cast<unsigned short *>(pw);
@@ -320,16 +326,16 @@ namespace earb {
       return o;
     }
 
-    // Barriers and counters (barrier parities follow counters that run on across tiles; every
-    // waiter of a barrier follows each of its phases)
-    //   tables_ready  16 evaluator warps -> cleaner, MMA   phase 1 / 1.5 of the tile are complete
-    //   a_full[s]     cleaner (17 - batches) + one per batch -> MMA   all mixed rows of the cell stored
-    //   a_free[s]     MMA commit -> cleaner                 the UMMAs reading the A stage have finished
-    //   b_full[t]     producer -> MMA                       stream stage t has landed (tx bytes)
-    //   b_empty[t]    MMA commit -> producer                the UMMAs reading stream stage t have finished
-    //   acc_full      MMA commit -> epilogue                every UMMA of the tile has finished
-    //   armed_uses[s]    cleaner s -> evaluators   uses of A stage s that are clean and armed
-    //   cleaned_uses[s]  cleaner s -> evaluators   uses of A stage s whose rows are zero again
+    // Barriers (parities follow the tile index, except the stream ring's, which runs on across tiles)
+    //   tables_ready  16 evaluator warps -> MMA            phase 1 / 1.5 of the tile are complete
+    //   a_full[k]     (17 - batches of cell k) arrivals by phase 1.5 + one per batch -> MMA
+    //                                                      all mixed rows of cell k are stored
+    //   a_free[k]     MMA commit -> evaluators of cell k + kD    the UMMAs reading the A stage of
+    //                                                      cell k have finished
+    //   b_full[t]     producer -> MMA                      stream stage t has landed (tx bytes)
+    //   b_empty[t]    MMA commit -> producer               the UMMAs reading stream stage t have finished
+    //   acc_full      MMA commit -> epilogue               every UMMA of the tile has finished (all A
+    //                                                      stages are free, the tables may be rewritten)
     __global__ void __launch_bounds__(kThreads, 1)
         extent_cell_kernel(int n_cells, int NC, int n_spk, const unsigned char *__restrict__ g_stream,
                            const unsigned char *__restrict__ g_sums, const float *__restrict__ g_centres,
@@ -338,10 +344,7 @@ namespace earb {
       extern __shared__ __align__(128) unsigned char smem_raw[];
       Smem sm;
       smem_layout(NC, smem_raw, &sm);
-      __shared__ __align__(8) uint64_t a_full[kD], a_free[kD];
       __shared__ __align__(8) uint64_t b_full[kBStages], b_empty[kBStages], acc_full, tables_ready;
-      // per A stage: number of uses armed / cleaned so far (use u of stage s = cell u * kD + s)
-      __shared__ uint32_t armed_uses[kD], cleaned_uses[kD];
       __shared__ uint32_t tmem_base_s;
 
       const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -351,34 +354,37 @@ namespace earb {
       const int p_begin = min(n_active, (int)blockIdx.x * per_cta), p_end = min(n_active, p_begin + per_cta);
       const int n_tiles = (p_end - p_begin + kTileRows - 1) / kTileRows;
       const int n_bstages = n_cells / kBCells;
+      // experiments (EARB200_CELL_DBG): bits 8..10 = A ring depth (default kD), 32 = no a_free wait
+      const int kd = ((dbg >> 8) & 7) ? min(kD, (dbg >> 8) & 7) : kD;
       if (n_tiles == 0) return;  // no passes for this CTA (small batches): nothing to set up
 
       for (int j = tid; j < (NC / 2) * 12; j += kThreads) sm.ctr[j] = g_centres[j];
+      for (int j = tid; j < n_cells * 12; j += kThreads) sm.points[j] = g_points[j];
       {
         const uint4 *src = reinterpret_cast<const uint4 *>(g_sums);
         uint4 *d1 = reinterpret_cast<uint4 *>(sm.sum1), *d2 = reinterpret_cast<uint4 *>(sm.sum2);
         const int n1 = (NC / 16) * kSum1Bytes / 16, n2 = (NC / 16) * kSum2Bytes / 16;
         for (int j = tid; j < n1; j += kThreads) d1[j] = src[j];
         for (int j = tid; j < n2; j += kThreads) d2[j] = src[n1 + j];
-        // the A ring starts all zeros
+        // the A ring starts all zeros (only so that no NaN pattern ever enters a UMMA: rows that
+        // are not mixed are masked out of the accumulators anyway)
         uint4 *a = reinterpret_cast<uint4 *>(sm.A);
         for (int j = tid; j < kD * kAStageBytes / 16; j += kThreads) a[j] = make_uint4(0u, 0u, 0u, 0u);
       }
       fence_proxy_async();
+      if (tid < NC) {
+        mbar_init(&sm.a_full[tid], kEvalWarps + 1);
+        mbar_init(&sm.a_free[tid], kMmaWarps);
+      }
       if (tid == 0) {
-        for (int s = 0; s < kD; s++) {
-          mbar_init(&a_full[s], kEvalWarps + 1);
-          mbar_init(&a_free[s], 1);
-        }
         for (int s = 0; s < kBStages; s++) {
           mbar_init(&b_full[s], 1);
-          mbar_init(&b_empty[s], 1);
+          mbar_init(&b_empty[s], kMmaWarps);
         }
-        mbar_init(&acc_full, 1);
+        mbar_init(&acc_full, kMmaWarps);
         mbar_init(&tables_ready, kEvalWarps);
-        for (int s = 0; s < kD; s++) armed_uses[s] = cleaned_uses[s] = 0;
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
       if (warp == kMmaWarp) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
                          smem_u32(&tmem_base_s)),
@@ -406,6 +412,9 @@ namespace earb {
         }
       } else if (warp == kMmaWarp) {
         // ------------------------------------------------------------ MMA issuer
+        // The whole warp walks the loop (warp-uniform control flow, so that descriptors and masks
+        // stay in uniform registers; a single divergent thread makes the compiler wrap every UMMA
+        // in a uniformisation loop); an elected lane issues.
         const uint32_t tm = __shfl_sync(0xffffffffu, tmem_base, 0);
         uint32_t leader;
         asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(leader));
@@ -415,18 +424,18 @@ namespace earb {
         const uint32_t idesc32 = idesc_base | ((uint32_t)(32 >> 3) << 17);
         const uint32_t sA_addr = smem_u32(sm.A), sB_addr = smem_u32(sm.B);
         const uint32_t s1_addr = smem_u32(sm.sum1), s2_addr = smem_u32(sm.sum2);
-        int g = 0;  // cell counter, continuous across tiles
+        int g = 0;  // cell counter of the stream ring, continuous across tiles
         for (int tile = 0; tile < n_tiles; tile++) {
-          const int n_mt = min(kMT, (p_end - (p_begin + tile * kTileRows) + 127) / 128);
-          mbar_wait(&tables_ready, (uint32_t)(tile & 1));
+          const uint32_t par = (uint32_t)(tile & 1);
+          mbar_wait(&tables_ready, par);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           if (leader) {
             // the all-ones cells: acc = indicator * [Gsum_hi | Gsum_mid], corr += indicator * Gsum_lo
+            // (M-tiles beyond the passes of the last tile hold zero indicators and are not read back)
             for (int ks = 0; ks < NC / 16; ks++) {
               const uint64_t d1 = kmajor_desc(s1_addr + ks * kSum1Bytes), d2 = kmajor_desc(s2_addr + ks * kSum2Bytes);
 #pragma unroll
               for (int mt = 0; mt < kMT; mt++) {
-                if (mt >= n_mt) break;
                 const uint32_t acc = tm + mt * kAccCols;
                 const uint32_t a_ind = tm + kColInd + mt * (NC / 2) + ks * 8;
                 umma_f16_ts(acc, a_ind, d1, idesc48, ks != 0);
@@ -436,72 +445,35 @@ namespace earb {
           }
           __syncwarp();
           for (int k = 0; k < n_cells; k++, g++) {
-            const int s = g % kD, bsg = g / kBCells, bs = bsg % kBStages, sub = g % kBCells;
+            const int s = k % kD, bsg = g / kBCells, bs = bsg % kBStages, sub = g % kBCells;
+            // the masks of the cell: rows that are not mixed keep their accumulators (rows
+            // without a pass are never mixed)
+            uint4 off[kMT];
+#pragma unroll
+            for (int mt = 0; mt < kMT; mt++) {
+              off[mt] = *reinterpret_cast<const uint4 *>(sm.mixed + k * kEvalWarps + 4 * mt);
+              off[mt].x = ~off[mt].x, off[mt].y = ~off[mt].y, off[mt].z = ~off[mt].z, off[mt].w = ~off[mt].w;
+            }
             if (sub == 0) mbar_wait(&b_full[bs], (uint32_t)((bsg / kBStages) & 1));
-            mbar_wait(&a_full[s], (uint32_t)((g / kD) & 1));
+            mbar_wait(&sm.a_full[k], par);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const bool any = sm.nmixed[k] != 0;
             if (leader) {
-              if (any) {
+              if (!(dbg & 1)) {
                 const uint64_t bd = kmajor_desc(sB_addr + bs * kBStageBytes + sub * kCellBBytes);
 #pragma unroll
                 for (int mt = 0; mt < kMT; mt++) {
-                  if (mt >= n_mt) break;
+                  if ((off[mt].x & off[mt].y & off[mt].z & off[mt].w) == 0xffffffffu) continue;
                   const uint32_t acc = tm + mt * kAccCols;
                   const uint32_t a_hi = sA_addr + s * kAStageBytes + mt * 2 * kAPlaneBytes;
-                  if (dbg & 1) continue;
-                  umma_f16_ss(acc, kmajor_desc(a_hi), bd, idesc48, 1);
-                  umma_f16_ss(acc + 24, kmajor_desc(a_hi + kAPlaneBytes), bd, idesc32, 1);
+                  umma_f16_ss_masked(acc, kmajor_desc(a_hi), bd, idesc48, off[mt]);
+                  umma_f16_ss_masked(acc + 24, kmajor_desc(a_hi + kAPlaneBytes), bd, idesc32, off[mt]);
                 }
               }
-              umma_commit(&a_free[s]);
+              umma_commit(&sm.a_free[k]);
               if (sub == kBCells - 1) umma_commit(&b_empty[bs]);
               if (k == n_cells - 1) umma_commit(&acc_full);
             }
             __syncwarp();
-          }
-        }
-      } else if (warp >= kCleanWarp) {
-        // ------------------------------------------------------------ cleaners (one per A stage)
-        const uint32_t s = (uint32_t)(warp - kCleanWarp);
-        unsigned char *stage = sm.A + s * kAStageBytes;
-        uint32_t use = 0;  // uses of this stage so far (continuous across tiles)
-        for (int tile = 0; tile < n_tiles; tile++) {
-          const uint32_t gbase = (uint32_t)(tile * n_cells);
-          mbar_wait(&tables_ready, (uint32_t)(tile & 1));
-          // first cell of this stage in the tile; its stage is clean (end of the previous tile): arm it
-          int k = (int)((s + kD - gbase % kD) % kD);
-          if (k < n_cells) {
-            if (lane == 0) {
-              mbar_arrive(&a_full[s], (uint32_t)(kEvalWarps + 1 - ((sm.nmixed[k] + 31) >> 5)));
-              counter_publish(&armed_uses[s], use + 1);
-            }
-          }
-          int r = 0;
-          uint32_t round_off = 0;
-          for (; k < n_cells; k += kD, use++) {
-            while (k >= (int)sm.round_end[r]) {
-              round_off = sm.off[sm.round_end[r]];
-              r++;
-            }
-            const uint32_t n = sm.nmixed[k], base = sm.off[k] - round_off;
-            mbar_wait(&a_free[s], use & 1);
-            for (uint32_t i = (uint32_t)lane; i < n && !(dbg & 2); i += 32) {
-              unsigned char *dst = stage + a_row_offset(sm.pool[base + i]);
-              *reinterpret_cast<uint4 *>(dst) = make_uint4(0u, 0u, 0u, 0u);
-              *reinterpret_cast<uint4 *>(dst + 128) = make_uint4(0u, 0u, 0u, 0u);
-              *reinterpret_cast<uint4 *>(dst + kAPlaneBytes) = make_uint4(0u, 0u, 0u, 0u);
-              *reinterpret_cast<uint4 *>(dst + kAPlaneBytes + 128) = make_uint4(0u, 0u, 0u, 0u);
-            }
-            fence_proxy_async();
-            __syncwarp();
-            if (lane == 0) {
-              if (k + kD < n_cells) {
-                mbar_arrive(&a_full[s], (uint32_t)(kEvalWarps + 1 - ((sm.nmixed[k + kD] + 31) >> 5)));
-                counter_publish(&armed_uses[s], use + 2);
-              }
-              counter_publish(&cleaned_uses[s], use + 1);
-            }
           }
         }
       } else {
@@ -510,12 +482,14 @@ namespace earb {
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
         const uint32_t row_own = (uint32_t)(warp * 32 + lane);
         const uint32_t sConst_addr = smem_u32(sm.consts);
-        const uint32_t lt_mask = (1u << lane) - 1u;
         for (int tile = 0; tile < n_tiles; tile++) {
-          const uint32_t gbase = (uint32_t)(tile * n_cells);
+          const uint32_t par = (uint32_t)(tile & 1);
           const int idx = p_begin + tile * kTileRows + (int)row_own;
           const bool valid = idx < p_end;
           int slot;
+          long long tstamp[8];
+          const bool trace = (dbg & 64) && blockIdx.x == 1 && lane == 0 && (warp == 0 || warp == 9);
+          if (trace) tstamp[0] = clock64();
           // ---- phase 1: pass constants to shared memory, cell classes from the centres
           {
             PassRegs c;
@@ -567,8 +541,8 @@ namespace earb {
                 weight_fn2(c, pk(xy.x, xy.y), pk(xy.z, xy.w), pk(zz.x, zz.y), t0, t1);
                 const bool real0 = valid && 2 * cp < n_cells, real1 = valid && 2 * cp + 1 < n_cells;
                 const bool one0 = real0 && t0 >= th.x, one1 = real1 && t1 >= th.z;
-                const unsigned mix0 = __ballot_sync(0xffffffffu, real0 && !one0 && !(t0 <= th.y) && !(dbg & 16));
-                const unsigned mix1 = __ballot_sync(0xffffffffu, real1 && !one1 && !(t1 <= th.w) && !(dbg & 16));
+                const unsigned mix0 = __ballot_sync(0xffffffffu, real0 && !one0 && !(t0 <= th.y));
+                const unsigned mix1 = __ballot_sync(0xffffffffu, real1 && !one1 && !(t1 <= th.w));
                 if (lane == 0) {
                   sm.mixed[(2 * cp) * kEvalWarps + warp] = mix0;
                   sm.mixed[(2 * cp + 1) * kEvalWarps + warp] = mix1;
@@ -580,8 +554,11 @@ namespace earb {
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
           }
+          if (trace) tstamp[1] = clock64();
           asm volatile("bar.sync 1, %0;" ::"n"(kEvalWarps * 32) : "memory");
-          // ---- phase 1.5: counts, prefix sums, rounds
+          if (trace) tstamp[2] = clock64();
+          // ---- phase 1.5: counts, prefix sums, rounds; the a_full barrier of every cell gets the
+          // arrivals its missing batches will not make
           if ((int)row_own < NC) {
             const int k = (int)row_own;
             uint32_t run = 0;
@@ -591,6 +568,7 @@ namespace earb {
               run += (uint32_t)__popc(sm.mixed[k * kEvalWarps + w]);
             }
             sm.nmixed[k] = (unsigned short)run;
+            if (k < n_cells) mbar_arrive(&sm.a_full[k], (uint32_t)(kEvalWarps + 1) - ((run + 31u) >> 5));
           }
           asm volatile("bar.sync 1, %0;" ::"n"(kEvalWarps * 32) : "memory");
           if (warp == 0) {
@@ -618,7 +596,11 @@ namespace earb {
               sm.nbp[NC] = (unsigned short)carry_nb;
             }
             __syncwarp();
-            if (lane == 0) {
+            if (lane == 0 && carry_off <= (uint32_t)kPoolCap) {
+              // the usual case: the lists of the whole tile fit the pool
+              sm.round_end[0] = (unsigned short)n_cells;
+              sm.round_end[NC] = 1;
+            } else if (lane == 0) {
               int n_rounds = 0, k = 0;
               while (k < n_cells) {
                 const uint32_t start = sm.off[k];
@@ -632,6 +614,7 @@ namespace earb {
           }
           asm volatile("bar.sync 1, %0;" ::"n"(kEvalWarps * 32) : "memory");
           if (lane == 0) mbar_arrive(&tables_ready);
+          if (trace) tstamp[3] = clock64();
 
           // ---- phase 2: rounds of cells; lists of the round, then its batches
           const int n_rounds = sm.round_end[NC];
@@ -639,21 +622,23 @@ namespace earb {
           for (int r = 0; r < n_rounds; r++) {
             const int k_hi = sm.round_end[r];
             const uint32_t round_off = sm.off[k_lo];
-            // the pool is free once the cleaner is through with the cells before this round
-            if (r > 0) {
-              // every cell before k_lo cleaned: stage s has been used for the cells g < gbase + k_lo
-              // with g % kD == s
-              const uint32_t g_lo = gbase + (uint32_t)k_lo;
-#pragma unroll
-              for (uint32_t s = 0; s < (uint32_t)kD; s++) counter_wait(&cleaned_uses[s], (g_lo + kD - 1 - s) / kD);
-            }
-            for (int k = k_lo; k < k_hi; k++) {
-              const uint32_t mm = sm.mixed[k * kEvalWarps + warp];
-              if ((mm >> lane) & 1u)
-                sm.pool[sm.off[k] - round_off + sm.pw[k * kEvalWarps + warp] + __popc(mm & lt_mask)] =
-                    (unsigned short)row_own;
+            // the pool is free once every warp is through with the batches of the round before
+            if (r > 0) asm volatile("bar.sync 1, %0;" ::"n"(kEvalWarps * 32) : "memory");
+            // thread = (cell, word of 32 passes): consecutive threads read consecutive words, and
+            // each walks the set bits of its word (a warp-uniform walk over the cells costs a
+            // shared-memory instruction per word for all 32 lanes: 6,600 per tile and SM)
+            for (int t = (int)row_own; t < (k_hi - k_lo) * kEvalWarps; t += kEvalWarps * 32) {
+              const int kw = k_lo * kEvalWarps + t, k = kw / kEvalWarps;
+              uint32_t mm = sm.mixed[kw];
+              unsigned short *dst = sm.pool + (sm.off[k] - round_off + sm.pw[kw]);
+              const uint32_t row0 = (uint32_t)(kw % kEvalWarps) * 32u;
+              while (mm) {
+                *dst++ = (unsigned short)(row0 + (uint32_t)__ffs((int)mm) - 1u);
+                mm &= mm - 1u;
+              }
             }
             asm volatile("bar.sync 1, %0;" ::"n"(kEvalWarps * 32) : "memory");
+            if (trace) tstamp[4] = clock64();
             int k = k_lo;
             const int b_end = sm.nbp[k_hi];
             for (int b = (int)sm.nbp[k_lo] + warp; b < b_end; b += kEvalWarps) {
@@ -684,15 +669,15 @@ namespace earb {
                 c.a_sin = fmaf(c.m, 1.57079632679490f, c.c);
               }
               // the 16 points of the cell: eight (x, x', y, y') then four (z, z', z'', z''')
-              // (warp-uniform loads through L1)
-              const float4 *pts = g_points + (size_t)k * 12;
+              // (warp-uniform shared-memory broadcasts)
+              const float4 *pts = sm.points + k * 12;
               uint32_t hi[kCell / 2], lo[kCell / 2];
 #pragma unroll
               for (int i = 0; i < kCell / 2; i++) hi[i] = lo[i] = 0u;
               if (!(dbg & 4))
 #pragma unroll
               for (int i = 0; i < kCell / 2; i += 2) {
-                const float4 xy0 = __ldg(pts + i), xy1 = __ldg(pts + i + 1), zz = __ldg(pts + 8 + i / 2);
+                const float4 xy0 = pts[i], xy1 = pts[i + 1], zz = pts[8 + i / 2];
                 float t[4];
                 weight_fn2(c, pk(xy0.x, xy0.y), pk(xy0.z, xy0.w), pk(zz.x, zz.y), t[0], t[1]);
                 weight_fn2(c, pk(xy1.x, xy1.y), pk(xy1.z, xy1.w), pk(zz.z, zz.w), t[2], t[3]);
@@ -706,26 +691,28 @@ namespace earb {
                   lo[i + h] = *reinterpret_cast<const uint32_t *>(&ll);
                 }
               }
-              // the A stage of the cell must be clean and armed
-              const uint32_t g = gbase + (uint32_t)k, s = g % kD;
-              if (!(dbg & 32)) counter_wait(&armed_uses[s], g / kD + 1);
-              if (active && !(dbg & 8)) {
-                unsigned char *dst = sm.A + s * kAStageBytes + a_row_offset(row);
+              // the A stage of the cell is free once the UMMAs of the cell kD before have finished
+              // (at the start of a tile every stage is free: acc_full)
+              if (k >= kd && !(dbg & 32)) mbar_wait(&sm.a_free[k - kd], par);
+              if (active) {
+                unsigned char *dst = sm.A + (k % kd) * kAStageBytes + a_row_offset(row);
                 *reinterpret_cast<uint4 *>(dst) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
                 *reinterpret_cast<uint4 *>(dst + 128) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
                 *reinterpret_cast<uint4 *>(dst + kAPlaneBytes) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
                 *reinterpret_cast<uint4 *>(dst + kAPlaneBytes + 128) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
               }
-              if (!(dbg & 8)) fence_proxy_async();
+              fence_proxy_async();
               __syncwarp();
-              if (lane == 0) mbar_arrive(&a_full[s]);
+              if (lane == 0) mbar_arrive(&sm.a_full[k]);
             }
             k_lo = k_hi;
           }
 
           // ---- epilogue: this thread's row of [main | corr]; results /= ||results|| in float
           // (ref polar_extent.cpp:271-273)
-          mbar_wait(&acc_full, (uint32_t)(tile & 1));
+          if (trace) tstamp[5] = clock64();
+          mbar_wait(&acc_full, par);
+          if (trace) tstamp[6] = clock64();
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           if (p_begin + tile * kTileRows + mt * 128 < p_end) {  // M-tiles without passes were not computed
             float r[48];
@@ -755,11 +742,11 @@ namespace earb {
             }
           }
           asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-          // the cleaner is through with the tile: tables, pool and constants may be overwritten
-          {
-            const uint32_t g_hi = gbase + (uint32_t)n_cells;
-#pragma unroll
-            for (uint32_t s = 0; s < (uint32_t)kD; s++) counter_wait(&cleaned_uses[s], (g_hi + kD - 1 - s) / kD);
+          if (trace) {
+            tstamp[7] = clock64();
+            printf("trace w%d tile %d: ph1 %lld bar %lld ph1.5 %lld pool %lld batches %lld accwait %lld epi %lld | items %u batches %u\n",
+                   warp, tile, tstamp[1] - tstamp[0], tstamp[2] - tstamp[1], tstamp[3] - tstamp[2], tstamp[4] - tstamp[3],
+                   tstamp[5] - tstamp[4], tstamp[6] - tstamp[5], tstamp[7] - tstamp[6], sm.off[NC], (unsigned)sm.nbp[NC]);
           }
         }
       }
