@@ -195,18 +195,17 @@ def run_reference(args):
         print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libear_ref.so not built"}))
         return
     threads = host_threads()
-    objs = synth_objects(400_000, 2)
-    # size one step at ~3 s of wall time on all threads
-    rate, n, dt = cpu_objects_throughput(objs, threads, 1.0)
-    step_n = int(max(threads * 500, min(len(objs[0]) // threads * threads, rate * 3.0)))
-    step_n -= step_n % threads
+    # the GPU arm's own input: the same 10^6 objects (rank 0's seed), every one of them per step
+    objs = synth_objects(args.objects, 2)
+    step_n = len(objs[0])
     calcs = [ref.Objects(LAYOUT) for _ in range(threads)]
-    per = step_n // threads
+    per = -(-step_n // threads)
 
     def step():
         def work(i):
-            sl = slice(i * per, (i + 1) * per)
-            calcs[i].calculate(*[a[sl] for a in objs], dtype=np.float32)
+            sl = slice(i * per, min(step_n, (i + 1) * per))
+            if sl.start < step_n:
+                calcs[i].calculate(*[a[sl] for a in objs], dtype=np.float32)
         ths = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
         [t.start() for t in ths]
         [t.join() for t in ths]
@@ -223,9 +222,11 @@ def run_reference(args):
         "unit": "vectors/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"configs[1] (SURVEY cfg 2) sample: {step_n} extent objects/step on {LAYOUT} "
-                               "(same distribution as the GPU arm's 1M objects/GPU)",
-                   "layout": LAYOUT},
+        "config": {"workload": f"configs[1] (SURVEY cfg 2): {step_n} extent objects/GPU on {LAYOUT} via the batched "
+                               "GainCalculatorObjects C-ABI (1,652-point spreading grid, depth != 0 for half)",
+                   "layout": LAYOUT, "objects_per_gpu": step_n,
+                   "note": "libear's GainCalculatorObjects::calculate<float> on the host cores, the GPU arm's "
+                           "own input (same seed), all of it every step"},
         "cpu_baseline": {"value": value, "unit": "vectors/s", "cores": threads, "kind": "reference",
                          "sample": f"{step_n} objects/step x {args.steps} steps, libear "
                                    f"GainCalculatorObjects::calculate<float>, xsimd ISA {ref.extent_isa()}"},
@@ -233,6 +234,23 @@ def run_reference(args):
         "gpu_launches": 0,
     }
     print(json.dumps(line))
+
+
+def ref_objects_threaded(ref, args_list, threads):
+    """libear on a list of object columns, one calculator per thread (checker, outside any timing)."""
+    n = len(args_list[0])
+    per = -(-n // threads)
+    outs = [None] * threads
+
+    def work(i):
+        sl = slice(i * per, min(n, (i + 1) * per))
+        if sl.start < n:
+            outs[i] = ref.Objects(LAYOUT).calculate(*[a[sl] for a in args_list], dtype=np.float32)
+    ths = [threading.Thread(target=work, args=(i,)) for i in range(threads)]
+    [t.start() for t in ths]
+    [t.join() for t in ths]
+    outs = [o for o in outs if o is not None]
+    return np.concatenate([o[0] for o in outs]), np.concatenate([o[1] for o in outs])
 
 
 # ------------------------------------------------------------------ our arm
@@ -281,6 +299,39 @@ def run_ours(args):
     hbm_peak, bf16_peak, peak_src = measured_peaks()
     stream = torch.cuda.current_stream().cuda_stream
     sampler = ClockSampler(local_rank)
+    # what the timed regions produced is compared with libear (oracle/_ref, the checker) AFTER the
+    # timing, on samples; a failed check makes the run exit non-zero
+    parity = {"checked_against": "libear (oracle/_ref) on samples of the buffers the timed regions wrote", "ok": True}
+    check = rank == 0 and not args.no_parity
+    if check:
+        from oracle import ref as oref
+        check = oref.available()
+        if not check:
+            parity = {"ok": None, "note": "oracle/_ref/libear_ref.so not built: nothing checked"}
+
+    def sustained(step_fn, units_per_step, seconds):
+        """the same step back to back for `seconds` of device time (clocks settle under load)"""
+        if seconds <= 0:
+            return None
+        s_sampler = ClockSampler(local_rank)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        step_fn()
+        e1.record()
+        torch.cuda.synchronize()
+        k = int(max(10, seconds * 1e3 / max(e0.elapsed_time(e1), 1e-3)))
+        barrier()
+        s_sampler.start()
+        e0.record()
+        for _ in range(k):
+            step_fn()
+        e1.record()
+        barrier()
+        s_sampler.stop()
+        ms = max_over_ranks(e0.elapsed_time(e1))
+        cl = s_sampler.summary()
+        return {"value": units_per_step * world * k / (ms * 1e-3), "steps": k, "seconds": ms * 1e-3,
+                "ms_per_step": ms / k, "sm_mhz": cl["sm_mhz"], "reasons": cl["reasons"]}
 
     # ---------------- objects: BASELINE config 1 (1M extent objects per GPU on 9+10+3)
     n = args.objects
@@ -343,6 +394,23 @@ def run_ours(args):
         e2e_dt = max_over_ranks(time.perf_counter() - t0)
         e2e_value = n * world * e2e_steps / e2e_dt
         e2e_checksum = float(h_direct[:1000].double().sum())
+
+    objects_sustained = sustained(step_objects, n, args.sustained)
+    if check:
+        # a strided sample of the rows the timed device path wrote, and the host path's rows
+        sl = slice(7, n, max(1, n // 20_000))
+        got_d, got_f = d_direct[sl].cpu().numpy(), d_diffuse[sl].cpu().numpy()
+        exp_d, exp_f = ref_objects_threaded(oref, [a[sl] for a in objs], host_threads())
+        fin = np.isfinite(exp_d).all(1) & np.isfinite(exp_f).all(1)   # libear's own acos(>1) NaNs, ~1 in 3e5
+        parity["gains_max_abs"] = float(max(np.abs(got_d[fin] - exp_d[fin]).max(), np.abs(got_f[fin] - exp_f[fin]).max()))
+        parity["gains_n_checked"] = int(fin.sum())
+        parity["gains_bar"] = 1e-5
+        if e2e_value is not None:
+            parity["e2e_rows_equal_device_rows"] = bool(
+                np.array_equal(h_direct[sl].numpy().view(np.uint32), got_d.view(np.uint32)) and
+                np.array_equal(h_diffuse[sl].numpy().view(np.uint32), got_f.view(np.uint32)))
+            parity["ok"] = parity["ok"] and parity["e2e_rows_equal_device_rows"]
+        parity["ok"] = parity["ok"] and parity["gains_max_abs"] < 1e-5 and fin.mean() > 0.999
 
     # ---------------- render: BASELINE config 2 (128 objects x 60 s x 48 kHz into 4+9+0)
     render = None
@@ -410,6 +478,20 @@ def run_ours(args):
                          "kernel": "render_tc_persistent_kernel<32>", "kernel_ms": k_ms / max(1, k_launches),
                          "algorithmic_bytes_per_launch": alg_bytes},
         }
+        if world == 1:
+            render["sustained"] = sustained(step_render, N * T / 1e6, args.sustained)
+        if check and world == 1:
+            wr = np.random.default_rng(17)
+            peak = float(y.abs().max())
+            worst = 0.0
+            starts = [0, T - 512] + [int(t) for t in wr.integers(0, T - 512, 14)]
+            for t0 in starts:
+                exp = oref.interp_matrix(x[:, t0:t0 + 512].cpu().numpy(), samples, gains, block_start0=t0)
+                worst = max(worst, float(np.abs(y[:, t0:t0 + 512].cpu().numpy() - exp).max()) / peak)
+            parity["render_audio_max_over_peak"] = worst
+            parity["render_windows_checked"] = len(starts)
+            parity["render_bar"] = 2e-6
+            parity["ok"] = parity["ok"] and worst < 2e-6
         # end to end: pinned host input/output through the C-ABI host entry point
         if world == 1 and not args.no_render_e2e:
             hx = torch.empty((N, T), dtype=torch.float32).pin_memory()
@@ -519,6 +601,25 @@ def run_ours(args):
                          "note": "8 B/sample; the FP32 butterflies (about 2,300 warp instructions per pair of "
                                  "blocks) bound the kernel before HBM does (DESIGN.md section 3, K4)"},
         }
+        if world == 1:
+            conv_block["sustained"] = sustained(step_conv, Cc * Tc / 1e6, args.sustained)
+        if check and world == 1 and Kc > 16:
+            wr = np.random.default_rng(5)
+            peak = float(ys.abs().max())
+            worst = 0.0
+            picks = [(0, 0), (Cc - 1, Kc - 9)] + [(int(wr.integers(0, Cc)), int(wr.integers(1, Kc - 9))) for _ in range(4)]
+            for c, k0 in picks:
+                # one block of history: the tail of block k0 - 1; the stream continues from step to
+                # step over the same input, so block 0 follows the last block of the step before
+                hist = xs[c, (k0 - 1) * Bc:k0 * Bc] if k0 > 0 else xs[c, (Kc - 1) * Bc:Kc * Bc]
+                rc = oref.Convolver(Bc, 1)
+                fid, _ = rc.add_filter(filt[c])
+                rc.set_filter(fid)
+                exp = rc.process(torch.cat([hist, xs[c, k0 * Bc:(k0 + 8) * Bc]]).cpu().numpy())[Bc:]
+                worst = max(worst, float(np.abs(ys[c, k0 * Bc:(k0 + 8) * Bc].cpu().numpy() - exp).max()) / peak)
+            parity["convolver_audio_max_over_peak"] = worst
+            parity["convolver_slices_checked"] = len(picks)
+            parity["ok"] = parity["ok"] and worst < 1e-6
         if world == 1 and not args.no_render_e2e:
             hx = torch.empty((Cc, Tc), dtype=torch.float32).pin_memory()
             hx.copy_(xs)
@@ -721,19 +822,24 @@ def run_ours(args):
                        "l2": "inputs+outputs 256 MB/step/GPU > 126 MB L2", "sharding": "objects, no collective"},
             "roofline": {"bound": "tensor", "achieved": core_tflops, "peak": bf16_peak, "unit": "TFLOP/s",
                          "frac": core_tflops / bf16_peak,
-                         "traffic": ncu_traffic("extent_core_tc_kernel") if n >= 262144 else None,
+                         "traffic": ncu_traffic("extent_cell_kernel") if n >= 262144 else None,
                          "peak_source": peak_src,
-                         "kernel": "extent_core_tc_kernel", "kernel_ms": core_ms / max(1, core_launches),
+                         "kernel": "extent_cell_kernel", "kernel_ms": core_ms / max(1, core_launches),
                          "algorithmic_flop_per_pass": FLOP_PER_PASS,
-                         "note": "contraction flops only; the kernel is FP32-ALU bound by the 1,652 weight "
-                                 "evaluations per pass (DESIGN.md section 4)",
+                         "note": "contraction flops of the reference's loop (all 1,652 points of every pass); the "
+                                 "kernel culls cells of 16 points whose weights are all 0 or all 1 and evaluates "
+                                 "the rest point by point -- issue-bound on that, not on the tensor pipe (DESIGN.md section 3)",
                          "weight_evals_per_s": weight_evals,
                          "kernel_share_of_step": core_ms / ms_total},
             "e2e": {"value": e2e_value, "unit": "vectors/s", "h2d_bytes_per_step": 8 * 8 * n,
                     "d2h_bytes_per_step": 2 * 4 * C_out * n, "steps": e2e_steps, "checksum": e2e_checksum},
             "gpu_launches": int(gpu_launches),
             "clocks": sampler.summary(),
+            "parity": parity,
         }
+        if objects_sustained is not None:
+            line["value_sustained"] = objects_sustained["value"]
+            line["sustained"] = objects_sustained
         if point_block is not None:
             line["point_sources"] = point_block
         if render is not None:
@@ -761,6 +867,8 @@ def run_ours(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if rank == 0 and parity.get("ok") is False:
+        raise SystemExit("bench.py: the parity check of the timed regions FAILED: " + json.dumps(parity))
 
 
 def main():
@@ -785,6 +893,9 @@ def main():
     ap.add_argument("--no-render-e2e", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiler runs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the libear check of the timed regions' output")
+    ap.add_argument("--sustained", type=float, default=3.0,
+                    help="seconds of back-to-back steps per block for the sustained figures (0 = off)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3  # timing rule: at least three warm-up steps

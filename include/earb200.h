@@ -190,11 +190,20 @@ void earb200_interp_destroy(earb200_interp *interp);
  * Unsorted sample indices are reported lazily by process, as in libear (:123-124). */
 int earb200_interp_set_points(earb200_interp *interp, int64_t n_points,
                               const int64_t *sample_idx, const float *gains);
+/* the same with the gain matrices already in device memory -- [n_points][n_in][n_out] floats, e.g.
+ * the `direct` rows earb200_objects_calculate_device wrote for n_in objects at each point: the
+ * hand-off GainCalculatorObjects -> GainInterpolator::interp_points
+ * (include/ear/dsp/gain_interpolator.hpp:42-43) without leaving HBM.  sample_idx stays a host
+ * array (it drives the host-side segmentation).  Returns after `stream` has drained. */
+int earb200_interp_set_points_device(earb200_interp *interp, int64_t n_points,
+                                     const int64_t *sample_idx, const float *d_gains, void *stream);
 /* process(block_start, nsamples, in, out): in is n_in planar channels of nsamples
  * floats, channel c at in + c*in_stride; out likewise (overwritten). */
 int earb200_interp_process_host(earb200_interp *interp, int64_t block_start,
                                 int64_t nsamples, const float *in, int64_t in_stride,
                                 float *out, int64_t out_stride);
+/* device buffers, asynchronous on `stream`.  d_out must not alias d_in (the kernels read the
+ * input through the read-only path while other CTAs already store output). */
 int earb200_interp_process_device(earb200_interp *interp, int64_t block_start,
                                   int64_t nsamples, const float *d_in, int64_t in_stride,
                                   float *d_out, int64_t out_stride, void *stream);
@@ -229,6 +238,9 @@ int earb200_convolver_crossfade_filter(earb200_convolver *conv, int channel, int
 int earb200_convolver_process_host(earb200_convolver *conv, int64_t n_blocks,
                                    const float *in, int64_t in_stride, float *out,
                                    int64_t out_stride);
+/* device buffers, asynchronous on `stream`; in-place use (d_out == d_in) is NOT supported: a
+ * run of blocks re-reads the input block before its first one (halo) after other CTAs may have
+ * stored their output. */
 int earb200_convolver_process_device(earb200_convolver *conv, int64_t n_blocks,
                                      const float *d_in, int64_t in_stride, float *d_out,
                                      int64_t out_stride, void *stream);
@@ -268,6 +280,8 @@ int64_t earb200_delay_get_delay(const earb200_delay *d);
 /* channel c at in + c*in_stride / out + c*out_stride; in may be NULL (silence) */
 int earb200_delay_process_host(earb200_delay *d, int64_t nsamples, const float *in,
                                int64_t in_stride, float *out, int64_t out_stride);
+/* device buffers, asynchronous on `stream`; in-place use (d_out == d_in) is NOT supported:
+ * out[t] reads in[t - delay], which another thread may already have overwritten. */
 int earb200_delay_process_device(earb200_delay *d, int64_t nsamples, const float *d_in,
                                  int64_t in_stride, float *d_out, int64_t out_stride,
                                  void *stream);
@@ -298,6 +312,10 @@ int64_t earb200_objects_renderer_launch_count(const earb200_objects_renderer *r)
 int earb200_objects_renderer_set_gains(earb200_objects_renderer *r, int64_t n_points,
                                        const int64_t *sample_idx, const float *direct,
                                        const float *diffuse);
+/* the same with device-resident gains (earb200_objects_calculate_device output): no host round trip */
+int earb200_objects_renderer_set_gains_device(earb200_objects_renderer *r, int64_t n_points,
+                                              const int64_t *sample_idx, const float *d_direct,
+                                              const float *d_diffuse, void *stream);
 /* n_blocks * 512 samples per channel: in = n_objects planar channels, out = C_out feeds */
 int earb200_objects_renderer_process_host(earb200_objects_renderer *r, int64_t block_start,
                                           int64_t n_blocks, const float *in, int64_t in_stride,

@@ -322,6 +322,12 @@ class GainInterpolator:
         g = np.ascontiguousarray(gains, dtype=np.float32).reshape(len(s), self.n_in, self.n_out)
         _chk(_lib.earb200_interp_set_points(self.h, C.c_int64(len(s)), _ptr(s), _ptr(g)))
 
+    def set_points_device(self, sample_idx, d_gains, stream=0):
+        """d_gains: device address of float32 [n_points][n_in][n_out] (no host round trip)."""
+        s = np.ascontiguousarray(sample_idx, dtype=np.int64)
+        _chk(_lib.earb200_interp_set_points_device(self.h, C.c_int64(len(s)), _ptr(s), _ptr(d_gains),
+                                                   C.c_void_p(int(stream))))
+
     def process(self, block_start, inp, out=None):
         """inp: float32 [n_in][nsamples] host array -> out float32 [n_out][nsamples]; with
         set_accumulate(True), `out` is the bus the result is added to."""
@@ -432,6 +438,11 @@ class ObjectsRenderer:
         d = np.ascontiguousarray(direct, dtype=np.float32).reshape(shape)
         f = np.ascontiguousarray(diffuse, dtype=np.float32).reshape(shape)
         _chk(_lib.earb200_objects_renderer_set_gains(self.h, C.c_int64(len(s)), _ptr(s), _ptr(d), _ptr(f)))
+
+    def set_gains_device(self, sample_idx, d_direct, d_diffuse, stream=0):
+        s = np.ascontiguousarray(sample_idx, dtype=np.int64)
+        _chk(_lib.earb200_objects_renderer_set_gains_device(self.h, C.c_int64(len(s)), _ptr(s), _ptr(d_direct),
+                                                            _ptr(d_diffuse), C.c_void_p(int(stream))))
 
     def process(self, block_start, x):
         """x: float32 [n_objects][n_blocks * 512] host array -> [C_out][n_blocks * 512]."""

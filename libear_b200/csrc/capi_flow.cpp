@@ -103,6 +103,16 @@ int earb200_objects_renderer_set_gains(earb200_objects_renderer *r, int64_t n_po
   });
 }
 
+int earb200_objects_renderer_set_gains_device(earb200_objects_renderer *r, int64_t n_points,
+                                              const int64_t *sample_idx, const float *d_direct,
+                                              const float *d_diffuse, void *stream) {
+  return guarded([&] {
+    if (!r || !sample_idx || !d_direct || !d_diffuse) throw Error(INVALID_ARGUMENT, "null argument");
+    chk(earb200_interp_set_points_device(r->direct, n_points, sample_idx, d_direct, stream));
+    chk(earb200_interp_set_points_device(r->diffuse, n_points, sample_idx, d_diffuse, stream));
+  });
+}
+
 int earb200_objects_renderer_process_device(earb200_objects_renderer *r, int64_t block_start, int64_t n_blocks,
                                             const float *d_in, int64_t in_stride, float *d_out,
                                             int64_t out_stride, void *stream) {

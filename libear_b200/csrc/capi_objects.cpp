@@ -69,18 +69,18 @@ struct earb200_objects {
   int S = 0;
   ExtentGrid grid{};
   DeviceBuffer<int32_t> d_out_index, d_identity_index;
-  DeviceBuffer<float> d_grid_xyz, d_grid_gains, d_grid_sums;
   // tcgen05 extent core: points as float4, gain table as the UMMA B image (TF32 hi | lo)
   DeviceBuffer<float4> d_grid_points;
   DeviceBuffer<float> d_grid_bimage;
   DeviceBuffer<unsigned int> d_n_active;
-  int use_tc = 1;  // EARB200_EXTENT_PATH=cuda selects the FFMA warp-per-pass core
   // cell-culled tcgen05 extent core: per-cell stream [fp16 gain image | point coordinates],
   // cell centres + class thresholds
   DeviceBuffer<unsigned char> d_cell_stream, d_cell_sums;
   DeviceBuffer<float> d_cell_centres, d_cell_points;
   int n_cells = 0;
-  int use_cells = 1;  // EARB200_EXTENT_PATH=tf32 selects the first-generation tcgen05 core
+  // 0: the first-generation tcgen05 core (all weights evaluated, TF32 x 3): grids with more cells
+  // than the cell core's tables hold, and EARB200_EXTENT_PATH=tf32 (cross-check, tested)
+  int use_cells = 1;
   // per-chunk scratch
   // Scratch capacity in objects.  A call is cut into chunks sized so that every CTA of the extent
   // core gets whole rounds of 512 passes (its time goes with the number of rounds, not with how
@@ -110,7 +110,6 @@ struct earb200_objects {
   } scratch[2];
   cudaStream_t s_epi = nullptr;
   int64_t chunk_counter = 0;
-  DeviceBuffer<unsigned long long> d_counter;
   // staging for the *_host entry points
   DeviceBuffer<double> d_in, d_out_d;
   DeviceBuffer<float> d_out_f;
@@ -180,8 +179,6 @@ namespace {
     o.grid.n_points_pad = Pp;
     o.grid.n_blocks = NB;
     o.grid.n_spk = o.S;
-    if (extent_core_smem_bytes(o.grid) > 227 * 1024)
-      throw Error(INTERNAL_ERROR, "extent tables do not fit in shared memory");
 
     std::vector<double> xyz(3 * (size_t)P), gains((size_t)P * o.S);
     for (int p = 0; p < P; p++) {
@@ -192,7 +189,7 @@ namespace {
     panner_handle_host(o.panner, P, xyz.data(), gains.data(), nullptr, nullptr);
     o.launches++;
 
-    std::vector<float> fxyz(3 * (size_t)Pp), fg((size_t)o.S * Pp, 0.0f), fsum((size_t)NB * 32, 0.0f);
+    std::vector<float> fxyz(3 * (size_t)Pp), fg((size_t)o.S * Pp, 0.0f);
     for (int p = 0; p < Pp; p++) {
       const int q = p < P ? p : P - 1;  // padding repeats the last point, with zero gains
       fxyz[p] = (float)pts[q].x;
@@ -200,17 +197,7 @@ namespace {
       fxyz[2 * Pp + p] = (float)pts[q].z;
     }
     for (int p = 0; p < P; p++)
-      for (int sp = 0; sp < o.S; sp++) {
-        float g = (float)gains[(size_t)p * o.S + sp];
-        fg[(size_t)sp * Pp + p] = g;
-        fsum[(size_t)(p / EARB_EXT_BLOCK) * 32 + sp] += g;
-      }
-    EARB_CUDA(cudaMemcpy(o.d_grid_xyz.reserve(fxyz.size()), fxyz.data(), sizeof(float) * fxyz.size(),
-                         cudaMemcpyHostToDevice));
-    EARB_CUDA(cudaMemcpy(o.d_grid_gains.reserve(fg.size()), fg.data(), sizeof(float) * fg.size(),
-                         cudaMemcpyHostToDevice));
-    EARB_CUDA(cudaMemcpy(o.d_grid_sums.reserve(fsum.size()), fsum.data(), sizeof(float) * fsum.size(),
-                         cudaMemcpyHostToDevice));
+      for (int sp = 0; sp < o.S; sp++) fg[(size_t)sp * Pp + p] = (float)gains[(size_t)p * o.S + sp];
 
     {
       std::vector<float4> pts4(Pp);
@@ -222,13 +209,11 @@ namespace {
       EARB_CUDA(cudaMemcpy(o.d_grid_bimage.reserve(image.size()), image.data(), sizeof(float) * image.size(),
                            cudaMemcpyHostToDevice));
       const char *path = std::getenv("EARB200_EXTENT_PATH");
-      o.use_tc = !(path && std::string(path) == "cuda");
-      o.use_cells = o.use_tc && !(path && std::string(path) == "tf32");
       ExtentCells cells;
       extent_cells_build(P, fxyz.data(), Pp, cells);
       o.n_cells = cells.n_cells;
-      if (!extent_cell_supported(cells))
-        throw Error(INTERNAL_ERROR, "extent cell tables do not fit the extent core");
+      o.use_cells = extent_cell_supported(cells) && !(path && std::string(path) == "tf32");
+      if (o.use_cells) {
       std::vector<unsigned char> cs(extent_cell_stream_bytes(cells)), sums(extent_cell_sum_bytes(cells));
       extent_cell_build_stream(cells, o.S, Pp, fg.data(), cs.data());
       extent_cell_build_sums(cells, o.S, Pp, fg.data(), sums.data());
@@ -241,6 +226,7 @@ namespace {
                            cudaMemcpyHostToDevice));
       EARB_CUDA(cudaMemcpy(o.d_cell_points.reserve(cpnt.size()), cpnt.data(), sizeof(float) * cpnt.size(),
                            cudaMemcpyHostToDevice));
+      }
     }
     for (earb200_objects::Scratch &sc : o.scratch) {
       sc.d_passes.reserve(2 * earb200_objects::kChunk);
@@ -255,7 +241,6 @@ namespace {
     EARB_CUDA(cudaEventCreateWithFlags(&o.ev_fb, cudaEventDisableTiming));
     EARB_CUDA(cudaHostAlloc((void **)&o.h_active, sizeof(unsigned int) * earb200_objects::kFeedbackSlots, cudaHostAllocDefault));
     EARB_CUDA(cudaStreamCreateWithFlags(&o.s_epi, cudaStreamNonBlocking));
-    o.d_counter.reserve(1);
   }
 
   // features libear rejects (ref gain_calculator_objects.cpp:37-43), same order
@@ -312,7 +297,7 @@ namespace {
     EARB_CUDA(cudaStreamWaitEvent(stream, sc.ev_epi, 0));
     EARB_CUDA(cudaMemsetAsync(sc.d_n_active.ptr, 0, 2 * sizeof(unsigned int), stream));
     launch_objects_prelude(m, c, sc.d_passes.ptr, sc.d_aux.ptr, sc.d_n_active.ptr, sc.d_point_list.ptr,
-                           d_region != nullptr, !o.use_tc, stream);
+                           d_region != nullptr, stream);
     if (fb_slot >= 0 && fb_slot < earb200_objects::kFeedbackSlots) {
       EARB_CUDA(cudaMemcpyAsync(o.h_active + fb_slot, sc.d_n_active.ptr, sizeof(unsigned int), cudaMemcpyDeviceToHost,
                                 stream));
@@ -324,12 +309,9 @@ namespace {
       launch_extent_cell(o.n_cells, o.grid.n_spk, o.d_cell_stream.ptr, o.d_cell_sums.ptr, o.d_cell_centres.ptr,
                          o.d_cell_points.ptr, sc.d_n_active.ptr, sc.d_passes.ptr, sc.d_results.ptr, o.n_sms,
                          stream);
-    else if (o.use_tc)
+    else
       launch_extent_core_tc(o.grid, o.d_grid_points.ptr, o.d_grid_bimage.ptr, sc.d_n_active.ptr, sc.d_passes.ptr,
                             sc.d_results.ptr, o.n_sms, stream);
-    else
-      launch_extent_core(o.grid, o.d_grid_xyz.ptr, o.d_grid_gains.ptr, o.d_grid_sums.ptr, sc.d_n_active.ptr,
-                         sc.d_passes.ptr, sc.d_results.ptr, o.d_counter.ptr, o.n_sms, stream);
     o.timer.stop(stream);
     if (o.timer.enabled) o.timed_passes += 2 * m;
     EARB_CUDA(cudaEventRecord(sc.ev_core, stream));
@@ -686,6 +668,9 @@ int earb200_objects_calculate_device(earb200_objects *calc, int64_t n,
     if (n < 0) throw Error(INVALID_ARGUMENT, "negative batch size");
     if (n == 0) return;
     if (!d_direct || !d_diffuse) throw Error(INVALID_ARGUMENT, "null output buffer");
+    if (!d_in->azimuth || !d_in->elevation || !d_in->distance || !d_in->width || !d_in->height || !d_in->depth ||
+        !d_in->gain || !d_in->diffuse)
+      throw Error(INVALID_ARGUMENT, "null metadata field (all eight arrays are required)");
     check_flags(n, d_in->flags);
     use_device(calc->device);
     ObjectsSoA soa{d_in->azimuth, d_in->elevation, d_in->distance, d_in->width, d_in->height,

@@ -22,6 +22,7 @@ struct earb200_interp {
   bool sorted = true;
   DeviceBuffer<float> d_gains;
   DeviceBuffer<float> d_images;  // tcgen05 path: per-point TF32 hi/lo images in UMMA layout
+  DeviceBuffer<char> d_same;     // set_points_device: equality flags of neighbouring points
   int64_t n_points = 0;
   // plan cache keyed by (block_start, nsamples, buffer alignment): a caller that walks the same
   // chunks every pass (chunked mixing with the bus reduce of chunk k behind the render of chunk
@@ -249,6 +250,42 @@ int earb200_interp_set_points(earb200_interp *interp, int64_t n_points,
         h.launches++;
       }
     }
+  });
+}
+
+// interp_points whose gain matrices are already on the device (the output of the gain
+// calculators' *_device entry points): no host round trip.  Synchronises `stream`.
+int earb200_interp_set_points_device(earb200_interp *interp, int64_t n_points, const int64_t *sample_idx,
+                                     const float *d_gains, void *stream) {
+  return guarded([&] {
+    if (!interp || n_points < 0 || (n_points > 0 && (!sample_idx || !d_gains)))
+      throw Error(INVALID_ARGUMENT, "null argument");
+    earb200_interp &h = *interp;
+    use_device(h.device);
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t mat = (size_t)h.N * h.M;
+    h.sample_idx.assign(sample_idx, sample_idx + n_points);
+    h.same_as_prev.assign(n_points, 0);
+    h.sorted = std::is_sorted(h.sample_idx.begin(), h.sample_idx.end());
+    h.n_points = n_points;
+    h.plans.clear();
+    if (n_points == 0) return;
+    h.d_gains.reserve(mat * n_points);
+    EARB_CUDA(cudaMemcpyAsync(h.d_gains.ptr, d_gains, sizeof(float) * mat * n_points, cudaMemcpyDeviceToDevice, st));
+    if (n_points > 1) {
+      char *d_flags = h.d_same.reserve((size_t)n_points);
+      launch_render_points_same((long)mat, (long)n_points, h.d_gains.ptr, d_flags, st);
+      EARB_CUDA(cudaMemcpyAsync(h.same_as_prev.data() + 1, d_flags + 1, (size_t)(n_points - 1), cudaMemcpyDeviceToHost,
+                                st));
+      h.launches++;
+    }
+    if (h.use_tc) {
+      h.d_images.reserve(render_tc_image_floats(h.N, h.M) * n_points);
+      launch_render_prepare_points(h.N, h.M, (long)n_points, h.d_gains.ptr, h.d_images.ptr, st);
+      h.launches++;
+    }
+    EARB_CUDA(cudaGetLastError());
+    EARB_CUDA(cudaStreamSynchronize(st));
   });
 }
 

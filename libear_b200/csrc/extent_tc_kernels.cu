@@ -20,10 +20,12 @@
 //                             canonical layout, prepared once per layout) through a
 //                             shared-memory ring with cp.async.bulk, 64 points per stage.
 //
-// The threshold decisions (weight exactly 1 / exactly 0) are the reference's float comparisons
-// with the reference's operation order (polar_extent_simd.hpp:39-95); weights on the 10-degree
-// fade use one branch-free polynomial acos.  3xTF32 keeps the contraction at fp32 accuracy
-// (weights off the fade are 0 or 1, exact in TF32).
+// The weight is NOT computed with the reference's threshold comparisons
+// (polar_extent_simd.hpp:39-95: 1 for angle <= start, 0 for angle >= end, the fade m * angle + c in
+// between) but as clamp(m * angle + c, 0, 1) with one branch-free polynomial asin -- the fade is 1
+// at `start`, 0 at `end` and monotone, so the two agree everywhere except for rounding at the two
+// ends of the fade (measured 1.5e-7 on the gains, bar 1e-5).  3xTF32 keeps the contraction at fp32
+// accuracy (weights off the fade are exactly 0 or 1, exact in TF32).
 #include <cuda_runtime.h>
 
 #include <algorithm>
@@ -540,11 +542,8 @@ namespace earb {
                              const unsigned int *d_n_active, const ExtentPass *d_passes, float *d_results,
                              int n_sms, cudaStream_t stream) {
     const size_t smem = extent_tc_smem_bytes(grid);
-    static bool configured = false;
-    if (!configured) {
-      cudaFuncSetAttribute(extent_core_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      configured = true;
-    }
+    // the attribute is per device: set it on every launch (a few hundred nanoseconds)
+    cudaFuncSetAttribute(extent_core_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     extent_core_tc_kernel<<<(unsigned)n_sms, kThreads, smem, stream>>>(grid, d_points, d_bimage, d_n_active,
                                                                          d_passes, d_results);
   }

@@ -8,7 +8,6 @@
 
 #include "tables.h"
 
-#define EARB_CORE_THREADS 1024
 
 namespace earb {
 
@@ -43,8 +42,7 @@ namespace earb {
   // core reads)
   void launch_objects_prelude(long n, const ObjectsSoA &in, ExtentPass *d_passes, ObjectAux *d_aux,
                               unsigned int *d_counters, int32_t *d_point_list, bool all_points,
-                              bool thresholds, cudaStream_t stream);
-  size_t extent_core_smem_bytes(const ExtentGrid &grid);
+                              cudaStream_t stream);
 #define EXTENT_TC_STAGE_POINTS 64
   // tcgen05 extent core (extent_tc_kernels.cu): thread-per-pass weights feeding 3xTF32 UMMAs
   size_t extent_tc_smem_bytes(const ExtentGrid &grid);
@@ -81,11 +79,6 @@ namespace earb {
   void launch_extent_cell(int n_cells, int n_spk, const unsigned char *d_stream, const unsigned char *d_sums,
                           const float *d_centres, const float *d_points, const unsigned int *d_n_active,
                           const ExtentPass *d_passes, float *d_results, int n_sms, cudaStream_t stream);
-  // FFMA extent core (objects_kernels.cu), warp per pass
-  void launch_extent_core(const ExtentGrid &grid, const float *d_xyz, const float *d_gains,
-                          const float *d_block_sums, const unsigned int *d_n_active,
-                          const ExtentPass *d_passes, float *d_results,
-                          unsigned long long *d_counter, int n_sms, cudaStream_t stream);
   // self-test: counts the elements where the epilogue's branch-free square root differs from sqrt()
   void launch_selftest_fast_sqrt(const double *d_x, long n, unsigned long long *d_n_mismatch, cudaStream_t stream);
   // two launches: the point source gains of the objects that need them (d_point_gains
@@ -144,6 +137,8 @@ namespace earb {
   size_t render_tc_image_floats(int N, int M);
   void launch_render_prepare_points(int N, int M, long n_points, const float *d_gains, float *d_images,
                                     cudaStream_t stream);
+  // d_flags[i] (i >= 1) = gain matrix i equals matrix i - 1 (mat floats each)
+  void launch_render_points_same(long mat, long n_points, const float *d_gains, char *d_flags, cudaStream_t stream);
   int render_tile_samples(int M);
   size_t render_smem_bytes(int N, int M);
   void launch_render(int N, int M, const float *in, long in_stride, float *out, long out_stride,

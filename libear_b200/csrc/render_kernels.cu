@@ -411,4 +411,20 @@ namespace earb {
     }
 #undef EARB_RENDER_CASE
   }
+  namespace {
+    // flags[i] = gain matrix i equals matrix i - 1 element for element (constant_interp,
+    // ref include/ear/dsp/gain_interpolator.hpp:139-141); one block per point
+    __global__ void render_points_same_kernel(long mat, const float *__restrict__ gains, char *__restrict__ flags) {
+      const long i = (long)blockIdx.x + 1;
+      const float *a = gains + (i - 1) * mat, *b = a + mat;
+      int same = 1;
+      for (long k = threadIdx.x; k < mat; k += blockDim.x) same &= (a[k] == b[k]);
+      same = __syncthreads_and(same);
+      if (threadIdx.x == 0) flags[i] = (char)same;
+    }
+  }  // namespace
+  void launch_render_points_same(long mat, long n_points, const float *d_gains, char *d_flags, cudaStream_t stream) {
+    if (n_points < 2) return;
+    render_points_same_kernel<<<(unsigned)(n_points - 1), 256, 0, stream>>>(mat, d_gains, d_flags);
+  }
 }  // namespace earb

@@ -317,6 +317,38 @@ def delay_process(x, delay, call_size=None):
     return out
 
 
+def fft_kiss(x, forward=True, n_fft=None):
+    """libear's own KISS transforms (src/fft_kiss.cpp:52-99): forward float32 [batch][n_fft] ->
+    complex64 [batch][n_fft/2+1]; reverse complex64 -> float32 [batch][n_fft], unnormalised."""
+    if forward:
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        n_fft = x.shape[-1]
+        x = x.reshape(-1, n_fft)
+        out = np.zeros((len(x), n_fft // 2 + 1), dtype=np.complex64)
+        _chk(lib().ref_fft_kiss(C.c_long(n_fft), C.c_long(len(x)), 1, _p(x), _p(out)))
+        return out
+    x = np.ascontiguousarray(x, dtype=np.complex64)
+    n_fft = n_fft or 2 * (x.shape[-1] - 1)
+    x = x.reshape(-1, n_fft // 2 + 1)
+    out = np.zeros((len(x), n_fft), dtype=np.float32)
+    _chk(lib().ref_fft_kiss(C.c_long(n_fft), C.c_long(len(x)), 0, _p(x), _p(out)))
+    return out
+
+
+def vbs_process(block_size, x, n_out, sizes):
+    """libear's VariableBlockSizeAdapter over calls of the given sizes around the probe process
+    function of ref_capi.cpp::ref_vbs_process.  x: float32 [n_in][sum(sizes)] -> ([n_out][T], delay)."""
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    n_in, T = x.shape
+    sizes = np.ascontiguousarray(sizes, dtype=np.int64)
+    assert int(sizes.sum()) == T
+    out = np.zeros((n_out, T), dtype=np.float32)
+    delay = C.c_int(0)
+    _chk(lib().ref_vbs_process(C.c_long(block_size), n_in, n_out, len(sizes),
+                               sizes.ctypes.data_as(C.POINTER(C.c_long)), _p(x), _p(out), C.byref(delay)))
+    return out, delay.value
+
+
 def conversion(pos, ext=None, to_polar=True):
     """ear::conversion::extentCartToPolar / extentPolarToCart (point* when ext is None) per row."""
     pos = _f64(pos).reshape(-1, 3)

@@ -11,6 +11,7 @@
 // (point_source_panner.cpp:473-557) from the reference's own linkable pieces
 // (getAugmentedLayout, FACETS, Triplet, QuadRegion, VirtualNgon) and the first
 // region whose handleRemap() returns a value is reported.
+#include <complex>
 #include <cstdint>
 #include <cstring>
 #include <map>
@@ -41,6 +42,7 @@
 #include "ear/dsp/block_convolver.hpp"
 #include "ear/dsp/delay_buffer.hpp"
 #include "ear/dsp/gain_interpolator.hpp"
+#include "ear/dsp/variable_block_size.hpp"
 #include "ear/fft.hpp"
 #include "ear/gain_calculators.hpp"
 #include "hoa/hoa.hpp"
@@ -726,6 +728,66 @@ int ref_conversion(long n, int to_polar, const double *pos, const double *ext,
       }
       pos_out[3 * i] = r.X, pos_out[3 * i + 1] = r.Y, pos_out[3 * i + 2] = r.Z;
     }
+  }
+  return 0;
+  REF_CATCH
+}
+
+// ---- FFT plug-in: libear's own KISS transforms (src/fft_kiss.cpp:52-99) -----
+// forward: batch x n_fft reals -> batch x (n_fft/2+1) complex (interleaved re, im), unpacked bins;
+// reverse: unnormalised c2r
+int ref_fft_kiss(long n_fft, long batch, int forward, const float *in, float *out) {
+  REF_TRY
+  auto plan = get_fft_kiss<float>().plan((size_t)n_fft);
+  auto work = plan->alloc_workbuf();
+  const long nc = n_fft / 2 + 1;
+  std::vector<float> re(n_fft);
+  std::vector<std::complex<float>> cx(nc);
+  for (long b = 0; b < batch; b++) {
+    if (forward) {
+      std::copy(in + b * n_fft, in + (b + 1) * n_fft, re.begin());
+      plan->transform_forward(re.data(), cx.data(), *work);
+      for (long k = 0; k < nc; k++) {
+        out[2 * (b * nc + k)] = cx[k].real();
+        out[2 * (b * nc + k) + 1] = cx[k].imag();
+      }
+    } else {
+      for (long k = 0; k < nc; k++) cx[k] = {in[2 * (b * nc + k)], in[2 * (b * nc + k) + 1]};
+      plan->transform_reverse(cx.data(), re.data(), *work);
+      std::copy(re.begin(), re.end(), out + b * n_fft);
+    }
+  }
+  return 0;
+  REF_CATCH
+}
+
+// ---- VariableBlockSizeAdapter (src/dsp/variable_block_size_impl.cpp:44-81) --
+// Runs libear's adapter over `n_calls` calls of the given sizes.  The inner fixed-block process
+// function is the probe both sides of the parity test use (tests/cpp/facade_test.cpp, mode "vbs"):
+//   out[o][i] = (o + 2) * in[o % n_in][i] + 0.25f * call_index      (call_index counts inner calls)
+// in: [n_in][T] planar, out: [n_out][T] planar, T = sum(sizes)
+int ref_vbs_process(long block_size, int n_in, int n_out, int n_calls, const long *sizes,
+                    const float *in, float *out, int *delay) {
+  REF_TRY
+  long T = 0;
+  for (int c = 0; c < n_calls; c++) T += sizes[c];
+  int inner_calls = 0;
+  dsp::VariableBlockSizeAdapter adapter(
+      (size_t)block_size, (size_t)n_in, (size_t)n_out, [&](const float *const *i, float *const *o) {
+        for (int oc = 0; oc < n_out; oc++)
+          for (long t = 0; t < block_size; t++)
+            o[oc][t] = (float)(oc + 2) * i[oc % n_in][t] + 0.25f * (float)inner_calls;
+        inner_calls++;
+      });
+  if (delay) *delay = adapter.get_delay();
+  std::vector<const float *> in_p(n_in);
+  std::vector<float *> out_p(n_out);
+  long pos = 0;
+  for (int c = 0; c < n_calls; c++) {
+    for (int k = 0; k < n_in; k++) in_p[k] = in + (size_t)k * T + pos;
+    for (int k = 0; k < n_out; k++) out_p[k] = out + (size_t)k * T + pos;
+    adapter.process((size_t)sizes[c], in_p.data(), out_p.data());
+    pos += sizes[c];
   }
   return 0;
   REF_CATCH

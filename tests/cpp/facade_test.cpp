@@ -468,8 +468,45 @@ static int run_objects(const std::string &layout_name) {
   return 0;
 }
 
+// mode "vbs <block_size> <n_in> <n_out> <size>...": the facade's VariableBlockSizeAdapter over calls
+// of the given sizes, around the same probe process function as oracle/ref_capi.cpp::ref_vbs_process
+// runs libear's adapter with (ref src/dsp/variable_block_size_impl.cpp:44-81,
+// tests/variable_block_size_tests.cpp).  stdin: float32 [n_in][T] raw, stdout: float32 [n_out][T] raw.
+// Host-only: needs no device.
+static int run_vbs(int argc, char **argv) {
+  using namespace ear::dsp;
+  const size_t B = std::stoul(argv[2]), n_in = std::stoul(argv[3]), n_out = std::stoul(argv[4]);
+  std::vector<size_t> sizes;
+  size_t T = 0;
+  for (int a = 5; a < argc; a++) {
+    sizes.push_back(std::stoul(argv[a]));
+    T += sizes.back();
+  }
+  std::vector<float> x(n_in * T), y(n_out * T, -7.0f);
+  if (std::fread(x.data(), sizeof(float), x.size(), stdin) != x.size()) return 3;
+  int inner_calls = 0;
+  VariableBlockSizeAdapter adapter(B, n_in, n_out, [&](const float *const *i, float *const *o) {
+    for (size_t oc = 0; oc < n_out; oc++)
+      for (size_t t = 0; t < B; t++) o[oc][t] = (float)(oc + 2) * i[oc % n_in][t] + 0.25f * (float)inner_calls;
+    inner_calls++;
+  });
+  if (adapter.get_delay() != (int)B) return 4;
+  PtrAdapterConst in(n_in);
+  PtrAdapter out(n_out);
+  size_t pos = 0;
+  for (size_t n : sizes) {
+    in.set_strided(x.data(), T, pos);
+    out.set_strided(y.data(), T, pos);
+    adapter.process(n, in.ptrs(), out.ptrs());
+    pos += n;
+  }
+  std::fwrite(y.data(), sizeof(float), y.size(), stdout);
+  return 0;
+}
+
 int main(int argc, char **argv) {
   try {
+    if (argc >= 5 && std::string(argv[1]) == "vbs") return run_vbs(argc, argv);
     if (argc >= 3 && std::string(argv[1]) == "objects") return run_objects(argv[2]);
     test_layouts();
     test_decorrelators();

@@ -131,6 +131,19 @@ def gen_interp():
     out["cfg3/x16"], out["cfg3/samples"], out["cfg3/gains"] = x16, samples, g
     out["cfg3/out"] = ref.interp_matrix(x16.astype(np.float32), samples, g)
     np.savez_compressed(os.path.join(HERE, "interp.npz"), **out)
+    # the same shape with float32 noise (NOT float16-exact: x_lo != 0, so both cross terms of a
+    # split-TF32 contraction are exercised), libear's output and the float64 result of the same ramp
+    N, M, T = 128, 14, 1024
+    x = np.clip(rng.normal(0, 0.25, (N, T)), -1, 1).astype(np.float32)
+    samples = np.arange(0, T + 512, 512, dtype=np.int64)
+    g = (rng.uniform(0, 1, (len(samples), N, M)) / np.sqrt(N)).astype(np.float32)
+    t = np.arange(T)
+    k0 = np.searchsorted(samples, t, side="right") - 1
+    p_ = (t - samples[k0]) / 512.0
+    gg = g[k0].astype(np.float64) * (1 - p_)[:, None, None] + g[k0 + 1].astype(np.float64) * p_[:, None, None]
+    np.savez_compressed(os.path.join(HERE, "interp_f32.npz"), x=x, samples=samples, gains=g,
+                        libear=ref.interp_matrix(x, samples, g),
+                        float64=np.einsum("nt,tnm->mt", x.astype(np.float64), gg))
 
 
 def gen_convolver():

@@ -1,0 +1,171 @@
+"""Round-2 parity additions:
+  a9   the FFT plug-in against libear's OWN KISS transforms (ref src/fft_kiss.cpp:61-88: n/2+1
+       unpacked bins, unnormalised c2r), not just numpy;
+  K3   gains handed over on the device (set_points_device) = gains set from the host, bit for bit;
+  arms every environment-selected kernel arm that is still in the library runs under test
+       (EARB200_EXTENT_PATH=tf32, EARB200_RENDER_PATH=cuda, EARB200_RENDER_WIDE=0), in a subprocess;
+  dev  handles on two devices of ONE process (kernel attributes are per device);
+  float32-noise fixture at the BASELINE render shape (128 x 14)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.mark.parametrize("n_fft", [32, 256, 1024, 4096])
+def test_fft_against_libears_kiss_fft(eb, ref, n_fft):
+    rng = np.random.default_rng(n_fft + 1)
+    x = rng.normal(0, 0.25, (19, n_fft)).astype(np.float32)
+    fft = eb.FFT(n_fft)
+    X, X_ref = fft.forward(x), ref.fft_kiss(x)
+    assert X.shape == X_ref.shape == (19, n_fft // 2 + 1)
+    assert np.abs(X - X_ref).max() / np.abs(X_ref).max() < 1e-6
+    back, back_ref = fft.reverse(X_ref), ref.fft_kiss(X_ref, forward=False, n_fft=n_fft)
+    assert np.abs(back - back_ref).max() / np.abs(back_ref).max() < 1e-6
+    # libear's c2r is unnormalised: reverse(forward(x)) = n_fft * x
+    assert np.abs(back_ref / n_fft - x).max() < 1e-5
+
+
+@pytest.mark.parametrize("N,M,T", [(128, 14, 8192), (5, 3, 1500), (32, 24, 4096)])
+def test_set_points_device_equals_host(eb, N, M, T):
+    import torch
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(N * M)
+    samples = np.arange(0, T + 512, 512, dtype=np.int64)
+    gains = (rng.uniform(0, 1, size=(len(samples), N, M)) / np.sqrt(N)).astype(np.float32)
+    gains[3] = gains[2]                       # a constant segment (constant_interp)
+    x = rng.normal(0, 0.25, (N, T)).astype(np.float32)
+    a = eb.GainInterpolator(N, M)
+    a.set_points(samples, gains)
+    exp = a.process(0, x)
+    b = eb.GainInterpolator(N, M)
+    d_g = torch.from_numpy(gains).to(dev)
+    b.set_points_device(samples, d_g.data_ptr(), stream=torch.cuda.current_stream().cuda_stream)
+    got = b.process(0, x)
+    assert np.array_equal(got.view(np.uint32), exp.view(np.uint32))
+
+
+def test_objects_gains_hand_over_on_the_device(eb, ref):
+    """GainCalculatorObjects -> GainInterpolator::interp_points -> process without leaving HBM
+    (ref include/ear/dsp/gain_interpolator.hpp:42-43), against the same chain through libear."""
+    import torch
+    dev = torch.device("cuda", 0)
+    layout, N, T, n_pts = "4+7+0", 64, 4096, 5
+    rng = np.random.default_rng(21)
+    az0 = rng.uniform(-180, 180, N)
+    el = np.degrees(np.arcsin(rng.uniform(-1, 1, N)))
+    w, h = rng.uniform(0, 180, N), rng.uniform(0, 90, N)
+    gain = rng.uniform(0.2, 1, N)
+    gc = eb.GainCalculatorObjects(layout)
+    M = gc.num_outputs
+    d_gains = torch.empty((n_pts, N, M), dtype=torch.float32, device=dev)
+    d_diff = torch.empty((n_pts, N, M), dtype=torch.float32, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    ref_gains = np.empty((n_pts, N, M), dtype=np.float32)
+    keep = []
+    for k in range(n_pts):
+        cols = [az0 + 5.0 * k, el, np.ones(N), w, h, np.zeros(N), gain, np.zeros(N)]
+        d_in = torch.from_numpy(np.stack(cols)).to(dev)
+        keep.append(d_in)
+        gc.calculate_device(N, [d_in[j].data_ptr() for j in range(8)], d_gains[k].data_ptr(), d_diff[k].data_ptr(),
+                            stream=stream)
+        ref_gains[k] = ref.Objects(layout).calculate(*cols, dtype=np.float32)[0]
+    samples = np.arange(n_pts, dtype=np.int64) * 1024
+    gi = eb.GainInterpolator(N, M)
+    gi.set_points_device(samples, d_gains.data_ptr(), stream=stream)
+    x = rng.normal(0, 0.25, (N, T)).astype(np.float32)
+    got = gi.process(0, x)
+    exp = ref.interp_matrix(x, samples, ref_gains)
+    assert np.abs(got - exp).max() / np.abs(exp).max() < 1e-5   # gains differ by <= 1e-5 (float extent core)
+
+
+ARM_SCRIPT = r"""
+import sys, numpy as np
+sys.path.insert(0, {root!r})
+import libear_b200 as eb
+from oracle import ref
+rng = np.random.default_rng(5)
+n = 3000
+az = rng.uniform(-180, 180, n); el = np.degrees(np.arcsin(rng.uniform(-1, 1, n)))
+cols = [az, el, rng.uniform(0.2, 1.5, n), rng.uniform(0, 360, n), rng.uniform(0, 360, n),
+        np.where(rng.uniform(size=n) < 0.5, 0.0, rng.uniform(0, 1, n)), rng.uniform(0, 1, n), rng.uniform(0, 1, n)]
+d, f = eb.GainCalculatorObjects("9+10+3").calculate(*cols)
+d_ref, f_ref = ref.Objects("9+10+3").calculate(*cols, dtype=np.float32)
+ok = np.isfinite(d_ref).all(1)
+print("OBJ", max(np.abs(d[ok] - d_ref[ok]).max(), np.abs(f[ok] - f_ref[ok]).max()))
+for N, M, T in [(128, 14, 4096), (32, 24, 3000), (7, 5, 2111)]:
+    x = rng.normal(0, 0.25, (N, T)).astype(np.float32)
+    samples = np.arange(0, T + 512, 512)
+    g = (rng.uniform(0, 1, (len(samples), N, M)) / np.sqrt(N)).astype(np.float32)
+    gi = eb.GainInterpolator(N, M); gi.set_points(samples, g)
+    out = gi.process(0, x); exp = ref.interp_matrix(x, samples, g)
+    print("RENDER", np.abs(out - exp).max() / np.abs(exp).max())
+"""
+
+
+@pytest.mark.parametrize("env", [{"EARB200_EXTENT_PATH": "tf32"}, {"EARB200_RENDER_PATH": "cuda"},
+                                 {"EARB200_RENDER_WIDE": "0"}])
+def test_environment_selected_arms(ref, env):
+    e = dict(os.environ)
+    e.update(env)
+    r = subprocess.run([sys.executable, "-c", ARM_SCRIPT.format(root=ROOT)], env=e, capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-3000:]
+    lines = [line.split() for line in r.stdout.strip().splitlines()]
+    obj = [float(v) for k, v in lines if k == "OBJ"]
+    ren = [float(v) for k, v in lines if k == "RENDER"]
+    assert len(obj) == 1 and len(ren) == 3
+    assert obj[0] < 1e-5 and max(ren) < 1e-6, (obj, ren)
+
+
+def test_handles_on_two_devices_of_one_process(eb, ref):
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    rng = np.random.default_rng(8)
+    n = 2000
+    cols = [rng.uniform(-180, 180, n), np.degrees(np.arcsin(rng.uniform(-1, 1, n))), rng.uniform(0.2, 1.5, n),
+            rng.uniform(0, 360, n), rng.uniform(0, 360, n), rng.uniform(0, 1, n), rng.uniform(0, 1, n),
+            rng.uniform(0, 1, n)]
+    outs = []
+    for device in (0, 1, 0):
+        gc = eb.GainCalculatorObjects("9+10+3", device=device)
+        outs.append(gc.calculate(*cols))
+    for d, f in outs[1:]:
+        assert np.array_equal(d, outs[0][0]) and np.array_equal(f, outs[0][1])
+    N, M, T = 128, 24, 4096
+    x = rng.normal(0, 0.25, (N, T)).astype(np.float32)
+    samples = np.arange(0, T + 512, 512)
+    g = (rng.uniform(0, 1, (len(samples), N, M)) / np.sqrt(N)).astype(np.float32)
+    res = []
+    for device in (0, 1):
+        gi = eb.GainInterpolator(N, M, device=device)
+        gi.set_points(samples, g)
+        res.append(gi.process(0, x))
+        conv = eb.BlockConvolver(512, 2, 1, device=device)
+        fid, _ = conv.add_filter(rng.normal(size=512).astype(np.float32))
+        conv.set_filter(fid)
+        conv.process(x[:2, :2048])
+    assert np.array_equal(res[0], res[1])
+
+
+def test_render_float32_noise_fixture_cfg3_shape(eb, ref):
+    """tests/golden/interp_f32.npz: 128 x 14, float32 noise (NOT float16-exact, so the x_lo cross
+    terms of the 3xTF32 split are exercised) with libear's output stored; bar 1e-6 of peak against
+    libear AND against the float64 result of the same ramp (both float results sit a few 1e-7 from
+    it: 128 float accumulations per sample in different orders)."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "interp_f32.npz"))
+    x, samples, gains, exp, truth = g["x"], g["samples"], g["gains"], g["libear"], g["float64"]
+    gi = eb.GainInterpolator(x.shape[0], gains.shape[2])
+    gi.set_points(samples, gains)
+    out = gi.process(0, x)
+    peak = np.abs(truth).max()
+    e_ref, e_64, ref_64 = (np.abs(out - exp).max() / peak, np.abs(out - truth).max() / peak,
+                           np.abs(exp - truth).max() / peak)
+    print(f"128x14 f32 fixture: gpu-vs-libear {e_ref:.2e}, gpu-vs-f64 {e_64:.2e}, libear-vs-f64 {ref_64:.2e}")
+    assert e_64 < 1e-6 and e_ref < 1e-6 and e_64 < 2 * ref_64

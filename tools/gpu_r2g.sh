@@ -10,11 +10,11 @@ timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench_$tag.json 2
 cat gpurun_out/bench_$tag.json
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref_$tag.json 2> gpurun_out/bench_ref_$tag.err; echo "ref rc=$?"
 cat gpurun_out/bench_ref_$tag.json
-PCMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-render-e2e --no-e2e --no-mix"
+PCMD="python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-render-e2e --no-e2e --no-mix --no-parity --sustained 0"
 timeout 600 $PCMD > gpurun_out/plain_$tag.log 2>&1 &&
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_$tag.csv $PCMD > gpurun_out/ncu_launches_$tag.log 2>&1
 echo "ncu launches rc=$?"
-CMD="python bench.py --steps 1 --warmup 3 --objects 262144 --no-render --no-convolver --no-mix --no-flow --no-points --no-cpu-baseline --no-e2e"
+CMD="python bench.py --steps 1 --warmup 3 --objects 262144 --no-render --no-convolver --no-mix --no-flow --no-points --no-cpu-baseline --no-e2e --no-parity --sustained 0"
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:extent_cell -s 2 -c 1 -f -o gpurun_out/prof_cell_$tag $CMD > gpurun_out/ncu_cell_$tag.log 2>&1
 echo "ncu cell rc=$?"
 ls -la gpurun_out
