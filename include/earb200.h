@@ -215,6 +215,62 @@ int64_t earb200_interp_launch_count(const earb200_interp *interp);
 int earb200_interp_set_profiling(earb200_interp *interp, int enable);
 int earb200_interp_kernel_time(earb200_interp *interp, double *ms, int64_t *launches);
 
+/* ------------------------------------------------- node-wide loudspeaker bus (exchange step)
+ * Object-sharded mixing: libear's contract is "gains are applied to this channel, and summed with
+ * other objects into an n-channel bus" (include/ear/gain_calculators.hpp:43-56, docs/dsp.rst:40-71);
+ * with the objects spread over the GPUs of one node the sum over GPUs is the one exchange step of
+ * the path.  The bus [n_channels][n_samples] is cut into one time slice per rank.  A rank renders
+ * its objects with earb200_interp_process_device_bus: the render kernel's epilogue stores every
+ * tile straight into the staging slot the rank has at the slice's owner (peer stores over NVLink,
+ * riding on the render), and earb200_bus_reduce finishes the step: flags published at system
+ * scope, the owner's sum over the slots in rank order (deterministic), optionally stored into every
+ * rank's full bus.  No collective library is involved; the host program only has to hand one
+ * 64-byte IPC handle per rank around (or, with all ranks in one process, call connect_local). */
+typedef struct earb200_bus earb200_bus;
+
+/* at most 8 ranks (the GPUs of one node); n_samples = length of the bus in samples */
+int earb200_bus_create(int device, int rank, int n_ranks, int n_channels, int64_t n_samples,
+                       earb200_bus **out);
+void earb200_bus_destroy(earb200_bus *bus);
+/* one process per GPU: every rank exports its handle (earb200_bus_ipc_handle_bytes() bytes), the
+ * host program gathers them in rank order and every rank opens the array */
+int earb200_bus_ipc_handle_bytes(void);
+int earb200_bus_get_ipc_handle(earb200_bus *bus, void *handle_out);
+int earb200_bus_open_ipc(earb200_bus *bus, const void *handles_in_rank_order);
+/* all ranks in this process: the handles of all ranks, in rank order */
+int earb200_bus_connect_local(earb200_bus *const *buses, int n);
+/* the slice [t0, t1) of the bus that `rank` owns */
+int earb200_bus_slice(const earb200_bus *bus, int rank, int64_t *t0, int64_t *t1);
+/* GainInterpolator::process of this rank's objects into the bus samples [bus_t0, bus_t0 + nsamples).
+ * d_partial (row pitch partial_stride) is this rank's private partial bus: needed in accumulate
+ * mode (groups of objects mixed one after the other: all but the last call go through
+ * earb200_interp_process_device into d_partial, the last one through this call, which reads
+ * d_partial and stores the sum to the bus), for more than 128 input channels and for calls that are
+ * not whole aligned tiles (those are rendered into d_partial and pushed); otherwise it may be NULL. */
+int earb200_interp_process_device_bus(earb200_interp *interp, int64_t block_start, int64_t nsamples,
+                                      const float *d_in, int64_t in_stride, float *d_partial,
+                                      int64_t partial_stride, earb200_bus *bus, int64_t bus_t0,
+                                      void *stream);
+/* a partial bus rendered some other way: [n_channels][n] for the bus samples [t0, t0 + n) */
+int earb200_bus_push(earb200_bus *bus, const float *d_partial, int64_t partial_stride, int64_t t0,
+                     int64_t n, void *stream);
+/* Tells every peer that this rank's tiles of the epoch are in place (stream order: after the
+ * renders queued so far).  earb200_bus_reduce does it itself when it has not been done; the separate
+ * call is for hosts that drive several ranks through ONE stream or device, where every rank has to
+ * publish before any rank starts waiting. */
+int earb200_bus_publish(earb200_bus *bus, void *stream);
+/* Ends the epoch (once per rank, after the rank's renders of the epoch, on the same stream): waits
+ * for the tiles of all ranks and sums the slots of this rank's slice in rank order.
+ * d_out (nullable): this rank's slice of the summed bus, [n_channels][t1 - t0], row pitch
+ * out_stride (reduce-scatter).  gather != 0: the summed slice also goes to every rank's full bus
+ * (all-reduce); queue earb200_bus_wait_result before reading earb200_bus_result(), and consume the
+ * result on the same stream before the next epoch's reduce. */
+int earb200_bus_reduce(earb200_bus *bus, float *d_out, int64_t out_stride, int gather, void *stream);
+int earb200_bus_wait_result(earb200_bus *bus, void *stream);
+const float *earb200_bus_result(const earb200_bus *bus);   /* [n_channels][...], device memory */
+int64_t earb200_bus_result_stride(const earb200_bus *bus); /* its row pitch in floats */
+int64_t earb200_bus_launch_count(const earb200_bus *bus);
+
 /* ----------------------------------------------------- block convolver (K4)
  * replaces ear::dsp::block_convolver::{Context,Filter,BlockConvolver}
  * (include/ear/dsp/block_convolver.hpp:28-112, src/dsp/block_convolver_impl.cpp) and

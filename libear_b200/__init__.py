@@ -31,8 +31,9 @@ for _f in ("earb200_objects_launch_count", "earb200_interp_launch_count",
            "earb200_convolver_launch_count", "earb200_direct_speakers_launch_count",
            "earb200_delay_launch_count", "earb200_delay_get_delay", "earb200_fft_launch_count",
            "earb200_fft_size", "earb200_objects_renderer_block_size", "earb200_conversion_launch_count",
-           "earb200_objects_renderer_launch_count"):
+           "earb200_objects_renderer_launch_count", "earb200_bus_result_stride", "earb200_bus_launch_count"):
     getattr(_lib, _f).restype = C.c_int64
+_lib.earb200_bus_result.restype = C.c_void_p
 
 
 # exception classes mirroring libear's (include/ear/exceptions.hpp:8-43)
@@ -341,10 +342,78 @@ class GainInterpolator:
                                               C.c_int64(n), _ptr(out), C.c_int64(n)))
         return out
 
+    def process_device_bus(self, block_start, nsamples, d_in, in_stride, bus, bus_t0, d_partial=None,
+                           partial_stride=0, stream=0):
+        """process() of this rank's objects into the node-wide bus (Bus)."""
+        _chk(_lib.earb200_interp_process_device_bus(self.h, C.c_int64(block_start), C.c_int64(nsamples), _ptr(d_in),
+                                                    C.c_int64(in_stride), _ptr(d_partial), C.c_int64(partial_stride),
+                                                    bus.h, C.c_int64(bus_t0), C.c_void_p(int(stream))))
+
     def process_device(self, block_start, nsamples, d_in, in_stride, d_out, out_stride, stream=0):
         _chk(_lib.earb200_interp_process_device(self.h, C.c_int64(block_start), C.c_int64(nsamples),
                                                 _ptr(d_in), C.c_int64(in_stride), _ptr(d_out),
                                                 C.c_int64(out_stride), C.c_void_p(int(stream))))
+
+
+class Bus:
+    """The loudspeaker bus shared by the GPUs of one node (earb200_bus_*, include/earb200.h): the
+    exchange step of object-sharded mixing over peer memory.  One instance per rank."""
+
+    def __init__(self, n_channels, n_samples, rank=0, n_ranks=1, device=0):
+        self.n_channels, self.n_samples, self.rank, self.n_ranks = n_channels, n_samples, rank, n_ranks
+        self.h = C.c_void_p()
+        _chk(_lib.earb200_bus_create(device, rank, n_ranks, n_channels, C.c_int64(n_samples), C.byref(self.h)))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            if _lib is not None:  # None while the interpreter shuts down
+                _lib.earb200_bus_destroy(self.h)
+            self.h = None
+
+    def ipc_handle(self):
+        buf = C.create_string_buffer(_lib.earb200_bus_ipc_handle_bytes())
+        _chk(_lib.earb200_bus_get_ipc_handle(self.h, buf))
+        return buf.raw
+
+    def open_ipc(self, handles):
+        """handles: the ipc_handle() of every rank, in rank order."""
+        _chk(_lib.earb200_bus_open_ipc(self.h, b"".join(handles)))
+
+    @staticmethod
+    def connect_local(buses):
+        """All ranks in this process: wire them up with direct peer access."""
+        arr = (C.c_void_p * len(buses))(*[b.h for b in buses])
+        _chk(_lib.earb200_bus_connect_local(arr, len(buses)))
+
+    def slice(self, rank=None):
+        t0, t1 = C.c_int64(0), C.c_int64(0)
+        _chk(_lib.earb200_bus_slice(self.h, self.rank if rank is None else rank, C.byref(t0), C.byref(t1)))
+        return t0.value, t1.value
+
+    def push(self, d_partial, partial_stride, t0, n, stream=0):
+        _chk(_lib.earb200_bus_push(self.h, _ptr(d_partial), C.c_int64(partial_stride), C.c_int64(t0), C.c_int64(n),
+                                   C.c_void_p(int(stream))))
+
+    def publish(self, stream=0):
+        _chk(_lib.earb200_bus_publish(self.h, C.c_void_p(int(stream))))
+
+    def wait_result(self, stream=0):
+        _chk(_lib.earb200_bus_wait_result(self.h, C.c_void_p(int(stream))))
+
+    def reduce(self, d_out=None, out_stride=0, gather=False, stream=0):
+        _chk(_lib.earb200_bus_reduce(self.h, _ptr(d_out), C.c_int64(out_stride), int(gather), C.c_void_p(int(stream))))
+
+    @property
+    def result_ptr(self):
+        return _lib.earb200_bus_result(self.h)
+
+    @property
+    def result_stride(self):
+        return _lib.earb200_bus_result_stride(self.h)
+
+    @property
+    def launch_count(self):
+        return _lib.earb200_bus_launch_count(self.h)
 
 
 class BlockConvolver:

@@ -46,6 +46,13 @@ struct earb200_interp {
   int use_tc = 0;  // tensor-core (tcgen05) fast path; EARB200_RENDER_PATH=cuda selects the FFMA kernel
 };
 
+// capi_bus.cpp: the slots this rank stores to in the current epoch
+struct earb200_bus;
+earb::RenderBus earb200_bus_map(const earb200_bus &bus, int64_t t_origin);
+int64_t earb200_bus_capacity(const earb200_bus *bus);
+int earb200_bus_num_channels(const earb200_bus *bus);
+void earb200_bus_count_launch(earb200_bus *bus);
+
 namespace {
   // align: sample phase p in [0, 4) such that call-relative samples t with (t + p) % 4 == 0
   // are 16-byte aligned in both buffers, or -1 when no such phase exists
@@ -137,11 +144,21 @@ namespace {
   }
 
   void process_device(earb200_interp &h, int64_t block_start, int64_t nsamples, const float *d_in,
-                      int64_t in_stride, float *d_out, int64_t out_stride, cudaStream_t stream) {
+                      int64_t in_stride, float *d_out, int64_t out_stride, cudaStream_t stream,
+                      earb200_bus *bus = nullptr, int64_t bus_t0 = 0) {
     if (nsamples < 0) throw Error(INVALID_ARGUMENT, "negative sample count");
     if (nsamples == 0) return;
-    if (!d_in || !d_out) throw Error(INVALID_ARGUMENT, "null buffer");
+    if (!d_in || (!d_out && !bus)) throw Error(INVALID_ARGUMENT, "null buffer");
     use_device(h.device);
+    if (bus) {
+      if (earb200_bus_num_channels(bus) != h.M) throw Error(INVALID_ARGUMENT, "the bus has another channel count");
+      if (bus_t0 < 0 || bus_t0 + nsamples > earb200_bus_capacity(bus))
+        throw Error(INVALID_ARGUMENT, "the call reaches outside the bus");
+      if (!d_out) {  // no partial bus: the output imposes no alignment, take the input's
+        out_stride = 4;
+        d_out = reinterpret_cast<float *>(reinterpret_cast<uintptr_t>(d_in) & 15);
+      }
+    }
     // the TMA path needs 16-byte aligned rows in both buffers at a common sample phase
     int align = -1;
     const uintptr_t ia = reinterpret_cast<uintptr_t>(d_in), oa = reinterpret_cast<uintptr_t>(d_out);
@@ -150,10 +167,25 @@ namespace {
       align = (int)((ia / 4) & 3);
     const earb200_interp::Plan &pl = build_plan(h, block_start, nsamples, align);
     RenderPlan plan{pl.d_items.ptr, pl.n_items[0], pl.n_items[1], pl.n_items[2], pl.n_items[3], h.use_tc,
-                    h.n_sms, (long)nsamples, h.d_images.ptr, h.accumulate, (long)h.n_points};
+                    h.n_sms, (long)nsamples, h.d_images.ptr, h.accumulate, (long)h.n_points, RenderBus{}};
+    // Bus mode.  Fused: every item is a tile of the tcgen05 kernel, whose epilogue stores to the bus
+    // slots itself (accumulate mode and the earlier input groups of N > 128 read / write the
+    // caller's partial bus).  Otherwise (ragged or unaligned calls, the FFMA kernels): render into
+    // the partial bus, then push it.
+    const bool have_partial = reinterpret_cast<uintptr_t>(d_out) > 15;
+    const bool fused = bus && h.use_tc && pl.n_items[2] + pl.n_items[3] == 0 &&
+                       (have_partial || (!h.accumulate && h.N <= 128));
+    if (bus && !fused && !have_partial)
+      throw Error(INVALID_ARGUMENT, "this call needs a partial-bus buffer (accumulate mode, more than 128 "
+                                    "input channels, or a call that is not made of whole aligned tiles)");
+    if (fused) plan.bus = earb200_bus_map(*bus, bus_t0);
     h.timer.start(stream);
     launch_render(h.N, h.M, d_in, (long)in_stride, d_out, (long)out_stride, plan, pl.d_segs.ptr,
                   h.d_gains.ptr, stream);
+    if (bus && !fused) {
+      launch_bus_push(d_out, out_stride, h.M, bus_t0, nsamples, earb200_bus_map(*bus, bus_t0), stream);
+      earb200_bus_count_launch(bus);
+    }
     h.timer.stop(stream);
     EARB_CUDA(cudaGetLastError());
     if (h.use_tc) {
@@ -296,6 +328,18 @@ int earb200_interp_process_device(earb200_interp *interp, int64_t block_start,
     if (!interp) throw Error(INVALID_ARGUMENT, "null argument");
     process_device(*interp, block_start, nsamples, d_in, in_stride, d_out, out_stride,
                    (cudaStream_t)stream);
+  });
+}
+
+// process() whose output goes to the node-wide bus (earb200_bus_*): the partial result of this
+// rank's objects for the bus samples [bus_t0, bus_t0 + nsamples)
+int earb200_interp_process_device_bus(earb200_interp *interp, int64_t block_start, int64_t nsamples,
+                                      const float *d_in, int64_t in_stride, float *d_partial,
+                                      int64_t partial_stride, earb200_bus *bus, int64_t bus_t0, void *stream) {
+  return guarded([&] {
+    if (!interp || !bus) throw Error(INVALID_ARGUMENT, "null argument");
+    process_device(*interp, block_start, nsamples, d_in, in_stride, d_partial, partial_stride, (cudaStream_t)stream,
+                   bus, bus_t0);
   });
 }
 

@@ -113,6 +113,17 @@ namespace earb {
 #define RENDER_TC_TILE 256
   // work items of one call, grouped: full 16-byte aligned RENDER_PIPE_TILE-sample tiles go to
   // the TMA-staged kernel ("fast"), ragged / unaligned runs to the direct kernel ("slow")
+  // Loudspeaker bus shared by the GPUs of one node (csrc/capi_bus.cpp): the bus is cut into one
+  // time slice per rank; a rank's render stores every output tile straight into the slot it has
+  // in the staging memory of the slice's OWNER -- peer stores over NVLink from the kernel's
+  // epilogue -- and the owner sums the slots.  n_ranks == 0: no bus, plain `out`.
+#define EARB_BUS_MAX_RANKS 8
+  struct RenderBus {
+    float *slot[EARB_BUS_MAX_RANKS];  // per owner: this rank's slot there, [M][slice_len] floats
+    long long slice_len;              // samples per slice
+    long long t_origin;               // bus sample of the call's sample 0
+    int n_ranks;
+  };
   struct RenderPlan {
     const RenderItem *d_items;  // [fast ramp | fast const | slow ramp | slow const]
     long n_fast_ramp, n_fast_const, n_slow_ramp, n_slow_const;
@@ -122,6 +133,7 @@ namespace earb {
     const float *d_images;  // per-point gain-matrix images (tcgen05 path)
     int accumulate;         // out += result instead of out = result (mixing channel groups)
     long n_points;          // interpolation points behind d_images
+    RenderBus bus;          // n_ranks > 0: results go to the bus slots (accumulate still READS `out`)
   };
   // tcgen05 / TMEM variant of the fast path (render_tc_kernels.cu)
   bool render_tc_supported(int N, int M);
@@ -132,7 +144,7 @@ namespace earb {
   bool launch_render_tc(int N, int M, const float *in, long in_stride, long n_samples, float *out,
                         long out_stride, const RenderItem *d_items, long n_tiles,
                         const RenderSegment *d_segs, const float *d_images, long n_points, int n_sms,
-                        int accumulate, cudaStream_t stream);
+                        int accumulate, const RenderBus &bus, cudaStream_t stream);
   // per-point gain-matrix images for the tcgen05 kernel (TF32 hi/lo split in UMMA layout)
   size_t render_tc_image_floats(int N, int M);
   void launch_render_prepare_points(int N, int M, long n_points, const float *d_gains, float *d_images,
@@ -144,6 +156,22 @@ namespace earb {
   void launch_render(int N, int M, const float *in, long in_stride, float *out, long out_stride,
                      const RenderPlan &plan, const RenderSegment *d_segs, const float *d_gains,
                      cudaStream_t stream);
+
+  // ---- bus exchange between the GPUs of a node (bus_kernels.cu)
+  // flags[src] of every peer <- epoch (release at system scope): this rank's stores of the epoch
+  // into the peers' slots are complete
+  void launch_bus_signal(uint32_t *const *peer_flags, int n_ranks, int rank, uint32_t epoch, cudaStream_t stream);
+  // waits until flags[r] >= epoch for every rank, then out[m][t] = sum over r of slot r (own slice);
+  // gather != null: also stores the summed slice into every rank's full bus
+  void launch_bus_reduce(const uint32_t *flags, int n_ranks, uint32_t epoch, const float *slots, long long slot_floats,
+                         int M, long long slice_len, long long valid_len, float *out, long long out_stride,
+                         float *const *gather, long long gather_stride, long long gather_offset, int n_sms,
+                         cudaStream_t stream);
+  // local [M][T] partial bus -> the slots (the path for calls the fused epilogue cannot take)
+  void launch_bus_push(const float *partial, long long partial_stride, int M, long long t_origin, long long n,
+                       const RenderBus &bus, cudaStream_t stream);
+  // waits until flags[r] >= epoch for every rank (the gather of an epoch has landed everywhere)
+  void launch_bus_wait(const uint32_t *flags, int n_ranks, uint32_t epoch, cudaStream_t stream);
 
   // ---- K4: partitioned FFT convolver bank (convolver_kernels.cu)
 #define CONV_THREADS 128

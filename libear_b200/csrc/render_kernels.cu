@@ -387,7 +387,7 @@ namespace earb {
       // the ramp and constant tiles are adjacent in the item list: one persistent launch
       if (!launch_render_tc(N, M, in, in_stride, plan.n_samples, out, out_stride, fast_ramp,
                             n_fast_ramp + n_fast_const, d_segs, plan.d_images, plan.n_points, plan.n_sms,
-                            plan.accumulate, stream))
+                            plan.accumulate, plan.bus, stream))
         throw std::runtime_error("cuTensorMapEncodeTiled failed for the render input");
       n_fast_ramp = n_fast_const = 0;
     }

@@ -251,7 +251,7 @@ namespace earb {
                                     const RenderItem *__restrict__ items, int n_tiles,
                                     const RenderSegment *__restrict__ segs,
                                     const float *__restrict__ images, int n_stages, int accumulate,
-                                    int n_groups) {
+                                    int n_groups, const RenderBus bus) {
       extern __shared__ __align__(128) unsigned char smem_raw[];
       constexpr int kEpiWarps = EPI;
       constexpr int kProducerWarp = kConvWarps + kEpiWarps, kMmaWarp = kProducerWarp + 1;
@@ -481,6 +481,7 @@ namespace earb {
           constexpr int MO = NP / 2;               // output channels per work unit
           const int Mg = min(MO, M - grp * MO);    // output channels of this group
           float *const og = out + (long)grp * MO * out_stride;
+          const bool to_bus = bus.n_ranks > 0;
           // accumulate mode: the bus values this thread will add to are fetched before waiting for
           // the accumulators, so their latency hides behind the MMAs of this tile
           // (wide units read the bus inside the loop instead: 64 more registers would not fit)
@@ -501,6 +502,16 @@ namespace earb {
             const int j = j0 + jj;
             const long t = item.t0 + j * 128 + q * 32 + lane;
             const float p = ramp ? (float)(t - seg.ramp_start) * seg.scale : 0.0f;
+            // where this sample's results go: the caller's buffer, or this rank's slot in the
+            // staging memory of the GPU that owns the sample's time slice (a peer store)
+            float *dst = og + t;
+            long dst_stride = out_stride;
+            if (to_bus) {
+              const long long bt = (long long)t + bus.t_origin;
+              const int owner = (int)(bt / bus.slice_len);
+              dst = bus.slot[owner] + (long long)grp * MO * bus.slice_len + (bt - (long long)owner * bus.slice_len);
+              dst_stride = (long)bus.slice_len;
+            }
             if (NP == 32) {
               // main and correction accumulators, each [16 x g_a (start point) | 16 x g_b (end point)]
               float a[32], b[32];
@@ -513,7 +524,7 @@ namespace earb {
                   const float sb = a[16 + m] + b[16 + m];
                   float r = ramp ? fmaf(p, sb - sa, sa) : sa;
                   if (accumulate) r += prev[jj][m];  // mix into the bus
-                  if (EARB_RENDER_EXPERIMENT < 3) __stcs(og + (long)m * out_stride + t, r);
+                  if (EARB_RENDER_EXPERIMENT < 3) __stcs(dst + (long)m * dst_stride, r);
                 }
               }
             } else {
@@ -522,11 +533,11 @@ namespace earb {
 #pragma unroll
               for (int h = 0; h < 4; h++) {
                 if (h * 8 < Mg) {
-                  float bus[8];
+                  float mix[8];
                   if (accumulate) {
 #pragma unroll
                     for (int m = 0; m < 8; m++)
-                      bus[m] = (h * 8 + m < Mg) ? __ldcs(og + (long)(h * 8 + m) * out_stride + t) : 0.0f;
+                      mix[m] = (h * 8 + m < Mg) ? __ldcs(og + (long)(h * 8 + m) * out_stride + t) : 0.0f;
                   }
                   float sa[8], sb[8], ca[8], cb[8];
                   tmem_ld8x4(acc + j * 128 + h * 8, acc + j * 128 + 32 + h * 8, acc + j * 128 + 64 + h * 8,
@@ -536,8 +547,8 @@ namespace earb {
                     if (h * 8 + m < Mg) {
                       const float va = sa[m] + ca[m], vb = sb[m] + cb[m];
                       float r = ramp ? fmaf(p, vb - va, va) : va;
-                      if (accumulate) r += bus[m];
-                      if (EARB_RENDER_EXPERIMENT < 3) __stcs(og + (long)(h * 8 + m) * out_stride + t, r);
+                      if (accumulate) r += mix[m];
+                      if (EARB_RENDER_EXPERIMENT < 3) __stcs(dst + (long)(h * 8 + m) * dst_stride, r);
                     }
                   }
                 }
@@ -683,7 +694,7 @@ namespace earb {
   bool launch_render_tc(int N, int M, const float *in, long in_stride, long n_samples, float *out,
                         long out_stride, const RenderItem *d_items, long n_tiles,
                         const RenderSegment *d_segs, const float *d_images, long n_points, int n_sms,
-                        int accumulate, cudaStream_t stream) {
+                        int accumulate, const RenderBus &bus, cudaStream_t stream) {
     if (n_tiles <= 0) return true;
     EncodeTiledFn encode = encode_tiled();
     if (!encode) return false;
@@ -711,18 +722,21 @@ namespace earb {
                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
         return false;
       const int acc_mode = (accumulate || k0 > 0) ? 1 : 0;
+      // input groups accumulate into `out`; only the last one stores to the bus slots
+      RenderBus gbus = bus;
+      if (k0 + sh.max_in < N) gbus.n_ranks = 0;
       if (sh.NP == 64)  // wide units: the read-out of 2 x 64 accumulator columns always wants eight warps
         render_tc_persistent_kernel<64, 8><<<grid, threads_for(8), smem_for(Ng, 64), stream>>>(
             map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 64), acc_mode,
-            sh.n_out_groups);
+            sh.n_out_groups, gbus);
       else if (Ng <= 64)  // few input channels: the read-out sets the pace, eight epilogue warps
         render_tc_persistent_kernel<32, 8><<<grid, threads_for(8), smem_for(Ng, 32), stream>>>(
             map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 32), acc_mode,
-            sh.n_out_groups);
+            sh.n_out_groups, gbus);
       else
         render_tc_persistent_kernel<32, 4><<<grid, threads_for(4), smem_for(Ng, 32), stream>>>(
             map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 32), acc_mode,
-            sh.n_out_groups);
+            sh.n_out_groups, gbus);
       d_images += (size_t)n_points * sh.n_out_groups * padded_k(Ng) * sh.NP;
     }
     return true;
