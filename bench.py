@@ -426,20 +426,26 @@ def run_ours(args):
         gi = eb.GainInterpolator(N, M, device=local_rank)
         gi.set_points(samples, gains)
 
-        from libear_b200.sharding import chunked_bus, mix_pipelined
-        side_stream = torch.cuda.Stream(dev) if world > 1 else None
-        if world > 1:
-            # object-sharded mixing: the bus is kept chunk-major so that each time chunk is summed
-            # over the GPUs by one contiguous all-reduce on a side stream while the next one renders
-            del y
-            y, y_ranges = chunked_bus(M, T, args.mix_chunks, device=dev)
-            y_per = y.shape[2]
+        from libear_b200.sharding import connect_bus
+        rbus = None
+        if world > 1 and args.exchange == "bus":
+            # object-sharded mixing (128 objects per GPU into ONE bus): the render kernel's epilogue
+            # stores every tile into the slot of the GPU that owns its time slice (peer stores over
+            # NVLink); the owners sum; the summed slices are gathered into every rank's full bus
+            rbus = connect_bus(eb.Bus(M, T, rank=rank, n_ranks=world, device=local_rank))
 
-            def render_chunk(k, t0, t1):
-                gi.process_device(t0, t1 - t0, x.data_ptr() + 4 * t0, T, y[k].data_ptr(), y_per, stream=stream)
-
+            def step_render(gather=bool(args.bus_gather)):
+                gi.process_device_bus(0, T, x.data_ptr(), T, rbus, 0, stream=stream)
+                if gather:
+                    rbus.reduce(gather=True, stream=stream)
+                    rbus.wait_result(stream=stream)
+                else:
+                    rbus.reduce(d_out=y.data_ptr(), out_stride=T, stream=stream)
+        elif world > 1:
+            # comparison arm: render, then one NCCL all-reduce of the bus
             def step_render():
-                mix_pipelined(y, render_chunk, reduce_stream=side_stream, ranges=y_ranges)
+                gi.process_device(0, T, x.data_ptr(), T, y.data_ptr(), T, stream=stream)
+                dist.all_reduce(y)
         else:
             def step_render():
                 gi.process_device(0, T, x.data_ptr(), T, y.data_ptr(), T, stream=stream)
@@ -463,13 +469,27 @@ def run_ours(args):
         gpu_launches += gi.launch_count - rl0
         alg_bytes = 4.0 * T * (N + M) + 4.0 * N * M * len(samples)
         achieved = alg_bytes * args.steps / (k_ms * 1e-3) / 1e9
+        rs_ms = None
+        if rbus is not None and args.bus_gather:
+            # the same step ending with every rank holding its time slice only (reduce-scatter)
+            step_render(gather=False)
+            barrier()
+            r0.record()
+            for _ in range(args.steps):
+                step_render(gather=False)
+            r1.record()
+            barrier()
+            rs_ms = max_over_ranks(r0.elapsed_time(r1)) / args.steps
         render = {
             "metric": "render Msamples/s (input object-samples)",
             "value": N * T * world * args.steps / (r_ms * 1e-3) / 1e6, "unit": "Msamples/s",
-            "ms_per_step": r_ms / args.steps,
+            "ms_per_step": r_ms / args.steps, "ms_per_step_reduce_scatter": rs_ms,
             "config": {"workload": f"configs[2] (SURVEY cfg 3): {N} objects/GPU x 60 s x 48 kHz into {R['layout']} (M={M}), "
                                    f"{R['ramp']}-sample linear gain ramps; inputs 1.6 GB/step > L2",
-                       "bus_reduce": (f"nccl all_reduce(sum, f32) of the [M x T] bus, {args.mix_chunks} time chunk(s)")
+                       "bus_reduce": ("node-wide bus over peer memory (earb200_bus_*): tiles stored into the owners' "
+                                      "slots by the render epilogue, deterministic sum per time slice"
+                                      + (", gather to every rank" if args.bus_gather else ", no gather (reduce-scatter)")
+                                      if rbus is not None else "nccl all_reduce(sum, f32) of the [M x T] bus after the render")
                        if world > 1 else "none"},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                          "frac": achieved / hbm_peak,
@@ -492,6 +512,32 @@ def run_ours(args):
             parity["render_windows_checked"] = len(starts)
             parity["render_bar"] = 2e-6
             parity["ok"] = parity["ok"] and worst < 2e-6
+        if world > 1 and not args.no_parity:
+            # rank 0 renders the objects of ALL ranks for a window alone and compares with the summed bus
+            Tw = 8192
+            xw = [torch.empty((N, Tw), dtype=torch.float32, device=dev) for _ in range(world)]
+            dist.all_gather(xw, x[:, :Tw].contiguous())
+            gw = [None] * world
+            dist.all_gather_object(gw, gains[:Tw // R["ramp"] + 1])
+            step_render()
+            torch.cuda.synchronize()
+            if rank == 0:
+                got = torch.empty((M, Tw), dtype=torch.float32, device=dev)
+                if rbus is not None and args.bus_gather:
+                    rbus.copy_result(got.data_ptr(), Tw, 0, Tw, stream=stream)
+                else:   # the NCCL arm's bus, or rank 0's slice of the reduce-scatter (it starts at sample 0)
+                    got.copy_(y[:, :Tw])
+                want = torch.zeros((M, Tw), dtype=torch.float32, device=dev)
+                for r in range(world):
+                    gr = eb.GainInterpolator(N, M, device=local_rank)
+                    gr.set_points(samples[:Tw // R["ramp"] + 1], gw[r])
+                    gr.set_accumulate(r > 0)
+                    gr.process_device(0, Tw, xw[r].data_ptr(), Tw, want.data_ptr(), Tw, stream=stream)
+                torch.cuda.synchronize()
+                err = float((got - want).abs().max() / want.abs().max())
+                parity["sharded_render_vs_one_gpu_max_over_peak"] = err
+                parity["ok"] = parity["ok"] and err < 1e-6
+            del xw
         # end to end: pinned host input/output through the C-ABI host entry point
         if world == 1 and not args.no_render_e2e:
             hx = torch.empty((N, T), dtype=torch.float32).pin_memory()
@@ -694,7 +740,7 @@ def run_ours(args):
         lay5 = "4+7+0"
         T5 = args.mix_samples
         n_total = args.mix_objects
-        from libear_b200.sharding import chunked_bus, mix_pipelined, object_groups, reduce_bus, shard_range
+        from libear_b200.sharding import connect_bus, object_groups, reduce_bus, shard_range
         obj_a, obj_b = shard_range(n_total, rank, world)
         n_local = obj_b - obj_a
         # HOA order 3 (ACN 0..15, SN3D): design on the device, apply as a static 16 -> 12 matrix
@@ -749,24 +795,32 @@ def run_ours(args):
         bus = torch.empty((M5, T5), device=dev, dtype=torch.float32)
         red0, red1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
-        mix_side = torch.cuda.Stream(dev) if world > 1 else None
-        cbus, cranges = chunked_bus(M5, T5, args.mix_chunks if world > 1 else 1, device=dev)
-        c_per = cbus.shape[2]
+        mbus, slice5 = None, None
+        if world > 1 and args.exchange == "bus":
+            mbus = connect_bus(eb.Bus(M5, T5, rank=rank, n_ranks=world, device=local_rank))
+            s0, s1 = mbus.slice()
+            slice5 = torch.empty((M5, max(1, s1 - s0)), dtype=torch.float32, device=dev)
 
-        def mix_chunk(k, t0, t1):
-            for g0, g1, gi in groups:
-                gi.process_device(t0, t1 - t0, xo[g0].data_ptr() + 4 * t0, T5, cbus[k].data_ptr(), c_per,
-                                  stream=stream)
-
-        def step_mix(timed_reduce=False):
-            if timed_reduce:  # the exchange step on its own: render everything, then one all-reduce
-                for g0, g1, gi in groups:
-                    gi.process_device(0, T5, xo[g0].data_ptr(), T5, bus.data_ptr(), T5, stream=stream)
+        def step_mix(timed_reduce=False, gather=bool(args.bus_gather)):
+            # the groups of <= 256 objects accumulate into this rank's partial bus; with the node-wide
+            # bus the LAST group's render stores the finished partial tiles into the owners' slots
+            for g0, g1, gi in groups[:-1] if mbus is not None else groups:
+                gi.process_device(0, T5, xo[g0].data_ptr(), T5, bus.data_ptr(), T5, stream=stream)
+            if mbus is not None:
+                g0, g1, gi = groups[-1]
+                gi.process_device_bus(0, T5, xo[g0].data_ptr(), T5, mbus, 0, d_partial=bus.data_ptr(),
+                                      partial_stride=T5, stream=stream)
+            if timed_reduce:
                 red0.record()
+            if mbus is not None and gather:
+                mbus.reduce(gather=True, stream=stream)
+                mbus.wait_result(stream=stream)
+            elif mbus is not None:
+                mbus.reduce(d_out=slice5.data_ptr(), out_stride=slice5.shape[1], stream=stream)
+            elif world > 1:
                 reduce_bus(bus)
+            if timed_reduce:
                 red1.record()
-            else:             # the one collective, chunked and hidden behind the rendering
-                mix_pipelined(cbus, mix_chunk, reduce_stream=mix_side, ranges=cranges)
 
         for _ in range(args.warmup):
             step_mix()
@@ -787,16 +841,29 @@ def run_ours(args):
             step_mix(timed_reduce=True)
             torch.cuda.synchronize()
             reduce_ms = max_over_ranks(red0.elapsed_time(red1))
+        mix_rs_ms = None
+        if mbus is not None and args.bus_gather:
+            step_mix(gather=False)
+            barrier()
+            m0.record()
+            for _ in range(args.steps):
+                step_mix(gather=False)
+            m1.record()
+            barrier()
+            mix_rs_ms = max_over_ranks(m0.elapsed_time(m1)) / args.steps
         mix_bytes = 4.0 * T5 * (n_local + M5 * (2 * len(groups) - 1)) + 4.0 * n_local * M5 * n_pts
         mix_block = {
             "metric": "object mixing Msamples/s (input object-samples, whole job)",
             "value": n_total * T5 / (mix_ms * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": mix_ms,
-            "scaling": "strong",
+            "ms_per_step_reduce_scatter": mix_rs_ms, "scaling": "strong",
             "config": {"workload": f"configs[4] (SURVEY cfg 5): {n_total} extent objects x {T5 / 48000:.0f} s x 48 kHz into {lay5} (M={M5}), "
                                    f"{n_local} objects/GPU in groups of 256, gains from GainCalculatorObjects at "
                                    f"{n_pts} points; HOA order 3 (16 ch) decode alongside",
-                       "bus_reduce": (f"nccl all_reduce(sum, f32) of the [M x T] bus, {args.mix_chunks} time chunk(s); "
-                                      "bus_reduce_ms is the reduce on its own")
+                       "bus_reduce": (("node-wide bus over peer memory (earb200_bus_*): the last group's render stores the "
+                                       "partial tiles into the owners' slots, deterministic sum per time slice, gather to "
+                                       "every rank; bus_reduce_ms is what remains after the last render"
+                                       if mbus is not None else
+                                       "nccl all_reduce(sum, f32) of the [M x T] bus after the render; bus_reduce_ms is the reduce"))
                        if world > 1 else "none (1 GPU)"},
             "roofline": {"bound": "hbm", "achieved": mix_bytes / (mix_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                          "frac": mix_bytes / (mix_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None,
@@ -808,7 +875,42 @@ def run_ours(args):
                     "apply_msamples_per_s": 16 * T5 / (hoa_ms * 1e-3) / 1e6,
                     "apply_gbs": 4.0 * T5 * (16 + M5) / (hoa_ms * 1e-3) / 1e9},
         }
-        del xo, bus, cbus, groups
+        if world > 1 and not args.no_parity:
+            # rank 0 renders a window of ALL 4,096 objects alone and compares with the summed bus
+            Tw = 4096
+            n_max = shard_range(n_total, 0, world)[1]
+            xw = [torch.zeros((n_max, Tw), dtype=torch.float32, device=dev) for _ in range(world)]
+            mine = torch.zeros((n_max, Tw), dtype=torch.float32, device=dev)
+            mine[:n_local] = xo[:, :Tw]
+            dist.all_gather(xw, mine)
+            gw = [None] * world
+            dist.all_gather_object(gw, gains5[:2])
+            step_mix()
+            torch.cuda.synchronize()
+            if rank == 0:
+                got = torch.empty((M5, Tw), dtype=torch.float32, device=dev)
+                if mbus is not None and args.bus_gather:
+                    mbus.copy_result(got.data_ptr(), Tw, 0, Tw, stream=stream)
+                elif mbus is not None:
+                    got.copy_(slice5[:, :Tw])
+                else:
+                    got.copy_(bus[:, :Tw])
+                want = torch.zeros((M5, Tw), dtype=torch.float32, device=dev)
+                first = True
+                for r in range(world):
+                    nr = gw[r].shape[1]
+                    for g0, g1 in object_groups(nr, 256):
+                        gr = eb.GainInterpolator(g1 - g0, M5, device=local_rank)
+                        gr.set_points(samples5[:2], gw[r][:, g0:g1])
+                        gr.set_accumulate(not first)
+                        first = False
+                        gr.process_device(0, Tw, xw[r][g0].data_ptr(), Tw, want.data_ptr(), Tw, stream=stream)
+                torch.cuda.synchronize()
+                err = float((got - want).abs().max() / want.abs().max())
+                parity["sharded_mix_vs_one_gpu_max_over_peak"] = err
+                parity["ok"] = parity["ok"] and err < 1e-6
+            del xw, mine
+        del xo, bus, groups, mbus
 
     if rank == 0:
         line = {
@@ -886,10 +988,12 @@ def main():
     ap.add_argument("--conv-blocks", type=int, default=56250, help="blocks per channel (cfg4: 10 min)")
     ap.add_argument("--mix-objects", type=int, default=4096, help="objects of the whole job (cfg5)")
     ap.add_argument("--mix-samples", type=int, default=2_880_000)
-    ap.add_argument("--mix-chunks", type=int, default=1,
-                    help="time chunks of the bus reduce at N > 1 (chunk k reduced on a side stream while chunk "
-                         "k + 1 renders); 1 = render, then one all-reduce -- the faster form as measured, see "
-                         "DESIGN.md section 7")
+    ap.add_argument("--bus-gather", type=int, default=1,
+                    help="1: every rank ends with the whole summed bus (all-reduce semantics, like the NCCL arm); "
+                         "0: every rank ends with its time slice only (reduce-scatter semantics)")
+    ap.add_argument("--exchange", default="bus", choices=["bus", "nccl"],
+                    help="the exchange step of object-sharded mixing at N > 1: the node-wide bus of the C ABI (peer "
+                         "stores from the render epilogue), or the comparison arm: render, then one NCCL all-reduce")
     ap.add_argument("--no-render-e2e", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiler runs)")
     ap.add_argument("--no-cpu-baseline", action="store_true")

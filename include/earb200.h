@@ -269,6 +269,9 @@ int earb200_bus_reduce(earb200_bus *bus, float *d_out, int64_t out_stride, int g
 int earb200_bus_wait_result(earb200_bus *bus, void *stream);
 const float *earb200_bus_result(const earb200_bus *bus);   /* [n_channels][...], device memory */
 int64_t earb200_bus_result_stride(const earb200_bus *bus); /* its row pitch in floats */
+/* the samples [t0, t0 + n) of the full bus into a planar device buffer (row pitch dst_stride) */
+int earb200_bus_copy_result(const earb200_bus *bus, float *d_dst, int64_t dst_stride, int64_t t0,
+                            int64_t n, void *stream);
 int64_t earb200_bus_launch_count(const earb200_bus *bus);
 
 /* ----------------------------------------------------- block convolver (K4)

@@ -403,6 +403,10 @@ class Bus:
     def reduce(self, d_out=None, out_stride=0, gather=False, stream=0):
         _chk(_lib.earb200_bus_reduce(self.h, _ptr(d_out), C.c_int64(out_stride), int(gather), C.c_void_p(int(stream))))
 
+    def copy_result(self, d_dst, dst_stride, t0, n, stream=0):
+        _chk(_lib.earb200_bus_copy_result(self.h, _ptr(d_dst), C.c_int64(dst_stride), C.c_int64(t0), C.c_int64(n),
+                                          C.c_void_p(int(stream))))
+
     @property
     def result_ptr(self):
         return _lib.earb200_bus_result(self.h)

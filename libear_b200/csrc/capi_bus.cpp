@@ -51,6 +51,7 @@ namespace {
 RenderBus earb200_bus_map(const earb200_bus &b, int64_t t_origin) {
   RenderBus m{};
   m.n_ranks = b.n_ranks;
+  m.rank = b.rank;
   m.slice_len = b.slice_len;
   m.t_origin = t_origin;
   for (int o = 0; o < b.n_ranks; o++) m.slot[o] = b.slots(o, (int)(b.epoch & 1)) + (size_t)b.rank * b.slot_floats;
@@ -164,6 +165,19 @@ int earb200_bus_slice(const earb200_bus *bus, int rank, int64_t *t0, int64_t *t1
 const float *earb200_bus_result(const earb200_bus *bus) { return bus ? bus->full(bus->rank) : nullptr; }
 int64_t earb200_bus_result_stride(const earb200_bus *bus) { return bus ? bus->slice_len * bus->n_ranks : 0; }
 int64_t earb200_bus_launch_count(const earb200_bus *bus) { return bus ? bus->launches : 0; }
+
+// the samples [t0, t0 + n) of this rank's full bus into a caller's planar buffer (device to device)
+int earb200_bus_copy_result(const earb200_bus *bus, float *d_dst, int64_t dst_stride, int64_t t0, int64_t n,
+                            void *stream) {
+  return guarded([&] {
+    if (!bus || !d_dst) throw Error(INVALID_ARGUMENT, "null argument");
+    if (t0 < 0 || n < 0 || t0 + n > bus->slice_len * bus->n_ranks) throw Error(INVALID_ARGUMENT, "range outside the bus");
+    use_device(bus->device);
+    EARB_CUDA(cudaMemcpy2DAsync(d_dst, sizeof(float) * dst_stride, bus->full(bus->rank) + t0,
+                                sizeof(float) * bus->slice_len * bus->n_ranks, sizeof(float) * n, bus->M,
+                                cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  });
+}
 
 // a local [M][n] partial bus (bus samples t0 ...) into the slots: for renders that did not go
 // through earb200_interp_process_device_bus

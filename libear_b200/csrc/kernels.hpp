@@ -123,6 +123,9 @@ namespace earb {
     long long slice_len;              // samples per slice
     long long t_origin;               // bus sample of the call's sample 0
     int n_ranks;
+    int rank;  // rank r starts its walk over the tiles r / n_ranks of the way in: at any moment the
+               // ranks store into DIFFERENT owners (all ranks walking the time axis in step would
+               // all store into the one GPU that owns the current slice: 8-to-1 incast on its links)
   };
   struct RenderPlan {
     const RenderItem *d_items;  // [fast ramp | fast const | slow ramp | slow const]

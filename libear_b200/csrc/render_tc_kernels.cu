@@ -258,6 +258,8 @@ namespace earb {
       constexpr int kBLoadWarp = kMmaWarp + kMT;  // streams the gain-matrix images
       const int Kp = (N + kCh - 1) / kCh * kCh;  // K padded to whole stages
       const int n_iters = Kp / kCh;
+      // bus mode: this rank's walk over the tiles starts rank / n_ranks of the way in (RenderBus)
+      const int tile_shift = bus.n_ranks > 0 ? (int)((long)bus.rank * n_tiles / bus.n_ranks) : 0;
       // a work unit = one 256-sample tile x one group of 16 output channels; the groups of a tile
       // are adjacent units, so they run on neighbouring CTAs at the same time and the second read
       // of the tile's input is served by L2
@@ -308,7 +310,8 @@ namespace earb {
           uint32_t phase = 0;  // parity of the `empty` completion to wait for, once the ring wrapped
           bool wrapped = false;
           for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, L++) {
-          const int tile = unit / n_groups, grp = unit - tile * n_groups;
+          const int tile0 = unit / n_groups, grp = unit - tile0 * n_groups;
+          const int tile = tile0 + tile_shift < n_tiles ? tile0 + tile_shift : tile0 + tile_shift - n_tiles;
           (void)grp;
             const int t0 = (int)items[tile].t0;
             for (int it = 0; it < n_iters; it++) {
@@ -334,7 +337,8 @@ namespace earb {
           const size_t img = (size_t)Kp * NP;                            // floats per point image
           int L = 0;
           for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, L++) {
-          const int tile = unit / n_groups, grp = unit - tile * n_groups;
+          const int tile0 = unit / n_groups, grp = unit - tile0 * n_groups;
+          const int tile = tile0 + tile_shift < n_tiles ? tile0 + tile_shift : tile0 + tile_shift - n_tiles;
           (void)grp;
             const int ab = L & 1;
             if (L >= 2) mbar_wait(&acc_full[ab], (uint32_t)(((L >> 1) - 1) & 1));
@@ -366,7 +370,8 @@ namespace earb {
         const uint32_t b_tile_step = (uint32_t)((2 * Kp * NP * sizeof(float)) >> 4);  // next B buffer
         int g = 0, L = 0;
         for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, L++) {
-          const int tile = unit / n_groups, grp = unit - tile * n_groups;
+          const int tile0 = unit / n_groups, grp = unit - tile0 * n_groups;
+          const int tile = tile0 + tile_shift < n_tiles ? tile0 + tile_shift : tile0 + tile_shift - n_tiles;
           (void)grp;
           const int ab = L & 1;
           // B of this tile: rows 0..31 = [a | b] hi, 32..63 = [a | b] lo
@@ -472,7 +477,8 @@ namespace earb {
         const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
         int L = 0;
         for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, L++) {
-          const int tile = unit / n_groups, grp = unit - tile * n_groups;
+          const int tile0 = unit / n_groups, grp = unit - tile0 * n_groups;
+          const int tile = tile0 + tile_shift < n_tiles ? tile0 + tile_shift : tile0 + tile_shift - n_tiles;
           (void)grp;
           const int ab = L & 1;
           const RenderItem item = items[tile];

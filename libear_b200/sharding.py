@@ -2,8 +2,11 @@
 
 Gain calculation, the convolver bank and HOA shard by objects / channels with no data-path
 collective; object-sharded mixing has the one exchange step: every rank renders its objects into a
-partial [M x T] loudspeaker bus and the buses are summed (`reduce_bus`, one all-reduce; NCCL over
-NVLink on the GPUs, gloo in the CPU tests).  One process per GPU, `torch.distributed` plumbing."""
+partial [M x T] loudspeaker bus and the buses are summed.  On the GPUs that step is part of the
+product: the node-wide bus of the C ABI (libear_b200.Bus: peer stores from the render epilogue, a
+deterministic sum per time slice; `connect_bus` hands the IPC handles around).  `reduce_bus` /
+`mix_pipelined` are the torch.distributed all-reduce form (gloo in the CPU tests, NCCL as the
+comparison arm of bench.py).  One process per GPU, `torch.distributed` plumbing."""
 
 
 def shard_range(n_units, rank, world):
@@ -20,6 +23,28 @@ def object_groups(n_objects, max_group=256):
     """Groups of <= max_group objects a rank mixes one after the other into its bus (the render
     kernel's tensor-core path takes up to 256 input channels per launch)."""
     return [(g, min(n_objects, g + max_group)) for g in range(0, n_objects, max_group)]
+
+
+def bus_slices(n_samples, world, tile=256):
+    """The time slices [t0, t1) of a node-wide bus (libear_b200.Bus / earb200_bus_slice): rank r owns
+    slice r; slices are whole render tiles, the last ones may be short or empty."""
+    per = -(-int(n_samples) // world)
+    per = -(-per // tile) * tile
+    return [(min(n_samples, r * per), min(n_samples, (r + 1) * per)) for r in range(world)]
+
+
+def connect_bus(bus, group=None):
+    """One process per GPU: hand the ranks' IPC handles around (any transport would do: here the
+    process group's all_gather_object) and open them.  The exchange itself never touches
+    torch.distributed or NCCL: it is stores over NVLink from the render kernel's epilogue."""
+    import torch.distributed as dist
+    if bus.n_ranks == 1:
+        return bus
+    handles = [None] * bus.n_ranks
+    dist.all_gather_object(handles, bus.ipc_handle(), group=group)
+    bus.open_ipc(handles)
+    dist.barrier(group=group)
+    return bus
 
 
 def reduce_bus(bus, group=None):

@@ -105,12 +105,10 @@ def test_sharded_mix_equals_single_gpu_render(eb, ref, name, devices, mode):
             got = sl.cpu().numpy()[:, :t1 - t0]
             assert np.abs(got - want[:, t0:t1]).max() / (peak * scale) < 1e-6, (name, mode, epoch, r, "slice")
             # the gathered full bus of every rank
-            stride = buses[r].result_stride
-            import ctypes
-            full = torch.empty((M, stride), dtype=torch.float32, device=torch.device("cuda", d))
+            full = torch.full((M, T), float("nan"), dtype=torch.float32, device=torch.device("cuda", d))
             with torch.cuda.device(d):
-                ctypes.CDLL("libcudart.so").cudaMemcpy(ctypes.c_void_p(full.data_ptr()), ctypes.c_void_p(buses[r].result_ptr),
-                                                       ctypes.c_size_t(4 * M * stride), 3)
+                buses[r].copy_result(full.data_ptr(), T, 0, T, stream=torch.cuda.current_stream(full.device).cuda_stream)
+                torch.cuda.synchronize(d)
             assert np.abs(full.cpu().numpy()[:, :T] - want).max() / (peak * scale) < 1e-6, (name, mode, epoch, r, "full")
 
 

@@ -11,7 +11,8 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from libear_b200.sharding import chunk_ranges, chunked_bus, mix_pipelined, object_groups, reduce_bus, shard_range
+from libear_b200.sharding import (bus_slices, chunk_ranges, chunked_bus, mix_pipelined, object_groups, reduce_bus,
+                                   shard_range)
 
 
 def test_shard_range_is_a_partition():
@@ -40,6 +41,16 @@ def test_chunk_ranges():
         c = chunk_ranges(T, k)
         assert c[0][0] == 0 and c[-1][1] == T and len(c) <= k
         assert all(a[1] == b[0] for a, b in zip(c, c[1:])) and all(a % 512 == 0 for a, _ in c)
+
+
+def test_bus_slices_partition_the_bus_in_whole_tiles():
+    assert bus_slices(2_880_000, 8) == [(r * 360_192, min(2_880_000, (r + 1) * 360_192)) for r in range(8)]
+    assert bus_slices(4096, 2) == [(0, 2048), (2048, 4096)]
+    assert bus_slices(300, 4) == [(0, 256), (256, 300), (300, 300), (300, 300)]
+    for T, w in ((9572, 2), (1, 8), (2_880_000, 4), (256 * 37 + 100, 4)):
+        sl = bus_slices(T, w)
+        assert sl[0][0] == 0 and sl[-1][1] == T and all(a[1] == b[0] for a, b in zip(sl, sl[1:]))
+        assert all(a % 256 == 0 for a, _ in sl if a < T)
 
 
 def _free_port():
@@ -90,6 +101,20 @@ def _worker(rank, world, port, out_dir):
         mine, mine_region, _ = pan.handle(dirs[sl])
         full_gains, full_region, _ = pan.handle(dirs)
         ok_slice = bool(np.array_equal(mine, full_gains[sl]) and np.array_equal(mine_region, full_region[sl]))
+        # the IPC handles of a node-wide bus travel through the process group (connect_bus): every
+        # rank ends with all handles in rank order
+        from libear_b200.sharding import connect_bus
+
+        class FakeBus:
+            n_ranks = world
+
+            def ipc_handle(self):
+                return bytes([rank]) * 64
+
+            def open_ipc(self, handles):
+                self.opened = handles
+        fb = connect_bus(FakeBus())
+        ok_slice = ok_slice and fb.opened == [bytes([r]) * 64 for r in range(world)]
         np.save(os.path.join(out_dir, f"r{rank}.npy"), np.array([err, float(ok_slice), a, b]))
     finally:
         dist.destroy_process_group()
