@@ -410,7 +410,7 @@ def run_ours(args):
                 np.array_equal(h_direct[sl].numpy().view(np.uint32), got_d.view(np.uint32)) and
                 np.array_equal(h_diffuse[sl].numpy().view(np.uint32), got_f.view(np.uint32)))
             parity["ok"] = parity["ok"] and parity["e2e_rows_equal_device_rows"]
-        parity["ok"] = parity["ok"] and parity["gains_max_abs"] < 1e-5 and fin.mean() > 0.999
+        parity["ok"] = bool(parity["ok"] and parity["gains_max_abs"] < 1e-5 and fin.mean() > 0.999)
 
     # ---------------- render: BASELINE config 2 (128 objects x 60 s x 48 kHz into 4+9+0)
     render = None
@@ -594,6 +594,41 @@ def run_ours(args):
         point_block["note"] = ("n1024 is launch-latency-bound (three small kernels per call); n1M runs the FP64 "
                                "region scan at 112 algorithmic bytes per object")
         del gcp
+
+    # ---------------- the north star's "5200-point" wording: the extent panner on the 5,200-point
+    # t-design instead of libear's 1,652-point grid.  Throughput only: libear has no such path, so
+    # there is nothing to compare the gains with
+    p5200_block = None
+    if not args.no_points:
+        n52 = min(n, 262_144)
+        gc52 = eb.GainCalculatorObjects(LAYOUT, device=local_rank, grid="tdesign5200")
+        d52 = torch.empty((n52, C_out), dtype=torch.float32, device=dev)
+        f52 = torch.empty((n52, C_out), dtype=torch.float32, device=dev)
+        for _ in range(args.warmup):
+            gc52.calculate_device(n52, soa, d52.data_ptr(), f52.data_ptr(), stream=stream)
+        barrier()
+        q0, q1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        l52 = gc52.launch_count
+        q0.record()
+        for _ in range(args.steps):
+            gc52.calculate_device(n52, soa, d52.data_ptr(), f52.data_ptr(), stream=stream)
+        q1.record()
+        barrier()
+        q_ms = max_over_ranks(q0.elapsed_time(q1)) / args.steps
+        gpu_launches += gc52.launch_count - l52
+        passes52 = n52 + int(np.count_nonzero(objs[5][:n52]))
+        p5200_block = {
+            "metric": "object gain vectors/s (9+10+3, extent, 5,200-point grid)", "unit": "vectors/s",
+            "value": n52 * world / (q_ms * 1e-3), "ms_per_step": q_ms, "objects_per_gpu": n52,
+            "contraction_tflops": 2.0 * 5200 * 22 * passes52 / (q_ms * 1e-3) / 1e12,
+            "weight_evals_per_s": 5200.0 * passes52 / (q_ms * 1e-3),
+            "kernel": "extent_core_tc_kernel (every weight evaluated, TF32 x 3; the cell-culled core's tables hold "
+                      "2,048 points)",
+            "note": "THROUGHPUT ONLY, parity unpinned: libear's extent panner has 1,652 points "
+                    "(src/object_based/polar_extent.cpp:12-39, 104); the 5,200-point t-design is the grid the north "
+                    "star names, and there is no reference output on it",
+        }
+        del gc52, d52, f52
 
     # ---------------- convolver: BASELINE config 4 (24 channels x 10 min, 512-tap decorrelators, B = 512)
     conv_block = None
@@ -913,6 +948,7 @@ def run_ours(args):
         del xo, bus, groups, mbus
 
     if rank == 0:
+        parity = {k: (bool(v) if isinstance(v, np.bool_) else v) for k, v in parity.items()}
         line = {
             "metric": "object gain vectors/s (9+10+3, extent)", "value": value, "unit": "vectors/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -944,6 +980,8 @@ def run_ours(args):
             line["sustained"] = objects_sustained
         if point_block is not None:
             line["point_sources"] = point_block
+        if p5200_block is not None:
+            line["extent_p5200"] = p5200_block
         if render is not None:
             line["render"] = render
         if conv_block is not None:

@@ -144,6 +144,15 @@ enum {
 };
 
 int earb200_objects_create(const earb200_layout *layout, int device, earb200_objects **out);
+/* extension: the virtual-source grid of the extent panner.  EARB200_GRID_LIBEAR = libear's own
+ * 1,652-point grid (generatePanningPositionsEven(37), src/object_based/polar_extent.cpp:12-39, 104;
+ * what earb200_objects_create uses and all parity rests on); EARB200_GRID_TDESIGN_5200 = the
+ * 5,200-point t-design of resources/Design_5200_100_random.dat: a throughput shape only -- libear
+ * has no extent panner on that grid, so there is no reference output (parity unpinned). */
+enum { EARB200_GRID_LIBEAR = 0, EARB200_GRID_TDESIGN_5200 = 1 };
+int earb200_objects_create_with_grid(const earb200_layout *layout, int device, int grid,
+                                     earb200_objects **out);
+int earb200_objects_grid_points(const earb200_objects *calc);
 void earb200_objects_destroy(earb200_objects *calc);
 int earb200_objects_num_outputs(const earb200_objects *calc); /* C_out incl. LFE */
 /* direct / diffuse: [n][C_out] row-major, float (out_is_double = 0) or double;

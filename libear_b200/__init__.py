@@ -222,11 +222,20 @@ OBJ_DIVERGENCE, OBJ_ZONE_EXCLUSION, OBJ_CARTESIAN_POSITION = 8, 16, 32
 class GainCalculatorObjects:
     """ear::GainCalculatorObjects (include/ear/gain_calculators.hpp:37-64), batched."""
 
-    def __init__(self, layout, device=0):
+    def __init__(self, layout, device=0, grid="libear"):
+        """grid: "libear" (1,652 points, the reference's) or "tdesign5200" (throughput shape only:
+        no reference to compare with)."""
         self.layout = _as_layout(layout)
         self.h = C.c_void_p()
-        _chk(_lib.earb200_objects_create(self.layout.h, device, C.byref(self.h)))
+        if grid == "libear":
+            _chk(_lib.earb200_objects_create(self.layout.h, device, C.byref(self.h)))
+        else:
+            kinds = {"tdesign5200": 1}
+            if grid not in kinds:
+                raise InvalidArgument("unknown extent grid %r" % (grid,))
+            _chk(_lib.earb200_objects_create_with_grid(self.layout.h, device, kinds[grid], C.byref(self.h)))
         self.num_outputs = _lib.earb200_objects_num_outputs(self.h)
+        self.grid_points = _lib.earb200_objects_grid_points(self.h)
 
     def __del__(self):
         if getattr(self, "h", None):

@@ -143,7 +143,7 @@ const int64_t earb200_objects::kChunkFixed = [] {
 }();
 
 namespace {
-  void objects_init(earb200_objects &o, const HostLayout &layout, int device) {
+  void objects_init(earb200_objects &o, const HostLayout &layout, int device, int grid_kind = 0) {
     use_device(device);
     o.device = device;
     o.layout = layout;
@@ -169,7 +169,13 @@ namespace {
 
     // extent grid: positions, cached point-source gains (computed by K1 on the device),
     // per-block sums (ref polar_extent.cpp:98-165)
-    std::vector<Vec3> pts = extentGridPositions(37);
+    // grid_kind 0: libear's generatePanningPositionsEven(37), 1,652 points (polar_extent.cpp:12-39,
+    // 104) -- the grid all parity rests on.  1: the 5,200-point spherical t-design of
+    // resources/Design_5200_100_random.dat (the grid BASELINE.json's north star names for the
+    // spreading panner; libear itself only uses it for the HOA decoder): throughput shape only,
+    // there is no reference output to compare with.
+    if (grid_kind != 0 && grid_kind != 1) throw Error(INVALID_ARGUMENT, "unknown extent grid");
+    std::vector<Vec3> pts = grid_kind == 0 ? extentGridPositions(37) : hoaDesignPoints();
     const int P = (int)pts.size();
     // padded to whole B stages of the tcgen05 core (a multiple of the FFMA core's 32-point blocks)
     static_assert(EXTENT_TC_STAGE_POINTS % EARB_EXT_BLOCK == 0, "padding");
@@ -617,6 +623,15 @@ int earb200_objects_create(const earb200_layout *layout, int device, earb200_obj
     *out = o.release();
   });
 }
+int earb200_objects_create_with_grid(const earb200_layout *layout, int device, int grid, earb200_objects **out) {
+  return guarded([&] {
+    if (!layout || !out) throw Error(INVALID_ARGUMENT, "null argument");
+    auto o = std::make_unique<earb200_objects>();
+    objects_init(*o, layout->layout, device, grid);
+    *out = o.release();
+  });
+}
+int earb200_objects_grid_points(const earb200_objects *calc) { return calc ? calc->grid.n_points : 0; }
 void earb200_objects_destroy(earb200_objects *calc) { delete calc; }
 int earb200_objects_num_outputs(const earb200_objects *calc) { return calc ? calc->n_out : 0; }
 int64_t earb200_objects_launch_count(const earb200_objects *calc) {

@@ -169,3 +169,26 @@ def test_render_float32_noise_fixture_cfg3_shape(eb, ref):
                            np.abs(exp - truth).max() / peak)
     print(f"128x14 f32 fixture: gpu-vs-libear {e_ref:.2e}, gpu-vs-f64 {e_64:.2e}, libear-vs-f64 {ref_64:.2e}")
     assert e_64 < 1e-6 and e_ref < 1e-6 and e_64 < 2 * ref_64
+
+
+def test_extent_on_the_5200_point_grid_is_a_sane_throughput_shape(eb):
+    """BASELINE.json's north star names a 5,200-point spreading grid; libear's extent panner has
+    1,652 points and no code path on the t-design, so this shape has NO reference
+    output: parity unpinned.  What can be checked: the gains are finite and power-normalised, LFE
+    stays silent, and -- both grids sampling the same weighting function -- they stay close to the
+    1,652-point result (a sanity bound, not a parity claim)."""
+    rng = np.random.default_rng(52)
+    n = 4000
+    cols = [rng.uniform(-180, 180, n), np.degrees(np.arcsin(rng.uniform(-1, 1, n))), np.ones(n),
+            rng.uniform(30, 360, n), rng.uniform(30, 360, n), np.zeros(n), rng.uniform(0.1, 1, n), np.zeros(n)]
+    big = eb.GainCalculatorObjects("9+10+3", grid="tdesign5200")
+    assert big.grid_points == 5200
+    d, f = big.calculate(*cols)
+    d0, _ = eb.GainCalculatorObjects("9+10+3").calculate(*cols)
+    assert np.isfinite(d).all() and (f == 0).all()
+    assert np.abs(np.linalg.norm(d.astype(np.float64), axis=1) - cols[6]).max() < 1e-5
+    lfe = eb.Layout("9+10+3").is_lfe
+    assert (d[:, lfe] == 0).all()
+    assert np.abs(d - d0).max() < 0.08 and np.abs(d - d0).mean() < 0.01
+    with pytest.raises(eb.InvalidArgument):
+        eb.GainCalculatorObjects("9+10+3", grid="nope")
