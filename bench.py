@@ -383,7 +383,7 @@ def run_ours(args):
                                                        C.c_void_p(h_diffuse.data_ptr()), None))
 
     if args.no_e2e:   # profiler runs only: the line then carries no end-to-end number
-        e2e_value, e2e_checksum = None, None
+        e2e_value, e2e_checksum, e2e_floor = None, None, None
     else:
         step_e2e_abi()
         barrier()
@@ -394,6 +394,29 @@ def run_ours(args):
         e2e_dt = max_over_ranks(time.perf_counter() - t0)
         e2e_value = n * world * e2e_steps / e2e_dt
         e2e_checksum = float(h_direct[:1000].double().sum())
+        # the floor the host path cannot go below on this box: the same bytes, copies only (inputs in
+        # on one stream while the outputs of the step go out on another), no kernels
+        s_a, s_b = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        d_cols = [torch.empty(n, dtype=torch.float64, device=dev) for _ in range(8)]
+
+        def copies():
+            with torch.cuda.stream(s_a):
+                for dc, hc in zip(d_cols, h_in):
+                    dc.copy_(hc, non_blocking=True)
+            with torch.cuda.stream(s_b):
+                h_direct.copy_(d_direct, non_blocking=True)
+                h_diffuse.copy_(d_diffuse, non_blocking=True)
+        copies()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            copies()
+        torch.cuda.synchronize()
+        floor_dt = max_over_ranks(time.perf_counter() - t0)
+        e2e_floor = {"value": n * world * e2e_steps / floor_dt, "unit": "vectors/s", "ms_per_step": floor_dt / e2e_steps * 1e3,
+                     "what": "host<->device copies of one step alone (pinned, both directions at once), no kernels: "
+                             "the PCIe / host-memory bound of the end-to-end path on this box"}
+        del d_cols
 
     objects_sustained = sustained(step_objects, n, args.sustained)
     if check:
@@ -970,7 +993,8 @@ def run_ours(args):
                          "weight_evals_per_s": weight_evals,
                          "kernel_share_of_step": core_ms / ms_total},
             "e2e": {"value": e2e_value, "unit": "vectors/s", "h2d_bytes_per_step": 8 * 8 * n,
-                    "d2h_bytes_per_step": 2 * 4 * C_out * n, "steps": e2e_steps, "checksum": e2e_checksum},
+                    "d2h_bytes_per_step": 2 * 4 * C_out * n, "steps": e2e_steps, "checksum": e2e_checksum,
+                    "floor": e2e_floor},
             "gpu_launches": int(gpu_launches),
             "clocks": sampler.summary(),
             "parity": parity,

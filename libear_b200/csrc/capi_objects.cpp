@@ -284,7 +284,7 @@ namespace {
   template <typename OutT>
   cudaEvent_t objects_run_chunk(earb200_objects &o, int64_t start, int64_t m, const ObjectsSoA &in, int n_out,
                                 const int32_t *d_out_index, OutT *d_direct, OutT *d_diffuse, int32_t *d_region,
-                                cudaStream_t stream, int fb_slot = -1) {
+                                cudaStream_t stream, int fb_slot = -1, bool epilogue_in_line = false) {
     ObjectsSoA c = in;
     if (c.xyz) {
       c.xyz += 3 * start;
@@ -320,14 +320,18 @@ namespace {
                             sc.d_results.ptr, o.n_sms, stream);
     o.timer.stop(stream);
     if (o.timer.enabled) o.timed_passes += 2 * m;
+    // the epilogue on the side stream (it runs beside the next chunk's prelude); in line, on the
+    // core's own stream, was measured slower on the host path as well (e2e 220-225 against 234-236 M
+    // vectors/s), although there the copy out of the chunk waits for it
+    cudaStream_t s_epi = epilogue_in_line ? stream : o.s_epi;
     EARB_CUDA(cudaEventRecord(sc.ev_core, stream));
-    EARB_CUDA(cudaStreamWaitEvent(o.s_epi, sc.ev_core, 0));
+    if (!epilogue_in_line) EARB_CUDA(cudaStreamWaitEvent(o.s_epi, sc.ev_core, 0));
     launch_objects_epilogue<OutT>(o.panner.d_tables, o.grid.n_spk, m, c, sc.d_passes.ptr, sc.d_aux.ptr,
                                   sc.d_results.ptr, sc.d_point_gains.ptr, sc.d_n_active.ptr, sc.d_point_list.ptr,
                                   o.n_sms, n_out, d_out_index,
                                   d_direct + start * n_out, d_diffuse + start * n_out,
-                                  d_region ? d_region + start : nullptr, o.s_epi);
-    EARB_CUDA(cudaEventRecord(sc.ev_epi, o.s_epi));
+                                  d_region ? d_region + start : nullptr, s_epi);
+    EARB_CUDA(cudaEventRecord(sc.ev_epi, s_epi));
     o.launches += 4;
     return sc.ev_epi;
   }
@@ -384,9 +388,37 @@ namespace {
       for (int64_t k = 0; k < samples; k++) deep += src[5][k * stride] != 0.0;
       o.passes_per_object = 1.0 + (double)deep / (double)samples;
     }
-    // two rounds per chunk: small enough for the copies of neighbouring chunks to hide behind it
+    // Two rounds per chunk: small enough for the copies of neighbouring chunks to hide behind it.
+    // The copies are the critical path (10^6 objects: 3.65 ms of PCIe traffic against 2.4 ms of
+    // kernels), so what the schedule can still save is the fill (first chunk in + computed before
+    // the copy out starts) and the drain (last chunk out after everything else has finished): the
+    // first and the last two chunks are a quarter and a half of the others.
     const int64_t chunk = pick_chunk(o, o.passes_per_object, 2);
-    const int64_t n_chunks = (n + chunk - 1) / chunk;
+    std::vector<int64_t> sizes;
+    {
+      const bool ramp = !earb200_objects::kChunkFixed && n >= 5 * chunk;
+      const int64_t q = chunk / 4 / 128 * 128, h = chunk / 2 / 128 * 128;
+      int64_t left = n;
+      auto take = [&](int64_t m) {
+        m = std::min(m, left);
+        if (m > 0) sizes.push_back(m);
+        left -= m;
+      };
+      if (ramp) {
+        take(q);
+        take(h);
+        while (left > chunk + h + q) take(chunk);
+        // what remains (between h + q and chunk + h + q): its last quarter-chunk and half-chunk close
+        // the schedule, the rest goes before them
+        const int64_t rest = left - h - q;
+        take(rest);
+        take(h);
+        take(q);
+      } else {
+        while (left > 0) take(chunk);
+      }
+    }
+    const int64_t n_chunks = (int64_t)sizes.size();
     while ((int64_t)o.ev_in.size() < n_chunks) {
       cudaEvent_t a, b;
       EARB_CUDA(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
@@ -401,9 +433,9 @@ namespace {
     OutT *d_out = reinterpret_cast<OutT *>(sizeof(OutT) == 8 ? (void *)o.d_out_d.reserve(2 * n_el)
                                                               : (void *)o.d_out_f.reserve(2 * n_el));
     OutT *d_direct = d_out, *d_diffuse = d_out + n_el;
-    for (int64_t k = 0; k < n_chunks; k++) {
-      const int64_t start = k * chunk;
-      const int64_t m = std::min<int64_t>(chunk, n - start);
+    int64_t start = 0;
+    for (int64_t k = 0; k < n_chunks; start += sizes[k], k++) {
+      const int64_t m = sizes[k];
       for (int f = 0; f < 8; f++)
         EARB_CUDA(cudaMemcpyAsync(d + (size_t)f * n + start, src[f] + start, sizeof(double) * m,
                                   cudaMemcpyHostToDevice, o.s_in));
