@@ -98,66 +98,55 @@ namespace earb {
     return true;
   }
 
-  // Pan one position. `out` receives T.n_real gains (S for a full layout, 2 for 0+2+0).
-  // `aug` is caller-provided scratch of EARB_MAX_AUG doubles.
-  __device__ inline PspHit psp_handle(const PspTables &T, double x, double y, double z,
-                                      double *out, double *aug) {
-    PspHit hit;
-    hit.region = -1;
-    hit.inner = -1;
-    const int A = T.n_aug;
-    for (int a = 0; a < A; a++) aug[a] = 0.0;
-
-    for (int r = 0; r < T.n_regions && hit.region < 0; r++) {
-      const int kind = T.regions[r].kind;
-      const int idx = T.regions[r].index;
-      if (kind == EARB_REGION_TRIPLET) {
-        double pv[3];
-        const PspTriplet &t = T.tri[idx];
-        if (psp_triplet(t, x, y, z, pv)) {
-          aug[t.ch[0]] = pv[0];
-          aug[t.ch[1]] = pv[1];
-          aug[t.ch[2]] = pv[2];
-          hit.region = r;
-        }
-      } else if (kind == EARB_REGION_QUAD) {
-        double pvs[4];
-        const PspQuad &q = T.quad[idx];
-        if (psp_quad(q, x, y, z, pvs)) {
-#pragma unroll
-          for (int i = 0; i < 4; i++) aug[q.ch[i]] = pvs[i];
-          hit.region = r;
-        }
-      } else {
-        const PspNgon &g = T.ngon[idx];
-        for (int k = 0; k < g.n; k++) {
-          double pv[3];
-          const PspTriplet &t = T.tri[g.first_tri + k];
-          if (psp_triplet(t, x, y, z, pv)) {
-            // spread the virtual centre speaker's gain over all n real vertices and
-            // renormalise; the two edge vertices keep their own gain as well
-            const double centre = g.centre_downmix * pv[2];
-            double sumsq = 0.0;
-            for (int i = 0; i < g.n; i++) {
-              double v = 0.0;
-              if (i == t.ch[0]) v = pv[0];
-              if (i == t.ch[1]) v = pv[1];
-              v = v + centre;
-              aug[g.ch[i]] = v;
-              sumsq += v * v;
-            }
-            const double norm = sqrt(sumsq);
-            for (int i = 0; i < g.n; i++) aug[g.ch[i]] /= norm;
-            hit.region = r;
-            hit.inner = k;
-            break;
-          }
-        }
-      }
+  // One candidate of the first-match scan: region r (for a virtual n-gon: its inner triplet k).
+  // On acceptance the gains of the region's vertices are written to aug[] (which the caller has
+  // zeroed) and true is returned.
+  __device__ inline bool psp_try_candidate(const PspTables &T, int r, int k, double x, double y, double z,
+                                           double *aug) {
+    const int kind = T.regions[r].kind;
+    const int idx = T.regions[r].index;
+    if (kind == EARB_REGION_TRIPLET) {
+      double pv[3];
+      const PspTriplet &t = T.tri[idx];
+      if (!psp_triplet(t, x, y, z, pv)) return false;
+      aug[t.ch[0]] = pv[0];
+      aug[t.ch[1]] = pv[1];
+      aug[t.ch[2]] = pv[2];
+      return true;
     }
+    if (kind == EARB_REGION_QUAD) {
+      double pvs[4];
+      const PspQuad &q = T.quad[idx];
+      if (!psp_quad(q, x, y, z, pvs)) return false;
+#pragma unroll
+      for (int i = 0; i < 4; i++) aug[q.ch[i]] = pvs[i];
+      return true;
+    }
+    const PspNgon &g = T.ngon[idx];
+    double pv[3];
+    const PspTriplet &t = T.tri[g.first_tri + k];
+    if (!psp_triplet(t, x, y, z, pv)) return false;
+    // spread the virtual centre speaker's gain over all n real vertices and
+    // renormalise; the two edge vertices keep their own gain as well
+    const double centre = g.centre_downmix * pv[2];
+    double sumsq = 0.0;
+    for (int i = 0; i < g.n; i++) {
+      double v = 0.0;
+      if (i == t.ch[0]) v = pv[0];
+      if (i == t.ch[1]) v = pv[1];
+      v = v + centre;
+      aug[g.ch[i]] = v;
+      sumsq += v * v;
+    }
+    const double norm = sqrt(sumsq);
+    for (int i = 0; i < g.n; i++) aug[g.ch[i]] /= norm;
+    return true;
+  }
 
-    // 0/1 downmix of the extra loudspeakers into their mid-layer parents, then
-    // power normalisation
+  // 0/1 downmix of the extra loudspeakers into their mid-layer parents, power normalisation, and
+  // the stereo downmix of 0+2+0: aug[] -> out[T.n_real]
+  __device__ inline void psp_finish(const PspTables &T, const double *aug, double *out) {
+    const int A = T.n_aug;
     const int S5 = T.stereo ? 5 : T.n_real;
     double full[EARB_MAX_SPK];
     for (int s = 0; s < S5; s++) full[s] = 0.0;
@@ -183,6 +172,85 @@ namespace earb {
       double scale = pow(0.5, 0.5 * back / (front + back));
       out[0] = l * scale;
       out[1] = r * scale;
+    }
+  }
+
+  // Pan one position. `out` receives T.n_real gains (S for a full layout, 2 for 0+2+0).
+  // `aug` is caller-provided scratch of EARB_MAX_AUG doubles.
+  __device__ inline PspHit psp_handle(const PspTables &T, double x, double y, double z,
+                                      double *out, double *aug) {
+    PspHit hit;
+    hit.region = -1;
+    hit.inner = -1;
+    const int A = T.n_aug;
+    for (int a = 0; a < A; a++) aug[a] = 0.0;
+    for (int r = 0; r < T.n_regions && hit.region < 0; r++) {
+      if (T.regions[r].kind == EARB_REGION_NGON) {
+        const int n = T.ngon[T.regions[r].index].n;
+        for (int k = 0; k < n; k++)
+          if (psp_try_candidate(T, r, k, x, y, z, aug)) {
+            hit.region = r;
+            hit.inner = k;
+            break;
+          }
+      } else if (psp_try_candidate(T, r, -1, x, y, z, aug)) {
+        hit.region = r;
+      }
+    }
+    psp_finish(T, aug, out);
+    return hit;
+  }
+
+  // The same scan by a whole warp for ONE position: lane c tests candidate c of the scan order (the
+  // inner triplets of a virtual n-gon count one candidate each), the first accepting candidate --
+  // lowest index, as in the serial scan -- wins and its lane finishes.  Every candidate test is the
+  // serial code on the same inputs, so region, inner index and gains are bit-identical to
+  // psp_handle; what changes is the latency: two rounds of tests instead of up to 44 in a row.
+  // All 32 lanes must call it; `out` is written by one lane only.
+  __device__ inline PspHit psp_handle_warp(const PspTables &T, double x, double y, double z, double *out,
+                                           double *aug) {
+    const int lane = (int)(threadIdx.x & 31u);
+    PspHit hit;
+    hit.region = -1;
+    hit.inner = -1;
+    const int A = T.n_aug;
+    int n_cand = 0;
+    for (int r = 0; r < T.n_regions; r++)
+      n_cand += T.regions[r].kind == EARB_REGION_NGON ? T.ngon[T.regions[r].index].n : 1;
+    for (int c0 = 0; c0 < n_cand; c0 += 32) {
+      const int c = c0 + lane;
+      // candidate c -> (region, inner)
+      int r = 0, k = -1, acc = 0;
+      bool valid = false;
+      for (int rr = 0; rr < T.n_regions; rr++) {
+        const int cnt = T.regions[rr].kind == EARB_REGION_NGON ? T.ngon[T.regions[rr].index].n : 1;
+        if (c < acc + cnt) {
+          r = rr;
+          k = T.regions[rr].kind == EARB_REGION_NGON ? c - acc : -1;
+          valid = true;
+          break;
+        }
+        acc += cnt;
+      }
+      bool ok = false;
+      if (valid) {
+        for (int a = 0; a < A; a++) aug[a] = 0.0;
+        ok = psp_try_candidate(T, r, k, x, y, z, aug);
+      }
+      const unsigned won = __ballot_sync(0xffffffffu, ok);
+      if (won) {
+        const int first = __ffs((int)won) - 1;
+        if (lane == first) psp_finish(T, aug, out);
+        hit.region = __shfl_sync(0xffffffffu, r, first);
+        hit.inner = __shfl_sync(0xffffffffu, k, first);
+        return hit;
+      }
+    }
+    // no region accepted the position (never happens on the built-in layouts): the serial scan's
+    // result for that case is the normalisation of an all-zero vector
+    if (lane == 0) {
+      for (int a = 0; a < A; a++) aug[a] = 0.0;
+      psp_finish(T, aug, out);
     }
     return hit;
   }
