@@ -358,6 +358,13 @@ int earb200_delay_process_device(earb200_delay *d, int64_t nsamples, const float
 int earb200_delay_process_add_device(earb200_delay *d, int64_t nsamples, const float *d_in,
                                      int64_t in_stride, const float *d_add, int64_t add_stride,
                                      float *d_out, int64_t out_stride, void *stream);
+/* extension: out = BlockConvolver(in) + DelayBuffer(direct) in one pass (the decorrelated diffuse bus
+ * plus the compensation-delayed direct bus of the Objects signal flow, docs/dsp.rst:40-71); both
+ * handles advance as if their process() had been called.  d_out must alias neither input. */
+int earb200_convolver_process_add_delayed_device(earb200_convolver *conv, earb200_delay *d,
+                                                 int64_t n_blocks, const float *d_in, int64_t in_stride,
+                                                 const float *d_direct, int64_t direct_stride,
+                                                 float *d_out, int64_t out_stride, void *stream);
 int64_t earb200_delay_launch_count(const earb200_delay *d);
 
 /* ------------------------------------------------ Objects signal flow (8f.1)

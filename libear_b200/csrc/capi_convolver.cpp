@@ -71,14 +71,17 @@ struct earb200_convolver {
   KernelTimer timer;
 };
 
-namespace {
-  void conv_process_device(earb200_convolver &h, int64_t K, const float *d_in, int64_t in_stride,
-                           float *d_out, int64_t out_stride, cudaStream_t stream) {
+// `add`: {direct bus, its row pitch, delay, delay memory} to be joined in the store (fast path
+// only).  Returns true when it was (the caller otherwise adds the delayed bus itself).
+bool earb_conv_process_device(earb200_convolver &h, int64_t K, const float *d_in, int64_t in_stride,
+                              float *d_out, int64_t out_stride, cudaStream_t stream, const float *add,
+                              int64_t add_stride, int64_t add_delay, const float *add_mem) {
     if (K < 0) throw Error(INVALID_ARGUMENT, "negative block count");
-    if (K == 0) return;
+    if (K == 0) return false;
     if (!d_out) throw Error(INVALID_ARGUMENT, "null output buffer");
     use_device(h.device);
     const int nb = h.nb, C = h.C;
+    bool fused = false;
     if (h.filt_dirty) {
       h.d_filt.reserve(std::max<size_t>(h.filt_host.size(), 2));
       if (!h.filt_host.empty())
@@ -167,6 +170,10 @@ namespace {
     L.tw2 = h.d_tw2.ptr;
     h.timer.start(stream);
     if (h.use_fast && Kg == 0 && d_in) {
+      if (add) {
+        L.add = add, L.add_stride = (long)add_stride, L.add_delay = (long)add_delay, L.add_mem = add_mem;
+        fused = true;
+      }
       launch_convolver_fast(L, h.d_uniform.ptr, h.d_tw_fast.ptr, h.n_sms, stream);
       launch_conv_history(L, stream);
     } else {
@@ -176,8 +183,17 @@ namespace {
     EARB_CUDA(cudaGetLastError());
     h.cur = 1 - h.cur;
     h.launches += 2;
+    return fused;
+}
+
+namespace {
+  void conv_process_device(earb200_convolver &h, int64_t K, const float *d_in, int64_t in_stride,
+                           float *d_out, int64_t out_stride, cudaStream_t stream) {
+    earb_conv_process_device(h, K, d_in, in_stride, d_out, out_stride, stream, nullptr, 0, 0, nullptr);
   }
 }  // namespace
+
+int64_t earb200_convolver_block_size_internal(const earb200_convolver *conv) { return conv->B; }
 
 extern "C" {
 

@@ -52,7 +52,45 @@ namespace {
   }
 }  // namespace
 
+struct earb200_convolver;
+bool earb_conv_process_device(earb200_convolver &h, int64_t K, const float *d_in, int64_t in_stride,
+                              float *d_out, int64_t out_stride, cudaStream_t stream, const float *add,
+                              int64_t add_stride, int64_t add_delay, const float *add_mem);
+int64_t earb200_convolver_block_size_internal(const earb200_convolver *conv);
+
 extern "C" {
+
+// out = BlockConvolver(in) + DelayBuffer(direct): the last two stages of the Objects signal flow
+// (ref docs/dsp.rst:40-71) in one pass -- on the convolver's fast path the delayed direct bus joins
+// the decorrelated bus in the convolver's store and the delay line's memory is advanced by a tiny
+// kernel; on the generic path the two stages run one after the other.
+int earb200_convolver_process_add_delayed_device(earb200_convolver *conv, earb200_delay *d, int64_t n_blocks,
+                                                 const float *d_in, int64_t in_stride,
+                                                 const float *d_direct, int64_t direct_stride, float *d_out,
+                                                 int64_t out_stride, void *stream) {
+  return guarded([&] {
+    if (!conv || !d || !d_direct) throw Error(INVALID_ARGUMENT, "null argument");
+    if (n_blocks < 0) throw Error(INVALID_ARGUMENT, "negative block count");
+    if (n_blocks == 0) return;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int64_t n = n_blocks * earb200_convolver_block_size_internal(conv);
+    use_device(d->device);
+    const bool fused = d->delay > 0 && earb_conv_process_device(*conv, n_blocks, d_in, in_stride, d_out, out_stride, st,
+                                                                d_direct, direct_stride, d->delay,
+                                                                d->d_mem[d->cur].ptr);
+    if (fused) {
+      launch_delay_advance(d->C, n, d->delay, d_direct, direct_stride, d->d_mem[d->cur].ptr, d->d_mem[d->cur ^ 1].ptr,
+                           st);
+      EARB_CUDA(cudaGetLastError());
+      d->cur ^= 1;
+      d->launches++;
+    } else {
+      if (d->delay == 0)
+        earb_conv_process_device(*conv, n_blocks, d_in, in_stride, d_out, out_stride, st, nullptr, 0, 0, nullptr);
+      delay_process_device(*d, n, d_direct, direct_stride, d_out, out_stride, st, d_out, out_stride);
+    }
+  });
+}
 
 int earb200_delay_create(int n_channels, int64_t delay, int device, earb200_delay **out) {
   return guarded([&] {

@@ -7,7 +7,7 @@
 //       + BlockConvolver(diffuse bus, designDecorrelators(layout))      per loudspeaker channel
 //
 // Everything between the object audio and the loudspeaker feeds stays in HBM: two render
-// launches, one convolver launch and one fused delay + add launch per call.
+// launches and one convolver launch whose store adds the delayed direct bus.
 #include <memory>
 #include <vector>
 
@@ -22,7 +22,7 @@ struct earb200_objects_renderer {
   earb200_interp *direct = nullptr, *diffuse = nullptr;
   earb200_convolver *conv = nullptr;
   earb200_delay *delay = nullptr;
-  DeviceBuffer<float> d_direct, d_diffuse, d_dec, d_in, d_out;
+  DeviceBuffer<float> d_direct, d_diffuse, d_in, d_out;
   ~earb200_objects_renderer() {
     if (direct) earb200_interp_destroy(direct);
     if (diffuse) earb200_interp_destroy(diffuse);
@@ -44,11 +44,13 @@ namespace {
     use_device(h.device);
     const int64_t T = n_blocks * h.B;
     const size_t bus = (size_t)h.C * (size_t)T;
-    float *dir = h.d_direct.reserve(bus), *dif = h.d_diffuse.reserve(bus), *dec = h.d_dec.reserve(bus);
+    float *dir = h.d_direct.reserve(bus), *dif = h.d_diffuse.reserve(bus);
     chk(earb200_interp_process_device(h.direct, block_start, T, d_in, in_stride, dir, T, stream));
     chk(earb200_interp_process_device(h.diffuse, block_start, T, d_in, in_stride, dif, T, stream));
-    chk(earb200_convolver_process_device(h.conv, n_blocks, dif, T, dec, T, stream));
-    chk(earb200_delay_process_add_device(h.delay, T, dir, T, dec, T, d_out, out_stride, stream));
+    // decorrelators + compensation delay + sum in one pass: the delayed direct bus joins in the
+    // convolver's store
+    chk(earb200_convolver_process_add_delayed_device(h.conv, h.delay, n_blocks, dif, T, dir, T, d_out, out_stride,
+                                                     stream));
   }
 }  // namespace
 

@@ -224,6 +224,9 @@ namespace earb {
       const float2 *filt;     // [n_filters][B + 1] (num_blocks == 1)
       const int *filter_of;   // [C] filter id per channel (-1: none)
       const float2 *tw;       // [32][32]: tw[k1][b] = exp(-2 pi i b k1 / 1024)
+      const float *add;       // nullable: out += delay(add)  (ConvLaunch::add)
+      long add_stride, add_delay;
+      const float *add_mem;
     };
 
     // forward transform of the pair held in v (v[br5(a)] = z[lane + 32 a] for a < 16, odd slots
@@ -277,6 +280,7 @@ namespace earb {
       dit32<true, false>(v);  // inverse over b: v[n2] = y[lane + 32 n2]
     }
 
+    template <bool ADD>
     __global__ void __launch_bounds__(kWarps * 32, 2) convolver_fast_kernel(FastArgs a) {
       extern __shared__ float4 fsm[];
       float4 *tw_s = fsm;        // [16][32]: (tw[2j][lane], tw[2j + 1][lane])
@@ -343,6 +347,36 @@ namespace earb {
         for (int r = 0; r < 16; r++) v[br5(r)] = mk(xr[r], xi[r]);
         convolve_pair(v, tile, tw_s, twi_s, H_s, lane);
         float *y0 = y + (size_t)(2 * p) * kFastB;
+        if (ADD) {
+          // the delayed direct bus joins here: sample t of [add_mem; add] (the lines of the two
+          // blocks are loaded before the stores so that their latency overlaps)
+          const long t0 = (long)(2 * p) * kFastB + lane;
+          const float *am = a.add_mem + (long)c * a.add_delay, *ad = a.add + (long)c * a.add_stride - a.add_delay;
+          float d0[16], d1[16];
+#pragma unroll
+          for (int r = 0; r < 16; r++) {
+            const long t = t0 + 32 * r;
+            d0[r] = t < a.add_delay ? am[t] : __ldcs(ad + t);
+          }
+#pragma unroll
+          for (int r = 0; r < 16; r++) {
+            const long t = t0 + kFastB + 32 * r;
+            d1[r] = !has_second ? 0.0f : (t < a.add_delay ? am[t] : __ldcs(ad + t));
+          }
+#pragma unroll
+          for (int r = 0; r < 16; r++) __stcs(y0 + lane + 32 * r, (re(v[r]) + tail[r]) + d0[r]);
+          if (has_second) {
+#pragma unroll
+            for (int r = 0; r < 16; r++) {
+              __stcs(y0 + kFastB + lane + 32 * r, (im(v[r]) + re(v[r + 16])) + d1[r]);
+              tail[r] = im(v[r + 16]);
+            }
+          } else {
+#pragma unroll
+            for (int r = 0; r < 16; r++) tail[r] = re(v[r + 16]);
+          }
+          continue;
+        }
 #pragma unroll
         for (int r = 0; r < 16; r++) __stcs(y0 + lane + 32 * r, re(v[r]) + tail[r]);
         if (has_second) {
@@ -397,10 +431,19 @@ namespace earb {
     a.filt = reinterpret_cast<const float2 *>(L.filt);
     a.filter_of = d_filter_of;
     a.tw = reinterpret_cast<const float2 *>(d_tw_fast);
+    a.add = L.add;
+    a.add_stride = L.add_stride;
+    a.add_delay = L.add_delay;
+    a.add_mem = L.add_mem;
     const size_t smem = sizeof(float2) * (3072 + (size_t)kWarps * 32 * kRow);
-    cudaFuncSetAttribute(convolver_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     const long warps = (a.n_pairs + run - 1) / run;
     dim3 grid((unsigned)((warps + kWarps - 1) / kWarps), (unsigned)L.C);
-    convolver_fast_kernel<<<grid, kWarps * 32, smem, stream>>>(a);
+    if (a.add) {
+      cudaFuncSetAttribute(convolver_fast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      convolver_fast_kernel<true><<<grid, kWarps * 32, smem, stream>>>(a);
+    } else {
+      cudaFuncSetAttribute(convolver_fast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      convolver_fast_kernel<false><<<grid, kWarps * 32, smem, stream>>>(a);
+    }
   }
 }  // namespace earb

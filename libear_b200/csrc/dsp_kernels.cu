@@ -78,6 +78,14 @@ namespace earb {
       }
     }
 
+    __global__ void delay_advance_kernel(long n, long delay, const float *__restrict__ in, long in_stride,
+                                         const float *__restrict__ mem, float *__restrict__ mem_new) {
+      const int c = blockIdx.y;
+      for (long j = (long)blockIdx.x * blockDim.x + threadIdx.x; j < delay; j += (long)gridDim.x * blockDim.x)
+        mem_new[(long)c * delay + j] =
+            delay_fetch(mem + (long)c * delay, in ? in + (long)c * in_stride : nullptr, n + j, delay);
+    }
+
     int grid_x(long work_items, int rows, int n_sms) {
       long blocks = (work_items + (long)kThreads * kPerThread - 1) / ((long)kThreads * kPerThread);
       // a few waves of the machine spread over the channel rows
@@ -94,6 +102,13 @@ namespace earb {
     dim3 grid(grid_x(n + delay, C, n_sms), C);
     delay_kernel<<<grid, kThreads, 0, stream>>>(C, n, delay, in, in_stride, out, out_stride, mem, mem_new, add,
                                                 add_stride);
+  }
+
+  void launch_delay_advance(int C, long n, long delay, const float *in, long in_stride, const float *mem,
+                            float *mem_new, cudaStream_t stream) {
+    if (C <= 0 || delay <= 0) return;
+    dim3 grid((unsigned)((delay + 255) / 256), C);
+    delay_advance_kernel<<<grid, 256, 0, stream>>>(n, delay, in, in_stride, mem, mem_new);
   }
 
   void launch_add(int C, long n, const float *a, long a_stride, const float *b, long b_stride, float *out,

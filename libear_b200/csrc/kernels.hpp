@@ -176,6 +176,11 @@ namespace earb {
   // waits until flags[r] >= epoch for every rank (the gather of an epoch has landed everywhere)
   void launch_bus_wait(const uint32_t *flags, int n_ranks, uint32_t epoch, cudaStream_t stream);
 
+  // mem_new[c][j] = sample n + j of [mem; in]: the delay line's memory after n samples, without
+  // producing output (the delayed signal was consumed elsewhere: the convolver's fused store)
+  void launch_delay_advance(int C, long n, long delay, const float *in, long in_stride, const float *mem,
+                            float *mem_new, cudaStream_t stream);
+
   // ---- K4: partitioned FFT convolver bank (convolver_kernels.cu)
 #define CONV_THREADS 128
   struct ConvLaunch {
@@ -194,6 +199,12 @@ namespace earb {
     const int *uniform;     // [C]
     const unsigned char *faded;  // [C][nb + Kg]
     const float *tw2;       // [2B] complex: exp(-2 pi i k / 2B)
+    // fast path only: out = conv(in) + delay(add): the delayed direct bus of the Objects signal flow
+    // joins the decorrelated diffuse bus in the convolver's store (ref docs/dsp.rst:40-71);
+    // add [C][K * B] with row pitch add_stride, add_mem [C][add_delay] the delay line's memory
+    const float *add = nullptr;
+    long add_stride = 0, add_delay = 0;
+    const float *add_mem = nullptr;
   };
   size_t conv_smem_bytes(int B, int nb);
   void launch_convolver(const ConvLaunch &L, cudaStream_t stream);
