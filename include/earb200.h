@@ -166,6 +166,25 @@ int earb200_objects_calculate_device(earb200_objects *calc, int64_t n,
                                      const earb200_objects_soa *d_in, int out_is_double,
                                      void *d_direct, void *d_diffuse,
                                      int32_t *d_region_idx, void *stream);
+/* OPT-IN extensions beyond libear (PARITY UNPINNED).  libear 0.9 rejects objectDivergence and
+ * channelLock with ear::not_implemented (gain_calculator_objects.cpp:37-43; its tests require the
+ * throws) and so does this library -- unless the caller switches them on here.  The arithmetic
+ * then restates Rec. ITU-R BS.2127 as the EBU ADM Renderer implements it (csrc/objects_ext_kernels.cu);
+ * there is no libear output to compare it with.  zoneExclusion, screenRef / screen edge lock and
+ * Cartesian panning stay not_implemented. */
+enum { EARB200_EXT_DIVERGENCE = 1, EARB200_EXT_CHANNEL_LOCK = 2 };
+int earb200_objects_enable_extensions(earb200_objects *calc, uint32_t mask);
+typedef struct earb200_objects_ext {
+  const double *divergence;                /* objectDivergence.divergence in [0, 1]; NULL: none */
+  const double *divergence_azimuth_range;  /* objectDivergence.azimuthRange; NULL: 45 degrees   */
+  const double *channel_lock_max_distance; /* channelLock.maxDistance; < 0: flag off, +inf: no
+                                              limit; NULL: no object is locked                  */
+} earb200_objects_ext;
+/* device arrays, asynchronous on `stream`; a feature that is present but not enabled fails with
+ * EARB200_NOT_IMPLEMENTED and libear's message */
+int earb200_objects_calculate_ext_device(earb200_objects *calc, int64_t n, const earb200_objects_soa *d_in,
+                                         const earb200_objects_ext *d_ext, int out_is_double,
+                                         void *d_direct, void *d_diffuse, void *stream);
 /* PolarExtent::handle on Cartesian positions (src/object_based/polar_extent.cpp:281-302):
  * xyz [n][3], width/height/depth [n]; out [n][S] double.  Host buffers. */
 int earb200_objects_extent_host(earb200_objects *calc, int64_t n, const double *xyz,

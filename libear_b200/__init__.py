@@ -214,6 +214,10 @@ class _ObjectsSoA(C.Structure):
                                           "depth", "gain", "diffuse", "flags")]
 
 
+class _ObjectsExt(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in ("divergence", "divergence_azimuth_range", "channel_lock_max_distance")]
+
+
 # feature bits libear refuses with ear::not_implemented (earb200.h)
 OBJ_CARTESIAN, OBJ_CHANNEL_LOCK, OBJ_SCREEN_REF = 1, 2, 4
 OBJ_DIVERGENCE, OBJ_ZONE_EXCLUSION, OBJ_CARTESIAN_POSITION = 8, 16, 32
@@ -279,6 +283,19 @@ class GainCalculatorObjects:
         _chk(_lib.earb200_objects_calculate_device(self.h, C.c_int64(n), C.byref(soa), int(out_is_double),
                                                    _ptr(d_direct), _ptr(d_diffuse), _ptr(d_regions),
                                                    C.c_void_p(int(stream))))
+
+    def enable_extensions(self, divergence=False, channel_lock=False):
+        """OPT-IN features beyond libear (parity unpinned; libear throws not_implemented for both)."""
+        _chk(_lib.earb200_objects_enable_extensions(self.h, C.c_uint32(int(divergence) | 2 * int(channel_lock))))
+
+    def calculate_ext_device(self, n, d_soa, d_direct, d_diffuse, d_divergence=None, d_azimuth_range=None,
+                             d_lock_max_distance=None, out_is_double=False, stream=0):
+        """calculate_device with objectDivergence / channelLock arrays (device addresses or None)."""
+        soa = _ObjectsSoA(*[int(p) for p in d_soa], None)
+        ext = _ObjectsExt(*[None if p is None else int(p) for p in (d_divergence, d_azimuth_range, d_lock_max_distance)])
+        _chk(_lib.earb200_objects_calculate_ext_device(self.h, C.c_int64(n), C.byref(soa), C.byref(ext),
+                                                       int(out_is_double), _ptr(d_direct), _ptr(d_diffuse),
+                                                       C.c_void_p(int(stream))))
 
     def extent(self, xyz, width, height, depth):
         """ear::PolarExtent::handle (src/object_based/polar_extent.cpp:281-302): [n][S] double."""

@@ -115,6 +115,10 @@ struct earb200_objects {
   DeviceBuffer<float> d_out_f;
   DeviceBuffer<int32_t> d_region;
   int64_t launches = 0;
+  // opt-in extensions beyond libear (EARB200_EXT_*): 0 = the reference's behaviour (throws)
+  uint32_t extensions = 0;
+  DeviceBuffer<double> d_spk;                       // [S][5]: unit-distance x y z, azimuth, elevation
+  DeviceBuffer<double> d_ext_in, d_ext_g, d_ext_f;  // scratch of the extension path
   KernelTimer timer;
   int64_t timed_passes = 0;
   // streams / events of the pipelined *_host entry point
@@ -155,6 +159,17 @@ namespace {
     o.S = o.panner.tables.n_real;
     if (o.n_out > EARB_MAX_OUT) throw Error(INVALID_ARGUMENT, "too many output channels");
 
+    {  // loudspeaker positions (real, unit distance) for the opt-in channel lock
+      std::vector<double> spk;
+      for (const auto &ch : layout.channels) {
+        if (ch.lfe) continue;
+        const Vec3 p = cart(ch.pos.az, ch.pos.el, 1.0);
+        spk.insert(spk.end(), {p.x, p.y, p.z, ch.pos.az, ch.pos.el});
+      }
+      if (!spk.empty())
+        EARB_CUDA(cudaMemcpy(o.d_spk.reserve(spk.size()), spk.data(), sizeof(double) * spk.size(),
+                             cudaMemcpyHostToDevice));
+    }
     // LFE scatter map (ref gain_calculator_objects.cpp:51-52)
     std::vector<int32_t> out_index(EARB_MAX_SPK, 0), identity(EARB_MAX_SPK, 0);
     int s = 0;
@@ -367,6 +382,34 @@ namespace {
       o.fb_pending = true;
     }
     objects_join(o, stream);
+    EARB_CUDA(cudaGetLastError());
+  }
+
+  // OPT-IN divergence / channel lock (objects_ext_kernels.cu; parity unpinned: libear throws).
+  // Every object becomes three sources that go through the unchanged pipeline with unit gain; the
+  // results are combined in the power domain.  Chunks of 65,536 objects bound the scratch.
+  template <typename OutT>
+  void objects_run_ext(earb200_objects &o, int64_t n, const ObjectsSoA &in, const double *d_div,
+                       const double *d_range, const double *d_lock, OutT *d_direct, OutT *d_diffuse,
+                       cudaStream_t stream) {
+    const int64_t chunk = 65536;
+    double *sc = o.d_ext_in.reserve((size_t)chunk * (9 + 3 * 5 + 3));
+    double *xyz3 = sc, *w3 = xyz3 + 9 * chunk, *h3 = w3 + 3 * chunk, *d3 = h3 + 3 * chunk, *ones = d3 + 3 * chunk,
+           *zeros = ones + 3 * chunk, *weights = zeros + 3 * chunk;
+    double *g3 = o.d_ext_g.reserve((size_t)3 * chunk * o.n_out), *f3 = o.d_ext_f.reserve((size_t)3 * chunk * o.n_out);
+    for (int64_t start = 0; start < n; start += chunk) {
+      const int64_t m = std::min(chunk, n - start);
+      ObjectsSoA c{in.azimuth + start, in.elevation + start, in.distance + start, in.width + start,
+                   in.height + start, in.depth + start,     in.gain + start,     in.diffuse + start, nullptr};
+      launch_objects_ext_expand(m, c, d_div ? d_div + start : nullptr, d_range ? d_range + start : nullptr,
+                                d_lock ? d_lock + start : nullptr, o.S, o.d_spk.ptr, xyz3, w3, h3, d3, ones, zeros,
+                                weights, stream);
+      ObjectsSoA three{nullptr, nullptr, nullptr, w3, h3, d3, ones, zeros, xyz3};
+      objects_run<double>(o, 3 * m, three, o.n_out, o.d_out_index.ptr, g3, f3, nullptr, stream);
+      launch_objects_ext_combine<OutT>(m, o.n_out, g3, weights, c.gain, c.diffuse, d_direct + start * o.n_out,
+                                       d_diffuse + start * o.n_out, stream);
+      o.launches += 2;
+    }
     EARB_CUDA(cudaGetLastError());
   }
 
@@ -728,6 +771,47 @@ int earb200_objects_calculate_device(earb200_objects *calc, int64_t n,
     else
       objects_run<float>(*calc, n, soa, calc->n_out, calc->d_out_index.ptr, (float *)d_direct,
                          (float *)d_diffuse, d_region_idx, (cudaStream_t)stream);
+  });
+}
+
+int earb200_objects_enable_extensions(earb200_objects *calc, uint32_t mask) {
+  return guarded([&] {
+    if (!calc) throw Error(INVALID_ARGUMENT, "null argument");
+    if (mask & ~(uint32_t)(EARB200_EXT_DIVERGENCE | EARB200_EXT_CHANNEL_LOCK))
+      throw Error(NOT_IMPLEMENTED, "not implemented: only divergence and channelLock exist as extensions");
+    calc->extensions = mask;
+  });
+}
+
+// device arrays; ext fields may be null (feature absent from the whole batch)
+int earb200_objects_calculate_ext_device(earb200_objects *calc, int64_t n, const earb200_objects_soa *d_in,
+                                         const earb200_objects_ext *d_ext, int out_is_double, void *d_direct,
+                                         void *d_diffuse, void *stream) {
+  return guarded([&] {
+    if (!calc || !d_in || !d_ext) throw Error(INVALID_ARGUMENT, "null argument");
+    if (n < 0) throw Error(INVALID_ARGUMENT, "negative batch size");
+    if (n == 0) return;
+    if (!d_direct || !d_diffuse) throw Error(INVALID_ARGUMENT, "null output buffer");
+    if (!d_in->azimuth || !d_in->elevation || !d_in->distance || !d_in->width || !d_in->height || !d_in->depth ||
+        !d_in->gain || !d_in->diffuse)
+      throw Error(INVALID_ARGUMENT, "null metadata field (all eight arrays are required)");
+    // without the opt-in the behaviour is libear's (ref gain_calculator_objects.cpp:37-43)
+    if (d_ext->channel_lock_max_distance && !(calc->extensions & EARB200_EXT_CHANNEL_LOCK))
+      throw Error(NOT_IMPLEMENTED, "not implemented: channelLock");
+    if (d_ext->divergence && !(calc->extensions & EARB200_EXT_DIVERGENCE))
+      throw Error(NOT_IMPLEMENTED, "not implemented: divergence");
+    check_flags(n, d_in->flags);
+    use_device(calc->device);
+    ObjectsSoA soa{d_in->azimuth, d_in->elevation, d_in->distance, d_in->width, d_in->height,
+                   d_in->depth,   d_in->gain,      d_in->diffuse,  nullptr};
+    if (out_is_double)
+      objects_run_ext<double>(*calc, n, soa, d_ext->divergence, d_ext->divergence_azimuth_range,
+                              d_ext->channel_lock_max_distance, (double *)d_direct, (double *)d_diffuse,
+                              (cudaStream_t)stream);
+    else
+      objects_run_ext<float>(*calc, n, soa, d_ext->divergence, d_ext->divergence_azimuth_range,
+                             d_ext->channel_lock_max_distance, (float *)d_direct, (float *)d_diffuse,
+                             (cudaStream_t)stream);
   });
 }
 

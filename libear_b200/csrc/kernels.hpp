@@ -32,6 +32,15 @@ namespace earb {
     const double *xyz;
   };
 
+  // ---- opt-in extensions: divergence and channel lock (objects_ext_kernels.cu)
+  void launch_objects_ext_expand(long n, const ObjectsSoA &in, const double *divergence, const double *az_range,
+                                 const double *lock_max_distance, int n_spk, const double *d_spk, double *xyz3,
+                                 double *w3, double *h3, double *d3, double *ones, double *zeros, double *weights,
+                                 cudaStream_t stream);
+  template <typename OutT>
+  void launch_objects_ext_combine(long n, int n_out, const double *g3, const double *weights, const double *gain,
+                                  const double *diffuse, OutT *out_direct, OutT *out_diffuse, cudaStream_t stream);
+
   // ---- K1 / K2: gain calculation (objects_kernels.cu)
   void launch_psp_batch(const PspTables *d_tables, long n, const double *d_xyz,
                         double *d_gains, int32_t *d_region, int32_t *d_inner,
