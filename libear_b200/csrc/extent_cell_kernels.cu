@@ -58,6 +58,10 @@
 
 #include "kernels.hpp"
 
+#ifndef EARB_CELL_MMA_WARPS
+#define EARB_CELL_MMA_WARPS 2
+#endif
+
 namespace earb {
   namespace {
     constexpr int kCell = EXTENT_CELL_POINTS;  // 16 points per cell = K of one kind::f16 UMMA
@@ -72,7 +76,8 @@ namespace earb {
     // One issuer (a single thread).  Four issuer warps, one per M-tile, were measured slower
     // (0.441 against 0.406 ms per launch): the per-cell waits, fences and commits are paid four
     // times and the polling warps take issue slots from the evaluators.
-    constexpr int kMmaWarp = kEvalWarps, kMmaWarps = 1, kProdWarp = kMmaWarp + kMmaWarps;
+    constexpr int kMmaWarp = kEvalWarps, kMmaWarps = EARB_CELL_MMA_WARPS, kProdWarp = kMmaWarp + kMmaWarps;
+    constexpr int kMtPerIssuer = kMT / kMmaWarps;
     constexpr int kThreads = (kProdWarp + 1) * 32;  // 576
     constexpr int kBCells = 4;                       // cells per stream stage
     constexpr int kBStages = 4;
@@ -114,20 +119,24 @@ namespace earb {
           "l"(src), "r"(bytes), "r"(smem_u32(bar))
           : "memory");
     }
-    // waits for the phase with the given parity (the waiter follows every phase of the barrier); a
-    // protocol error traps after ~2 s instead of hanging the GPU
+    // waits for the phase with the given parity (the waiter follows every phase of the barrier, or
+    // the barrier completes once per tile and the parity is the tile's).  try_wait carries a
+    // suspend-time hint: the warp sleeps in hardware until the phase completes (or the hint runs
+    // out) instead of spinning -- a spinning evaluator warp took 41 loop iterations per batch, a
+    // fifth of all instructions the SM issued, from the warps it was waiting for.  A protocol error
+    // traps after ~2 s instead of hanging the GPU.
     __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
       uint32_t done;
       uint32_t spins = 0;
       do {
         asm volatile(
             "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
             "selp.u32 %0, 1, 0, p;\n\t}"
             : "=r"(done)
-            : "r"(smem_u32(bar)), "r"(parity)
+            : "r"(smem_u32(bar)), "r"(parity), "r"(20000u)
             : "memory");
-        if (!done && ++spins > 20000000u) __trap();
+        if (!done && ++spins > 200000u) __trap();
       } while (!done);
     }
     __device__ __forceinline__ void fence_proxy_async() {
@@ -410,8 +419,9 @@ namespace earb {
                        &b_full[bs]);
             }
         }
-      } else if (warp == kMmaWarp) {
-        // ------------------------------------------------------------ MMA issuer
+      } else if (warp >= kMmaWarp && warp < kMmaWarp + kMmaWarps) {
+        // ------------------------------------------------------------ MMA issuers (kMtPerIssuer M-tiles each)
+        const int mt_lo = (warp - kMmaWarp) * kMtPerIssuer;
         // The whole warp walks the loop (warp-uniform control flow, so that descriptors and masks
         // stay in uniform registers; a single divergent thread makes the compiler wrap every UMMA
         // in a uniformisation loop); an elected lane issues.
@@ -435,7 +445,8 @@ namespace earb {
             for (int ks = 0; ks < NC / 16; ks++) {
               const uint64_t d1 = kmajor_desc(s1_addr + ks * kSum1Bytes), d2 = kmajor_desc(s2_addr + ks * kSum2Bytes);
 #pragma unroll
-              for (int mt = 0; mt < kMT; mt++) {
+              for (int mi = 0; mi < kMtPerIssuer; mi++) {
+                const int mt = mt_lo + mi;
                 const uint32_t acc = tm + mt * kAccCols;
                 const uint32_t a_ind = tm + kColInd + mt * (NC / 2) + ks * 8;
                 umma_f16_ts(acc, a_ind, d1, idesc48, ks != 0);
@@ -448,11 +459,11 @@ namespace earb {
             const int s = k % kD, bsg = g / kBCells, bs = bsg % kBStages, sub = g % kBCells;
             // the masks of the cell: rows that are not mixed keep their accumulators (rows
             // without a pass are never mixed)
-            uint4 off[kMT];
+            uint4 off[kMtPerIssuer];
 #pragma unroll
-            for (int mt = 0; mt < kMT; mt++) {
-              off[mt] = *reinterpret_cast<const uint4 *>(sm.mixed + k * kEvalWarps + 4 * mt);
-              off[mt].x = ~off[mt].x, off[mt].y = ~off[mt].y, off[mt].z = ~off[mt].z, off[mt].w = ~off[mt].w;
+            for (int mi = 0; mi < kMtPerIssuer; mi++) {
+              off[mi] = *reinterpret_cast<const uint4 *>(sm.mixed + k * kEvalWarps + 4 * (mt_lo + mi));
+              off[mi].x = ~off[mi].x, off[mi].y = ~off[mi].y, off[mi].z = ~off[mi].z, off[mi].w = ~off[mi].w;
             }
             if (sub == 0) mbar_wait(&b_full[bs], (uint32_t)((bsg / kBStages) & 1));
             mbar_wait(&sm.a_full[k], par);
@@ -461,12 +472,13 @@ namespace earb {
               if (!(dbg & 1)) {
                 const uint64_t bd = kmajor_desc(sB_addr + bs * kBStageBytes + sub * kCellBBytes);
 #pragma unroll
-                for (int mt = 0; mt < kMT; mt++) {
-                  if ((off[mt].x & off[mt].y & off[mt].z & off[mt].w) == 0xffffffffu) continue;
+                for (int mi = 0; mi < kMtPerIssuer; mi++) {
+                  if ((off[mi].x & off[mi].y & off[mi].z & off[mi].w) == 0xffffffffu) continue;
+                  const int mt = mt_lo + mi;
                   const uint32_t acc = tm + mt * kAccCols;
                   const uint32_t a_hi = sA_addr + s * kAStageBytes + mt * 2 * kAPlaneBytes;
-                  umma_f16_ss_masked(acc, kmajor_desc(a_hi), bd, idesc48, off[mt]);
-                  umma_f16_ss_masked(acc + 24, kmajor_desc(a_hi + kAPlaneBytes), bd, idesc32, off[mt]);
+                  umma_f16_ss_masked(acc, kmajor_desc(a_hi), bd, idesc48, off[mi]);
+                  umma_f16_ss_masked(acc + 24, kmajor_desc(a_hi + kAPlaneBytes), bd, idesc32, off[mi]);
                 }
               }
               umma_commit(&sm.a_free[k]);

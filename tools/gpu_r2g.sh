@@ -18,3 +18,9 @@ CMD="python bench.py --steps 1 --warmup 3 --objects 262144 --no-render --no-conv
 timeout 600 ncu --set full --clock-control none --import-source on -k regex:extent_cell -s 2 -c 1 -f -o gpurun_out/prof_cell_$tag $CMD > gpurun_out/ncu_cell_$tag.log 2>&1
 echo "ncu cell rc=$?"
 ls -la gpurun_out
+RCMD="python bench.py --steps 2 --warmup 3 --no-convolver --no-mix --no-flow --no-points --no-cpu-baseline --no-e2e --no-render-e2e --no-parity --sustained 0 --objects 8192"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:render_tc_persistent -s 3 -c 1 -f -o gpurun_out/prof_render_$tag $RCMD > gpurun_out/ncu_render_$tag.log 2>&1
+echo "ncu render rc=$?"
+CCMD="python bench.py --steps 1 --warmup 3 --no-render --no-mix --no-flow --no-points --no-cpu-baseline --no-e2e --no-render-e2e --no-parity --sustained 0 --objects 8192"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:convolver_fast -s 3 -c 1 -f -o gpurun_out/prof_conv_$tag $CCMD > gpurun_out/ncu_conv_$tag.log 2>&1
+echo "ncu conv rc=$?"
