@@ -215,6 +215,15 @@ int earb200_direct_speakers_create(const earb200_layout *layout, int device, int
     // ref :79-82 (std::map::insert keeps the built-in entries on a key clash)
     h->substitutions = {{"LFE", "LFE1"}, {"LFEL", "LFE1"}, {"LFER", "LFE2"}};
     for (int i = 0; i < n_substitutions; i++) h->substitutions.insert({from[i], to[i]});
+    // libear builds the point-source panner in the constructor (configurePolarPanner(layout
+    // .withoutLfe()), ref gain_calculator_direct_speakers.cpp:84): layouts it rejects (a screen
+    // loudspeaker outside its range, an ill-formed 0+2+0, a degenerate hull) fail HERE, with the
+    // same error class.  The region tables are built on the host for that; only their copy to the
+    // device waits for the first channel that needs panning.
+    {
+      PspTables probe;
+      buildPspTables(h->layout.withoutLfe(), probe);
+    }
     *out = h.release();
   });
 }

@@ -90,3 +90,15 @@ def test_batch_is_one_launch(eb):
     single = np.stack([gc.calculate(**c)[0] for c in chans])
     assert np.abs(g - single).max() == 0.0
     assert np.allclose((g[:64] ** 2).sum(1), 1.0, atol=1e-12)
+
+
+def test_invalid_layouts_fail_at_construction_like_libear():
+    """libear builds the point-source panner in the GainCalculatorDirectSpeakers constructor
+    (ref src/direct_speakers/gain_calculator_direct_speakers.cpp:84), so a layout it cannot pan on
+    fails THERE, not at the first channel that happens to need panning.  No device needed: the
+    region tables are validated on the host."""
+    import libear_b200 as eb
+    names = ["M+000", "M+030", "M-030", "M+110", "M-110"]
+    pos = [[0, 0, 1], [0, 0, 1], [-30, 0, 1], [110, 0, 1], [-110, 0, 1]]   # two loudspeakers at one place
+    with pytest.raises(eb.InternalError):
+        eb.GainCalculatorDirectSpeakers(eb.Layout("broken", channels=dict(names=names, pos=pos)))
