@@ -69,8 +69,8 @@ int earb200_bus_create(int device, int rank, int n_ranks, int n_channels, int64_
     if (!out) throw Error(INVALID_ARGUMENT, "null argument");
     if (n_ranks < 1 || n_ranks > EARB_BUS_MAX_RANKS || rank < 0 || rank >= n_ranks)
       throw Error(INVALID_ARGUMENT, "invalid rank / number of ranks (at most 8: the GPUs of one node)");
-    if (n_channels < 1 || n_channels > EARB_MAX_OUT || n_samples < 1)
-      throw Error(INVALID_ARGUMENT, "invalid bus shape");
+    if (n_channels < 1 || n_channels > EARB_MAX_OUT || n_samples < 1 || n_samples > (int64_t)1 << 30)
+      throw Error(INVALID_ARGUMENT, "invalid bus shape (at most 2^30 samples)");
     use_device(device);
     auto b = std::make_unique<earb200_bus>();
     b->device = device, b->rank = rank, b->n_ranks = n_ranks, b->M = n_channels, b->T = n_samples;
