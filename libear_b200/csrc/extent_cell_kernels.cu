@@ -302,6 +302,7 @@ namespace earb {
       unsigned short *pool;   // [kPoolCap]
       uint64_t *a_full, *a_free;  // [NC] mbarriers, one pair per cell
       float4 *points;             // [n_cells][12] the 16 points of every cell (evaluator layout)
+      unsigned char *bcell;       // [NC * kEvalWarps] cell of every batch of the tile
     };
     __host__ __device__ inline size_t smem_layout(int NC, unsigned char *base, Smem *s) {
       size_t o = 0;
@@ -319,7 +320,9 @@ namespace earb {
       unsigned char *round_end = take((size_t)(NC + 1) * 2), *pool = take((size_t)kPoolCap * 2);
       unsigned char *a_full = take((size_t)NC * 8), *a_free = take((size_t)NC * 8);
       unsigned char *points = take((size_t)NC * 12 * 16);
+      unsigned char *bcell = take((size_t)NC * kEvalWarps);
       if (s) {
+        s->bcell = bcell;
         s->points = reinterpret_cast<float4 *>(points);
         s->a_full = reinterpret_cast<uint64_t *>(a_full), s->a_free = reinterpret_cast<uint64_t *>(a_free);
         s->A = A, s->B = B, s->consts = consts, s->sum1 = sum1, s->sum2 = sum2;
@@ -598,7 +601,10 @@ namespace earb {
               }
               if (k < NC) {
                 sm.off[k] = carry_off + io - n;
-                sm.nbp[k] = (unsigned short)(carry_nb + ib - nb);
+                const uint32_t b0 = carry_nb + ib - nb;
+                sm.nbp[k] = (unsigned short)b0;
+                // batch -> cell, so that a warp finds the cell of its next batch with one load
+                for (uint32_t j = 0; j < nb; j++) sm.bcell[b0 + j] = (unsigned char)k;
               }
               carry_off += __shfl_sync(0xffffffffu, io, 31);
               carry_nb += __shfl_sync(0xffffffffu, ib, 31);
@@ -654,7 +660,7 @@ namespace earb {
             int k = k_lo;
             const int b_end = sm.nbp[k_hi];
             for (int b = (int)sm.nbp[k_lo] + warp; b < b_end; b += kEvalWarps) {
-              while ((int)sm.nbp[k + 1] <= b) k++;
+              k = sm.bcell[b];
               const uint32_t n_mixed = sm.nmixed[k], first = (uint32_t)(b - (int)sm.nbp[k]) * 32u;
               const uint32_t item = first + (uint32_t)lane;
               const bool active = item < n_mixed;
