@@ -610,6 +610,12 @@ def run_ours(args):
             p_ms = max_over_ranks(p0.elapsed_time(p1)) / args.steps
             gpu_launches += gcp.launch_count - pl0
             p_bytes = npts * (64.0 + 2 * 4 * Cp)
+            if check and label == "n1024":
+                # configs[0] is "checked against libear's CPU path": all 1,024 rows
+                ed, ef = oref.Objects("0+5+0").calculate(*cols, dtype=np.float32)
+                perr = float(max(np.abs(dp_d.cpu().numpy() - ed).max(), np.abs(dp_f.cpu().numpy() - ef).max()))
+                parity["point_sources_1024_gains_max_abs"] = perr
+                parity["ok"] = bool(parity["ok"] and perr < 1e-6)
             point_block[label] = {"objects_per_gpu": npts, "value": npts * world / (p_ms * 1e-3), "us_per_call": p_ms * 1e3,
                                   "algorithmic_gbs": p_bytes / (p_ms * 1e-3) / 1e9,
                                   "hbm_frac": p_bytes / (p_ms * 1e-3) / 1e9 / hbm_peak}
