@@ -370,7 +370,19 @@ namespace {
       if (objects > 0) o.passes_per_object = active / objects;
       o.fb_pending = false;
     }
-    const int64_t chunk = pick_chunk(o, o.passes_per_object, 0);
+    int64_t chunk = pick_chunk(o, o.passes_per_object, 0);
+    if (!earb200_objects::kChunkFixed && n > chunk) {
+      // a short last chunk costs a whole set of launches: if the batch fits one chunk fewer without
+      // another round of 512 passes per CTA (the 2.5 % of slack in pick_chunk usually allows it),
+      // spread it evenly (10^6 objects: 4 x 250,112 instead of 4 x 246,272 + 14,912)
+      const int64_t n_chunks = (n + chunk - 1) / chunk, rest = n - (n_chunks - 1) * chunk;
+      if (rest < chunk / 4) {
+        const int64_t even = ((n + n_chunks - 2) / (n_chunks - 1) + 127) / 128 * 128;
+        const double ppo = std::min(2.0, std::max(0.05, o.passes_per_object));
+        const double rounds = std::ceil((double)chunk * ppo / (512.0 * o.n_sms));
+        if (even <= earb200_objects::kChunk && (double)even * ppo <= rounds * 512.0 * o.n_sms) chunk = even;
+      }
+    }
     const bool feed = !o.fb_pending && n > chunk;  // a call of one chunk has nothing to size
     if (feed) o.fb_count = 0;
     int slot = 0;
