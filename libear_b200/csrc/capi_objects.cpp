@@ -82,7 +82,10 @@ struct earb200_objects {
   // than the cell core's tables hold, and EARB200_EXTENT_PATH=tf32 (cross-check, tested)
   int use_cells = 1;
   // per-chunk scratch
-  // Scratch capacity in objects.  A call is cut into chunks sized so that every CTA of the extent
+  // Largest chunk in objects (the scratch itself grows on demand).  Measured on 10^6 cfg-2 objects
+  // per call: 262,144 -> 451 M vectors/s (4 launch sets), 524,288 -> 465 M (2), 1,048,576 -> 471 M
+  // (1): every set of launches has ~30 us of fixed cost and a partly filled last tile per CTA.
+  // A call is cut into chunks sized so that every CTA of the extent
   // core gets whole rounds of 512 passes (its time goes with the number of rounds, not with how
   // full the last one is): chunk = rounds * 512 * SMs / (passes per object), see pick_chunk.
   // EARB200_OBJECTS_CHUNK fixes the chunk size instead (tuning).
@@ -139,7 +142,7 @@ struct earb200_objects {
     if (s_out) cudaStreamDestroy(s_out);
   }
 };
-const int64_t earb200_objects::kChunk = 262144;
+const int64_t earb200_objects::kChunk = 1048576;
 const int64_t earb200_objects::kChunkFixed = [] {
   const char *e = std::getenv("EARB200_OBJECTS_CHUNK");
   const long long v = e ? std::atoll(e) : 0;
@@ -250,11 +253,9 @@ namespace {
       }
     }
     for (earb200_objects::Scratch &sc : o.scratch) {
-      sc.d_passes.reserve(2 * earb200_objects::kChunk);
-      sc.d_aux.reserve(earb200_objects::kChunk);
-      sc.d_results.reserve(2 * earb200_objects::kChunk * EARB_MAX_SPK);
-      sc.d_point_gains.reserve(earb200_objects::kChunk * EARB_MAX_SPK);
-      sc.d_point_list.reserve(earb200_objects::kChunk);
+      // the per-chunk scratch grows with the chunks a handle actually sees (objects_run_chunk):
+      // 1.3 KB per object and set -- a calculator used for a few thousand objects stays small, one
+      // fed 10^6 objects at a time holds 1.3 GB
       sc.d_n_active.reserve(2);
       EARB_CUDA(cudaEventCreateWithFlags(&sc.ev_core, cudaEventDisableTiming));
       EARB_CUDA(cudaEventCreateWithFlags(&sc.ev_epi, cudaEventDisableTiming));
@@ -314,6 +315,15 @@ namespace {
     c.gain += start;
     c.diffuse += start;
     earb200_objects::Scratch &sc = o.scratch[o.chunk_counter++ & 1];
+    if ((size_t)m > sc.d_aux.cap) {
+      // growing frees the old buffers, which synchronises the device: earlier chunks are done with them
+      const size_t cap = std::max<size_t>((size_t)m, 16384);
+      sc.d_passes.reserve(2 * cap);
+      sc.d_aux.reserve(cap);
+      sc.d_results.reserve(2 * cap * EARB_MAX_SPK);
+      sc.d_point_gains.reserve(cap * EARB_MAX_SPK);
+      sc.d_point_list.reserve(cap);
+    }
     // the epilogue of the chunk that used this scratch set two chunks ago must have read it
     EARB_CUDA(cudaStreamWaitEvent(stream, sc.ev_epi, 0));
     EARB_CUDA(cudaMemsetAsync(sc.d_n_active.ptr, 0, 2 * sizeof(unsigned int), stream));

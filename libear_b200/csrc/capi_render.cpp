@@ -34,6 +34,10 @@ struct earb200_interp {
     DeviceBuffer<RenderItem> d_items;
     DeviceBuffer<RenderSegment> d_segs;
     uint64_t last_use = 0;
+    cudaEvent_t used = nullptr;  // recorded after the last launch that read the buffers
+    ~Plan() {
+      if (used) cudaEventDestroy(used);
+    }
   };
   std::vector<std::unique_ptr<Plan>> plans;
   uint64_t plan_clock = 0;
@@ -58,10 +62,13 @@ namespace {
   // are 16-byte aligned in both buffers, or -1 when no such phase exists
   constexpr size_t kMaxPlans = 64;
 
-  earb200_interp::Plan &build_plan(earb200_interp &h, int64_t block_start, int64_t nsamples, int align) {
+  earb200_interp::Plan &build_plan(earb200_interp &h, int64_t block_start, int64_t nsamples, int align,
+                                   cudaStream_t stream) {
     for (auto &p : h.plans)
       if (p->n == nsamples && p->start == block_start && p->align == align) {
         p->last_use = ++h.plan_clock;
+        // the tables were uploaded on the stream of an earlier call: order this one behind it
+        if (p->used) EARB_CUDA(cudaStreamWaitEvent(stream, p->used, 0));
         return *p;
       }
     const int fast_tile = h.use_tc ? RENDER_TC_TILE : RENDER_PIPE_TILE;
@@ -112,8 +119,11 @@ namespace {
       for (; t < end; t += tile) emit(t, std::min<int64_t>(tile, end - t), false);
       cur = end;
     }
-    // a streaming caller never repeats a key: the least recently used plan is recycled together with
-    // its device buffers (grow-only), so steady state allocates nothing
+    // a streaming caller never repeats a key (block_start advances): the least recently used plan is
+    // recycled together with its device buffers (grow-only), so steady state allocates nothing, and
+    // the tables go up with asynchronous copies on the caller's stream -- ordered before the launch
+    // that reads them, and (through the plan's event) after the last launch that read the buffers'
+    // previous contents, whatever stream that was on
     std::unique_ptr<earb200_interp::Plan> plan;
     if (h.plans.size() >= kMaxPlans) {
       size_t lru = 0;
@@ -121,6 +131,7 @@ namespace {
         if (h.plans[i]->last_use < h.plans[lru]->last_use) lru = i;
       plan = std::move(h.plans[lru]);
       h.plans.erase(h.plans.begin() + lru);
+      if (plan->used) EARB_CUDA(cudaStreamWaitEvent(stream, plan->used, 0));
     } else {
       plan = std::make_unique<earb200_interp::Plan>();
     }
@@ -131,10 +142,12 @@ namespace {
     }
     plan->d_items.reserve(std::max<size_t>(all.size(), 1));
     plan->d_segs.reserve(std::max<size_t>(segs.size(), 1));
-    EARB_CUDA(cudaMemcpy(plan->d_items.ptr, all.data(), sizeof(RenderItem) * all.size(),
-                         cudaMemcpyHostToDevice));
-    EARB_CUDA(cudaMemcpy(plan->d_segs.ptr, segs.data(), sizeof(RenderSegment) * segs.size(),
-                         cudaMemcpyHostToDevice));
+    // (pageable source: the runtime has staged the bytes when the call returns, so the vectors may
+    // go out of scope)
+    EARB_CUDA(cudaMemcpyAsync(plan->d_items.ptr, all.data(), sizeof(RenderItem) * all.size(),
+                              cudaMemcpyHostToDevice, stream));
+    EARB_CUDA(cudaMemcpyAsync(plan->d_segs.ptr, segs.data(), sizeof(RenderSegment) * segs.size(),
+                              cudaMemcpyHostToDevice, stream));
     plan->start = block_start;
     plan->n = nsamples;
     plan->align = align;
@@ -165,7 +178,7 @@ namespace {
     if (ia % 4 == 0 && oa % 4 == 0 && in_stride % 4 == 0 && out_stride % 4 == 0 &&
         ((ia / 4) & 3) == ((oa / 4) & 3))
       align = (int)((ia / 4) & 3);
-    const earb200_interp::Plan &pl = build_plan(h, block_start, nsamples, align);
+    earb200_interp::Plan &pl = build_plan(h, block_start, nsamples, align, stream);
     RenderPlan plan{pl.d_items.ptr, pl.n_items[0], pl.n_items[1], pl.n_items[2], pl.n_items[3], h.use_tc,
                     h.n_sms, (long)nsamples, h.d_images.ptr, h.accumulate, (long)h.n_points, RenderBus{}};
     // Bus mode.  Fused: every item is a tile of the tcgen05 kernel, whose epilogue stores to the bus
@@ -188,6 +201,8 @@ namespace {
     }
     h.timer.stop(stream);
     EARB_CUDA(cudaGetLastError());
+    if (!pl.used) EARB_CUDA(cudaEventCreateWithFlags(&pl.used, cudaEventDisableTiming));
+    EARB_CUDA(cudaEventRecord(pl.used, stream));
     if (h.use_tc) {
       if (pl.n_items[0] + pl.n_items[1] > 0) h.launches += (h.N + 255) / 256;  // one per group of 256 inputs
       h.launches += (pl.n_items[2] > 0) + (pl.n_items[3] > 0);

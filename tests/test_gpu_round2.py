@@ -192,3 +192,29 @@ def test_extent_on_the_5200_point_grid_is_a_sane_throughput_shape(eb):
     assert np.abs(d - d0).max() < 0.08 and np.abs(d - d0).mean() < 0.01
     with pytest.raises(eb.InvalidArgument):
         eb.GainCalculatorObjects("9+10+3", grid="nope")
+
+
+def test_streaming_calls_recycle_plans(eb, ref):
+    """A streaming caller advances block_start on every process(): more distinct calls than the plan
+    cache holds (64), so plans and their device tables are recycled while earlier launches may still
+    be queued (the uploads now ride on the caller's stream behind the plan's event)."""
+    import torch
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(77)
+    N, M, T, call = 9, 7, 300 * 97, 97
+    x = rng.normal(0, 0.25, (N, T)).astype(np.float32)
+    samples = np.arange(0, T + 640, 640, dtype=np.int64)
+    gains = rng.uniform(0, 1, (len(samples), N, M)).astype(np.float32)
+    exp = ref.interp_matrix(x, samples, gains)
+    gi = eb.GainInterpolator(N, M)
+    gi.set_points(samples, gains)
+    d_x = torch.from_numpy(x).to(dev)
+    d_y = torch.full((M, T), float("nan"), dtype=torch.float32, device=dev)
+    streams = [torch.cuda.Stream(dev), torch.cuda.Stream(dev)]
+    torch.cuda.synchronize()
+    for k, t0 in enumerate(range(0, T, call)):      # nothing synchronises between the 300 calls
+        st = streams[k & 1]
+        gi.process_device(t0, call, d_x.data_ptr() + 4 * t0, T, d_y.data_ptr() + 4 * t0, T, stream=st.cuda_stream)
+    torch.cuda.synchronize()
+    got = d_y.cpu().numpy()
+    assert np.abs(got - exp).max() / np.abs(exp).max() < 1e-6
