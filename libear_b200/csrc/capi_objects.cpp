@@ -1,5 +1,6 @@
 // C ABI: layouts, point-source panner (K1) and Objects gain calculator (K1+K2).
 #include <cmath>
+#include <cstdio>
 #include <cstring>
 #include <memory>
 #include <vector>
@@ -498,28 +499,87 @@ namespace {
     OutT *d_out = reinterpret_cast<OutT *>(sizeof(OutT) == 8 ? (void *)o.d_out_d.reserve(2 * n_el)
                                                               : (void *)o.d_out_f.reserve(2 * n_el));
     OutT *d_direct = d_out, *d_diffuse = d_out + n_el;
+    // EARB200_HOST_TRACE=1: per-chunk timeline of the three streams on stderr (diagnostics)
+    static const bool trace = [] {
+      const char *e = std::getenv("EARB200_HOST_TRACE");
+      return e && *e == '1';
+    }();
+    std::vector<cudaEvent_t> tr;
+    auto mark = [&](cudaStream_t st) {
+      if (!trace) return;
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      cudaEventRecord(e, st);
+      tr.push_back(e);
+    };
+    mark(o.s_in);
+    // All copies in are queued ahead of the chunk loop, one piece per chunk.  An event trace
+    // (EARB200_HOST_TRACE=1) shows the copy out -- 192 B per object against 64 B in -- as the long
+    // pole: 47 GB/s while copies in run beside it, 54 GB/s afterwards, and the copies in crawling
+    // at 14 GB/s next to it.  Larger pieces (EARB200_HOST_PIECES=g: g chunks per copy) bring the
+    // input in sooner but make the chunks at the head of a piece wait: measured on one box
+    // g = 1 / 2 / 3 / 4: 233 / 230 / 226 / 221 M vectors/s, so g = 1 stays.
+    // piece_of[k]: the piece whose event chunk k waits for.
+    std::vector<int> piece_of(n_chunks, 0);
+    {
+      std::vector<int64_t> piece_end;  // chunk index one past the piece
+      // the first two chunks one by one (the fill must not wait for a large copy), then groups of
+      // kGroup chunks
+      static const int64_t kGroup = [] {
+        const char *e = std::getenv("EARB200_HOST_PIECES");
+        const long v = e ? std::atol(e) : 1;
+        return (int64_t)(v >= 1 && v <= 64 ? v : 1);
+      }();
+      const int64_t single = std::min<int64_t>(n_chunks, 2);
+      for (int64_t k = 0; k < single; k++) piece_end.push_back(k + 1);
+      for (int64_t k = single; k < n_chunks; k += kGroup) piece_end.push_back(std::min(n_chunks, k + kGroup));
+      int64_t k0 = 0, obj0 = 0;
+      for (size_t pc = 0; pc < piece_end.size(); pc++) {
+        int64_t m = 0;
+        for (int64_t k = k0; k < piece_end[pc]; k++) m += sizes[k], piece_of[k] = (int)pc;
+        for (int f = 0; f < 8; f++)
+          EARB_CUDA(cudaMemcpyAsync(d + (size_t)f * n + obj0, src[f] + obj0, sizeof(double) * m,
+                                    cudaMemcpyHostToDevice, o.s_in));
+        EARB_CUDA(cudaEventRecord(o.ev_in[pc], o.s_in));
+        k0 = piece_end[pc];
+        obj0 += m;
+      }
+    }
     int64_t start = 0;
     for (int64_t k = 0; k < n_chunks; start += sizes[k], k++) {
       const int64_t m = sizes[k];
-      for (int f = 0; f < 8; f++)
-        EARB_CUDA(cudaMemcpyAsync(d + (size_t)f * n + start, src[f] + start, sizeof(double) * m,
-                                  cudaMemcpyHostToDevice, o.s_in));
-      EARB_CUDA(cudaEventRecord(o.ev_in[k], o.s_in));
-      EARB_CUDA(cudaStreamWaitEvent(o.s_compute, o.ev_in[k], 0));
+      mark(o.s_in);  // [1 + 5k] (all copies in are queued ahead)
+      EARB_CUDA(cudaStreamWaitEvent(o.s_compute, o.ev_in[piece_of[k]], 0));
       cudaEvent_t done = objects_run_chunk<OutT>(o, start, m, soa, o.n_out, o.d_out_index.ptr, d_direct,
                                                  d_diffuse, d_reg, o.s_compute);
+      mark(o.s_compute);  // [2 + 5k] core done
+      mark(o.s_epi);      // [3 + 5k] epilogue done
       EARB_CUDA(cudaStreamWaitEvent(o.s_out, done, 0));
+      mark(o.s_out);      // [4 + 5k] copy out may start
       const size_t off = (size_t)start * o.n_out, cnt = (size_t)m * o.n_out;
       EARB_CUDA(cudaMemcpyAsync(direct + off, d_direct + off, sizeof(OutT) * cnt, cudaMemcpyDeviceToHost, o.s_out));
       EARB_CUDA(cudaMemcpyAsync(diffuse + off, d_diffuse + off, sizeof(OutT) * cnt, cudaMemcpyDeviceToHost, o.s_out));
       if (region_idx)
         EARB_CUDA(cudaMemcpyAsync(region_idx + start, d_reg + start, sizeof(int32_t) * m, cudaMemcpyDeviceToHost,
                                   o.s_out));
+      mark(o.s_out);      // [5 + 5k] copy out done
     }
     EARB_CUDA(cudaGetLastError());
     EARB_CUDA(cudaStreamSynchronize(o.s_out));
     EARB_CUDA(cudaStreamSynchronize(o.s_compute));
     EARB_CUDA(cudaStreamSynchronize(o.s_epi));
+    if (trace) {
+      auto at = [&](size_t i) {
+        float ms = 0.0f;
+        cudaEventElapsedTime(&ms, tr[0], tr[i]);
+        return ms;
+      };
+      for (int64_t k = 0; k < n_chunks; k++)
+        fprintf(stderr, "host-trace chunk %2lld (%7lld obj): in %.3f  core %.3f  epi %.3f  out %.3f -> %.3f ms\n",
+                (long long)k, (long long)sizes[k], at(1 + 5 * k), at(2 + 5 * k), at(3 + 5 * k), at(4 + 5 * k),
+                at(5 + 5 * k));
+      for (cudaEvent_t e : tr) cudaEventDestroy(e);
+    }
   }
 }  // namespace
 
