@@ -72,12 +72,14 @@ namespace earb {
       return r;
     }
     __device__ __forceinline__ float re(cx v) {
-      float a, b;
+      float a;
+      [[maybe_unused]] float b;
       asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
       return a;
     }
     __device__ __forceinline__ float im(cx v) {
-      float a, b;
+      [[maybe_unused]] float a;
+      float b;
       asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v));
       return b;
     }
@@ -375,19 +377,19 @@ namespace earb {
 #pragma unroll
             for (int r = 0; r < 16; r++) tail[r] = re(v[r + 16]);
           }
-          continue;
-        }
-#pragma unroll
-        for (int r = 0; r < 16; r++) __stcs(y0 + lane + 32 * r, re(v[r]) + tail[r]);
-        if (has_second) {
-#pragma unroll
-          for (int r = 0; r < 16; r++) {
-            __stcs(y0 + kFastB + lane + 32 * r, im(v[r]) + re(v[r + 16]));
-            tail[r] = im(v[r + 16]);
-          }
         } else {
 #pragma unroll
-          for (int r = 0; r < 16; r++) tail[r] = re(v[r + 16]);
+          for (int r = 0; r < 16; r++) __stcs(y0 + lane + 32 * r, re(v[r]) + tail[r]);
+          if (has_second) {
+#pragma unroll
+            for (int r = 0; r < 16; r++) {
+              __stcs(y0 + kFastB + lane + 32 * r, im(v[r]) + re(v[r + 16]));
+              tail[r] = im(v[r + 16]);
+            }
+          } else {
+#pragma unroll
+            for (int r = 0; r < 16; r++) tail[r] = re(v[r + 16]);
+          }
         }
       }
       if (p1 == a.n_pairs) {

@@ -352,7 +352,16 @@ namespace earb {
         extent_cell_kernel(int n_cells, int NC, int n_spk, const unsigned char *__restrict__ g_stream,
                            const unsigned char *__restrict__ g_sums, const float *__restrict__ g_centres,
                            const float4 *__restrict__ g_points, const unsigned int *__restrict__ n_active_ptr,
-                           const ExtentPass *__restrict__ passes, float *__restrict__ results, int dbg) {
+                           const ExtentPass *__restrict__ passes, float *__restrict__ results, int dbg_in) {
+      // experiment switches (skip the UMMAs / the evaluation / the a_free wait, ring depth, phase
+      // trace): only in builds with -DEARB_CELL_DEBUG (tools/gpu_dbg.sh, tools/gpu_trace.sh); the
+      // product build folds them away
+#ifdef EARB_CELL_DEBUG
+      const int dbg = dbg_in;
+#else
+      constexpr int dbg = 0;
+      (void)dbg_in;
+#endif
       extern __shared__ __align__(128) unsigned char smem_raw[];
       Smem sm;
       smem_layout(NC, smem_raw, &sm);
@@ -997,10 +1006,14 @@ namespace earb {
     const size_t smem = smem_layout(NC, nullptr, nullptr);
     // the attribute is per device: set it on every launch (a few hundred nanoseconds)
     cudaFuncSetAttribute(extent_cell_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+#ifdef EARB_CELL_DEBUG
     static const int dbg = [] {
       const char *e = std::getenv("EARB200_CELL_DBG");
       return e ? std::atoi(e) : 0;
     }();
+#else
+    const int dbg = 0;
+#endif
     extent_cell_kernel<<<(unsigned)n_sms, kThreads, smem, stream>>>(
         n_cells, NC, n_spk, d_stream, d_sums, d_centres, reinterpret_cast<const float4 *>(d_points), d_n_active,
         d_passes, d_results, dbg);

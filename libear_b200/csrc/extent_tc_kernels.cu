@@ -163,32 +163,6 @@ namespace earb {
     //   straight:        angle = q                         weight = sat(m q + c)
     //   circle:          angle = pi/2 - copysign(q, v)     weight = sat(m (-copysign(q, v)) + (m pi/2 + c))
     // share one saturating FMA whose operand is q with the inverted sign of v (one LOP3).
-    __device__ __forceinline__ float point_weight(const PassRegs &c, float x, float y, float z) {
-      const float xt = fmaf(x, c.b[0], fmaf(y, c.b[1], __fmul_rn(z, c.b[2])));
-      const float yt = fmaf(x, c.b[3], fmaf(y, c.b[4], __fmul_rn(z, c.b[5])));
-      const float zt = fmaf(x, c.b[6], fmaf(y, c.b[7], __fmul_rn(z, c.b[8])));
-      const float ax = fabsf(xt);
-      const float circle_test_dot = fmaf(ax, c.ct0, __fmul_rn(yt, c.ct1));
-      const float circle_dot = fmaf(ax, c.cc0, __fmul_rn(yt, c.cc1));
-      const bool is_sin = circle_test_dot >= c.sin_thr;
-      const float v = is_sin ? zt : circle_dot;
-      // rounding can leave |v| a few ulp above 1: u saturates
-      const float u = __saturatef(__fsub_rn(1.0f, fabsf(v)));
-      float p = 0.0012628264f;
-      p = fmaf(p, u, -0.0021685062f);
-      p = fmaf(p, u, 0.0035814755f);
-      p = fmaf(p, u, 0.0013143348f);
-      p = fmaf(p, u, 0.0082738195f);
-      p = fmaf(p, u, 0.0264650658f);
-      p = fmaf(p, u, 0.1178537458f);
-      p = fmaf(p, u, 1.4142135382f);
-      float sq;
-      asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(sq) : "f"(u));
-      const float q = fmaf(-sq, p, 1.57079632679490f);
-      // q carrying the inverted sign bit of circle_dot
-      const float qs = __uint_as_float(__float_as_uint(q) | (~__float_as_uint(circle_dot) & 0x80000000u));
-      return __saturatef(fmaf(c.m, is_sin ? q : qs, is_sin ? c.c : c.a_sin));
-    }
 
     // ---- packed fp32 (sm_100 FFMA2 / FMUL2 / FADD2: two FMAs per lane per issue slot).  The kernel
     // is issue-bound, so the weights of two virtual sources are evaluated side by side: the FMA-pipe
@@ -219,10 +193,9 @@ namespace earb {
       return r;
     }
     __device__ __forceinline__ f32x2 bc(float a) { return pk(a, a); }
-    __device__ __forceinline__ f32x2 abs2(f32x2 v) { return v & 0x7fffffff7fffffffull; }
 
-    // point_weight for two virtual sources at once: X, Y, Z hold the coordinates of both; the same
-    // operations in the same order per half, so each weight is bit-identical to point_weight's.
+    // the weight of two virtual sources at once: X, Y, Z hold the coordinates of both (the same
+    // operations in the same order per half)
     __device__ __forceinline__ void point_weight2(const PassRegs &c, f32x2 X, f32x2 Y, f32x2 Z, float &w0,
                                                   float &w1) {
       const f32x2 xt = fma2(X, bc(c.b[0]), fma2(Y, bc(c.b[1]), mul2(Z, bc(c.b[2]))));

@@ -89,11 +89,6 @@ namespace earb {
             : "memory");
       } while (!done);
     }
-    __device__ __forceinline__ float to_tf32(float x) {
-      uint32_t r;
-      asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-      return __uint_as_float(r);
-    }
     __device__ __forceinline__ void tmem_st16(uint32_t taddr, const float (&v)[16]) {
       asm volatile(
           "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
@@ -125,32 +120,6 @@ namespace earb {
         b[i] = __uint_as_float(r[1][i]);
         c[i] = __uint_as_float(r[2][i]);
         d[i] = __uint_as_float(r[3][i]);
-      }
-    }
-    // two 16-column loads in flight, one wait
-    __device__ __forceinline__ void tmem_ld16x2(uint32_t ta, uint32_t tb, float (&a)[16], float (&b)[16]) {
-      uint32_t r[16], q[16];
-      asm volatile(
-          "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-          : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-            "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]),
-            "=r"(r[15])
-          : "r"(ta)
-          : "memory");
-      asm volatile(
-          "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-          "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-          : "=r"(q[0]), "=r"(q[1]), "=r"(q[2]), "=r"(q[3]), "=r"(q[4]), "=r"(q[5]), "=r"(q[6]), "=r"(q[7]),
-            "=r"(q[8]), "=r"(q[9]), "=r"(q[10]), "=r"(q[11]), "=r"(q[12]), "=r"(q[13]), "=r"(q[14]),
-            "=r"(q[15])
-          : "r"(tb)
-          : "memory");
-      asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-      for (int i = 0; i < 16; i++) {
-        a[i] = __uint_as_float(r[i]);
-        b[i] = __uint_as_float(q[i]);
       }
     }
     __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
@@ -371,7 +340,6 @@ namespace earb {
         int g = 0, L = 0;
         for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, L++) {
           const int tile0 = unit / n_groups, grp = unit - tile0 * n_groups;
-          const int tile = tile0 + tile_shift < n_tiles ? tile0 + tile_shift : tile0 + tile_shift - n_tiles;
           (void)grp;
           const int ab = L & 1;
           // B of this tile: rows 0..31 = [a | b] hi, 32..63 = [a | b] lo
