@@ -73,9 +73,10 @@ namespace earb {
     // their issue by one thread set the pace, not the time a stage waits for them -- so the third
     // stage's 32 KB hold the point table instead.
     constexpr int kD = 2;
-    // One issuer (a single thread).  Four issuer warps, one per M-tile, were measured slower
-    // (0.441 against 0.406 ms per launch): the per-cell waits, fences and commits are paid four
-    // times and the polling warps take issue slots from the evaluators.
+    // MMA issuer warps (an elected lane of each issues for kMT / kMmaWarps M-tiles).  Measured on
+    // the final kernel, per 10^6 cfg-2 objects: 1 warp 1.582 ms, 2 warps 1.538 ms, 4 warps 1.598 ms
+    // (the per-cell waits, fences and commits are paid once per warp, and polling warps take issue
+    // slots from the evaluators).
     constexpr int kMmaWarp = kEvalWarps, kMmaWarps = EARB_CELL_MMA_WARPS, kProdWarp = kMmaWarp + kMmaWarps;
     constexpr int kMtPerIssuer = kMT / kMmaWarps;
     constexpr int kThreads = (kProdWarp + 1) * 32;  // 576
