@@ -101,7 +101,26 @@ namespace earb {
         bus.slot[owner][m * bus.slice_len + (bt - (long long)owner * bus.slice_len)] = partial[m * partial_stride + t];
       }
     }
+    // the runs of a call that the fused epilogue did not take (ragged heads / tails of segments,
+    // rendered into the partial bus by the FFMA kernels): one block per item
+    __global__ void __launch_bounds__(256)
+        bus_push_items_kernel(const RenderItem *__restrict__ items, const float *__restrict__ partial,
+                              long long partial_stride, int M, const RenderBus bus) {
+      const RenderItem it = items[blockIdx.x];
+      const long long total = (long long)M * it.len;
+      for (long long i = threadIdx.x; i < total; i += blockDim.x) {
+        const long long m = i / it.len, t = it.t0 + (i - m * it.len), bt = t + bus.t_origin;
+        const int owner = (int)(bt / bus.slice_len);
+        bus.slot[owner][m * bus.slice_len + (bt - (long long)owner * bus.slice_len)] = partial[m * partial_stride + t];
+      }
+    }
   }  // namespace
+
+  void launch_bus_push_items(const RenderItem *d_items, long n_items, const float *partial, long long partial_stride,
+                             int M, const RenderBus &bus, cudaStream_t stream) {
+    if (n_items <= 0) return;
+    bus_push_items_kernel<<<(unsigned)n_items, 256, 0, stream>>>(d_items, partial, partial_stride, M, bus);
+  }
 
   void launch_bus_signal(uint32_t *const *peer_flags, int n_ranks, int rank, uint32_t epoch, cudaStream_t stream) {
     PeerFlags pf{};

@@ -181,13 +181,15 @@ namespace {
     earb200_interp::Plan &pl = build_plan(h, block_start, nsamples, align, stream);
     RenderPlan plan{pl.d_items.ptr, pl.n_items[0], pl.n_items[1], pl.n_items[2], pl.n_items[3], h.use_tc,
                     h.n_sms, (long)nsamples, h.d_images.ptr, h.accumulate, (long)h.n_points, RenderBus{}};
-    // Bus mode.  Fused: every item is a tile of the tcgen05 kernel, whose epilogue stores to the bus
-    // slots itself (accumulate mode and the earlier input groups of N > 128 read / write the
-    // caller's partial bus).  Otherwise (ragged or unaligned calls, the FFMA kernels): render into
-    // the partial bus, then push it.
+    // Bus mode.  Fused: the epilogue of the tcgen05 kernel stores its tiles to the bus slots itself
+    // (accumulate mode and the earlier input groups of N > 128 read / write the caller's partial
+    // bus); the ragged runs between them (segment boundaries that are not tile-aligned: the FFMA
+    // kernels) are rendered into the partial bus and only THEY are pushed.  Without a tcgen05 path or
+    // without any tile: render into the partial bus, then push all of it.
     const bool have_partial = reinterpret_cast<uintptr_t>(d_out) > 15;
-    const bool fused = bus && h.use_tc && pl.n_items[2] + pl.n_items[3] == 0 &&
-                       (have_partial || (!h.accumulate && h.N <= 128));
+    const long n_slow = pl.n_items[2] + pl.n_items[3], n_fast = pl.n_items[0] + pl.n_items[1];
+    const bool fused = bus && h.use_tc && n_fast > 0 &&
+                       (have_partial || (n_slow == 0 && !h.accumulate && h.N <= 128));
     if (bus && !fused && !have_partial)
       throw Error(INVALID_ARGUMENT, "this call needs a partial-bus buffer (accumulate mode, more than 128 "
                                     "input channels, or a call that is not made of whole aligned tiles)");
@@ -197,6 +199,10 @@ namespace {
                   h.d_gains.ptr, stream);
     if (bus && !fused) {
       launch_bus_push(d_out, out_stride, h.M, bus_t0, nsamples, earb200_bus_map(*bus, bus_t0), stream);
+      earb200_bus_count_launch(bus);
+    } else if (bus && n_slow > 0) {
+      launch_bus_push_items(pl.d_items.ptr + n_fast, n_slow, d_out, out_stride, h.M, earb200_bus_map(*bus, bus_t0),
+                            stream);
       earb200_bus_count_launch(bus);
     }
     h.timer.stop(stream);

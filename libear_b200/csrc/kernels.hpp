@@ -182,6 +182,9 @@ namespace earb {
   // local [M][T] partial bus -> the slots (the path for calls the fused epilogue cannot take)
   void launch_bus_push(const float *partial, long long partial_stride, int M, long long t_origin, long long n,
                        const RenderBus &bus, cudaStream_t stream);
+  // the same for a list of runs (the items of a call the fused epilogue did not take)
+  void launch_bus_push_items(const RenderItem *d_items, long n_items, const float *partial, long long partial_stride,
+                             int M, const RenderBus &bus, cudaStream_t stream);
   // waits until flags[r] >= epoch for every rank (the gather of an epoch has landed everywhere)
   void launch_bus_wait(const uint32_t *flags, int n_ranks, uint32_t epoch, cudaStream_t stream);
 

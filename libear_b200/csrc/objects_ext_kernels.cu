@@ -23,7 +23,6 @@
 namespace earb {
   namespace {
     __device__ __forceinline__ double rad(double d) { return d * (3.141592653589793238462643383279502884 / 180.0); }
-    __device__ __forceinline__ double deg(double r) { return r * (180.0 / 3.141592653589793238462643383279502884); }
     __device__ __forceinline__ void cart(double az, double el, double dist, double &x, double &y, double &z) {
       // ref src/common/geom.cpp:82-87
       x = sin(rad(-az)) * cos(rad(el)) * dist;

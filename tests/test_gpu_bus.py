@@ -26,22 +26,25 @@ def device_sets():
     return sets
 
 
-def make_case(N, M, T, seed):
+def make_case(N, M, T, seed, spacing=512):
     rng = np.random.default_rng(seed)
     x = rng.normal(0, 0.25, (N, T)).astype(np.float32)
-    samples = np.arange(0, T + 512, 512, dtype=np.int64)
+    samples = np.arange(0, T + spacing, spacing, dtype=np.int64)
     gains = (rng.uniform(0, 1, (len(samples), N, M)) / np.sqrt(N)).astype(np.float32)
     return x, samples, gains
 
 
 @pytest.mark.parametrize("name,devices", device_sets())
-@pytest.mark.parametrize("mode", ["fused", "accumulate_groups", "ragged_push"])
+@pytest.mark.parametrize("mode", ["fused", "accumulate_groups", "ragged_push", "unaligned_points",
+                                  "unaligned_points_accumulate"])
 def test_sharded_mix_equals_single_gpu_render(eb, ref, name, devices, mode):
     import torch
     R = len(devices)
     N, M = 64 * R, 12
     T = 256 * 37 if mode != "ragged_push" else 256 * 37 + 100
-    x, samples, gains = make_case(N, M, T, 40 + R)
+    # unaligned_points: interpolation points every 1,000 samples, so segments end inside render tiles:
+    # the tiles go to the bus from the kernel's epilogue, the ragged runs between them are pushed
+    x, samples, gains = make_case(N, M, T, 40 + R, spacing=1000 if mode.startswith("unaligned") else 512)
     whole = eb.GainInterpolator(N, M, device=0)
     whole.set_points(samples, gains)
     exp = whole.process(0, x)
@@ -60,7 +63,7 @@ def test_sharded_mix_equals_single_gpu_render(eb, ref, name, devices, mode):
                 stream = torch.cuda.current_stream(dev).cuda_stream
                 xs = torch.from_numpy(x[r * per:(r + 1) * per] * scale).to(dev)
                 keep.append(xs)
-                if mode == "accumulate_groups":
+                if mode in ("accumulate_groups", "unaligned_points_accumulate"):
                     half = per // 2
                     g0 = eb.GainInterpolator(half, M, device=d)
                     g0.set_points(samples, gains[:, r * per:r * per + half])
@@ -76,11 +79,13 @@ def test_sharded_mix_equals_single_gpu_render(eb, ref, name, devices, mode):
                     gi = eb.GainInterpolator(per, M, device=d)
                     gi.set_points(samples, gains[:, r * per:(r + 1) * per])
                     part = None
+                    if mode == "unaligned_points":
+                        part = torch.full((M, T), float("nan"), dtype=torch.float32, device=dev)
                     if mode == "ragged_push":
                         part = torch.full((M, T + 4), float("nan"), dtype=torch.float32, device=dev)
                     gi.process_device_bus(0, T, xs.data_ptr(), T, buses[r], 0,
                                           d_partial=None if part is None else part.data_ptr(),
-                                          partial_stride=0 if part is None else T + 4, stream=stream)
+                                          partial_stride=0 if part is None else part.shape[1], stream=stream)
                     keep += [gi, part]
         # several ranks share a device (and its stream) here: all publish before any waits
         for r, d in enumerate(devices):
