@@ -61,7 +61,9 @@ def same_bits(a, b):
                           b.view(np.uint32 if b.dtype == np.float32 else np.uint64))
 
 
-@pytest.mark.parametrize("dtype,n", [(np.float32, 1_000_000), (np.float64, 600_000)])
+# 2.3 M objects: more than one chunk of the device path (chunks hold up to 2^20 objects), so the
+# second call runs on the pass counts the first one fed back and on an evenly split schedule
+@pytest.mark.parametrize("dtype,n", [(np.float32, 1_000_000), (np.float64, 600_000), (np.float32, 2_300_000)])
 def test_objects_calculate_device_twice(eb, ref, dtype, n):
     import torch
     dev = torch.device("cuda", 0)
