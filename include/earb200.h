@@ -185,6 +185,10 @@ typedef struct earb200_objects_ext {
 int earb200_objects_calculate_ext_device(earb200_objects *calc, int64_t n, const earb200_objects_soa *d_in,
                                          const earb200_objects_ext *d_ext, int out_is_double,
                                          void *d_direct, void *d_diffuse, void *stream);
+/* the same with host arrays (copies, runs, synchronises) */
+int earb200_objects_calculate_ext_host(earb200_objects *calc, int64_t n, const earb200_objects_soa *in,
+                                       const earb200_objects_ext *ext, int out_is_double, void *direct,
+                                       void *diffuse);
 /* PolarExtent::handle on Cartesian positions (src/object_based/polar_extent.cpp:281-302):
  * xyz [n][3], width/height/depth [n]; out [n][S] double.  Host buffers. */
 int earb200_objects_extent_host(earb200_objects *calc, int64_t n, const double *xyz,

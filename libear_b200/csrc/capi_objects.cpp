@@ -897,6 +897,44 @@ int earb200_objects_calculate_ext_device(earb200_objects *calc, int64_t n, const
   });
 }
 
+// host arrays: staged, run through the device entry point, copied back (drop-in semantics)
+int earb200_objects_calculate_ext_host(earb200_objects *calc, int64_t n, const earb200_objects_soa *in,
+                                       const earb200_objects_ext *ext, int out_is_double, void *direct,
+                                       void *diffuse) {
+  return guarded([&] {
+    if (!calc || !in || !ext) throw Error(INVALID_ARGUMENT, "null argument");
+    if (n < 0) throw Error(INVALID_ARGUMENT, "negative batch size");
+    if (n == 0) return;
+    if (!direct || !diffuse) throw Error(INVALID_ARGUMENT, "null output buffer");
+    if (!in->azimuth || !in->elevation || !in->distance || !in->width || !in->height || !in->depth || !in->gain ||
+        !in->diffuse)
+      throw Error(INVALID_ARGUMENT, "null metadata field (all eight arrays are required)");
+    earb200_objects &o = *calc;
+    use_device(o.device);
+    const double *src[11] = {in->azimuth, in->elevation, in->distance, in->width, in->height, in->depth, in->gain,
+                             in->diffuse, ext->divergence, ext->divergence_azimuth_range,
+                             ext->channel_lock_max_distance};
+    double *d = o.d_in.reserve(11 * (size_t)n);
+    const double *dev[11];
+    for (int f = 0; f < 11; f++) {
+      dev[f] = nullptr;
+      if (!src[f]) continue;
+      EARB_CUDA(cudaMemcpyAsync(d + (size_t)f * n, src[f], sizeof(double) * n, cudaMemcpyHostToDevice, 0));
+      dev[f] = d + (size_t)f * n;
+    }
+    earb200_objects_soa d_in{dev[0], dev[1], dev[2], dev[3], dev[4], dev[5], dev[6], dev[7], in->flags};
+    earb200_objects_ext d_ext{dev[8], dev[9], dev[10]};
+    const size_t n_el = (size_t)n * o.n_out, esz = out_is_double ? 8 : 4;
+    void *d_out = out_is_double ? (void *)o.d_out_d.reserve(2 * n_el) : (void *)o.d_out_f.reserve(2 * n_el);
+    void *d_dir = d_out, *d_dif = (char *)d_out + n_el * esz;
+    const int rc = earb200_objects_calculate_ext_device(calc, n, &d_in, &d_ext, out_is_double, d_dir, d_dif, nullptr);
+    if (rc != EARB200_OK) throw Error((Status)rc, last_error());
+    EARB_CUDA(cudaMemcpyAsync(direct, d_dir, n_el * esz, cudaMemcpyDeviceToHost, 0));
+    EARB_CUDA(cudaMemcpyAsync(diffuse, d_dif, n_el * esz, cudaMemcpyDeviceToHost, 0));
+    EARB_CUDA(cudaStreamSynchronize(0));
+  });
+}
+
 int earb200_objects_calculate_host(earb200_objects *calc, int64_t n,
                                    const earb200_objects_soa *in, int out_is_double,
                                    void *direct, void *diffuse, int32_t *region_idx) {

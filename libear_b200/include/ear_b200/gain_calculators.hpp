@@ -3,6 +3,7 @@
 // handle; like libear's, an instance is not thread-safe.  calculate_batch() is the addition a
 // GPU is for: many metadata blocks per call.
 #pragma once
+#include <limits>
 #include <cstdint>
 
 #include "layout.hpp"
@@ -76,8 +77,47 @@ namespace ear {
       const double *c = _soa.data();
       earb200_objects_soa in = {c, c + n, c + 2 * n, c + 3 * n, c + 4 * n, c + 5 * n, c + 6 * n, c + 7 * n,
                                 _flags.data()};
+      if (_extensions) {
+        // opt-in: polar objectDivergence / channelLock are computed instead of refused (see
+        // enableExtensions); the flags of what is enabled are cleared, everything else still throws
+        _ext.assign(3 * n, 0.0);
+        bool any_div = false, any_lock = false;
+        for (size_t i = 0; i < n; i++) {
+          const ObjectsTypeMetadata &m = metadata[i];
+          _ext[2 * n + i] = -1.0;
+          if ((_extensions & EARB200_EXT_DIVERGENCE) && m.objectDivergence.which() == 0) {
+            const PolarObjectDivergence &d = compat::get<PolarObjectDivergence>(m.objectDivergence);
+            _ext[i] = d.divergence;
+            _ext[n + i] = d.azimuthRange;
+            any_div = any_div || d.divergence != 0.0;
+            _flags[i] &= ~(int32_t)EARB200_OBJ_DIVERGENCE;
+          }
+          if ((_extensions & EARB200_EXT_CHANNEL_LOCK) && m.channelLock.flag) {
+            _ext[2 * n + i] = m.channelLock.maxDistance ? m.channelLock.maxDistance.get()
+                                                        : std::numeric_limits<double>::infinity();
+            any_lock = true;
+            _flags[i] &= ~(int32_t)EARB200_OBJ_CHANNEL_LOCK;
+          }
+        }
+        if (any_div || any_lock) {
+          const double *e = _ext.data();
+          earb200_objects_ext ext = {any_div ? e : nullptr, any_div ? e + n : nullptr, any_lock ? e + 2 * n : nullptr};
+          b200::check(earb200_objects_calculate_ext_host(_h.get(), (int64_t)n, &in, &ext, b200::is_double<T>::value,
+                                                         direct, diffuse));
+          return;
+        }
+      }
       b200::check(earb200_objects_calculate_host(_h.get(), (int64_t)n, &in, b200::is_double<T>::value, direct,
                                                  diffuse, nullptr));
+    }
+
+    /// OPT-IN, not in libear (which throws not_implemented for both, and so does this class by
+    /// default): compute polar objectDivergence and / or channelLock.  PARITY UNPINNED: there is no
+    /// libear output to compare with (see earb200.h, csrc/objects_ext_kernels.cu).
+    void enableExtensions(bool divergence, bool channelLock) {
+      _extensions = (divergence ? (uint32_t)EARB200_EXT_DIVERGENCE : 0u) |
+                    (channelLock ? (uint32_t)EARB200_EXT_CHANNEL_LOCK : 0u);
+      b200::check(earb200_objects_enable_extensions(_h.get(), _extensions));
     }
     template <typename T>
     void calculate_batch(const std::vector<ObjectsTypeMetadata> &metadata, std::vector<T> &direct,
@@ -96,8 +136,9 @@ namespace ear {
     };
     std::unique_ptr<earb200_objects, Deleter> _h;
     size_t _n_out = 0;
-    std::vector<double> _soa;
+    std::vector<double> _soa, _ext;
     std::vector<int32_t> _flags;
+    uint32_t _extensions = 0;
   };
 
   /// Gain calculator for typeDefinition == "DirectSpeakers"

@@ -468,6 +468,48 @@ static int run_objects(const std::string &layout_name) {
   return 0;
 }
 
+// OPT-IN extensions through libear's own metadata types: the default is libear's not_implemented;
+// after enableExtensions a fully diverged point source straight ahead sits half and half (in
+// power) on M+030 / M-030, and a locked object renders as the loudspeaker it snaps to
+static void test_extensions() {
+  Layout layout = getLayout("0+5+0");
+  GainCalculatorObjects gc(layout);
+  std::vector<double> direct(6), diffuse(6);
+  ObjectsTypeMetadata m;
+  m.position = PolarPosition(0.0, 0.0, 1.0);
+  m.objectDivergence = PolarObjectDivergence(1.0, 30.0);
+  bool threw = false;
+  try {
+    gc.calculate(m, direct, diffuse);
+  } catch (const not_implemented &) {
+    threw = true;
+  }
+  CHECK(threw);
+  gc.enableExtensions(true, true);
+  gc.calculate(m, direct, diffuse);
+  const std::vector<std::string> names = layout.channelNames();
+  for (size_t c = 0; c < names.size(); c++) {
+    const double want = (names[c] == "M+030" || names[c] == "M-030") ? std::sqrt(0.5) : 0.0;
+    CHECK(close(direct[c], want, 1e-6));
+  }
+  ObjectsTypeMetadata l;
+  l.position = PolarPosition(-107.0, 2.0, 1.0);
+  l.channelLock = ChannelLock(true, 0.2);
+  gc.calculate(l, direct, diffuse);
+  for (size_t c = 0; c < names.size(); c++) CHECK(close(direct[c], names[c] == "M-110" ? 1.0 : 0.0, 1e-9));
+  // zoneExclusion stays refused
+  ObjectsTypeMetadata z;
+  z.position = PolarPosition(0.0, 0.0, 1.0);
+  z.zoneExclusion.zones.push_back(PolarExclusionZone{0, 10, 0, 10, 0, 1, "zone"});
+  threw = false;
+  try {
+    gc.calculate(z, direct, diffuse);
+  } catch (const not_implemented &) {
+    threw = true;
+  }
+  CHECK(threw);
+}
+
 // mode "vbs <block_size> <n_in> <n_out> <size>...": the facade's VariableBlockSizeAdapter over calls
 // of the given sizes, around the same probe process function as oracle/ref_capi.cpp::ref_vbs_process
 // runs libear's adapter with (ref src/dsp/variable_block_size_impl.cpp:44-81,
@@ -518,6 +560,7 @@ int main(int argc, char **argv) {
     test_fft_plugin();
     test_delay_and_adapter();
     test_conversion();
+    test_extensions();
   } catch (const std::exception &e) {
     std::printf("FAIL unexpected exception: %s\n", e.what());
     return 2;
