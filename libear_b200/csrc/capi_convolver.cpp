@@ -82,6 +82,22 @@ bool earb_conv_process_device(earb200_convolver &h, int64_t K, const float *d_in
     use_device(h.device);
     const int nb = h.nb, C = h.C;
     bool fused = false;
+    // A filter change travels through a channel's queue for nb + 1 blocks
+    // (ref block_convolver_impl.cpp:114-122); only those blocks need the generic kernel (crossfades,
+    // per-partition filter tables).  A long call that starts with a change in flight is therefore cut
+    // in two: the head on the generic kernel, the rest -- uniform again -- on the fast one, instead of
+    // the whole call at a tenth of the speed.  (Not with a fused add: the caller falls back as a whole.)
+    if (h.use_fast && d_in && !add && K > (int64_t)nb + 1) {
+      bool uniform = true;
+      for (const ChannelQueue &q : h.chan) uniform = uniform && q.uniform();
+      if (!uniform) {
+        const int64_t head = (int64_t)nb + 1;
+        earb_conv_process_device(h, head, d_in, in_stride, d_out, out_stride, stream, nullptr, 0, 0, nullptr);
+        earb_conv_process_device(h, K - head, d_in + head * h.B, in_stride, d_out + head * h.B, out_stride, stream,
+                                 nullptr, 0, 0, nullptr);
+        return false;
+      }
+    }
     if (h.filt_dirty) {
       h.d_filt.reserve(std::max<size_t>(h.filt_host.size(), 2));
       if (!h.filt_host.empty())
