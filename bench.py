@@ -225,8 +225,10 @@ def run_reference(args):
         "config": {"workload": f"configs[1] (SURVEY cfg 2): {step_n} extent objects/GPU on {LAYOUT} via the batched "
                                "GainCalculatorObjects C-ABI (1,652-point spreading grid, depth != 0 for half)",
                    "layout": LAYOUT, "objects_per_gpu": step_n,
-                   "note": "libear's GainCalculatorObjects::calculate<float> on the host cores, the GPU arm's "
-                           "own input (same seed), all of it every step"},
+                   "passes_per_step_per_gpu": step_n + int(np.count_nonzero(objs[5])),
+                   "l2": "inputs+outputs 256 MB/step/GPU > 126 MB L2", "sharding": "objects, no collective"},
+        "note": "libear's GainCalculatorObjects::calculate<float> on the host cores, the GPU arm's own input (same "
+                "seed), all of it every step",
         "cpu_baseline": {"value": value, "unit": "vectors/s", "cores": threads, "kind": "reference",
                          "sample": f"{step_n} objects/step x {args.steps} steps, libear "
                                    f"GainCalculatorObjects::calculate<float>, xsimd ISA {ref.extent_isa()}"},
