@@ -166,6 +166,22 @@ int earb200_objects_calculate_device(earb200_objects *calc, int64_t n,
                                      const earb200_objects_soa *d_in, int out_is_double,
                                      void *d_direct, void *d_diffuse,
                                      int32_t *d_region_idx, void *stream);
+/* earb200_objects_calculate_device for callers that cannot call cudaMalloc (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid it).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, same results, same kernels, but the
+ * per-call scratch is a file-scope device array (csrc/objects_static.cu, 2,474,240 bytes, held by
+ * every GPU that loads the library until the process exits) instead of buffers the handle grows on
+ * demand, and all four kernels are queued on `stream` itself: the call makes no cudaMalloc / cudaFree
+ * and uses no allocating library routine.  n > EARB200_OBJECTS_STATIC_MAX fails with
+ * EARB200_INVALID_ARGUMENT.  Every call on a device shares the array (whatever the handle): calls
+ * that overlap on the GPU -- two streams, two threads -- race; order them on one stream or with
+ * events.  The first call on a device looks the array's address up (cudaGetSymbolAddress); make it
+ * outside stream capture. */
+#define EARB200_OBJECTS_STATIC_MAX 4096
+int earb200_objects_calculate_device_static(earb200_objects *calc, int64_t n,
+                                            const earb200_objects_soa *d_in, int out_is_double,
+                                            void *d_direct, void *d_diffuse,
+                                            int32_t *d_region_idx, void *stream);
 /* OPT-IN extensions beyond libear (PARITY UNPINNED).  libear 0.9 rejects objectDivergence and
  * channelLock with ear::not_implemented (gain_calculator_objects.cpp:37-43; its tests require the
  * throws) and so does this library -- unless the caller switches them on here.  The arithmetic

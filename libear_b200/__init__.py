@@ -284,6 +284,17 @@ class GainCalculatorObjects:
                                                    _ptr(d_direct), _ptr(d_diffuse), _ptr(d_regions),
                                                    C.c_void_p(int(stream))))
 
+    STATIC_MAX = 4096  # EARB200_OBJECTS_STATIC_MAX
+
+    def calculate_device_static(self, n, d_soa, d_direct, d_diffuse, d_regions=None, out_is_double=False,
+                                stream=0):
+        """calculate_device without any allocation (scratch in a file-scope device array that every
+        call on the device shares): n <= STATIC_MAX; calls that overlap on the GPU race."""
+        soa = _ObjectsSoA(*[int(p) for p in d_soa], None)
+        _chk(_lib.earb200_objects_calculate_device_static(self.h, C.c_int64(n), C.byref(soa), int(out_is_double),
+                                                          _ptr(d_direct), _ptr(d_diffuse), _ptr(d_regions),
+                                                          C.c_void_p(int(stream))))
+
     def enable_extensions(self, divergence=False, channel_lock=False):
         """OPT-IN features beyond libear (parity unpinned; libear throws not_implemented for both)."""
         _chk(_lib.earb200_objects_enable_extensions(self.h, C.c_uint32(int(divergence) | 2 * int(channel_lock))))

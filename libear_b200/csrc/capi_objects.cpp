@@ -986,4 +986,71 @@ int earb200_objects_extent_host(earb200_objects *calc, int64_t n, const double *
   });
 }
 
+// No counterpart in libear: earb200_objects_calculate_device without any allocation, for callers
+// that cannot call cudaMalloc.  The per-call scratch is the file-scope device array of
+// objects_static.cu (shared by every call on the device), carved up here; the four kernels are the
+// ones of objects_run_chunk, queued in line on the caller's stream.
+int earb200_objects_calculate_device_static(earb200_objects *calc, int64_t n, const earb200_objects_soa *d_in,
+                                            int out_is_double, void *d_direct, void *d_diffuse,
+                                            int32_t *d_region_idx, void *stream) {
+  return guarded([&] {
+    if (!calc || !d_in) throw Error(INVALID_ARGUMENT, "null argument");
+    if (n < 0) throw Error(INVALID_ARGUMENT, "negative batch size");
+    if (n > EARB_OBJECTS_STATIC_MAX)
+      throw Error(INVALID_ARGUMENT, "batch of " + std::to_string(n) + " objects exceeds the static scratch of " +
+                                        "earb200_objects_calculate_device_static (EARB200_OBJECTS_STATIC_MAX = " +
+                                        std::to_string(EARB_OBJECTS_STATIC_MAX) +
+                                        " objects per call); split the batch or use earb200_objects_calculate_device");
+    if (n == 0) return;
+    if (!d_direct || !d_diffuse) throw Error(INVALID_ARGUMENT, "null output buffer");
+    if (!d_in->azimuth || !d_in->elevation || !d_in->distance || !d_in->width || !d_in->height || !d_in->depth ||
+        !d_in->gain || !d_in->diffuse)
+      throw Error(INVALID_ARGUMENT, "null metadata field (all eight arrays are required)");
+    check_flags(n, d_in->flags);
+    earb200_objects &o = *calc;
+    use_device(o.device);
+    void *base = nullptr;
+    size_t bytes = 0;
+    EARB_CUDA(objects_static_scratch(o.device, &base, &bytes));
+    constexpr size_t N = EARB_OBJECTS_STATIC_MAX;
+    unsigned char *p = static_cast<unsigned char *>(base);
+    unsigned int *d_counters = reinterpret_cast<unsigned int *>(p);
+    p += 256;
+    ExtentPass *d_passes = reinterpret_cast<ExtentPass *>(p);
+    p += 2 * N * sizeof(ExtentPass);
+    ObjectAux *d_aux = reinterpret_cast<ObjectAux *>(p);
+    p += N * sizeof(ObjectAux);
+    float *d_results = reinterpret_cast<float *>(p);
+    p += 2 * N * EARB_MAX_SPK * sizeof(float);
+    double *d_point_gains = reinterpret_cast<double *>(p);
+    p += N * EARB_MAX_SPK * sizeof(double);
+    int32_t *d_point_list = reinterpret_cast<int32_t *>(p);
+    p += N * sizeof(int32_t);
+    if ((size_t)(p - static_cast<unsigned char *>(base)) != bytes) throw Error(INTERNAL_ERROR, "static scratch layout");
+
+    cudaStream_t s = (cudaStream_t)stream;
+    ObjectsSoA c{d_in->azimuth, d_in->elevation, d_in->distance, d_in->width, d_in->height,
+                 d_in->depth,   d_in->gain,      d_in->diffuse,  nullptr};
+    // the array keeps the previous call's contents: the two counters must start at zero
+    EARB_CUDA(cudaMemsetAsync(d_counters, 0, 2 * sizeof(unsigned int), s));
+    launch_objects_prelude(n, c, d_passes, d_aux, d_counters, d_point_list, d_region_idx != nullptr, s);
+    if (o.use_cells)
+      launch_extent_cell(o.n_cells, o.grid.n_spk, o.d_cell_stream.ptr, o.d_cell_sums.ptr, o.d_cell_centres.ptr,
+                         o.d_cell_points.ptr, d_counters, d_passes, d_results, o.n_sms, s);
+    else
+      launch_extent_core_tc(o.grid, o.d_grid_points.ptr, o.d_grid_bimage.ptr, d_counters, d_passes, d_results,
+                            o.n_sms, s);
+    if (out_is_double)
+      launch_objects_epilogue<double>(o.panner.d_tables, o.grid.n_spk, n, c, d_passes, d_aux, d_results,
+                                      d_point_gains, d_counters, d_point_list, o.n_sms, o.n_out, o.d_out_index.ptr,
+                                      (double *)d_direct, (double *)d_diffuse, d_region_idx, s);
+    else
+      launch_objects_epilogue<float>(o.panner.d_tables, o.grid.n_spk, n, c, d_passes, d_aux, d_results,
+                                     d_point_gains, d_counters, d_point_list, o.n_sms, o.n_out, o.d_out_index.ptr,
+                                     (float *)d_direct, (float *)d_diffuse, d_region_idx, s);
+    o.launches += 4;
+    EARB_CUDA(cudaGetLastError());
+  });
+}
+
 }  // extern "C"

@@ -52,6 +52,15 @@ namespace earb {
   void launch_objects_prelude(long n, const ObjectsSoA &in, ExtentPass *d_passes, ObjectAux *d_aux,
                               unsigned int *d_counters, int32_t *d_point_list, bool all_points,
                               cudaStream_t stream);
+  // scratch of earb200_objects_calculate_device_static (objects_static.cu): a file-scope device array,
+  // no cudaMalloc.  Layout: [counters, 256 B][passes 2N][aux N][results 2N x 24][point gains N x 24]
+  // [point list N], N = EARB_OBJECTS_STATIC_MAX objects per call.
+#define EARB_OBJECTS_STATIC_MAX 4096
+#define EARB_OBJECTS_STATIC_BYTES \
+  (256 + EARB_OBJECTS_STATIC_MAX * (2 * 96 + 24 + 2 * EARB_MAX_SPK * 4 + EARB_MAX_SPK * 8 + 4))
+  static_assert(sizeof(ExtentPass) == 96 && sizeof(ObjectAux) == 24, "static scratch layout");
+  // device address of that array on `device` (which must be current); looked up once per device
+  cudaError_t objects_static_scratch(int device, void **ptr, size_t *bytes);
 #define EXTENT_TC_STAGE_POINTS 64
   // tcgen05 extent core (extent_tc_kernels.cu): thread-per-pass weights feeding 3xTF32 UMMAs
   size_t extent_tc_smem_bytes(const ExtentGrid &grid);
