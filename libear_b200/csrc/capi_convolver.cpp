@@ -60,7 +60,16 @@ struct earb200_convolver {
   std::vector<float> filt_host;      // [n_filters][nb][B+1][2]
   bool filt_dirty = false;
   DeviceBuffer<float> d_filt, d_tw2, d_tw_fast;
-  bool use_fast = false;  // B = 512, one partition (EARB200_CONV_PATH=generic turns it off)
+  bool use_fast = false;  // B * nb <= 512 taps (EARB200_CONV_PATH=generic turns it off)
+  // fast path with B != 512: the whole filter as one 512-tap partition (1024-point spectrum, 513
+  // bins) and its taps (for the carried tail), per filter
+  std::vector<float> filt_fast_host, taps_host;
+  DeviceBuffer<float> d_filt_fast, d_taps;
+  // B != 512: the carried last_tail was made with a filter that set_filter has replaced since; the
+  // next block must run on the generic kernel (which adds the carried tail) before the fast one,
+  // whose start-of-call overlap is recomputed with the CURRENT filter, may take over
+  bool tail_stale = false;
+  bool force_generic = false;  // set around the head of a split call
   DeviceBuffer<float> d_hist[2], d_tail[2];
   int cur = 0;  // which of the ping-pong state buffers is current
   DeviceBuffer<short> d_ftab;
@@ -87,22 +96,48 @@ bool earb_conv_process_device(earb200_convolver &h, int64_t K, const float *d_in
     // per-partition filter tables).  A long call that starts with a change in flight is therefore cut
     // in two: the head on the generic kernel, the rest -- uniform again -- on the fast one, instead of
     // the whole call at a tenth of the speed.  (Not with a fused add: the caller falls back as a whole.)
-    if (h.use_fast && d_in && !add && K > (int64_t)nb + 1) {
+    // The same cut serves the other reasons a block cannot go to the fast kernel: with B != 512 it
+    // works on super-blocks of q = 512 / B blocks (the remainder goes first), and after set_filter
+    // the first block must add the tail the OLD filter left (tail_stale).
+    const int64_t q = h.use_fast ? 512 / h.B : 1;
+    int64_t head = 0;
+    if (h.use_fast && d_in && !h.force_generic) {
       bool uniform = true;
-      for (const ChannelQueue &q : h.chan) uniform = uniform && q.uniform();
-      if (!uniform) {
-        const int64_t head = (int64_t)nb + 1;
-        earb_conv_process_device(h, head, d_in, in_stride, d_out, out_stride, stream, nullptr, 0, 0, nullptr);
+      for (const ChannelQueue &cq : h.chan) uniform = uniform && cq.uniform();
+      if (!uniform)
+        head = (int64_t)nb + 1;
+      else if (h.B != 512 && h.tail_stale)
+        head = 1;
+      if (head < K) head += (K - head) % q;
+      head = std::min(head, K);
+      if (head > 0 && head < K && !add) {
+        h.force_generic = true;
+        try {
+          earb_conv_process_device(h, head, d_in, in_stride, d_out, out_stride, stream, nullptr, 0, 0, nullptr);
+        } catch (...) {
+          h.force_generic = false;
+          throw;
+        }
+        h.force_generic = false;
         earb_conv_process_device(h, K - head, d_in + head * h.B, in_stride, d_out + head * h.B, out_stride, stream,
                                  nullptr, 0, 0, nullptr);
         return false;
       }
     }
+    const bool fast_ok = h.use_fast && d_in && !h.force_generic && head == 0;
     if (h.filt_dirty) {
       h.d_filt.reserve(std::max<size_t>(h.filt_host.size(), 2));
       if (!h.filt_host.empty())
         EARB_CUDA(cudaMemcpyAsync(h.d_filt.ptr, h.filt_host.data(), sizeof(float) * h.filt_host.size(),
                                   cudaMemcpyHostToDevice, stream));
+      if (!h.filt_fast_host.empty()) {
+        h.d_filt_fast.reserve(h.filt_fast_host.size());
+        h.d_taps.reserve(h.taps_host.size());
+        EARB_CUDA(cudaMemcpyAsync(h.d_filt_fast.ptr, h.filt_fast_host.data(), sizeof(float) * h.filt_fast_host.size(),
+                                  cudaMemcpyHostToDevice, stream));
+        EARB_CUDA(cudaMemcpyAsync(h.d_taps.ptr, h.taps_host.data(), sizeof(float) * h.taps_host.size(),
+                                  cudaMemcpyHostToDevice, stream));
+      }
       h.filt_dirty = false;
     }
 
@@ -185,15 +220,22 @@ bool earb_conv_process_device(earb200_convolver &h, int64_t K, const float *d_in
     L.faded = h.d_faded.ptr;
     L.tw2 = h.d_tw2.ptr;
     h.timer.start(stream);
-    if (h.use_fast && Kg == 0 && d_in) {
+    if (fast_ok && Kg == 0) {
       if (add) {
         L.add = add, L.add_stride = (long)add_stride, L.add_delay = (long)add_delay, L.add_mem = add_mem;
         fused = true;
       }
+      L.filt_fast = h.d_filt_fast.ptr;
+      L.taps = h.d_taps.ptr;
       launch_convolver_fast(L, h.d_uniform.ptr, h.d_tw_fast.ptr, h.n_sms, stream);
       launch_conv_history(L, stream);
+      if (h.B != 512) {
+        launch_conv_generic_tail(L, h.d_uniform.ptr, stream);
+        h.launches++;
+      }
     } else {
       launch_convolver(L, stream);
+      h.tail_stale = false;  // the block(s) just processed left a tail made with the current filters
     }
     h.timer.stop(stream);
     EARB_CUDA(cudaGetLastError());
@@ -304,6 +346,23 @@ int earb200_convolver_add_filter(earb200_convolver *conv, int64_t n_taps, const 
         h.filt_host[base + ((size_t)p * (B + 1) + k) * 2 + 1] = (float)td[k].imag();
       }
     }
+    if (h.use_fast && h.B != 512) {
+      // the same taps as one partition of 512 (truncated to nb * B like the partitions above)
+      const size_t L = (size_t)h.nb * B, kept = std::min<size_t>((size_t)n_taps, L);
+      const size_t tbase = h.taps_host.size(), fbase = h.filt_fast_host.size();
+      h.taps_host.resize(tbase + L, 0.0f);
+      std::vector<std::complex<double>> td(1024);
+      for (size_t n = 0; n < kept; n++) {
+        h.taps_host[tbase + n] = taps[n];
+        td[n] = (double)taps[n];
+      }
+      fft_double(td);
+      h.filt_fast_host.resize(fbase + 2 * 513);
+      for (size_t k = 0; k <= 512; k++) {
+        h.filt_fast_host[fbase + 2 * k] = (float)td[k].real();
+        h.filt_fast_host[fbase + 2 * k + 1] = (float)td[k].imag();
+      }
+    }
     h.filter_blocks.push_back(parts);
     h.filt_dirty = true;
     *filter_id = (int)h.filter_blocks.size() - 1;
@@ -326,6 +385,7 @@ int earb200_convolver_set_filter(earb200_convolver *conv, int channel, int filte
     for (int c = 0; c < conv->C; c++)
       if (channel < 0 || c == channel)
         for (int &e : conv->chan[c].queue) e = f;  // ref :78-83
+    conv->tail_stale = true;
   });
 }
 

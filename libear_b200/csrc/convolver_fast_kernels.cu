@@ -1,5 +1,11 @@
-// K4 fast path: single-partition (num_blocks == 1) convolver bank with B = 512, no filter change
-// in flight -- the decorrelator case of the Objects signal flow (BASELINE config 4).
+// K4 fast path: convolver bank whose filters have at most 512 taps (B * num_blocks <= 512), no filter
+// change in flight -- the decorrelator case of the Objects signal flow (BASELINE config 4: B = 512,
+// one partition) and every finer partitioning of the same length (256 x 2, 128 x 4, 64 x 8 ...).
+// With a constant filter a uniformly partitioned convolver IS the linear convolution with the whole
+// filter, whatever the partition size, so those shapes run as ONE 512-tap partition over
+// super-blocks of 512 samples; what they carry between calls stays in libear's format (the last
+// num_blocks input blocks and last_tail of B samples): the start-of-call overlap is recomputed
+// from the input history, the tail for the next call by launch_conv_generic_tail.
 //
 // Same arithmetic as BlockConvolver::process (ref src/dsp/block_convolver_impl.cpp:143-237):
 // zero-pad to 2B, transform, multiply by the filter spectrum, transform back, overlap-add the
@@ -220,10 +226,12 @@ namespace earb {
       long in_stride;
       float *out;
       long out_stride;
-      const float *hist;      // [C][B] the input block before the call
-      const float *tail;      // [C][B] unnormalised tail before the call
-      float *tail_new;        // [C][B]
-      const float2 *filt;     // [n_filters][B + 1] (num_blocks == 1)
+      const float *hist;      // [C][hist_len] the input samples before the call (hist_len <= 512)
+      int hist_len;
+      int carried_tail;       // 1 (B = 512): overlap of the first block = tail; 0: recomputed from hist
+      const float *tail;      // [C][512] unnormalised tail before the call (carried_tail only)
+      float *tail_new;        // [C][512] (carried_tail only)
+      const float2 *filt;     // [n_filters][513]: 1024-point spectrum of the whole filter
       const int *filter_of;   // [C] filter id per channel (-1: none)
       const float2 *tw;       // [32][32]: tw[k1][b] = exp(-2 pi i b k1 / 1024)
       const float *add;       // nullable: out += delay(add)  (ConvLaunch::add)
@@ -322,14 +330,20 @@ namespace earb {
 
       cx v[32];
       float tail[16];
-      if (p0 == 0) {
+      if (p0 == 0 && a.carried_tail) {
 #pragma unroll
         for (int r = 0; r < 16; r++) tail[r] = a.tail[(size_t)c * kFastB + lane + 32 * r] * norm;
       } else {
-        // halo: the block before the run as the imaginary part of a pair
-        const float *xb = x + (size_t)(2 * p0 - 1) * kFastB;
+        // halo: the 512 samples before the run as the imaginary part of a pair -- input of this call,
+        // or (first run, B != 512) the input history, which is all a filter of hist_len taps reaches
+        const float *xb = p0 == 0 ? a.hist + (size_t)c * a.hist_len - (kFastB - a.hist_len)
+                                  : x + (size_t)(2 * p0 - 1) * kFastB;
+        const int first = p0 == 0 ? kFastB - a.hist_len : 0;
 #pragma unroll
-        for (int r = 0; r < 16; r++) v[br5(r)] = mk(0.0f, __ldg(xb + lane + 32 * r));
+        for (int r = 0; r < 16; r++) {
+          const int t = lane + 32 * r;
+          v[br5(r)] = mk(0.0f, t >= first ? __ldg(xb + t) : 0.0f);
+        }
         convolve_pair(v, tile, tw_s, twi_s, H_s, lane);
 #pragma unroll
         for (int r = 0; r < 16; r++) tail[r] = im(v[r + 16]);
@@ -392,7 +406,7 @@ namespace earb {
           }
         }
       }
-      if (p1 == a.n_pairs) {
+      if (p1 == a.n_pairs && a.carried_tail) {
 #pragma unroll
         for (int r = 0; r < 16; r++) a.tail_new[(size_t)c * kFastB + lane + 32 * r] = tail[r] * (float)(2 * kFastB);
       }
@@ -411,14 +425,14 @@ namespace earb {
       }
   }
 
-  bool conv_fast_supported(int B, int nb) { return B == kFastB && nb == 1; }
+  bool conv_fast_supported(int B, int nb) { return B >= 16 && B * nb <= kFastB && kFastB % B == 0; }
 
   void launch_convolver_fast(const ConvLaunch &L, const int *d_filter_of, const float *d_tw_fast, int n_sms,
                              cudaStream_t stream) {
     if (L.K <= 0) return;
     FastArgs a;
-    a.K = L.K;
-    a.n_pairs = (L.K + 1) / 2;
+    a.K = L.K * L.B / kFastB;  // super-blocks of 512 samples (the caller keeps K * B a multiple of 512)
+    a.n_pairs = (a.K + 1) / 2;
     // run length: amortise the one-block halo, keep a few waves of warps in flight
     int run = 32;
     while (run > 4 && (a.n_pairs + run - 1) / run * L.C < 16L * kWarps * n_sms) run /= 2;
@@ -428,9 +442,11 @@ namespace earb {
     a.out = L.out;
     a.out_stride = L.out_stride;
     a.hist = L.hist;
+    a.hist_len = L.B * L.nb;
+    a.carried_tail = L.B == kFastB;
     a.tail = L.tail;
     a.tail_new = L.tail_new;
-    a.filt = reinterpret_cast<const float2 *>(L.filt);
+    a.filt = reinterpret_cast<const float2 *>(a.carried_tail ? L.filt : L.filt_fast);
     a.filter_of = d_filter_of;
     a.tw = reinterpret_cast<const float2 *>(d_tw_fast);
     a.add = L.add;

@@ -325,7 +325,37 @@ namespace earb {
         hist_new[(size_t)c * total + idx] = v;
       }
     }
+    // libear's last_tail after the last block of a call, from the time-domain state: with a constant
+    // filter h (nb partitions of B taps) and the last nb input blocks x_{K-1-i},
+    //   tail[n] = sum_i (x_{K-1-i} * h_i)[B + n] = sum_i sum_{m > n} x_{K-1-i}[m] h[i B + B + n - m]
+    // (the second halves of the 2B-point products of block K-1; ref block_convolver_impl.cpp:214-236),
+    // unnormalised like the generic kernel's (x 2B).  One thread per (channel, n), double accumulator.
+    __global__ void conv_generic_tail_kernel(int B, int nb, const float *__restrict__ hist_new,
+                                             const float *__restrict__ taps, const int *__restrict__ filter_of,
+                                             float *__restrict__ tail_new) {
+      const int c = blockIdx.y;
+      const int n = blockIdx.x * blockDim.x + threadIdx.x;
+      if (n >= B) return;
+      const int f = filter_of[c];
+      double acc = 0.0;
+      if (f >= 0) {
+        const float *h = taps + (size_t)f * nb * B;
+        const float *x = hist_new + (size_t)c * nb * B;
+        for (int i = 0; i < nb; i++) {
+          const float *xb = x + (size_t)(nb - 1 - i) * B;  // block K-1-i (history is oldest first)
+          const float *hb = h + (size_t)i * B + B + n;     // hb[-m] = h[i B + B + n - m]
+          for (int m = n + 1; m < B; m++) acc += (double)xb[m] * (double)hb[-m];
+        }
+      }
+      tail_new[(size_t)c * B + n] = (float)(acc * (double)(2 * B));
+    }
   }  // namespace
+
+  void launch_conv_generic_tail(const ConvLaunch &L, const int *d_filter_of, cudaStream_t stream) {
+    const int threads = std::min(L.B, 128);
+    dim3 grid((unsigned)((L.B + threads - 1) / threads), (unsigned)L.C);
+    conv_generic_tail_kernel<<<grid, threads, 0, stream>>>(L.B, L.nb, L.hist_new, L.taps, d_filter_of, L.tail_new);
+  }
 
   size_t conv_smem_bytes(int B, int nb) {
     return sizeof(float2) * ((size_t)2 * B + (B + 2) + (size_t)nb * 2 * (B + 2)) + sizeof(float) * B;

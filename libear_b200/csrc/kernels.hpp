@@ -226,17 +226,27 @@ namespace earb {
     const float *add = nullptr;
     long add_stride = 0, add_delay = 0;
     const float *add_mem = nullptr;
+    // fast path with B * nb <= 512 other than one partition of 512: the whole filter as ONE 512-tap
+    // partition -- filt_fast [n_filters][513] complex (1024-point spectrum of the nb * B taps), and
+    // the taps themselves [n_filters][nb * B] for the carried tail (launch_conv_generic_tail)
+    const float *filt_fast = nullptr;
+    const float *taps = nullptr;
   };
   size_t conv_smem_bytes(int B, int nb);
   void launch_convolver(const ConvLaunch &L, cudaStream_t stream);
   void launch_conv_history(const ConvLaunch &L, cudaStream_t stream);  // hist -> hist_new only
-  // fast path (convolver_fast_kernels.cu): B = 512, one partition, no filter change in flight,
-  // non-null input; warp-per-block-pair register FFTs.  d_filter_of: [C] filter id per channel.
+  // fast path (convolver_fast_kernels.cu): B * nb <= 512 taps, no filter change in flight, non-null
+  // input, K * B a multiple of 512; warp-per-pair-of-512-samples register FFTs.  d_filter_of: [C]
+  // filter id per channel.  With B != 512 the carried state must be consistent with the current
+  // filter (no set_filter since the last processed block) and launch_conv_generic_tail must follow.
   bool conv_fast_supported(int B, int nb);
   size_t conv_fast_tw_floats();
   void conv_fast_build_tw(float *tw);
   void launch_convolver_fast(const ConvLaunch &L, const int *d_filter_of, const float *d_tw_fast, int n_sms,
                              cudaStream_t stream);
+  // tail_new [C][B] (unnormalised, as the generic kernel carries it) from hist_new and the taps of
+  // each channel's filter: what libear's last_tail holds after the last block of the call
+  void launch_conv_generic_tail(const ConvLaunch &L, const int *d_filter_of, cudaStream_t stream);
 
   // batched 2B-point real FFTs (the FFT plug-in seam): in [batch][2B] -> out [batch][B+1] complex
   // and back (unnormalised); tw2 = exp(-2 pi i k / 2B), k in [0, 2B)

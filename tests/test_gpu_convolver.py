@@ -144,3 +144,44 @@ def test_fast_path_matches_generic_kernel(eb, monkeypatch):
     assert np.abs(outs[0][C - 1]).max() == 0.0
     direct = np.stack([np.convolve(x[c].astype(np.float64), filt[c].astype(np.float64))[:B * K] for c in range(C - 1)])
     assert peak_err(outs[0][:C - 1], direct) < 1e-6
+
+
+@pytest.mark.parametrize("B,nb", [(128, 4), (64, 8), (256, 2), (16, 32), (32, 5), (256, 1)])
+def test_fast_path_for_any_partitioning_up_to_512_taps(eb, ref, B, nb):
+    """B * num_blocks <= 512: the call runs on the fast kernel as ONE 512-tap partition over
+    super-blocks of 512 samples; libear's state (num_blocks input blocks, last_tail of B samples) is
+    what is carried, so calls may alternate with the generic kernel -- block counts that are not whole
+    super-blocks, filter changes (set: the old filter's tail is still due), crossfades, silence."""
+    rng = np.random.default_rng(100 * B + nb)
+    q = 512 // B
+    n_ch = 3
+    L = B * nb
+    f = [rng.normal(size=n).astype(np.float32) for n in (L, max(1, L // 2 + 3), 7, L)]
+    blk = lambda k: rng.normal(0, 0.25, size=n_ch * B * k).astype(np.float32)
+    script = [("set", 0), ("run", blk(4 * q)), ("run", blk(q)), ("run", blk(3 * q + 1)), ("run", blk(17 * q)),
+              ("set", 1), ("run", blk(6 * q)), ("run", blk(2 * q)), ("xfade", 2), ("run", blk(5 * q + nb + 2)),
+              ("run", blk(8 * q)), ("silence", 3), ("run", blk(2 * q)), ("set", None), ("run", blk(2 * q)),
+              ("set", 3), ("run", blk(1)), ("run", blk(9 * q)), ("xfade", None), ("run", blk(3 * q)),
+              ("set", 0), ("run", blk(40 * q + q // 2))]
+    out, exp = run_script(eb, ref, B, nb, f, script, n_channels=n_ch)
+    assert peak_err(out, exp) < 1e-6
+
+
+def test_fast_path_other_partitionings_match_generic_kernel(eb, monkeypatch):
+    rng = np.random.default_rng(6)
+    C, B, nb, K = 4, 128, 4, 4 * 130
+    x = rng.normal(0, 0.25, size=(C, B * K)).astype(np.float32)
+    filt = rng.normal(size=(C, 512)).astype(np.float32)
+    outs = []
+    for path in ("fast", "generic"):
+        monkeypatch.setenv("EARB200_CONV_PATH", path)
+        g = eb.BlockConvolver(B, C, nb)
+        for c in range(C - 1):          # the last channel has no filter: silence out
+            fid, _ = g.add_filter(filt[c, :512 - 100 * c])
+            g.set_filter(fid, channel=c)
+        outs.append(np.concatenate([g.process(x[:, :B * 200]), g.process(x[:, B * 200:])], axis=1))
+    assert peak_err(outs[0], outs[1]) < 1e-6
+    assert np.abs(outs[0][C - 1]).max() == 0.0
+    direct = np.stack([np.convolve(x[c].astype(np.float64), filt[c, :512 - 100 * c].astype(np.float64))[:B * K]
+                       for c in range(C - 1)])
+    assert peak_err(outs[0][:C - 1], direct) < 1e-6
