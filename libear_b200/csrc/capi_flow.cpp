@@ -8,6 +8,7 @@
 //
 // Everything between the object audio and the loudspeaker feeds stays in HBM: two render
 // launches and one convolver launch whose store adds the delayed direct bus.
+#include <cstdlib>
 #include <memory>
 #include <vector>
 
@@ -31,6 +32,13 @@ struct earb200_objects_renderer {
   }
 };
 
+// capi_render.cpp
+struct earb200_interp;
+void earb_interp_share_segmentation(earb200_interp &a, earb200_interp &b);
+void earb_interp_process_pair_device(earb200_interp &a, earb200_interp &b, int64_t block_start, int64_t nsamples,
+                                     const float *d_in, int64_t in_stride, float *d_out_a, float *d_out_b,
+                                     int64_t out_stride, cudaStream_t stream);
+
 namespace {
   void chk(int rc) {
     if (rc != EARB200_OK) throw Error((Status)rc, last_error());
@@ -45,8 +53,18 @@ namespace {
     const int64_t T = n_blocks * h.B;
     const size_t bus = (size_t)h.C * (size_t)T;
     float *dir = h.d_direct.reserve(bus), *dif = h.d_diffuse.reserve(bus);
-    chk(earb200_interp_process_device(h.direct, block_start, T, d_in, in_stride, dir, T, stream));
-    chk(earb200_interp_process_device(h.diffuse, block_start, T, d_in, in_stride, dif, T, stream));
+    // both renders on one launch: every input tile is read from HBM once (the second unit of a tile
+    // runs on the neighbouring SM at the same time and finds it in L2)
+    static const bool paired = [] {
+      const char *e = std::getenv("EARB200_FLOW_PAIRED");
+      return !e || std::atoi(e) != 0;
+    }();
+    if (paired) {
+      earb_interp_process_pair_device(*h.direct, *h.diffuse, block_start, T, d_in, in_stride, dir, dif, T, stream);
+    } else {
+      chk(earb200_interp_process_device(h.direct, block_start, T, d_in, in_stride, dir, T, stream));
+      chk(earb200_interp_process_device(h.diffuse, block_start, T, d_in, in_stride, dif, T, stream));
+    }
     // decorrelators + compensation delay + sum in one pass: the delayed direct bus joins in the
     // convolver's store
     chk(earb200_convolver_process_add_delayed_device(h.conv, h.delay, n_blocks, dif, T, dir, T, d_out, out_stride,
@@ -102,6 +120,7 @@ int earb200_objects_renderer_set_gains(earb200_objects_renderer *r, int64_t n_po
     if (!r || !sample_idx || !direct || !diffuse) throw Error(INVALID_ARGUMENT, "null argument");
     chk(earb200_interp_set_points(r->direct, n_points, sample_idx, direct));
     chk(earb200_interp_set_points(r->diffuse, n_points, sample_idx, diffuse));
+    earb_interp_share_segmentation(*r->direct, *r->diffuse);
   });
 }
 
@@ -112,6 +131,7 @@ int earb200_objects_renderer_set_gains_device(earb200_objects_renderer *r, int64
     if (!r || !sample_idx || !d_direct || !d_diffuse) throw Error(INVALID_ARGUMENT, "null argument");
     chk(earb200_interp_set_points_device(r->direct, n_points, sample_idx, d_direct, stream));
     chk(earb200_interp_set_points_device(r->diffuse, n_points, sample_idx, d_diffuse, stream));
+    earb_interp_share_segmentation(*r->direct, *r->diffuse);
   });
 }
 

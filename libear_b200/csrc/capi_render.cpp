@@ -218,6 +218,72 @@ namespace {
   }
 }  // namespace
 
+// ---- two interpolators over the same input in one launch (capi_flow.cpp: the direct and the
+// diffuse render of the Objects signal flow, ref docs/dsp.rst:40-71)
+//
+// A segment between two points with equal gain matrices is "constant" (constant_interp, ref
+// gain_interpolator.hpp:139-141); rendered as a ramp it gives the same samples, because the ramp's
+// slope term is then exactly zero.  Two interpolators with the same sample indices therefore share
+// one segmentation once a segment counts as constant only where it is for both.
+void earb_interp_share_segmentation(earb200_interp &a, earb200_interp &b) {
+  if (a.sample_idx != b.sample_idx) return;
+  for (size_t i = 0; i < a.same_as_prev.size(); i++)
+    a.same_as_prev[i] = b.same_as_prev[i] = (char)(a.same_as_prev[i] && b.same_as_prev[i]);
+  a.plans.clear();
+  b.plans.clear();
+}
+
+// process() of both: the aligned tiles of both on ONE launch of the tcgen05 kernel (RenderPair: the
+// second read of every input tile is served by L2), the ragged runs per interpolator.  Falls back
+// to two calls when the two do not share shape, segmentation or the tcgen05 path.
+void earb_interp_process_pair_device(earb200_interp &a, earb200_interp &b, int64_t block_start, int64_t nsamples,
+                                     const float *d_in, int64_t in_stride, float *d_out_a, float *d_out_b,
+                                     int64_t out_stride, cudaStream_t stream) {
+  const uintptr_t ia = reinterpret_cast<uintptr_t>(d_in), oa = reinterpret_cast<uintptr_t>(d_out_a),
+                  ob = reinterpret_cast<uintptr_t>(d_out_b);
+  const bool aligned = ia % 4 == 0 && oa % 4 == 0 && ob % 4 == 0 && in_stride % 4 == 0 && out_stride % 4 == 0 &&
+                       ((ia / 4) & 3) == ((oa / 4) & 3) && ((ia / 4) & 3) == ((ob / 4) & 3);
+  const bool pairable = a.use_tc && b.use_tc && a.N == b.N && a.M == b.M && a.device == b.device && !a.accumulate &&
+                        !b.accumulate && a.n_points == b.n_points && a.n_points > 0 && a.sorted && aligned &&
+                        nsamples > 0 && d_in && d_out_a && d_out_b && a.sample_idx == b.sample_idx &&
+                        a.same_as_prev == b.same_as_prev;
+  if (!pairable) {
+    process_device(a, block_start, nsamples, d_in, in_stride, d_out_a, out_stride, stream);
+    process_device(b, block_start, nsamples, d_in, in_stride, d_out_b, out_stride, stream);
+    return;
+  }
+  use_device(a.device);
+  const int align = (int)((ia / 4) & 3);
+  earb200_interp::Plan &pl = build_plan(a, block_start, nsamples, align, stream);
+  const long n_fast = pl.n_items[0] + pl.n_items[1];
+  a.timer.start(stream);
+  if (n_fast > 0) {
+    RenderPair pair;
+    pair.images2 = b.d_images.ptr;
+    pair.out2 = d_out_b;
+    if (!launch_render_tc(a.N, a.M, d_in, (long)in_stride, (long)nsamples, d_out_a, (long)out_stride, pl.d_items.ptr,
+                          n_fast, pl.d_segs.ptr, a.d_images.ptr, (long)a.n_points, a.n_sms, 0, RenderBus{}, stream,
+                          pair))
+      throw Error(INTERNAL_ERROR, "cuTensorMapEncodeTiled failed for the render input");
+    a.launches += (a.N + 255) / 256;
+  }
+  if (pl.n_items[2] + pl.n_items[3] > 0) {
+    // the ragged runs: the FFMA kernels, per interpolator, on the same item list
+    const RenderPlan slow{pl.d_items.ptr + n_fast, 0, 0, pl.n_items[2], pl.n_items[3], 0, a.n_sms, (long)nsamples,
+                          nullptr, 0, (long)a.n_points, RenderBus{}};
+    launch_render(a.N, a.M, d_in, (long)in_stride, d_out_a, (long)out_stride, slow, pl.d_segs.ptr, a.d_gains.ptr,
+                  stream);
+    launch_render(b.N, b.M, d_in, (long)in_stride, d_out_b, (long)out_stride, slow, pl.d_segs.ptr, b.d_gains.ptr,
+                  stream);
+    a.launches += (pl.n_items[2] > 0) + (pl.n_items[3] > 0);
+    b.launches += (pl.n_items[2] > 0) + (pl.n_items[3] > 0);
+  }
+  a.timer.stop(stream);
+  EARB_CUDA(cudaGetLastError());
+  if (!pl.used) EARB_CUDA(cudaEventCreateWithFlags(&pl.used, cudaEventDisableTiming));
+  EARB_CUDA(cudaEventRecord(pl.used, stream));
+}
+
 extern "C" {
 
 int earb200_interp_set_accumulate(earb200_interp *interp, int enable) {

@@ -145,6 +145,14 @@ namespace earb {
                // ranks store into DIFFERENT owners (all ranks walking the time axis in step would
                // all store into the one GPU that owns the current slice: 8-to-1 incast on its links)
   };
+  // A second interpolator riding the same launch of the tcgen05 kernel: same input, same tiles and
+  // segments, its own gain images and output rows (the direct and the diffuse render of the Objects
+  // signal flow).  Its work units follow the first one's of the same tile, on the neighbouring CTA
+  // at the same time, so the tile's input comes from HBM once and from L2 the second time.
+  struct RenderPair {
+    const float *images2 = nullptr;
+    float *out2 = nullptr;  // same row pitch as `out`
+  };
   struct RenderPlan {
     const RenderItem *d_items;  // [fast ramp | fast const | slow ramp | slow const]
     long n_fast_ramp, n_fast_const, n_slow_ramp, n_slow_const;
@@ -165,7 +173,8 @@ namespace earb {
   bool launch_render_tc(int N, int M, const float *in, long in_stride, long n_samples, float *out,
                         long out_stride, const RenderItem *d_items, long n_tiles,
                         const RenderSegment *d_segs, const float *d_images, long n_points, int n_sms,
-                        int accumulate, const RenderBus &bus, cudaStream_t stream);
+                        int accumulate, const RenderBus &bus, cudaStream_t stream,
+                        const RenderPair &pair = RenderPair());
   // per-point gain-matrix images for the tcgen05 kernel (TF32 hi/lo split in UMMA layout)
   size_t render_tc_image_floats(int N, int M);
   void launch_render_prepare_points(int N, int M, long n_points, const float *d_gains, float *d_images,

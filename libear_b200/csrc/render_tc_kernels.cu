@@ -220,7 +220,7 @@ namespace earb {
                                     const RenderItem *__restrict__ items, int n_tiles,
                                     const RenderSegment *__restrict__ segs,
                                     const float *__restrict__ images, int n_stages, int accumulate,
-                                    int n_groups, const RenderBus bus) {
+                                    int n_groups, const RenderBus bus, const RenderPair pair) {
       extern __shared__ __align__(128) unsigned char smem_raw[];
       constexpr int kEpiWarps = EPI;
       constexpr int kProducerWarp = kConvWarps + kEpiWarps, kMmaWarp = kProducerWarp + 1;
@@ -233,6 +233,9 @@ namespace earb {
       // are adjacent units, so they run on neighbouring CTAs at the same time and the second read
       // of the tile's input is served by L2
       const int n_units = n_tiles * n_groups;
+      // output groups per interpolator: with a second one riding along (RenderPair) the groups
+      // [gpi, 2 gpi) of a tile are its
+      const int gpi = pair.out2 ? n_groups >> 1 : n_groups;
       float *sB = reinterpret_cast<float *>(smem_raw);       // [2 tiles][8 groups][Kp/4][8][4]
       float *sx = sB + (size_t)kBBufs * 2 * Kp * NP;         // [n_stages][kCh][kTile]
       __shared__ __align__(8) uint64_t full[kMaxStages], empty[kMaxStages];
@@ -312,8 +315,10 @@ namespace earb {
             const int ab = L & 1;
             if (L >= 2) mbar_wait(&acc_full[ab], (uint32_t)(((L >> 1) - 1) & 1));
             const RenderSegment seg = segs[items[tile].seg];
-            const float *pa = images + ((size_t)seg.pa * n_groups + grp) * img,
-                        *pb = images + ((size_t)seg.pb * n_groups + grp) * img;
+            const bool second = grp >= gpi;
+            const int gl = second ? grp - gpi : grp;
+            const float *im = second ? pair.images2 : images;
+            const float *pa = im + ((size_t)seg.pa * gpi + gl) * img, *pb = im + ((size_t)seg.pb * gpi + gl) * img;
             float *dst = sB + (size_t)ab * 2 * Kp * NP;
             mbar_expect_tx(&b_full[ab], 4 * quarter);
             bulk_g2s(dst, pa, quarter, &b_full[ab]);
@@ -453,8 +458,10 @@ namespace earb {
           const RenderSegment seg = segs[item.seg];
           const bool ramp = seg.ramp != 0;
           constexpr int MO = NP / 2;               // output channels per work unit
-          const int Mg = min(MO, M - grp * MO);    // output channels of this group
-          float *const og = out + (long)grp * MO * out_stride;
+          const bool second = grp >= gpi;
+          const int gl = second ? grp - gpi : grp;
+          const int Mg = min(MO, M - gl * MO);     // output channels of this group
+          float *const og = (second ? pair.out2 : out) + (long)gl * MO * out_stride;
           const bool to_bus = bus.n_ranks > 0;
           // bus mode: owner and offset of the tile's first sample, once per tile in 32-bit arithmetic
           // (a 64-bit division per sample group doubled the epilogue's instruction count: the last
@@ -678,7 +685,7 @@ namespace earb {
   bool launch_render_tc(int N, int M, const float *in, long in_stride, long n_samples, float *out,
                         long out_stride, const RenderItem *d_items, long n_tiles,
                         const RenderSegment *d_segs, const float *d_images, long n_points, int n_sms,
-                        int accumulate, const RenderBus &bus, cudaStream_t stream) {
+                        int accumulate, const RenderBus &bus, cudaStream_t stream, const RenderPair &pair) {
     if (n_tiles <= 0) return true;
     EncodeTiledFn encode = encode_tiled();
     if (!encode) return false;
@@ -692,7 +699,9 @@ namespace earb {
                            (int)kSmemBudget);
     }
     const TcShape sh = tc_shape(N, M);
-    const unsigned grid = (unsigned)std::min<long>(n_tiles * sh.n_out_groups, n_sms > 0 ? n_sms : 148);
+    const int n_groups = sh.n_out_groups * (pair.out2 ? 2 : 1);
+    RenderPair gpair = pair;
+    const unsigned grid = (unsigned)std::min<long>(n_tiles * n_groups, n_sms > 0 ? n_sms : 148);
     for (int k0 = 0; k0 < N; k0 += sh.max_in) {
       const int Ng = std::min(sh.max_in, N - k0);
       // the input group as a [Ng channels][n_samples] float tensor with a row pitch of in_stride floats
@@ -712,16 +721,17 @@ namespace earb {
       if (sh.NP == 64)  // wide units: the read-out of 2 x 64 accumulator columns always wants eight warps
         render_tc_persistent_kernel<64, 8><<<grid, threads_for(8), smem_for(Ng, 64), stream>>>(
             map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 64), acc_mode,
-            sh.n_out_groups, gbus);
+            n_groups, gbus, gpair);
       else if (Ng <= 64)  // few input channels: the read-out sets the pace, eight epilogue warps
         render_tc_persistent_kernel<32, 8><<<grid, threads_for(8), smem_for(Ng, 32), stream>>>(
             map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 32), acc_mode,
-            sh.n_out_groups, gbus);
+            n_groups, gbus, gpair);
       else
         render_tc_persistent_kernel<32, 4><<<grid, threads_for(4), smem_for(Ng, 32), stream>>>(
             map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 32), acc_mode,
-            sh.n_out_groups, gbus);
+            n_groups, gbus, gpair);
       d_images += (size_t)n_points * sh.n_out_groups * padded_k(Ng) * sh.NP;
+      if (gpair.images2) gpair.images2 += (size_t)n_points * sh.n_out_groups * padded_k(Ng) * sh.NP;
     }
     return true;
   }
