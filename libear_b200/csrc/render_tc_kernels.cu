@@ -207,11 +207,20 @@ namespace earb {
     // epilogue of the tile before; keeping the two small cross terms out of the main accumulator is
     // what holds the 1e-6 bar -- accumulating all three products into one accumulator measured
     // 1.7e-6 of peak at N = 128).  Either way 256 columns, and the A ring takes the other 256.
-    constexpr int kAccRegion = 256;
-    constexpr int kColAP = kAccRegion;
+    // NP = 48 (17..24 outputs: 9+10+3's feeds): per M-tile [main 48 | corr 48], TWO tile buffers =
+    // 384 columns -- the MMAs of a tile run under the read-out of the tile before, which is what
+    // paces the NP = 64 form -- and an A ring of two buffers in the remaining 128.
     constexpr int kBBufs = 2;  // gain-matrix buffers in shared memory
-    constexpr int kABufs = 4;  // A-operand ring in TMEM (power of two)
-    static_assert(kColAP + kABufs * kMT * 2 * kCh <= kTmemColsP, "TMEM budget");
+    template <int NP>
+    struct TmemPlan {
+      static constexpr int kAccBufs = NP == 64 ? 1 : 2;           // accumulator tile buffers
+      static constexpr int kAccTile = kMT * 2 * NP;               // columns of one tile's accumulators
+      static constexpr int kColA = kAccBufs * kAccTile;           // first column of the A ring
+      static constexpr int kABufs = (kTmemColsP - kColA) / (kMT * 2 * kCh);  // A-operand ring (power of two)
+      static_assert(kABufs == 2 || kABufs == 4, "A ring");
+      static_assert(kColA + kABufs * kMT * 2 * kCh <= kTmemColsP, "TMEM budget");
+    };
+    constexpr int kMaxABufs = 4;
 
     template <int NP, int EPI>
     __global__ void __launch_bounds__(threads_for(EPI), 1)
@@ -222,6 +231,8 @@ namespace earb {
                                     const float *__restrict__ images, int n_stages, int accumulate,
                                     int n_groups, const RenderBus bus, const RenderPair pair) {
       extern __shared__ __align__(128) unsigned char smem_raw[];
+      constexpr int kAccBufs = TmemPlan<NP>::kAccBufs, kAccTile = TmemPlan<NP>::kAccTile;
+      constexpr int kColAP = TmemPlan<NP>::kColA, kABufs = TmemPlan<NP>::kABufs;
       constexpr int kEpiWarps = EPI;
       constexpr int kProducerWarp = kConvWarps + kEpiWarps, kMmaWarp = kProducerWarp + 1;
       constexpr int kBLoadWarp = kMmaWarp + kMT;  // streams the gain-matrix images
@@ -239,7 +250,7 @@ namespace earb {
       float *sB = reinterpret_cast<float *>(smem_raw);       // [2 tiles][8 groups][Kp/4][8][4]
       float *sx = sB + (size_t)kBBufs * 2 * Kp * NP;         // [n_stages][kCh][kTile]
       __shared__ __align__(8) uint64_t full[kMaxStages], empty[kMaxStages];
-      __shared__ __align__(8) uint64_t a_full[kABufs], a_free[kABufs], b_full[kBBufs], acc_full[2], acc_free[2];
+      __shared__ __align__(8) uint64_t a_full[kMaxABufs], a_free[kMaxABufs], b_full[kBBufs], acc_full[2], acc_free[2];
       __shared__ uint32_t tmem_base_s;
 
       const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -338,8 +349,9 @@ namespace earb {
         // instruction descriptors: D f32, A/B tf32, both K-major, M = 128, N = 64 / 32
         const uint32_t idesc_base = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(128 >> 4) << 24);
         const uint32_t idesc64 = idesc_base | ((uint32_t)(64 >> 3) << 17);
+        const uint32_t idescW = idesc_base | ((uint32_t)(NP >> 3) << 17);  // wide units: N = NP
+        const uint32_t idescW2 = idesc_base | ((uint32_t)((2 * NP) >> 3) << 17);
         const uint32_t idesc32 = idesc_base | ((uint32_t)(32 >> 3) << 17);
-        const uint32_t b_lo_step = (uint32_t)((Kp * NP * sizeof(float)) >> 4);  // hi rows -> lo rows
         const uint64_t bdesc_base = b_desc(smem_u32(sB), Kp);
         const uint32_t b_tile_step = (uint32_t)((2 * Kp * NP * sizeof(float)) >> 4);  // next B buffer
         int g = 0, L = 0;
@@ -350,9 +362,9 @@ namespace earb {
           // B of this tile: rows 0..31 = [a | b] hi, 32..63 = [a | b] lo
           const int bb = L & 1;
           uint64_t bd = bdesc_base + (uint64_t)(bb * b_tile_step);
-          const uint32_t acc = NP == 32 ? tm + ab * 128 + j * 64 : tm + j * 128;
+          const uint32_t acc = tm + (kAccBufs == 2 ? ab * kAccTile : 0) + j * 2 * NP;
           mbar_wait(&b_full[bb], (uint32_t)((L >> 1) & 1));
-          if (NP == 32) {
+          if (kAccBufs == 2) {
             if (L >= 2) mbar_wait(&acc_free[ab], (uint32_t)(((L >> 1) - 1) & 1));  // tile L - 2 read out
           } else {
             if (L >= 1) mbar_wait(&acc_free[(L - 1) & 1], (uint32_t)(((L - 1) >> 1) & 1));  // tile L - 1
@@ -372,10 +384,12 @@ namespace earb {
                   umma_tf32_ts(acc, a_hi + ks * 8, bd, idesc64, (it | ks) != 0);
                   umma_tf32_ts(acc + 32, a_hi + kCh + ks * 8, bd, idesc32, 1);
                 } else {
-                  // wide: main (64 columns) (+)= x_hi * g_hi;  corr (+)= x_hi * g_lo + x_lo * g_hi
-                  umma_tf32_ts(acc, a_hi + ks * 8, bd, idesc64, (it | ks) != 0);
-                  umma_tf32_ts(acc + 64, a_hi + ks * 8, bd + b_lo_step, idesc64, (it | ks) != 0);
-                  umma_tf32_ts(acc + 64, a_hi + kCh + ks * 8, bd, idesc64, 1);
+                  // wide: [main | corr] (+)= x_hi * [g_hi | g_lo] in ONE UMMA of N = 2 NP (the lo rows
+                  // follow the hi rows in the B image, the correction columns the main ones in TMEM),
+                  // then corr += x_lo * g_hi.  Two instructions per K step instead of three: the issuing
+                  // thread, not the tensor pipe, paces this kernel.
+                  umma_tf32_ts(acc, a_hi + ks * 8, bd, idescW2, (it | ks) != 0);
+                  umma_tf32_ts(acc + NP, a_hi + kCh + ks * 8, bd, idescW, 1);
                 }
                 bd += (2 * 128) >> 4;
               }
@@ -486,7 +500,7 @@ namespace earb {
           }
           mbar_wait(&acc_full[ab], (uint32_t)((L >> 1) & 1));
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const uint32_t acc = NP == 32 ? lane_base + ab * 128 : lane_base;
+          const uint32_t acc = lane_base + (kAccBufs == 2 ? ab * kAccTile : 0);
 #pragma unroll
           for (int jj = 0; jj < kJ; jj++) {
             const int j = j0 + jj;
@@ -522,7 +536,7 @@ namespace earb {
               // wide: main and correction accumulators, each [32 x g_a | 32 x g_b], read out 8 output
               // channels at a time (32 live values: the 96-register form of the kernel has room for it)
 #pragma unroll
-              for (int h = 0; h < 4; h++) {
+              for (int h = 0; h < NP / 16; h++) {
                 if (h * 8 < Mg) {
                   float mix[8];
                   if (accumulate) {
@@ -531,8 +545,8 @@ namespace earb {
                       mix[m] = (h * 8 + m < Mg) ? __ldcs(og + (long)(h * 8 + m) * out_stride + t) : 0.0f;
                   }
                   float sa[8], sb[8], ca[8], cb[8];
-                  tmem_ld8x4(acc + j * 128 + h * 8, acc + j * 128 + 32 + h * 8, acc + j * 128 + 64 + h * 8,
-                             acc + j * 128 + 96 + h * 8, sa, sb, ca, cb);
+                  tmem_ld8x4(acc + j * 2 * NP + h * 8, acc + j * 2 * NP + NP / 2 + h * 8, acc + j * 2 * NP + NP + h * 8,
+                             acc + j * 2 * NP + NP + NP / 2 + h * 8, sa, sb, ca, cb);
 #pragma unroll
                   for (int m = 0; m < 8; m++) {
                     if (h * 8 + m < Mg) {
@@ -608,8 +622,9 @@ namespace earb {
     TcShape tc_shape(int N, int M) {
       static const int wide = [] {
         const char *e = std::getenv("EARB200_RENDER_WIDE");
-        return e ? std::atoi(e) : 1;
+        return e ? std::atoi(e) : 2;
       }();
+      if (M > 16 && M <= 24 && wide > 1) return {48, 128, 1};
       if (M > 16 && wide > 0) return {64, 128, (M + 31) / 32};
       return {32, 256, (M + 15) / 16};
     }
@@ -697,6 +712,8 @@ namespace earb {
                            (int)kSmemBudget);
       cudaFuncSetAttribute(render_tc_persistent_kernel<64, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                            (int)kSmemBudget);
+      cudaFuncSetAttribute(render_tc_persistent_kernel<48, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)kSmemBudget);
     }
     const TcShape sh = tc_shape(N, M);
     const int n_groups = sh.n_out_groups * (pair.out2 ? 2 : 1);
@@ -718,7 +735,11 @@ namespace earb {
       // input groups accumulate into `out`; only the last one stores to the bus slots
       RenderBus gbus = bus;
       if (k0 + sh.max_in < N) gbus.n_ranks = 0;
-      if (sh.NP == 64)  // wide units: the read-out of 2 x 64 accumulator columns always wants eight warps
+      if (sh.NP == 48)
+        render_tc_persistent_kernel<48, 8><<<grid, threads_for(8), smem_for(Ng, 48), stream>>>(
+            map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 48), acc_mode,
+            n_groups, gbus, gpair);
+      else if (sh.NP == 64)  // wide units: the read-out of 2 x 64 accumulator columns always wants eight warps
         render_tc_persistent_kernel<64, 8><<<grid, threads_for(8), smem_for(Ng, 64), stream>>>(
             map, Ng, M, out, out_stride, d_items, (int)n_tiles, d_segs, d_images, stages_for(Ng, 64), acc_mode,
             n_groups, gbus, gpair);
