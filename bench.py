@@ -783,7 +783,8 @@ def run_ours(args):
         f_ms = max_over_ranks(f0.elapsed_time(f1)) / args.steps
         gpu_launches += fr.launch_count - fl0
         # one pass over the objects' audio and the feeds is the least any implementation moves;
-        # the pipeline as built reads the input twice and passes two 24-channel buses through HBM
+        # the pipeline as built reads the input once from HBM and once from L2 (both renders on one
+        # launch) and passes two 24-channel buses through HBM
         f_bytes = 4.0 * Tf * (Nf + Cf) + 2 * 4.0 * Nf * Cf * len(f_samples)
         flow_block = {
             "metric": "Objects signal flow Msamples/s (input object-samples)",
@@ -794,7 +795,8 @@ def run_ours(args):
                        "sharding": "objects replicated per GPU, no collective"},
             "roofline": {"bound": "hbm", "achieved": f_bytes / (f_ms * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
                          "frac": f_bytes / (f_ms * 1e-3) / 1e9 / hbm_peak, "traffic": None, "peak_source": peak_src,
-                         "kernel": "render_tc_persistent_kernel x2 + convolver_fast_kernel + delay_kernel",
+                         "kernel": "render_tc_persistent_kernel (direct + diffuse paired) + convolver_fast_kernel<add> "
+                                   "+ delay_advance_kernel",
                          "algorithmic_bytes_per_step": f_bytes,
                          "note": "whole pipeline against the bytes of a single fused pass"},
         }
