@@ -65,6 +65,11 @@ struct earb200_convolver {
   // bins) and its taps (for the carried tail), per filter
   std::vector<float> filt_fast_host, taps_host;
   DeviceBuffer<float> d_filt_fast, d_taps;
+  // fast path, long calls: the 2048-point spectrum of the whole filter (all 2,048 bins), per filter
+  // (EARB200_CONV_PATH=pair keeps long calls on the 1024-point kernel)
+  bool use_wide = false;
+  std::vector<float> filt_wide_host;
+  DeviceBuffer<float> d_filt_wide;
   // B != 512: the carried last_tail was made with a filter that set_filter has replaced since; the
   // next block must run on the generic kernel (which adds the carried tail) before the fast one,
   // whose start-of-call overlap is recomputed with the CURRENT filter, may take over
@@ -136,6 +141,11 @@ bool earb_conv_process_device(earb200_convolver &h, int64_t K, const float *d_in
         EARB_CUDA(cudaMemcpyAsync(h.d_filt_fast.ptr, h.filt_fast_host.data(), sizeof(float) * h.filt_fast_host.size(),
                                   cudaMemcpyHostToDevice, stream));
         EARB_CUDA(cudaMemcpyAsync(h.d_taps.ptr, h.taps_host.data(), sizeof(float) * h.taps_host.size(),
+                                  cudaMemcpyHostToDevice, stream));
+      }
+      if (!h.filt_wide_host.empty()) {
+        h.d_filt_wide.reserve(h.filt_wide_host.size());
+        EARB_CUDA(cudaMemcpyAsync(h.d_filt_wide.ptr, h.filt_wide_host.data(), sizeof(float) * h.filt_wide_host.size(),
                                   cudaMemcpyHostToDevice, stream));
       }
       h.filt_dirty = false;
@@ -227,6 +237,7 @@ bool earb_conv_process_device(earb200_convolver &h, int64_t K, const float *d_in
       }
       L.filt_fast = h.d_filt_fast.ptr;
       L.taps = h.d_taps.ptr;
+      L.filt_wide = h.use_wide ? h.d_filt_wide.ptr : nullptr;
       launch_convolver_fast(L, h.d_uniform.ptr, h.d_tw_fast.ptr, h.n_sms, stream);
       launch_conv_history(L, stream);
       if (h.B != 512) {
@@ -296,6 +307,7 @@ int earb200_convolver_create(int64_t block_size, int n_channels, int64_t num_blo
     }
     const char *path = std::getenv("EARB200_CONV_PATH");
     h->use_fast = conv_fast_supported(h->B, h->nb) && !(path && std::string(path) == "generic");
+    h->use_wide = h->use_fast && !(path && std::string(path) == "pair");
     if (h->use_fast) {
       std::vector<float> twf(conv_fast_tw_floats());
       conv_fast_build_tw(twf.data());
@@ -361,6 +373,18 @@ int earb200_convolver_add_filter(earb200_convolver *conv, int64_t n_taps, const 
       for (size_t k = 0; k <= 512; k++) {
         h.filt_fast_host[fbase + 2 * k] = (float)td[k].real();
         h.filt_fast_host[fbase + 2 * k + 1] = (float)td[k].imag();
+      }
+    }
+    if (h.use_wide) {
+      // the same taps (truncated to nb * B like the partitions above) as ONE 2048-point spectrum
+      const size_t kept = std::min<size_t>((size_t)n_taps, (size_t)h.nb * B), fbase = h.filt_wide_host.size();
+      std::vector<std::complex<double>> td(2048);
+      for (size_t n = 0; n < kept; n++) td[n] = (double)taps[n];
+      fft_double(td);
+      h.filt_wide_host.resize(fbase + 2 * 2048);
+      for (size_t k = 0; k < 2048; k++) {
+        h.filt_wide_host[fbase + 2 * k] = (float)td[k].real();
+        h.filt_wide_host[fbase + 2 * k + 1] = (float)td[k].imag();
       }
     }
     h.filter_blocks.push_back(parts);

@@ -233,7 +233,10 @@ namespace earb {
       float *tail_new;        // [C][512] (carried_tail only)
       const float2 *filt;     // [n_filters][513]: 1024-point spectrum of the whole filter
       const int *filter_of;   // [C] filter id per channel (-1: none)
-      const float2 *tw;       // [32][32]: tw[k1][b] = exp(-2 pi i b k1 / 1024)
+      const float2 *tw;       // [32][32]: tw[k1][b] = exp(-2 pi i b k1 / 1024), then (wide kernel)
+                              // [32][32]: exp(-2 pi i (lane + 32 r) / 2048) at [r][lane]
+      const float2 *filt_wide;  // wide kernel: [n_filters][2048], 2048-point spectrum of the whole filter
+      int run_sb;               // wide kernel: super-blocks of 512 samples per warp (a multiple of 6)
       const float *add;       // nullable: out += delay(add)  (ConvLaunch::add)
       long add_stride, add_delay;
       const float *add_mem;
@@ -245,9 +248,11 @@ namespace earb {
     // tw_s / H_s hold two consecutive slots per float4: [slot / 2][lane] = (slot, slot + 1);
     // twi_s pairs the slots the inverse needs together: [n1][lane] = (n1, n1 + 16).  H_s carries the
     // 1 / (2B) scale (a power of two: exact), so v comes back normalised.
+    // PRUNED = false: all 32 slots hold input (v[br5(a)] = z[lane + 32 a], a < 32).
+    template <bool PRUNED = true>
     __device__ __forceinline__ void convolve_pair(cx (&v)[32], cx *tile, const float4 *tw_s, const float4 *twi_s,
                                                   const float4 *H_s, int lane) {
-      dit32<false, true>(v);  // over a: v[k1] = A_lane[k1]
+      dit32<false, PRUNED>(v);  // over a: v[k1] = A_lane[k1]
 #pragma unroll
       for (int k1 = 0; k1 < 32; k1 += 2) {
         const float4 t = tw_s[(k1 >> 1) * 32 + lane];
@@ -411,9 +416,193 @@ namespace earb {
         for (int r = 0; r < 16; r++) a.tail_new[(size_t)c * kFastB + lane + 32 * r] = tail[r] * (float)(2 * kFastB);
       }
     }
+
+    // ---------------------------------------------------------------- long calls: 2048-point units
+    // With a constant 512-tap filter nothing ties the transform to 1,024 points: a 2,048-point
+    // transform carries blocks of 1,536 samples (1,536 + 511 <= 2,048) -- three quarters of the
+    // transform are signal instead of half.  A unit is 3,072 consecutive samples of a channel, the
+    // first 1,536 as real part and the second 1,536 as imaginary part of z; its transform is split
+    // by one radix-2 step (decimation in frequency) into two 1,024-point problems that run through
+    // the register transforms above:
+    //     even bins: s[n] = z[n] + z[n + 1024]                     * H[2k]     -> e[n]
+    //     odd bins:  d[n] = (z[n] - z[n + 1024]) exp(-2 pi i n / 2048) * H[2k + 1] -> o[n]
+    //     y[n] = e[n] + exp(+2 pi i n / 2048) o[n],   y[n + 1024] = e[n] - exp(+2 pi i n / 2048) o[n]
+    // (z[n + 1024] is zero for n >= 512).  y[n], y[n + 512], y[n + 1024] and y[n + 1536] of both
+    // blocks end in the same lane, so the overlap-add and the carried tail stay in registers as
+    // before.  Per output sample: 2 x 1,024-point transform pairs per 3,072 samples instead of one
+    // per 1,024 -- about 0.72 of the packed operations of the 1024-point kernel (which prunes its
+    // zero half) and two thirds of its shared-memory traffic.  The halo of a run and the super-blocks
+    // that do not fill a unit at the end of the channel go through the 1024-point pair code, with
+    // the even bins as its spectrum (they ARE the 1,024-point spectrum of the filter).
+#ifndef EARB_WIDE_WARPS
+#define EARB_WIDE_WARPS 12
+#endif
+    constexpr int kWideWarps = EARB_WIDE_WARPS;
+    constexpr int kUnitSb = 6;  // super-blocks of 512 samples per unit
+
+    template <bool ADD>
+    __global__ void __launch_bounds__(kWideWarps * 32, 1) convolver_wide_kernel(FastArgs a) {
+      extern __shared__ float4 fsm[];
+      float4 *tw_s = fsm;           // [16][32]: (tw[2j][lane], tw[2j + 1][lane])
+      float4 *twi_s = tw_s + 512;   // [16][32]: (tw[n1][lane], tw[n1 + 16][lane])
+      float4 *He_s = twi_s + 512;   // [16][32]: even bins (k = lane + 32 slot -> bin 2k), x 1 / 2048
+      float4 *Ho_s = He_s + 512;    // [16][32]: odd bins (bin 2k + 1), x 1 / 2048
+      float2 *w2_s = reinterpret_cast<float2 *>(Ho_s + 512);  // [32][32]: exp(-2 pi i (lane + 32 r) / 2048)
+      cx *tiles = reinterpret_cast<cx *>(w2_s + 1024);        // kWideWarps x 32 x kRow complex numbers
+      const int c = blockIdx.y;
+      const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+      const int f = a.filter_of[c];
+      const float norm = 1.0f / 2048.0f;                    // of the 2048-point transform (exact)
+      const float tail_norm = 1.0f / (float)(2 * kFastB);   // the carried tails are libear's: x 2B
+      for (int i = threadIdx.x; i < 1024; i += kWideWarps * 32) {
+        const int slot = i >> 5, L = i & 31;
+        const float2 w = a.tw[i];
+        reinterpret_cast<float2 *>(tw_s)[((slot >> 1) * 32 + L) * 2 + (slot & 1)] = w;
+        reinterpret_cast<float2 *>(twi_s)[((slot & 15) * 32 + L) * 2 + (slot >> 4)] = w;
+        w2_s[i] = a.tw[1024 + i];
+        const int k = L + 32 * slot;
+        float2 he = make_float2(0.0f, 0.0f), ho = he;
+        if (f >= 0) {
+          he = a.filt_wide[(size_t)f * 2048 + 2 * k];
+          ho = a.filt_wide[(size_t)f * 2048 + 2 * k + 1];
+        }
+        reinterpret_cast<float2 *>(He_s)[((slot >> 1) * 32 + L) * 2 + (slot & 1)] = make_float2(he.x * norm, he.y * norm);
+        reinterpret_cast<float2 *>(Ho_s)[((slot >> 1) * 32 + L) * 2 + (slot & 1)] = make_float2(ho.x * norm, ho.y * norm);
+      }
+      __syncthreads();
+
+      const long s0 = ((long)blockIdx.x * kWideWarps + warp) * a.run_sb;
+      if (s0 >= a.K) return;
+      const long s1 = min(a.K, s0 + (long)a.run_sb);
+      cx *tile = tiles + (size_t)warp * 32 * kRow;
+      const float *x = a.in + (size_t)c * a.in_stride;
+      float *y = a.out + (size_t)c * a.out_stride;
+      // ADD: sample t of [add_mem; add], the delayed direct bus
+      const float *am = ADD ? a.add_mem + (long)c * a.add_delay : nullptr;
+      const float *ad = ADD ? a.add + (long)c * a.add_stride - a.add_delay : nullptr;
+      auto delayed = [&](long t) -> float { return t < a.add_delay ? am[t] : __ldcs(ad + t); };
+
+      cx v[32];
+      float tail[16];
+      if (s0 == 0 && a.carried_tail) {
+#pragma unroll
+        for (int r = 0; r < 16; r++) tail[r] = a.tail[(size_t)c * kFastB + lane + 32 * r] * tail_norm;
+      } else {
+        // halo: the 512 samples before the run as the imaginary part of a 1024-point pair (even bins
+        // x 1 / 2048: the result comes out halved)
+        const float *xb = s0 == 0 ? a.hist + (size_t)c * a.hist_len - (kFastB - a.hist_len)
+                                  : x + (size_t)(s0 - 1) * kFastB;
+        const int first = s0 == 0 ? kFastB - a.hist_len : 0;
+#pragma unroll
+        for (int r = 0; r < 16; r++) {
+          const int t = lane + 32 * r;
+          v[br5(r)] = mk(0.0f, t >= first ? __ldg(xb + t) : 0.0f);
+        }
+        convolve_pair<true>(v, tile, tw_s, twi_s, He_s, lane);
+#pragma unroll
+        for (int r = 0; r < 16; r++) tail[r] = 2.0f * im(v[r + 16]);
+      }
+
+      long sb = s0;
+      for (; sb + kUnitSb <= s1; sb += kUnitSb) {
+        const float *xu = x + (size_t)sb * kFastB;
+        float *yu = y + (size_t)sb * kFastB;
+        // the next unit's 12 KB (96 lines) on their way into L2 while this one is transformed
+        if (sb + 2 * kUnitSb <= s1) {
+#pragma unroll
+          for (int j = 0; j < 3; j++)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(xu + kUnitSb * kFastB + (lane + 32 * j) * 32));
+        }
+        cx so[32];
+#pragma unroll
+        for (int r = 0; r < 16; r++) {
+          const cx za = mk(__ldcs(xu + lane + 32 * r), __ldcs(xu + 3 * kFastB + lane + 32 * r));
+          const cx zb = mk(__ldcs(xu + 2 * kFastB + lane + 32 * r), __ldcs(xu + 5 * kFastB + lane + 32 * r));
+          const float2 w = w2_s[r * 32 + lane];
+          v[br5(r)] = add2(za, zb);
+          so[br5(r)] = cmulf(sub2(za, zb), w.x, w.y);
+        }
+#pragma unroll
+        for (int r = 16; r < 32; r++) {
+          const cx za = mk(__ldcs(xu + lane + 32 * r), __ldcs(xu + 3 * kFastB + lane + 32 * r));
+          const float2 w = w2_s[r * 32 + lane];
+          v[br5(r)] = za;
+          so[br5(r)] = cmulf(za, w.x, w.y);
+        }
+        convolve_pair<false>(v, tile, tw_s, twi_s, He_s, lane);  // v[q] = e[lane + 32 q]
+#pragma unroll
+        for (int i = 0; i < 32; i++) {
+          const cx t = v[i];
+          v[i] = so[i];
+          so[i] = t;
+        }
+        convolve_pair<false>(v, tile, tw_s, twi_s, Ho_s, lane);  // v[q] = o[lane + 32 q]; so = e
+        float *ya = yu, *yb = yu + 3 * kFastB;
+        const long ta = (long)sb * kFastB + lane, tb = ta + 3 * kFastB;
+#pragma unroll
+        for (int q = 0; q < 16; q++) {
+          const float2 w0 = w2_s[q * 32 + lane], w1 = w2_s[(q + 16) * 32 + lane];
+          const cx t0 = cmulcf(v[q], w0.x, w0.y), t1 = cmulcf(v[q + 16], w1.x, w1.y);
+          const cx ylo0 = add2(so[q], t0), yhi0 = sub2(so[q], t0);            // y[n], y[n + 1024], n = lane + 32 q
+          const cx ylo1 = add2(so[q + 16], t1), yhi1 = sub2(so[q + 16], t1);  // y[n + 512], y[n + 1536]
+          float oa0 = re(ylo0) + tail[q], oa1 = re(ylo1), oa2 = re(yhi0);
+          float ob0 = im(ylo0) + re(yhi1), ob1 = im(ylo1), ob2 = im(yhi0);
+          tail[q] = im(yhi1);
+          if (ADD) {
+            oa0 += delayed(ta + 32 * q);
+            oa1 += delayed(ta + 32 * (q + 16));
+            oa2 += delayed(ta + 32 * (q + 32));
+            ob0 += delayed(tb + 32 * q);
+            ob1 += delayed(tb + 32 * (q + 16));
+            ob2 += delayed(tb + 32 * (q + 32));
+          }
+          __stcs(ya + lane + 32 * q, oa0);
+          __stcs(ya + lane + 32 * (q + 16), oa1);
+          __stcs(ya + lane + 32 * (q + 32), oa2);
+          __stcs(yb + lane + 32 * q, ob0);
+          __stcs(yb + lane + 32 * (q + 16), ob1);
+          __stcs(yb + lane + 32 * (q + 32), ob2);
+        }
+      }
+      // what does not fill a unit (end of the channel only): 1024-point pairs, results doubled
+      for (; sb < s1; sb += 2) {
+        const bool has_second = sb + 1 < a.K;
+        const float *x0 = x + (size_t)sb * kFastB;
+#pragma unroll
+        for (int r = 0; r < 16; r++)
+          v[br5(r)] = mk(__ldcs(x0 + lane + 32 * r), has_second ? __ldcs(x0 + kFastB + lane + 32 * r) : 0.0f);
+        convolve_pair<true>(v, tile, tw_s, twi_s, He_s, lane);
+#pragma unroll
+        for (int i = 0; i < 32; i++) v[i] = add2(v[i], v[i]);
+        float *y0 = y + (size_t)sb * kFastB;
+        const long t0 = (long)sb * kFastB + lane;
+#pragma unroll
+        for (int r = 0; r < 16; r++) {
+          float o = re(v[r]) + tail[r];
+          if (ADD) o += delayed(t0 + 32 * r);
+          __stcs(y0 + lane + 32 * r, o);
+        }
+        if (has_second) {
+#pragma unroll
+          for (int r = 0; r < 16; r++) {
+            float o = im(v[r]) + re(v[r + 16]);
+            if (ADD) o += delayed(t0 + kFastB + 32 * r);
+            __stcs(y0 + kFastB + lane + 32 * r, o);
+            tail[r] = im(v[r + 16]);
+          }
+        } else {
+#pragma unroll
+          for (int r = 0; r < 16; r++) tail[r] = re(v[r + 16]);
+        }
+      }
+      if (s1 == a.K && a.carried_tail) {
+#pragma unroll
+        for (int r = 0; r < 16; r++) a.tail_new[(size_t)c * kFastB + lane + 32 * r] = tail[r] * (float)(2 * kFastB);
+      }
+    }
   }  // namespace
 
-  size_t conv_fast_tw_floats() { return 2 * 1024; }
+  size_t conv_fast_tw_floats() { return 2 * 2048; }
 
   void conv_fast_build_tw(float *tw) {
     const double pi = 3.141592653589793238462643383279502884;
@@ -423,6 +612,12 @@ namespace earb {
         tw[2 * (k1 * 32 + b)] = (float)cos(ang);
         tw[2 * (k1 * 32 + b) + 1] = (float)sin(ang);
       }
+    // the radix-2 step of the wide kernel: exp(-2 pi i n / 2048), n = lane + 32 r at [r][lane]
+    for (int n = 0; n < 1024; n++) {
+      const double ang = -2.0 * pi * (double)n / 2048.0;
+      tw[2 * (1024 + n)] = (float)cos(ang);
+      tw[2 * (1024 + n) + 1] = (float)sin(ang);
+    }
   }
 
   bool conv_fast_supported(int B, int nb) { return B >= 16 && B * nb <= kFastB && kFastB % B == 0; }
@@ -453,6 +648,25 @@ namespace earb {
     a.add_stride = L.add_stride;
     a.add_delay = L.add_delay;
     a.add_mem = L.add_mem;
+    a.filt_wide = reinterpret_cast<const float2 *>(L.filt_wide);
+    a.run_sb = 0;
+    if (a.filt_wide && a.K >= 16 * kUnitSb) {
+      // long call: 2048-point units; run length: amortise the halo pair, keep a few waves in flight
+      int units = 16;
+      while (units > 2 && (a.K + units * kUnitSb - 1) / (units * kUnitSb) * L.C < 6L * kWideWarps * n_sms) units /= 2;
+      a.run_sb = units * kUnitSb;
+      const size_t wsmem = sizeof(float2) * (5 * 1024 + (size_t)kWideWarps * 32 * kRow);
+      const long wwarps = (a.K + a.run_sb - 1) / a.run_sb;
+      dim3 wgrid((unsigned)((wwarps + kWideWarps - 1) / kWideWarps), (unsigned)L.C);
+      if (a.add) {
+        cudaFuncSetAttribute(convolver_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem);
+        convolver_wide_kernel<true><<<wgrid, kWideWarps * 32, wsmem, stream>>>(a);
+      } else {
+        cudaFuncSetAttribute(convolver_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem);
+        convolver_wide_kernel<false><<<wgrid, kWideWarps * 32, wsmem, stream>>>(a);
+      }
+      return;
+    }
     const size_t smem = sizeof(float2) * (3072 + (size_t)kWarps * 32 * kRow);
     const long warps = (a.n_pairs + run - 1) / run;
     dim3 grid((unsigned)((warps + kWarps - 1) / kWarps), (unsigned)L.C);

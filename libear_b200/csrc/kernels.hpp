@@ -240,6 +240,9 @@ namespace earb {
     // the taps themselves [n_filters][nb * B] for the carried tail (launch_conv_generic_tail)
     const float *filt_fast = nullptr;
     const float *taps = nullptr;
+    // fast path, long calls (convolver_wide_kernel): filt_wide [n_filters][2048] complex, the
+    // 2048-point spectrum of the whole filter; null: the 1024-point kernel takes the call
+    const float *filt_wide = nullptr;
   };
   size_t conv_smem_bytes(int B, int nb);
   void launch_convolver(const ConvLaunch &L, cudaStream_t stream);

@@ -185,3 +185,50 @@ def test_fast_path_other_partitionings_match_generic_kernel(eb, monkeypatch):
     direct = np.stack([np.convolve(x[c].astype(np.float64), filt[c, :512 - 100 * c].astype(np.float64))[:B * K]
                        for c in range(C - 1)])
     assert peak_err(outs[0][:C - 1], direct) < 1e-6
+
+
+@pytest.mark.parametrize("K", [96, 97, 101, 196, 293, 600])
+def test_wide_kernel_long_calls(eb, ref, K):
+    """Calls of at least 96 super-blocks run on the 2048-point kernel (units of 3,072 samples; the
+    halo of a run and the super-blocks that do not fill a unit on 1024-point pairs): every residue
+    of the block count modulo 6, odd counts, several runs per channel, carried tails across calls
+    that alternate with the 1024-point kernel (short calls) -- against libear."""
+    rng = np.random.default_rng(K)
+    B, n_ch = 512, 3
+    f = [rng.normal(size=n).astype(np.float32) for n in (512, 200)]
+    blk = lambda k: rng.normal(0, 0.25, size=n_ch * B * k).astype(np.float32)
+    script = [("set", 0), ("run", blk(3)), ("run", blk(K)), ("run", blk(5)), ("run", blk(K + 2)), ("set", 1),
+              ("run", blk(K + 3)), ("xfade", 0), ("run", blk(K + 4))]
+    out, exp = run_script(eb, ref, B, 1, f, script, n_channels=n_ch)
+    assert peak_err(out, exp) < 1e-6
+
+
+@pytest.mark.parametrize("B,nb", [(128, 4), (64, 5), (16, 32)])
+def test_wide_kernel_other_partitionings(eb, ref, B, nb):
+    rng = np.random.default_rng(7 * B + nb)
+    q, n_ch = 512 // B, 2
+    f = [rng.normal(size=n).astype(np.float32) for n in (B * nb, 9)]
+    blk = lambda k: rng.normal(0, 0.25, size=n_ch * B * k).astype(np.float32)
+    script = [("set", 0), ("run", blk(100 * q)), ("run", blk(2 * q)), ("run", blk(131 * q + 1)), ("set", 1),
+              ("run", blk(99 * q + q // 2)), ("xfade", 0), ("run", blk(120 * q))]
+    out, exp = run_script(eb, ref, B, nb, f, script, n_channels=n_ch)
+    assert peak_err(out, exp) < 1e-6
+
+
+def test_wide_kernel_matches_pair_kernel(eb, monkeypatch):
+    rng = np.random.default_rng(8)
+    C, B, K = 4, 512, 1000
+    x = rng.normal(0, 0.25, size=(C, B * K)).astype(np.float32)
+    filt = rng.normal(size=(C, 512)).astype(np.float32)
+    outs = []
+    for path in ("fast", "pair"):
+        monkeypatch.setenv("EARB200_CONV_PATH", path)
+        g = eb.BlockConvolver(B, C, 1)
+        for c in range(C - 1):          # the last channel has no filter: silence out
+            fid, _ = g.add_filter(filt[c])
+            g.set_filter(fid, channel=c)
+        outs.append(np.concatenate([g.process(x[:, :B * 400]), g.process(x[:, B * 400:])], axis=1))
+    assert peak_err(outs[0], outs[1]) < 1e-6
+    assert np.abs(outs[0][C - 1]).max() == 0.0
+    direct = np.stack([np.convolve(x[c].astype(np.float64), filt[c].astype(np.float64))[:B * K] for c in range(C - 1)])
+    assert peak_err(outs[0][:C - 1], direct) < 1e-6
