@@ -706,12 +706,13 @@ def run_ours(args):
                                    "5.5 GB/step > L2", "sharding": "replicated channels per GPU, no collective"},
             "roofline": {"bound": "hbm", "achieved": c_achieved, "peak": hbm_peak, "unit": "GB/s",
                          "frac": c_achieved / hbm_peak,
-                         "traffic": ncu_traffic("convolver_fast_kernel") if (Cc, Kc) == (24, 56250) else None,
+                         "traffic": ncu_traffic("convolver_wide_kernel") if (Cc, Kc) == (24, 56250) else None,
                          "peak_source": peak_src,
-                         "kernel": "convolver_fast_kernel", "kernel_ms": ck_ms / max(1, ck_n),
+                         "kernel": "convolver_wide_kernel", "kernel_ms": ck_ms / max(1, ck_n),
                          "algorithmic_bytes_per_launch": c_bytes,
-                         "note": "8 B/sample; the FP32 butterflies (about 2,300 warp instructions per pair of "
-                                 "blocks) bound the kernel before HBM does (DESIGN.md section 3, K4)"},
+                         "note": "8 B/sample; the packed-FP32 butterflies (about 3,000 warp instructions per unit "
+                                 "of 3,072 samples, three quarters of them FFMA2 / FADD2 / FMUL2) bound the kernel "
+                                 "before HBM does (DESIGN.md section 3, K4)"},
         }
         if world == 1:
             conv_block["sustained"] = sustained(step_conv, Cc * Tc / 1e6, args.sustained)

@@ -68,6 +68,7 @@ struct earb200_convolver {
   // fast path, long calls: the 2048-point spectrum of the whole filter (all 2,048 bins), per filter
   // (EARB200_CONV_PATH=pair keeps long calls on the 1024-point kernel)
   bool use_wide = false;
+  int wide_mode = 1;  // EARB200_CONV_PATH=wide: 2 (every call long enough for one run; tests)
   std::vector<float> filt_wide_host;
   DeviceBuffer<float> d_filt_wide;
   // B != 512: the carried last_tail was made with a filter that set_filter has replaced since; the
@@ -238,6 +239,7 @@ bool earb_conv_process_device(earb200_convolver &h, int64_t K, const float *d_in
       L.filt_fast = h.d_filt_fast.ptr;
       L.taps = h.d_taps.ptr;
       L.filt_wide = h.use_wide ? h.d_filt_wide.ptr : nullptr;
+      L.wide = h.wide_mode;
       launch_convolver_fast(L, h.d_uniform.ptr, h.d_tw_fast.ptr, h.n_sms, stream);
       launch_conv_history(L, stream);
       if (h.B != 512) {
@@ -308,6 +310,7 @@ int earb200_convolver_create(int64_t block_size, int n_channels, int64_t num_blo
     const char *path = std::getenv("EARB200_CONV_PATH");
     h->use_fast = conv_fast_supported(h->B, h->nb) && !(path && std::string(path) == "generic");
     h->use_wide = h->use_fast && !(path && std::string(path) == "pair");
+    h->wide_mode = path && std::string(path) == "wide" ? 2 : 1;
     if (h->use_fast) {
       std::vector<float> twf(conv_fast_tw_floats());
       conv_fast_build_tw(twf.data());

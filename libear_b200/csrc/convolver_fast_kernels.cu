@@ -437,11 +437,16 @@ namespace earb {
 #ifndef EARB_WIDE_WARPS
 #define EARB_WIDE_WARPS 12
 #endif
-    constexpr int kWideWarps = EARB_WIDE_WARPS;
+    constexpr int kWideWarps = EARB_WIDE_WARPS;       // per CTA
+    constexpr int kWideCtas = kWideWarps <= 6 ? 2 : 1;  // per SM (168 registers: 12 warps per SM)
+    constexpr int kWideResident = kWideWarps * kWideCtas;
     constexpr int kUnitSb = 6;  // super-blocks of 512 samples per unit
+#ifndef EARB_WIDE_UNITS
+#define EARB_WIDE_UNITS 16
+#endif
 
     template <bool ADD>
-    __global__ void __launch_bounds__(kWideWarps * 32, 1) convolver_wide_kernel(FastArgs a) {
+    __global__ void __launch_bounds__(kWideWarps * 32, kWideCtas) convolver_wide_kernel(FastArgs a) {
       extern __shared__ float4 fsm[];
       float4 *tw_s = fsm;           // [16][32]: (tw[2j][lane], tw[2j + 1][lane])
       float4 *twi_s = tw_s + 512;   // [16][32]: (tw[n1][lane], tw[n1 + 16][lane])
@@ -650,10 +655,19 @@ namespace earb {
     a.add_mem = L.add_mem;
     a.filt_wide = reinterpret_cast<const float2 *>(L.filt_wide);
     a.run_sb = 0;
-    if (a.filt_wide && a.K >= 16 * kUnitSb) {
-      // long call: 2048-point units; run length: amortise the halo pair, keep a few waves in flight
-      int units = 16;
-      while (units > 2 && (a.K + units * kUnitSb - 1) / (units * kUnitSb) * L.C < 6L * kWideWarps * n_sms) units /= 2;
+    // Long calls go to the 2048-point kernel: L.wide = 1 when runs of at least 8 units still fill the
+    // GPU four times over (cfg 4: 24 channels x 10 min; the Objects flow's 24 x 60 s stay on the
+    // pair kernel, whose shorter runs balance better there: 0.85 against 0.95 ms for the flow),
+    // 2 (EARB200_CONV_PATH=wide, tests) whenever a run of 16 units exists.
+    int units = EARB_WIDE_UNITS;
+    if (L.wide == 1) {
+      while (units > 8 && (a.K + units * kUnitSb - 1) / (units * kUnitSb) * L.C < 4L * kWideResident * n_sms) units /= 2;
+    } else {
+      while (units > 2 && (a.K + units * kUnitSb - 1) / (units * kUnitSb) * L.C < 6L * kWideResident * n_sms) units /= 2;
+    }
+    const bool wide = a.filt_wide && a.K >= 16 * kUnitSb &&
+                      (L.wide == 2 || (L.wide == 1 && (a.K + units * kUnitSb - 1) / (units * kUnitSb) * L.C >= 4L * kWideResident * n_sms));
+    if (wide) {
       a.run_sb = units * kUnitSb;
       const size_t wsmem = sizeof(float2) * (5 * 1024 + (size_t)kWideWarps * 32 * kRow);
       const long wwarps = (a.K + a.run_sb - 1) / a.run_sb;

@@ -243,6 +243,7 @@ namespace earb {
     // fast path, long calls (convolver_wide_kernel): filt_wide [n_filters][2048] complex, the
     // 2048-point spectrum of the whole filter; null: the 1024-point kernel takes the call
     const float *filt_wide = nullptr;
+    int wide = 1;  // 0: never, 1: when the call is long enough to fill the GPU with long runs, 2: whenever possible
   };
   size_t conv_smem_bytes(int B, int nb);
   void launch_convolver(const ConvLaunch &L, cudaStream_t stream);

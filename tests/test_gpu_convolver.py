@@ -188,11 +188,13 @@ def test_fast_path_other_partitionings_match_generic_kernel(eb, monkeypatch):
 
 
 @pytest.mark.parametrize("K", [96, 97, 101, 196, 293, 600])
-def test_wide_kernel_long_calls(eb, ref, K):
-    """Calls of at least 96 super-blocks run on the 2048-point kernel (units of 3,072 samples; the
+def test_wide_kernel_long_calls(eb, ref, K, monkeypatch):
+    """With EARB200_CONV_PATH=wide calls of at least 96 super-blocks run on the 2048-point kernel
+    (by default only calls that fill the GPU with long runs do: units of 3,072 samples; the
     halo of a run and the super-blocks that do not fill a unit on 1024-point pairs): every residue
     of the block count modulo 6, odd counts, several runs per channel, carried tails across calls
     that alternate with the 1024-point kernel (short calls) -- against libear."""
+    monkeypatch.setenv("EARB200_CONV_PATH", "wide")
     rng = np.random.default_rng(K)
     B, n_ch = 512, 3
     f = [rng.normal(size=n).astype(np.float32) for n in (512, 200)]
@@ -204,7 +206,8 @@ def test_wide_kernel_long_calls(eb, ref, K):
 
 
 @pytest.mark.parametrize("B,nb", [(128, 4), (64, 5), (16, 32)])
-def test_wide_kernel_other_partitionings(eb, ref, B, nb):
+def test_wide_kernel_other_partitionings(eb, ref, B, nb, monkeypatch):
+    monkeypatch.setenv("EARB200_CONV_PATH", "wide")
     rng = np.random.default_rng(7 * B + nb)
     q, n_ch = 512 // B, 2
     f = [rng.normal(size=n).astype(np.float32) for n in (B * nb, 9)]
@@ -221,7 +224,7 @@ def test_wide_kernel_matches_pair_kernel(eb, monkeypatch):
     x = rng.normal(0, 0.25, size=(C, B * K)).astype(np.float32)
     filt = rng.normal(size=(C, 512)).astype(np.float32)
     outs = []
-    for path in ("fast", "pair"):
+    for path in ("wide", "pair"):
         monkeypatch.setenv("EARB200_CONV_PATH", path)
         g = eb.BlockConvolver(B, C, 1)
         for c in range(C - 1):          # the last channel has no filter: silence out
