@@ -787,6 +787,10 @@ namespace earb {
     }
 
     // ---------------------------------------------------------------- host: cell clustering
+    constexpr int kTablePoints = 1652, kTableCells = 104;
+    const short kCells1652[kTableCells * kCell] = {
+#include "extent_cells_1652.inc"
+    };
     struct V3 {
       double x, y, z;
     };
@@ -834,8 +838,39 @@ namespace earb {
     std::vector<int> all(n_points);
     for (int p = 0; p < n_points; p++) all[p] = p;
     std::vector<std::vector<int>> cells;
-    bisect(pts, all, cells);
     const int n_cells = n_points_pad / kCell;
+    // The reference's grid (37 rows, 1,652 points -- the same for every layout) comes with a
+    // clustering searched offline (tools/gen_extent_cells.py: the bisection below, then re-splits,
+    // moves and swaps between neighbouring cells that shrink the caps).  The table is only taken if
+    // it is a partition of this grid's points; centres and radii are computed from the points below
+    // either way, so it decides how many cells are mixed, never what the result is.
+    // EARB200_EXTENT_CELLS=bisect: the run-time bisection for this grid too.
+    bool from_table = false;
+    {
+      const char *e = std::getenv("EARB200_EXTENT_CELLS");
+      if (n_points == kTablePoints && n_cells == kTableCells && !(e && std::strcmp(e, "bisect") == 0)) {
+        std::vector<char> seen(n_points, 0);
+        bool ok = true;
+        cells.assign(n_cells, {});
+        for (int c = 0; c < n_cells && ok; c++)
+          for (int i = 0; i < kCell; i++) {
+            const int p = kCells1652[c * kCell + i];
+            if (p < 0) continue;
+            if (p >= n_points || seen[p]) {
+              ok = false;
+              break;
+            }
+            seen[p] = 1;
+            cells[c].push_back(p);
+          }
+        for (int p = 0; p < n_points && ok; p++) ok = seen[p] != 0;
+        from_table = ok;
+      }
+    }
+    if (!from_table) {
+      cells.clear();
+      bisect(pts, all, cells);
+    }
     while ((int)cells.size() < n_cells) cells.push_back({});
     out.n_cells = n_cells;
     out.order.assign((size_t)n_cells * kCell, -1);
@@ -856,19 +891,24 @@ namespace earb {
         if (n > 0) v[0] /= n, v[1] /= n, v[2] /= n;
       };
       normalise(ctr);
-      for (int it = 0; it < 400; it++) {
+      // (Badoiu-Clarkson: steps of 1 / (it + 2) towards the farthest point converge to the smallest
+      // enclosing ball; the best centre seen is kept)
+      double best[3] = {ctr[0], ctr[1], ctr[2]}, best_dmin = -2.0;
+      for (int it = 0; it < 4000; it++) {
         int far = cell[0];
         double dmin = 2.0;
         for (int i : cell) {
           const double d = pts[i].x * ctr[0] + pts[i].y * ctr[1] + pts[i].z * ctr[2];
           if (d < dmin) dmin = d, far = i;
         }
-        const double step = 0.02;
+        if (dmin > best_dmin) best_dmin = dmin, best[0] = ctr[0], best[1] = ctr[1], best[2] = ctr[2];
+        const double step = 1.0 / (double)(it + 2);
         ctr[0] += step * (pts[far].x - ctr[0]);
         ctr[1] += step * (pts[far].y - ctr[1]);
         ctr[2] += step * (pts[far].z - ctr[2]);
         normalise(ctr);
       }
+      ctr[0] = best[0], ctr[1] = best[1], ctr[2] = best[2];
       // the radius is taken from the centre as the kernel sees it (float)
       const float cf[3] = {(float)ctr[0], (float)ctr[1], (float)ctr[2]};
       double c64[3] = {cf[0], cf[1], cf[2]};
