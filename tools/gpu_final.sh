@@ -12,3 +12,5 @@ for k in epilogue prelude; do
   timeout 600 ncu --set full --clock-control none --cache-control none --import-source on -k regex:objects_$k -s 2 -c 1 -f -o gpurun_out/prof_${k}_$tag $OBJ > gpurun_out/ncu_${k}_$tag.log 2>&1
   echo "ncu $k rc=$?"
 done
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:extent_cell -s 3 -c 1 -f -o gpurun_out/prof_cell_$tag $OBJ > gpurun_out/ncu_cell_$tag.log 2>&1
+echo "ncu cell rc=$?"
