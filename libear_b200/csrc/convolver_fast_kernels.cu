@@ -518,6 +518,15 @@ namespace earb {
           for (int j = 0; j < 3; j++)
             asm volatile("prefetch.global.L2 [%0];" ::"l"(xu + kUnitSb * kFastB + (lane + 32 * j) * 32));
         }
+        if (ADD) {
+          // ... and this unit's 12 KB of the delayed direct bus, which the combine step at the end of
+          // the unit adds: from DRAM they would cost a full memory latency per step
+          const long t_unit = (long)sb * kFastB;
+          if (t_unit >= a.add_delay) {
+#pragma unroll
+            for (int j = 0; j < 3; j++) asm volatile("prefetch.global.L2 [%0];" ::"l"(ad + t_unit + (lane + 32 * j) * 32));
+          }
+        }
         cx so[32];
 #pragma unroll
         for (int r = 0; r < 16; r++) {
@@ -544,6 +553,22 @@ namespace earb {
         convolve_pair<false>(v, tile, tw_s, twi_s, Ho_s, lane);  // v[q] = o[lane + 32 q]; so = e
         float *ya = yu, *yb = yu + 3 * kFastB;
         const long ta = (long)sb * kFastB + lane, tb = ta + 3 * kFastB;
+        // ADD: the six samples of the delayed direct bus that step q stores on top of are loaded one
+        // step ahead, before the stores of the step in between (the compiler may not move a load
+        // above a store that could alias it, and a load issued right before its use costs an L2
+        // round trip per step with three warps per scheduler)
+        const bool near_mem = ADD && (long)sb * kFastB < a.add_delay;  // the unit reaches into add_mem
+        auto load_add = [&](int q, float(&d)[6]) {
+          if (near_mem) {
+            d[0] = delayed(ta + 32 * q), d[1] = delayed(ta + 32 * (q + 16)), d[2] = delayed(ta + 32 * (q + 32));
+            d[3] = delayed(tb + 32 * q), d[4] = delayed(tb + 32 * (q + 16)), d[5] = delayed(tb + 32 * (q + 32));
+          } else {
+            d[0] = __ldcs(ad + ta + 32 * q), d[1] = __ldcs(ad + ta + 32 * (q + 16)), d[2] = __ldcs(ad + ta + 32 * (q + 32));
+            d[3] = __ldcs(ad + tb + 32 * q), d[4] = __ldcs(ad + tb + 32 * (q + 16)), d[5] = __ldcs(ad + tb + 32 * (q + 32));
+          }
+        };
+        float dn[6] = {0.0f, 0.0f, 0.0f, 0.0f, 0.0f, 0.0f};
+        if (ADD) load_add(0, dn);
 #pragma unroll
         for (int q = 0; q < 16; q++) {
           const float2 w0 = w2_s[q * 32 + lane], w1 = w2_s[(q + 16) * 32 + lane];
@@ -554,12 +579,9 @@ namespace earb {
           float ob0 = im(ylo0) + re(yhi1), ob1 = im(ylo1), ob2 = im(yhi0);
           tail[q] = im(yhi1);
           if (ADD) {
-            oa0 += delayed(ta + 32 * q);
-            oa1 += delayed(ta + 32 * (q + 16));
-            oa2 += delayed(ta + 32 * (q + 32));
-            ob0 += delayed(tb + 32 * q);
-            ob1 += delayed(tb + 32 * (q + 16));
-            ob2 += delayed(tb + 32 * (q + 32));
+            oa0 += dn[0], oa1 += dn[1], oa2 += dn[2];
+            ob0 += dn[3], ob1 += dn[4], ob2 += dn[5];
+            if (q + 1 < 16) load_add(q + 1, dn);
           }
           __stcs(ya + lane + 32 * q, oa0);
           __stcs(ya + lane + 32 * (q + 16), oa1);
@@ -655,18 +677,41 @@ namespace earb {
     a.add_mem = L.add_mem;
     a.filt_wide = reinterpret_cast<const float2 *>(L.filt_wide);
     a.run_sb = 0;
-    // Long calls go to the 2048-point kernel: L.wide = 1 when runs of at least 8 units still fill the
-    // GPU four times over (cfg 4: 24 channels x 10 min; the Objects flow's 24 x 60 s stay on the
-    // pair kernel, whose shorter runs balance better there: 0.85 against 0.95 ms for the flow),
-    // 2 (EARB200_CONV_PATH=wide, tests) whenever a run of 16 units exists.
+    // Which kernel, and how long the runs (units of 3,072 samples per warp; every run pays one halo
+    // pair, about half a unit).  A CTA is kWideWarps runs of ONE channel and an SM holds one CTA, so
+    // the launch proceeds in waves of n_sms CTAs: cost(u) = waves(u) x (u + 1/2) unit times.
+    //   * long calls (cfg 4: 24 channels x 10 min): runs of 16 units, eight waves;
+    //   * shorter ones (24 channels x 60 s): the run length that minimises the cost --
+    //     usually the shortest that fits the whole call into ONE wave -- if that comes within a
+    //     quarter of the ideal (all warps of the GPU busy all the time); else the pair kernel, whose
+    //     short runs fill the GPU with less work;
+    //   * L.wide == 2 (EARB200_CONV_PATH=wide, tests): wide whenever a run of 16 units exists.
+    const long total_units = a.K / kUnitSb;
+    auto ctas_at = [&](int u) {
+      const long warps = (a.K + (long)u * kUnitSb - 1) / ((long)u * kUnitSb);
+      return (long)L.C * ((warps + kWideWarps - 1) / kWideWarps);
+    };
     int units = EARB_WIDE_UNITS;
-    if (L.wide == 1) {
-      while (units > 8 && (a.K + units * kUnitSb - 1) / (units * kUnitSb) * L.C < 4L * kWideResident * n_sms) units /= 2;
-    } else {
+    bool wide = false;
+    if (a.filt_wide && L.wide == 2 && a.K >= 16 * kUnitSb) {
       while (units > 2 && (a.K + units * kUnitSb - 1) / (units * kUnitSb) * L.C < 6L * kWideResident * n_sms) units /= 2;
+      wide = true;
+    } else if (a.filt_wide && L.wide == 1 && a.K >= 16 * kUnitSb) {
+      if (ctas_at(units) >= 4L * n_sms) {
+        wide = true;
+      } else {
+        double best = 1e30;
+        for (int u = 4; u <= 64 && (long)u <= total_units; u++) {
+          const double cost = (double)((ctas_at(u) + n_sms - 1) / n_sms) * ((double)u + 0.5);
+          if (cost < best) best = cost, units = u;
+        }
+        const double ideal = (double)total_units * L.C / ((double)kWideResident * n_sms) + 0.5;
+        // (with the delayed bus joining, the one-wave form measured level with the pair kernel on the
+        // Objects flow -- 0.864 against 0.850 ms -- while without it is a fifth faster at that size:
+        // 24 channels x 60 s in 0.181 against 0.228 ms; those calls stay on the pair kernel)
+        wide = best <= 1.25 * ideal && !a.add;
+      }
     }
-    const bool wide = a.filt_wide && a.K >= 16 * kUnitSb &&
-                      (L.wide == 2 || (L.wide == 1 && (a.K + units * kUnitSb - 1) / (units * kUnitSb) * L.C >= 4L * kWideResident * n_sms));
     if (wide) {
       a.run_sb = units * kUnitSb;
       const size_t wsmem = sizeof(float2) * (5 * 1024 + (size_t)kWideWarps * 32 * kRow);
