@@ -235,3 +235,31 @@ def test_wide_kernel_matches_pair_kernel(eb, monkeypatch):
     assert np.abs(outs[0][C - 1]).max() == 0.0
     direct = np.stack([np.convolve(x[c].astype(np.float64), filt[c].astype(np.float64))[:B * K] for c in range(C - 1)])
     assert peak_err(outs[0][:C - 1], direct) < 1e-6
+
+
+def test_wide_kernel_one_wave_plan(eb, ref, monkeypatch):
+    """Default kernel choice on a call that fills the GPU about once (24 channels x 1,807 blocks): the
+    2048-point kernel with the run length of the wave model (runs of 5 units, one wave of CTAs),
+    not the 16-unit runs of long calls -- against the pair kernel on every channel and against
+    libear on two of them."""
+    rng = np.random.default_rng(9)
+    C, B, K = 24, 512, 1807
+    x = rng.normal(0, 0.25, size=(C, B * K)).astype(np.float32)
+    filt = rng.normal(size=(C, 512)).astype(np.float32)
+    outs = []
+    for path in (None, "pair"):
+        if path:
+            monkeypatch.setenv("EARB200_CONV_PATH", path)
+        else:
+            monkeypatch.delenv("EARB200_CONV_PATH", raising=False)
+        g = eb.BlockConvolver(B, C, 1)
+        for c in range(C):
+            fid, _ = g.add_filter(filt[c])
+            g.set_filter(fid, channel=c)
+        outs.append(np.concatenate([g.process(x[:, :B * 3]), g.process(x[:, B * 3:])], axis=1))
+    assert peak_err(outs[0], outs[1]) < 1e-6
+    for c in (0, C - 1):
+        r = ref.Convolver(B, 1)
+        fid, _ = r.add_filter(filt[c])
+        r.set_filter(fid)
+        assert peak_err(outs[0][c], r.process(x[c])) < 1e-6, c
