@@ -68,6 +68,59 @@ def swap_search(pts, cells, rounds):
     return cells
 
 
+def cap_ws(p, c0, iters=120):
+    """bounding cap from a warm start (Badoiu-Clarkson steps, the best centre seen)"""
+    ctr = c0 / np.linalg.norm(c0)
+    best_c, best_d = ctr, (p @ ctr).min()
+    for it in range(iters):
+        j = np.argmin(p @ ctr)
+        ctr = ctr + (p[j] - ctr) / (it + 3.0)
+        ctr /= np.linalg.norm(ctr)
+        d = (p @ ctr).min()
+        if d > best_d:
+            best_c, best_d = ctr.copy(), d
+    return best_c, float(np.arccos(np.clip(best_d, -1, 1)))
+
+
+def deep_swap(pts, cells, rounds, top=3):
+    """swaps of one of the `top` farthest points of a cell with any point of a neighbouring cell
+    (and moves into cells with free slots), accepted when the sum of the two radii falls"""
+    cells = [list(c) for c in cells]
+    ctr, rad = xc.caps(pts, cells)
+    for rd in range(rounds):
+        improved = 0
+        for a in np.argsort(-rad):
+            near = [int(b) for b in np.argsort(-(ctr @ ctr[a]))[1:7]]
+            far_a = [cells[a][i] for i in np.argsort(pts[cells[a]] @ ctr[a])[:top]]
+            best, best_move = 1e-6, None
+            for b in near:
+                base = rad[a] + rad[b]
+                opts = [(s, t) for s in far_a for t in cells[b]]
+                if len(cells[b]) < CELL and len(cells[a]) > 1:
+                    opts += [(s, None) for s in far_a]
+                for s, t in opts:
+                    na = [q for q in cells[a] if q != s]
+                    nb = [q for q in cells[b] if q != t] + [s]
+                    if t is not None:
+                        na.append(t)
+                    (c1, r1), (c2, r2) = cap_ws(pts[na], ctr[a]), cap_ws(pts[nb], ctr[b])
+                    if base - (r1 + r2) > best:
+                        # confirm with the full search before accepting
+                        (c1, r1), (c2, r2) = xc.cap(pts[na]), xc.cap(pts[nb])
+                        if base - (r1 + r2) > best:
+                            best, best_move = base - (r1 + r2), (b, na, nb, c1, r1, c2, r2)
+            if best_move:
+                b, na, nb, c1, r1, c2, r2 = best_move
+                cells[a], cells[b] = na, nb
+                ctr[a], rad[a], ctr[b], rad[b] = c1, r1, c2, r2
+                improved += 1
+        print(f"  deep round {rd}: {improved} moves, mean radius {np.degrees(rad).mean():.3f} "
+              f"max {np.degrees(rad).max():.2f}", flush=True)
+        if not improved:
+            break
+    return cells
+
+
 def main():
     rounds = int(sys.argv[1]) if len(sys.argv) > 1 else 8
     grid, order, _, radius = eb.extent_cells(37)
@@ -81,10 +134,13 @@ def main():
     xc.evaluate(pts, cells, passes, "re-split")
     cells = swap_search(pts, cells, rounds)
     xc.evaluate(pts, cells, passes, "moved / swapped")
+    if "--deep" in sys.argv:
+        cells = deep_swap(pts, cells, rounds)
+        xc.evaluate(pts, cells, passes, "deep swaps")
     flat = sorted(p for c in cells for p in c)
     assert flat == list(range(1652)) and len(cells) == 104 and max(len(c) for c in cells) <= CELL
     # cells in the order of the bisection's first point (keeps neighbouring cells close in the list)
-    out = os.path.join(ROOT, "libear_b200", "csrc", "extent_cells_1652.inc")
+    out = os.environ.get("EARB_CELLS_OUT", os.path.join(ROOT, "libear_b200", "csrc", "extent_cells_1652.inc"))
     with open(out, "w") as f:
         f.write("// generated by tools/gen_extent_cells.py -- do not edit.  Cells of the 1,652-point extent grid\n"
                 "// (37 rows): 104 x 16 point indices, -1 = empty slot.\n")
